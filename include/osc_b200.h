@@ -1,0 +1,294 @@
+/* osc_b200.h -- C ABI of the batched operational-space controller (B200 / sm_100a).
+ *
+ * This is the drop-in boundary for ONE hot path of sai2-primitives: the per-tick controller math
+ *   robot->updateModel(); controller->updateControllerTaskModels(); controller->computeControlTorques()
+ * (reference call sites: examples/05-using_robot_controller/05-using_robot_controller.cpp:143-148,195)
+ * evaluated for B independent robot instances per call.  The reference has no FFI of its own: its boundary is
+ * the C++ class API of a static library.  The C++ facade in include/Sai2PrimitivesBatched.h keeps
+ * those class and method names and calls the entry points below; INTEGRATION.md shows the binding a maintainer adds.
+ *
+ * Conventions
+ *   - plain C, opaque handles, plain pointers and sizes; no exceptions cross the boundary.
+ *   - every function returns an int status: OSC_OK (0) or a negative OSC_ERR_* code; osc_last_error() returns the
+ *     message (thread local), worded like the std::invalid_argument the reference throws at the cited line.
+ *   - "real" buffers are double for an OSC_PRECISION_F64 batch and float for an OSC_PRECISION_F32 batch.
+ *   - matrices in user buffers are ROW-major per robot (J is 6 x n with linear rows first, like
+ *     Sai2Model::JWorldFrame as used at src/tasks/MotionForceTask.cpp:293-298).
+ *   - batch buffers come in three layouts: AOS [B][k] (robot-major, what a host loop over robots produces),
+ *     SOA [k][B] (the device-resident layout, zero-copy friendly) and UNIFORM [k] (one value broadcast to all robots).
+ *   - buffers may live in host or device memory (OSC_MEM_*); device buffers must be on the batch's device.
+ *   - calls are asynchronous on the batch's stream; a call that writes a HOST buffer returns after the data landed.
+ *   - one host thread drives one batch; a batch lives on one GPU; shard robots over GPUs with one batch per GPU
+ *     (independent robots, no inter-GPU traffic, no collective: SURVEY.md 8e).
+ */
+#ifndef OSC_B200_H_
+#define OSC_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OSC_MAX_DOF 8
+#define OSC_MAX_TASKS 4
+#define OSC_POPC_RING_CAPACITY 1024 /* bounded stand-in for the unbounded std::queue, POPCExplicitForceControl.h:44 (quirk Q9) */
+#define OSC_MAX_SINGULARITY_BUFFER 256 /* >= BUFFER_SIZE = 200, SingularityHandler.cpp:16 */
+
+/* ---- status codes ---- */
+enum {
+	OSC_OK = 0,
+	OSC_ERR_INVALID_ARGUMENT = -1, /* the reference throws std::invalid_argument */
+	OSC_ERR_CUDA = -2,
+	OSC_ERR_NO_DEVICE = -3, /* no CUDA device / extension cannot run: the product path never falls back to the CPU */
+	OSC_ERR_UNSUPPORTED = -4
+};
+
+enum { OSC_PRECISION_F64 = 64, OSC_PRECISION_F32 = 32 };
+enum { OSC_LAYOUT_AOS = 0, OSC_LAYOUT_SOA = 1, OSC_LAYOUT_UNIFORM = 2 };
+enum { OSC_MEM_HOST = 0, OSC_MEM_DEVICE = 1 };
+enum { OSC_JOINT_REVOLUTE = 0, OSC_JOINT_PRISMATIC = 1 };
+
+/* TaskType, src/tasks/TemplateTask.h:19-23 */
+enum { OSC_TASK_UNDEFINED = 0, OSC_TASK_JOINT = 1, OSC_TASK_MOTION_FORCE = 2 };
+/* DynamicDecouplingType, src/helper_modules/Sai2PrimitivesCommonDefinitions.h:9-16 */
+enum { OSC_FULL_DYNAMIC_DECOUPLING = 0, OSC_BOUNDED_INERTIA_ESTIMATES = 1, OSC_IMPEDANCE = 2 };
+/* SingularityType, src/tasks/SingularityHandler.h:25-29 */
+enum { OSC_NO_SINGULARITY = 0, OSC_TYPE_1_SINGULARITY = 1, OSC_TYPE_2_SINGULARITY = 2 };
+
+/* per-robot status bits (field OSC_F_STATUS) */
+enum {
+	OSC_STATUS_NAN_TORQUE = 1 << 0,          /* a singular-task torque was NaN and zeroed, SingularityHandler.cpp:358 */
+	OSC_STATUS_POPC_RING_OVERFLOW = 1 << 1,  /* Q9: the passivity window outgrew OSC_POPC_RING_CAPACITY, oldest dropped */
+	OSC_STATUS_POPC_RC_NAN = 1 << 2,         /* Q8 */
+	OSC_STATUS_SVD_NOT_CONVERGED = 1 << 3,
+	OSC_STATUS_NOT_POSITIVE_DEFINITE = 1 << 4, /* a Cholesky pivot was <= 0 (the reference's llt() would return garbage) */
+	OSC_STATUS_SINGULAR_BRANCH = 1 << 5,     /* informational: robot is in the blend / fully singular branch */
+	OSC_STATUS_BAD_GOAL_ORIENTATION = 1 << 6 /* orientationError would throw (Appendix B): goal not orthonormal */
+};
+
+/* ---- robot model: stands in for Sai2Model::Sai2Model(urdf) (un-vendored sai2-model) ----
+ * A serial chain with fixed links already merged into their movable parent.  Joint i connects body i-1 (or the
+ * welded root for i = 0) to body i; its origin (xyz, rot) is expressed in the parent body frame. */
+typedef struct osc_chain_desc {
+	int32_t n;
+	int32_t joint_type[OSC_MAX_DOF];
+	double joint_axis[OSC_MAX_DOF][3];
+	double joint_xyz[OSC_MAX_DOF][3];
+	double joint_rot[OSC_MAX_DOF][9];
+	double mass[OSC_MAX_DOF];
+	double com[OSC_MAX_DOF][3];
+	double inertia[OSC_MAX_DOF][9]; /* about the com, body frame */
+	double q_lower[OSC_MAX_DOF], q_upper[OSC_MAX_DOF], effort[OSC_MAX_DOF]; /* Sai2Model::jointLimits(), SingularityHandler.cpp:43-51 */
+	double world_rot[9], world_xyz[3]; /* T_world_robot */
+	double gravity[3];
+} osc_chain_desc;
+
+/* MotionForceTask constructors, src/tasks/MotionForceTask.h:96-110, MotionForceTask.cpp:16-90 */
+typedef struct osc_mft_desc {
+	int32_t body;         /* movable body the control link is fixed in (the link's own offset is folded into frame_*) */
+	double frame_xyz[3];  /* compliant frame in that body's frame */
+	double frame_rot[9];
+	int32_t partial;      /* 0: full 6-DoF constructor (.cpp:16-31); 1: partial constructor (.cpp:33-90) */
+	int32_t n_dirs_translation;
+	double dirs_translation[3][3];
+	int32_t n_dirs_rotation;
+	double dirs_rotation[3][3];
+	int32_t parametrization_in_compliant_frame;
+	double loop_timestep;
+} osc_mft_desc;
+
+/* Runtime parameters of a MotionForceTask (uniform over the batch).  Defaults: MotionForceTask.h:40-75,
+ * SingularityHandler.cpp:10-20, MotionForceTask.cpp:197.  osc_mft_set_params applies the reference's side effects
+ * when force_space_dim/axis, moment_space_dim/axis (.cpp:830-890), closed_loop_* (.cpp:973-986) or
+ * passivity_enabled (POPCExplicitForceControl.cpp:25-28) change. */
+typedef struct osc_mft_params {
+	double kp_pos[3], kv_pos[3], ki_pos[3];
+	double kp_ori[3], kv_ori[3], ki_ori[3];
+	double kp_force, kv_force, ki_force;
+	double kp_moment, kv_moment, ki_moment;
+	double kff_force, kff_moment;
+	double max_force_control_feedback_output, max_moment_control_feedback_output;
+	int32_t force_space_dimension;
+	double force_or_motion_axis[3];
+	int32_t moment_space_dimension;
+	double moment_or_rotmotion_axis[3];
+	int32_t closed_loop_force_control, closed_loop_moment_control;
+	int32_t passivity_enabled;
+	int32_t use_velocity_saturation;
+	double linear_saturation_velocity, angular_saturation_velocity;
+	int32_t dynamic_decoupling_type;
+	double bie_threshold;
+	int32_t singularity_handling_enabled; /* enable/disableSingularityHandling, SingularityHandler.h:113-121 */
+	int32_t enforce_type_1_strategy;      /* handleAllSingularitiesAsType1 */
+	double s_min, s_max;
+	double kp_type_1, kv_type_1, kv_type_2;
+	double s_abs_tol, type_1_tol, type_2_torque_ratio, type_2_angle_threshold, perturb_step_size;
+	int32_t buffer_size;
+	double sensor_rot[9], sensor_xyz[3]; /* _T_control_to_sensor, MotionForceTask.cpp:794-803 */
+	int32_t apply_disturbance_compensation; /* 0 (default) reproduces quirk Q1: the tau_prec term is identically zero */
+} osc_mft_params;
+
+/* JointTask constructors, src/tasks/JointTask.h:56-75, JointTask.cpp:14-43 */
+typedef struct osc_joint_task_desc {
+	int32_t k;                                 /* task dof = rows of the joint selection matrix */
+	double selection[OSC_MAX_DOF * OSC_MAX_DOF]; /* k x n row-major; ignored when full != 0 */
+	int32_t full;
+	double loop_timestep;
+} osc_joint_task_desc;
+
+/* defaults JointTask.h:31-45 */
+typedef struct osc_joint_task_params {
+	double kp[OSC_MAX_DOF], kv[OSC_MAX_DOF], ki[OSC_MAX_DOF];
+	int32_t use_velocity_saturation;
+	double saturation_velocity[OSC_MAX_DOF];
+	int32_t dynamic_decoupling_type;
+	double bie_threshold;
+} osc_joint_task_params;
+
+/* ---- per-robot fields (set / get).  "task" is the index in the hierarchy, or -1 for robot-level fields. ---- */
+enum {
+	/* robot level (task = -1) */
+	OSC_F_Q = 0,            /* n   in/out  robot->setQ / q() */
+	OSC_F_DQ = 1,           /* n   in/out */
+	OSC_F_TAU = 2,          /* n   out     computeControlTorques() result */
+	OSC_F_M = 3,            /* n*n out     Sai2Model::M() */
+	OSC_F_MINV = 4,         /* n*n out     Sai2Model::MInv() */
+	OSC_F_N_TOTAL = 5,      /* n*n out     N_prec after the last task, RobotController.cpp:58 */
+	OSC_F_STATUS = 6,       /* 1 (int32) out */
+	OSC_F_GRAVITY = 7,      /* n   out     jointGravityVector() (valid when gravity compensation is on) */
+	/* any task */
+	OSC_F_TASK_TORQUES = 20,   /* n   out  this task's computeTorques result */
+	OSC_F_N_TASK = 21,         /* n*n out  getTaskNullspace() */
+	OSC_F_N_PREC = 22,         /* n*n out  getPreviousTasksNullspace() */
+	OSC_F_N_TASK_AND_PREC = 23,/* n*n out  getTaskAndPreviousNullspace() */
+	/* MotionForceTask */
+	OSC_F_GOAL_POSITION = 40,             /* 3 in/out */
+	OSC_F_GOAL_ORIENTATION = 41,          /* 9 in/out row-major */
+	OSC_F_GOAL_LINEAR_VELOCITY = 42,      /* 3 */
+	OSC_F_GOAL_ANGULAR_VELOCITY = 43,     /* 3 */
+	OSC_F_GOAL_LINEAR_ACCELERATION = 44,  /* 3 */
+	OSC_F_GOAL_ANGULAR_ACCELERATION = 45, /* 3 */
+	OSC_F_GOAL_FORCE = 46,                /* 3 */
+	OSC_F_GOAL_MOMENT = 47,               /* 3 */
+	OSC_F_SENSED_FORCE_WORLD = 48,        /* 3 out (in: use osc_mft_update_sensed_force_and_moment) */
+	OSC_F_SENSED_MOMENT_WORLD = 49,       /* 3 */
+	OSC_F_CURRENT_POSITION = 50,          /* 3 out */
+	OSC_F_CURRENT_ORIENTATION = 51,       /* 9 out */
+	OSC_F_CURRENT_LINEAR_VELOCITY = 52,   /* 3 out */
+	OSC_F_CURRENT_ANGULAR_VELOCITY = 53,  /* 3 out */
+	OSC_F_ORIENTATION_ERROR = 54,         /* 3 out */
+	OSC_F_UNIT_MASS_FORCE = 55,           /* 6 out getUnitMassForce() */
+	OSC_F_JACOBIAN = 56,                  /* 6*n out _jacobian */
+	OSC_F_PROJECTED_JACOBIAN = 57,        /* 6*n out _projected_jacobian */
+	OSC_F_LAMBDA_WORLD = 58,              /* 36 out U_ns Lambda_ns U_ns^T: the basis-independent form of _Lambda_ns */
+	OSC_F_LAMBDA_MODIFIED_WORLD = 59,     /* 36 out same for _Lambda_ns_modified */
+	OSC_F_ALPHA = 60,                     /* 1 out _alpha */
+	OSC_F_SINGULAR_VALUES = 61,           /* 6 out _svd_s (zero padded) */
+	OSC_F_NS_RANK = 62,                   /* 1 (int32) out cols(_task_range_ns), 0 when fully singular */
+	OSC_F_SINGULARITY_TYPES = 63,         /* 6 (int32) out _singularity_types zero padded */
+	OSC_F_SINGULARITY_COUNTERS = 64,      /* 2 (int32) out _type_1_counter, _type_2_counter */
+	OSC_F_INTEGRATED_POSITION_ERROR = 65, /* 3 in/out */
+	OSC_F_INTEGRATED_ORIENTATION_ERROR = 66,
+	OSC_F_INTEGRATED_FORCE_ERROR = 67,
+	OSC_F_INTEGRATED_MOMENT_ERROR = 68,
+	OSC_F_POPC_RC = 69,                   /* 1 out _Rc */
+	OSC_F_POPC_OBSERVER = 70,             /* 1 out _passivity_observer_value */
+	OSC_F_Q_PRIOR = 71,                   /* n in/out setType1Posture */
+	OSC_F_DESIRED_POSITION = 72,          /* 3 out */
+	OSC_F_DESIRED_ORIENTATION = 73,       /* 9 out */
+	OSC_F_DESIRED_LINEAR_VELOCITY = 74,   /* 3 out */
+	OSC_F_DESIRED_ANGULAR_VELOCITY = 75,  /* 3 out */
+	/* JointTask (k = task dof) */
+	OSC_F_JT_GOAL_POSITION = 80,     /* k in/out */
+	OSC_F_JT_GOAL_VELOCITY = 81,     /* k */
+	OSC_F_JT_GOAL_ACCELERATION = 82, /* k */
+	OSC_F_JT_CURRENT_POSITION = 83,  /* k out */
+	OSC_F_JT_CURRENT_VELOCITY = 84,  /* k out */
+	OSC_F_JT_INTEGRATED_ERROR = 85,  /* k in/out */
+	OSC_F_JT_LAMBDA_WORLD = 86,      /* k*k out R Lambda R^T : basis-independent form of _M_partial */
+	OSC_F_JT_LAMBDA_MODIFIED_WORLD = 87, /* k*k out */
+	OSC_F_JT_RANGE_RANK = 88,        /* 1 (int32) out cols(_current_task_range), 0 when the range is empty */
+	OSC_F_JT_DESIRED_VELOCITY = 89   /* k out */
+};
+
+typedef struct osc_batch osc_batch_t;
+
+/* ---- life cycle ---- */
+const char* osc_last_error(void);
+int osc_version(void);
+int osc_device_count(void);
+/* Sai2Model(urdf) + B copies of the robot on `device`; q is initialised to q0 (may be NULL = zeros), dq to zero. */
+int osc_batch_create(const osc_chain_desc* chain, int64_t n_robots, int precision, int device, const double* q0, osc_batch_t** out);
+void osc_batch_destroy(osc_batch_t* batch);
+int osc_batch_set_stream(osc_batch_t* batch, void* cuda_stream);
+int osc_synchronize(osc_batch_t* batch);
+int64_t osc_batch_size(const osc_batch_t* batch);
+int osc_batch_dof(const osc_batch_t* batch);
+int osc_batch_precision(const osc_batch_t* batch);
+
+/* ---- hierarchy construction: RobotController::RobotController, src/RobotController.cpp:8-51 ----
+ * Tasks are appended in priority order; the constructor rules of the reference are enforced (same dt, nothing after a
+ * full joint task).  Both return the task index (>= 0) or an error code.  Adding a task reads the current model
+ * (call osc_update_model first when q was changed), like initialSetup()/reInitializeTask() do. */
+int osc_batch_add_motion_force_task(osc_batch_t* batch, const osc_mft_desc* desc);
+int osc_batch_add_joint_task(osc_batch_t* batch, const osc_joint_task_desc* desc);
+int osc_batch_task_count(const osc_batch_t* batch);
+int osc_batch_task_type(const osc_batch_t* batch, int task);
+int osc_batch_task_dof(const osc_batch_t* batch, int task); /* MotionForceTask: _pos_range + _ori_range; JointTask: _task_dof */
+
+void osc_mft_default_params(osc_mft_params* p);
+void osc_joint_task_default_params(osc_joint_task_params* p, int k);
+int osc_mft_get_params(const osc_batch_t* batch, int task, osc_mft_params* out);
+/* returns a bit mask >= 0 of the resets it performed: 1 linear (goal position <- current, linear integrators),
+ * 2 angular, 4 passivity observer re-initialised */
+int osc_mft_set_params(osc_batch_t* batch, int task, const osc_mft_params* p);
+int osc_joint_task_get_params(const osc_batch_t* batch, int task, osc_joint_task_params* out);
+int osc_joint_task_set_params(osc_batch_t* batch, int task, const osc_joint_task_params* p);
+/* RobotController::enableGravityCompensation, src/RobotController.h:31-33 */
+int osc_enable_gravity_compensation(osc_batch_t* batch, int enable);
+
+/* ---- per-robot data ---- */
+int osc_field_size(const osc_batch_t* batch, int task, int field); /* scalars per robot, < 0 on error */
+int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int layout, int mem);
+int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout, int mem);
+/* MotionForceTask::updateSensedForceAndMoment, src/tasks/MotionForceTask.cpp:805-828 (sensor-frame wrench in) */
+int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const void* force, const void* moment, int layout, int mem);
+
+/* ---- the tick ---- */
+/* robot->updateModel(): kinematics, M (composite rigid body), M^-1.  examples/05...cpp:145 */
+int osc_update_model(osc_batch_t* batch);
+/* robot->updateKinematics() only */
+int osc_update_kinematics(osc_batch_t* batch);
+/* task->updateTaskModel(N_prec), src/tasks/TemplateTask.h:42.  n_prec_task = -1 uses identity, otherwise
+ * getTaskAndPreviousNullspace() of that (already updated) task: the manual chaining of examples/04...cpp:141-150 */
+int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task);
+/* RobotController::updateControllerTaskModels, src/RobotController.cpp:53-60 */
+int osc_update_task_models(osc_batch_t* batch);
+/* task->computeTorques() (with_tau_prec = 0, TemplateTask.h:49) or task->computeTorques(tau_prec) (TemplateTask.h:58)
+ * where tau_prec is the batch's running OSC_F_TAU; the result lands in OSC_F_TASK_TORQUES of the task. */
+int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec);
+/* RobotController::computeControlTorques, src/RobotController.cpp:62-74 (stacked = 1), or the plain sum of the
+ * no-argument computeTorques() of every task as in examples/04...cpp:188-206 (stacked = 0).
+ * tau_out may be NULL (read OSC_F_TAU later). */
+int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
+/* updateModel + updateControllerTaskModels + computeControlTorques in one call; uses the fused single-launch kernel
+ * when the hierarchy is [MotionForceTask, full JointTask], otherwise the sequence above. */
+int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
+/* 1 if osc_tick runs the fused kernel for the current hierarchy / parameters */
+int osc_tick_is_fused(const osc_batch_t* batch);
+/* number of kernels launched by this batch since creation (bench.py's gpu_launches) */
+int64_t osc_launch_count(const osc_batch_t* batch);
+
+/* RobotController::reinitializeTasks / TemplateTask::reInitializeTask; task = -1 for all */
+int osc_reinitialize_tasks(osc_batch_t* batch, int task);
+
+/* ---- controller-state snapshot (MPC rollouts: fork, roll out, restore) ---- */
+int64_t osc_snapshot_bytes(const osc_batch_t* batch);
+int osc_snapshot(osc_batch_t* batch, void* dst, int mem);
+int osc_restore(osc_batch_t* batch, const void* src, int mem);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OSC_B200_H_ */
