@@ -1,0 +1,97 @@
+// osc_host.h -- host-side state of a batch and the per-(precision, dof) operation table.
+// The C ABI (osc_capi.cu) is precision/dof agnostic; everything that launches a templated kernel goes through Ops,
+// implemented once per (T, N) in osc_ops_inst.cu (compiled once per instantiation so the builds run in parallel).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/osc_b200.h"
+
+namespace osc {
+
+struct TaskH {
+	int type = OSC_TASK_UNDEFINED;
+	osc_mft_desc md{};
+	osc_mft_params mp{};
+	osc_joint_task_desc jd{};
+	osc_joint_task_params jp{};
+	int dof = 0;           // MotionForceTask: _pos_range + _ori_range; JointTask: k
+	double P6[6][6]{};     // _partial_task_projection
+	double frame_p[3]{}, frame_R[3][3]{};  // compliant frame in the CANONICAL body frame
+	void *P = nullptr, *S = nullptr;
+	int32_t* I = nullptr;
+	int64_t p_rows = 0, s_rows = 0, i_rows = 0;
+	void* popc_ring = nullptr;
+};
+
+struct Loc {
+	int arena = 0;   // 0 P, 1 S, 2 I
+	int offset = 0;
+	int width = 0;
+	bool is_int = false;
+	bool writable = false;
+	int special = 0; // != 0: computed by Ops::pack_special into a temporary
+	int owner = -1;  // task index or -1 (robot)
+};
+
+struct Batch;
+
+struct Ops {
+	virtual ~Ops() {}
+	virtual void robot_rows(int64_t& p, int64_t& s, int64_t& i) = 0;
+	virtual void task_rows(int type, int64_t& p, int64_t& s, int64_t& i) = 0;
+	virtual int set_chain(Batch& b) = 0;  // convert the canonical chain to ChainC<T,N>
+	virtual int model(Batch& b, int dynamics) = 0;
+	virtual int task_init(Batch& b, int t) = 0;
+	virtual int task_reinit(Batch& b, int t) = 0;
+	virtual int mft_reset(Batch& b, int t, int flags) = 0;  // 1 linear, 2 angular, 4 popc, 8 lin integrators, 16 ang integrators
+	virtual int task_update(Batch& b, int t, int src) = 0;
+	virtual int task_compute(Batch& b, int t, int with_tau_prec, int accumulate) = 0;
+	virtual int add_gravity(Batch& b) = 0;
+	virtual int update_sensed(Batch& b, int t, const void* tmp6) = 0;
+	virtual bool locate(Batch& b, int task, int field, Loc& loc) = 0;
+	virtual int pack_special(Batch& b, const Loc& loc, void* tmp) = 0;
+	virtual bool fused_supported(Batch& b) = 0;
+	virtual int tick_fused(Batch& b, int stacked) = 0;
+};
+
+Ops* make_ops(int precision, int n);  // nullptr when that (precision, dof) pair was not compiled in
+
+struct Batch {
+	osc_chain_desc chain_user{};   // as given
+	osc_chain_desc chain{};        // canonical: every joint axis = local z
+	double Qc[OSC_MAX_DOF][3][3]{}; // body-frame change: canonical body i = user body i * Qc[i]
+	int n = 0;
+	int64_t B = 0, stride = 0;
+	int precision = 64, device = 0;
+	size_t esz = 8;
+	cudaStream_t stream = nullptr;
+	void *P = nullptr, *S = nullptr;
+	int32_t* I = nullptr;
+	int64_t p_rows = 0, s_rows = 0, i_rows = 0;
+	std::vector<TaskH> tasks;
+	double dt = 0;
+	bool closed = false;  // a full joint task was added: no further task (RobotController.cpp:36-49)
+	bool gravity = false;
+	int64_t launches = 0;
+	Ops* ops = nullptr;
+	void* chain_dev = nullptr;  // ChainC<T,N> host copy owned by ops
+	// staging
+	void* stage = nullptr; size_t stage_bytes = 0;
+	void* stage2 = nullptr; size_t stage2_bytes = 0;
+	void* ensure_stage(size_t bytes);
+	void* ensure_stage2(size_t bytes);
+};
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what);
+#define OSC_CUDA(x)                                      \
+	do {                                                 \
+		cudaError_t e_ = (x);                            \
+		if (e_ != cudaSuccess) return cuda_fail(e_, #x); \
+	} while (0)
+
+}  // namespace osc

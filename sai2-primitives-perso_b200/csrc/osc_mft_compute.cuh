@@ -1,0 +1,250 @@
+// osc_mft_compute.cuh -- MotionForceTask::computeTorques (src/tasks/MotionForceTask.cpp:270-509), the sigma selection
+// matrices (.cpp:892-971), POPCExplicitForceControl::computePassivitySaturatedForce
+// (src/helper_modules/POPCExplicitForceControl.cpp:30-96) and SingularityHandler::computeTorques
+// (src/tasks/SingularityHandler.cpp:297-368).
+#pragma once
+#include "osc_mft_update.cuh"
+
+namespace osc {
+
+// sigmaForce / sigmaMoment (.cpp:892-925 / 932-966): Psel (a a^T | I - a a^T) Psel^T with a = rot * axis
+template <class T> OSC_DEV void sigma_matrix(int dim, const T (&Psel)[3][3], const T (&rot)[3][3], const T (&axis)[3], T (&S)[3][3]) {
+	if (dim == 0) {
+		OSC_UNROLL for (int i = 0; i < 3; ++i)
+			OSC_UNROLL for (int j = 0; j < 3; ++j) S[i][j] = T(0);
+		return;
+	}
+	if (dim == 3) {
+		OSC_UNROLL for (int i = 0; i < 3; ++i)
+			OSC_UNROLL for (int j = 0; j < 3; ++j) S[i][j] = Psel[i][j];
+		return;
+	}
+	T a[3];
+	mv3(rot, axis, a);
+	T Mid[3][3], Tmp[3][3];
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) {
+			const T aa = a[i] * a[j];
+			Mid[i][j] = (dim == 1) ? aa : ((i == j ? T(1) : T(0)) - aa);
+		}
+	mm3(Psel, Mid, Tmp);
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) S[i][j] = Tmp[i][0] * Psel[j][0] + Tmp[i][1] * Psel[j][1] + Tmp[i][2] * Psel[j][2];
+}
+// P (I - S) P^T  (sigmaPosition / sigmaOrientation, .cpp:927-930, 968-971)
+template <class T> OSC_DEV void sigma_complement(const T (&Psel)[3][3], const T (&S)[3][3], T (&O)[3][3]) {
+	T Mid[3][3], Tmp[3][3];
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) Mid[i][j] = (i == j ? T(1) : T(0)) - S[i][j];
+	mm3(Psel, Mid, Tmp);
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) O[i][j] = Tmp[i][0] * Psel[j][0] + Tmp[i][1] * Psel[j][1] + Tmp[i][2] * Psel[j][2];
+}
+
+// POPCExplicitForceControl::computePassivitySaturatedForce; the std::queue is a ring of OSC_POPC_RING_CAPACITY slots
+// in HBM (quirk Q9).  Returns R_c * vcl - kv_f * vr.
+template <class T, int N>
+OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>& tI, int64_t stride, int64_t r, const T (&fd)[3], const T (&fs)[3],
+						const T (&vcl)[3], const T (&vr)[3], T (&out)[3], int& status) {
+	using L = MftL<N>;
+	const T kv = tc.kv_force;
+	if (!tc.passivity || tc.popc_ring == nullptr) {  // .cpp:33-35
+		OSC_UNROLL for (int a = 0; a < 3; ++a) out[a] = vcl[a] - kv * vr[a];
+		return;
+	}
+	T PO = tP(L::POPC_PO), Ec = tP(L::POPC_ECORR), Rc = tP(L::POPC_RC), vsq = tP(L::POPC_VSQ);
+	int counter = tI(L::POPC_COUNTER), head = tI(L::POPC_HEAD), len = tI(L::POPC_LEN);
+	T Fcmd[3], fdiff[3];
+	OSC_UNROLL for (int a = 0; a < 3; ++a) { Fcmd[a] = tc.kff_force * fd[a] + Rc * vcl[a] - kv * vr[a]; fdiff[a] = fs[a] - fd[a]; }
+	const T vc2 = dot3(vcl, vcl);
+	const T p = (dot3(fdiff, vcl) - dot3(Fcmd, vr)) * tc.dt;
+	PO += p;
+	T* ring = tc.popc_ring;
+	if (len == 1024) {  // overflow: drop the oldest sample (status bit), Q9
+		head = (head + 1) & 1023; --len; status |= 2;
+	}
+	ring[(int64_t)((head + len) & 1023) * stride + r] = p;
+	++len;
+	if (PO + Ec > T(0)) {  // _stored_energy_PO is identically 0 (.cpp:13)
+		while (len > 250) {
+			const T front = ring[(int64_t)head * stride + r];
+			if (PO + Ec > front) {
+				if (front > T(0)) PO -= front;
+				head = (head + 1) & 1023; --len;
+			} else break;
+		}
+	}
+	if (counter <= 0) {  // .cpp:64-90
+		counter = 50;
+		const T old = Rc;
+		if (PO + Ec < T(0)) {
+			Rc = T(1) + (PO + Ec) / (vsq * tc.dt);
+			if (Rc > T(1)) Rc = T(1);
+			if (Rc < T(0)) Rc = T(0);
+			if (Rc != Rc) status |= 4;  // quirk Q8
+		} else {
+			Rc = (T(1) + (T(0.1) * T(50) - T(1)) * Rc) / (T(0.1) * T(50));
+		}
+		Ec += (T(1) - old) * vsq * tc.dt;
+		vsq = T(0);
+	}
+	--counter;
+	vsq += vc2;
+	OSC_UNROLL for (int a = 0; a < 3; ++a) out[a] = Rc * vcl[a] - kv * vr[a];
+	tP(L::POPC_PO) = PO; tP(L::POPC_ECORR) = Ec; tP(L::POPC_RC) = Rc; tP(L::POPC_VSQ) = vsq;
+	tI(L::POPC_COUNTER) = counter; tI(L::POPC_HEAD) = head; tI(L::POPC_LEN) = len;
+}
+
+// The control law: returns F* (unit mass force) and F_f (force feedback + feed-forward); updates integrators and caches.
+template <class T, int N>
+OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
+							 const T (&J)[6][N], const T (&dq)[N], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status) {
+	using L = MftL<N>;
+	T v[3], w[3];
+	OSC_UNROLL for (int a = 0; a < 3; ++a) {
+		T sv = T(0), sw = T(0);
+		OSC_UNROLL for (int j = 0; j < N; ++j) { sv = Num<T>::fma_(J[a][j], dq[j], sv); sw = Num<T>::fma_(J[3 + a][j], dq[j], sw); }
+		v[a] = sv; w[a] = sw;
+	}
+	T Rg[3][3], xg[3];
+	ld_mat<T, 3, 3>(tP, L::GOAL_ORI, Rg);
+	ld_vec<T, 3>(tP, L::GOAL_POS, xg);
+	T oe[3];
+	orientation_error<T>(Rg, R, oe);  // .cpp:291-292 (_orientation_error, for getters)
+	st_vec<T, 3>(tS, L::ORI_ERR, oe);
+	st_vec<T, 3>(tS, L::CUR_V, v);
+	st_vec<T, 3>(tS, L::CUR_W, w);
+	st_vec<T, 3>(tP, L::CUR_POS, x);
+	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
+
+	T rot[3][3];
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) rot[i][j] = tc.in_compliant_frame ? R[i][j] : (i == j ? T(1) : T(0));
+	T Sf[3][3], Sm[3][3], Sp[3][3], So[3][3];
+	sigma_matrix<T>(tc.force_dim, tc.Pt, rot, tc.force_axis, Sf);
+	sigma_matrix<T>(tc.moment_dim, tc.Pr, rot, tc.moment_axis, Sm);
+	sigma_complement<T>(tc.Pt, Sf, Sp);
+	sigma_complement<T>(tc.Pr, Sm, So);
+	T gf_[3], gm_[3], gf[3], gm[3], fs[3], ms[3];
+	ld_vec<T, 3>(tP, L::GOAL_FORCE, gf_);
+	ld_vec<T, 3>(tP, L::GOAL_MOMENT, gm_);
+	mv3(rot, gf_, gf);  // getGoalForce / getGoalMoment, .cpp:755-769
+	mv3(rot, gm_, gm);
+	ld_vec<T, 3>(tP, L::SENSED_F, fs);
+	ld_vec<T, 3>(tP, L::SENSED_M, ms);
+
+	T Ffb[3], Mfb[3];
+	if (tc.closed_loop_force) {  // .cpp:327-349
+		T e[3], se[3], ie[3], raw[3], fb[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = fs[a] - gf[a];
+		mv3(Sf, e, se);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_F + a) + se[a] * tc.dt; tP(L::INT_F + a) = ie[a]; }
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_force * e[a] - tc.ki_force * ie[a];
+		mv3(Sf, raw, fb);
+		const T nf = norm3(fb);
+		if (nf > tc.max_force_fb) {
+			const T sc = tc.max_force_fb / nf;
+			OSC_UNROLL for (int a = 0; a < 3; ++a) fb[a] *= sc;
+		}
+		T a1[3], a2[3], a3[3], a4[3];
+		mv3(Sf, gf, a1); mv3(Sf, fs, a2); mv3(Sf, fb, a3); mv3(Sf, v, a4);
+		popc_force<T, N>(tc, tP, tI, stride, r, a1, a2, a3, a4, Ffb, status);
+	} else {  // .cpp:352-353
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_force * v[a];
+		mv3(Sf, raw, Ffb);
+	}
+	if (tc.closed_loop_moment) {  // .cpp:357-378
+		T e[3], se[3], ie[3], raw[3], mb[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = ms[a] - gm[a];
+		mv3(Sm, e, se);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_M + a) + se[a] * tc.dt; tP(L::INT_M + a) = ie[a]; }
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_moment * e[a] - tc.ki_moment * ie[a];
+		mv3(Sm, raw, mb);
+		const T nm = norm3(mb);
+		if (nm > tc.max_moment_fb) {
+			const T sc = tc.max_moment_fb / nm;
+			OSC_UNROLL for (int a = 0; a < 3; ++a) mb[a] *= sc;
+		}
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = mb[a] - tc.kv_moment * w[a];
+		mv3(Sm, raw, Mfb);
+	} else {  // .cpp:381-382
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_moment * w[a];
+		mv3(Sm, raw, Mfb);
+	}
+
+	// desired <- goal (.cpp:387-392; the internal OTG is the "next" row f-1)
+	T vd[3], wd[3], ad[3], bd[3];
+	ld_vec<T, 3>(tP, L::GOAL_LINVEL, vd);
+	ld_vec<T, 3>(tP, L::GOAL_ANGVEL, wd);
+	ld_vec<T, 3>(tP, L::GOAL_LINACC, ad);
+	ld_vec<T, 3>(tP, L::GOAL_ANGACC, bd);
+	// linear motion (.cpp:411-437)
+	T ex[3], sex[3], ip[3], Fp[3], Fo[3];
+	OSC_UNROLL for (int a = 0; a < 3; ++a) ex[a] = x[a] - xg[a];
+	mv3(Sp, ex, sex);
+	OSC_UNROLL for (int a = 0; a < 3; ++a) { ip[a] = tP(L::INT_POS + a) + sex[a] * tc.dt; tP(L::INT_POS + a) = ip[a]; }
+	if (tc.use_vel_sat) {
+		T mx = T(0);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) mx = Num<T>::abs_(tc.kv_pos[a]) > mx ? Num<T>::abs_(tc.kv_pos[a]) : mx;
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			const T kvi = Num<T>::abs_(tc.kv_pos[a]) > T(1e-6) * mx ? T(1) / tc.kv_pos[a] : T(0);  // computePseudoInverse
+			vd[a] = -tc.kp_pos[a] * kvi * sex[a] - tc.ki_pos[a] * kvi * ip[a];
+		}
+		const T nv = norm3(vd);
+		if (nv > tc.lin_sat) {
+			const T sc = tc.lin_sat / nv;
+			OSC_UNROLL for (int a = 0; a < 3; ++a) vd[a] *= sc;
+		}
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = ad[a] - tc.kv_pos[a] * (v[a] - vd[a]);
+		mv3(Sp, raw, Fp);
+	} else {
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = ad[a] - tc.kp_pos[a] * ex[a] - tc.kv_pos[a] * (v[a] - vd[a]) - tc.ki_pos[a] * ip[a];
+		mv3(Sp, raw, Fp);
+	}
+	// angular motion (.cpp:441-468)
+	T eo[3], io[3];
+	mv3(So, oe, eo);  // desired orientation == goal orientation
+	OSC_UNROLL for (int a = 0; a < 3; ++a) { io[a] = tP(L::INT_ORI + a) + eo[a] * tc.dt; tP(L::INT_ORI + a) = io[a]; }
+	if (tc.use_vel_sat) {
+		T mx = T(0);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) mx = Num<T>::abs_(tc.kv_ori[a]) > mx ? Num<T>::abs_(tc.kv_ori[a]) : mx;
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			const T kvi = Num<T>::abs_(tc.kv_ori[a]) > T(1e-6) * mx ? T(1) / tc.kv_ori[a] : T(0);
+			wd[a] = -tc.kp_ori[a] * kvi * eo[a] - tc.ki_ori[a] * kvi * io[a];
+		}
+		const T nw = norm3(wd);
+		if (nw > tc.ang_sat) {
+			const T sc = tc.ang_sat / nw;
+			OSC_UNROLL for (int a = 0; a < 3; ++a) wd[a] *= sc;
+		}
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = bd[a] - tc.kv_ori[a] * (w[a] - wd[a]);
+		mv3(So, raw, Fo);
+	} else {
+		T raw[3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = bd[a] - tc.kp_ori[a] * eo[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io[a];
+		mv3(So, raw, Fo);
+	}
+	st_vec<T, 3>(tS, L::DES_POS, xg);
+	st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
+	st_vec<T, 3>(tS, L::DES_LINVEL, vd);
+	st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+	// assemble (.cpp:470-487; quirk Q3: the moment feed-forward is scaled under the *force* flag)
+	T ffh[3], fft[3];
+	mv3(Sf, gf, ffh);
+	mv3(Sm, gm, fft);
+	if (tc.closed_loop_force) {
+		OSC_UNROLL for (int a = 0; a < 3; ++a) { ffh[a] *= tc.kff_force; fft[a] *= tc.kff_moment; }
+	}
+	OSC_UNROLL for (int a = 0; a < 3; ++a) {
+		Fstar[a] = Fp[a]; Fstar[3 + a] = Fo[a];
+		Ff[a] = Ffb[a] + ffh[a]; Ff[3 + a] = Mfb[a] + fft[a];
+	}
+	st_vec<T, 6>(tS, L::UMF, Fstar);
+}
+
+}  // namespace osc
