@@ -29,6 +29,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default) /* libosc_b200.so is built with -fvisibility=hidden: only this header is exported */
+#endif
 
 #define OSC_MAX_DOF 8
 #define OSC_MAX_TASKS 4
@@ -288,6 +291,9 @@ int64_t osc_snapshot_bytes(const osc_batch_t* batch);
 int osc_snapshot(osc_batch_t* batch, void* dst, int mem);
 int osc_restore(osc_batch_t* batch, const void* src, int mem);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

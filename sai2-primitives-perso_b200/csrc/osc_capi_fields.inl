@@ -1,0 +1,53 @@
+// osc_capi_fields.inl -- per-robot field access
+
+extern "C" {
+
+int osc_field_size(const osc_batch_t* batch, int task, int field) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	Loc l;
+	if (!b->ops->locate(*b, task, field, l)) return invalid("unknown field for this task");
+	return l.width;
+}
+
+int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int layout, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b || !data) return invalid("null argument");
+	Loc l;
+	if (!b->ops->locate(*b, task, field, l)) return invalid("unknown field for this task");
+	if (!l.writable || l.special) return invalid("field is read-only");
+	if (int rc = use_device(*b)) return rc;
+	return import_rows(*b, row_ptr(*b, l), l.width, l.is_int, data, layout, mem);
+}
+
+int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b || !out) return invalid("null argument");
+	Loc l;
+	if (!b->ops->locate(*b, task, field, l)) return invalid("unknown field for this task");
+	if (int rc = use_device(*b)) return rc;
+	const void* rows = nullptr;
+	if (l.special) {
+		void* tmp = b->ensure_stage2((size_t)l.width * b->stride * 8);
+		if (!tmp) return invalid("out of device memory (staging)");
+		if (int rc = b->ops->pack_special(*b, l, tmp)) return rc;
+		rows = tmp;
+	} else {
+		rows = row_ptr(*b, l);
+	}
+	return export_rows(*b, rows, l.width, l.is_int, out, layout, mem);
+}
+
+int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const void* force, const void* moment, int layout, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b || !force || !moment) return invalid("null argument");
+	if (task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_MOTION_FORCE) return invalid("not a MotionForceTask");
+	if (int rc = use_device(*b)) return rc;
+	char* tmp = (char*)b->ensure_stage2((size_t)6 * b->stride * 8);
+	if (!tmp) return invalid("out of device memory (staging)");
+	if (int rc = import_rows(*b, tmp, 3, false, force, layout, mem)) return rc;
+	if (int rc = import_rows(*b, tmp + (size_t)3 * b->stride * b->esz, 3, false, moment, layout, mem)) return rc;
+	return b->ops->update_sensed(*b, task, tmp);
+}
+
+}  // extern "C"

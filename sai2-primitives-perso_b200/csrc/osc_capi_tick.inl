@@ -1,0 +1,137 @@
+// osc_capi_tick.inl -- the per-tick entry points and the controller-state snapshot
+
+namespace osc {
+static int check_task(Batch* b, int task) {
+	if (!b) return invalid("null batch");
+	if (task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
+	return OSC_OK;
+}
+static int emit_tau(Batch& b, void* tau_out, int layout, int mem) {
+	if (!tau_out) return OSC_OK;
+	Loc l;
+	b.ops->locate(b, -1, OSC_F_TAU, l);
+	return export_rows(b, row_ptr(b, l), l.width, false, tau_out, layout, mem);
+}
+}  // namespace osc
+
+extern "C" {
+
+int osc_update_model(osc_batch_t* batch) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (int rc = use_device(*b)) return rc;
+	return b->ops->model(*b, 1);
+}
+int osc_update_kinematics(osc_batch_t* batch) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (int rc = use_device(*b)) return rc;
+	return b->ops->model(*b, 0);
+}
+int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
+	Batch* b = (Batch*)batch;
+	if (int rc = check_task(b, task)) return rc;
+	if (n_prec_task >= (int)b->tasks.size() || n_prec_task == task)
+		return invalid("N_prec matrix size not consistent with robot dof in updateTaskModel\n");
+	if (int rc = use_device(*b)) return rc;
+	return b->ops->task_update(*b, task, n_prec_task < 0 ? -1 : n_prec_task);
+}
+int osc_update_task_models(osc_batch_t* batch) {  // RobotController.cpp:53-60
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
+	if (int rc = use_device(*b)) return rc;
+	for (int t = 0; t < (int)b->tasks.size(); ++t)
+		if (int rc = b->ops->task_update(*b, t, t - 1)) return rc;
+	return OSC_OK;
+}
+int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
+	Batch* b = (Batch*)batch;
+	if (int rc = check_task(b, task)) return rc;
+	if (int rc = use_device(*b)) return rc;
+	return b->ops->task_compute(*b, task, with_tau_prec, 0);
+}
+int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {  // RobotController.cpp:62-74
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
+	if (int rc = use_device(*b)) return rc;
+	for (int t = 0; t < (int)b->tasks.size(); ++t)
+		if (int rc = b->ops->task_compute(*b, t, (stacked && t > 0) ? 1 : 0, t == 0 ? 1 : 2)) return rc;
+	if (b->gravity)
+		if (int rc = b->ops->add_gravity(*b)) return rc;
+	return emit_tau(*b, tau_out, layout, mem);
+}
+int osc_tick_is_fused(const osc_batch_t* batch) {
+	Batch* b = (Batch*)batch;
+	return b && b->ops->fused_supported(*b) ? 1 : 0;
+}
+int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
+	if (int rc = use_device(*b)) return rc;
+	if (b->ops->fused_supported(*b)) {
+		if (int rc = b->ops->tick_fused(*b, stacked)) return rc;
+		return emit_tau(*b, tau_out, layout, mem);
+	}
+	if (int rc = b->ops->model(*b, 1)) return rc;
+	if (int rc = osc_update_task_models(batch)) return rc;
+	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
+}
+
+int osc_reinitialize_tasks(osc_batch_t* batch, int task) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (task >= (int)b->tasks.size()) return invalid("task index out of range");
+	if (int rc = use_device(*b)) return rc;
+	for (int t = 0; t < (int)b->tasks.size(); ++t)
+		if (task < 0 || t == task)
+			if (int rc = b->ops->task_reinit(*b, t)) return rc;
+	return OSC_OK;
+}
+
+// snapshot = persistent reals + persistent ints of the robot and of every task (+ the passivity ring when allocated)
+static int64_t snapshot_walk(Batch& b, char* buf, int mem, int dir) {
+	int64_t off = 0;
+	auto seg = [&](void* dev, size_t bytes) -> int {
+		if (buf && bytes) {
+			cudaMemcpyKind kind = mem == OSC_MEM_HOST ? (dir ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost) : cudaMemcpyDeviceToDevice;
+			cudaError_t e = dir ? cudaMemcpyAsync(dev, buf + off, bytes, kind, b.stream) : cudaMemcpyAsync(buf + off, dev, bytes, kind, b.stream);
+			if (e != cudaSuccess) return cuda_fail(e, "snapshot copy");
+		}
+		off += (int64_t)bytes;
+		return OSC_OK;
+	};
+	if (seg(b.P, (size_t)b.p_rows * b.stride * b.esz)) return -1;
+	if (seg(b.I, (size_t)b.i_rows * b.stride * 4)) return -1;
+	for (TaskH& t : b.tasks) {
+		if (seg(t.P, (size_t)t.p_rows * b.stride * b.esz)) return -1;
+		if (seg(t.I, (size_t)t.i_rows * b.stride * 4)) return -1;
+		if (t.popc_ring && seg(t.popc_ring, (size_t)OSC_POPC_RING_CAPACITY * b.stride * b.esz)) return -1;
+	}
+	return off;
+}
+int64_t osc_snapshot_bytes(const osc_batch_t* batch) {
+	Batch* b = (Batch*)batch;
+	if (!b) return 0;
+	return snapshot_walk(*b, nullptr, OSC_MEM_DEVICE, 0);
+}
+int osc_snapshot(osc_batch_t* batch, void* dst, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b || !dst) return invalid("null argument");
+	if (int rc = use_device(*b)) return rc;
+	if (snapshot_walk(*b, (char*)dst, mem, 0) < 0) return OSC_ERR_CUDA;
+	if (mem == OSC_MEM_HOST) OSC_CUDA(cudaStreamSynchronize(b->stream));
+	return OSC_OK;
+}
+int osc_restore(osc_batch_t* batch, const void* src, int mem) {
+	Batch* b = (Batch*)batch;
+	if (!b || !src) return invalid("null argument");
+	if (int rc = use_device(*b)) return rc;
+	if (snapshot_walk(*b, (char*)src, mem, 1) < 0) return OSC_ERR_CUDA;
+	if (mem == OSC_MEM_HOST) OSC_CUDA(cudaStreamSynchronize(b->stream));
+	return OSC_OK;
+}
+
+}  // extern "C"

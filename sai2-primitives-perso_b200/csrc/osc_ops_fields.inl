@@ -1,0 +1,136 @@
+// osc_ops_fields.inl -- field id -> storage location (included inside the anonymous namespace of osc_ops_inst.cu)
+
+template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int field, Loc& l) {
+	l = Loc{};
+	l.owner = task;
+	auto set = [&](int arena, int off, int w, bool wr, bool is_int = false) {
+		l.arena = arena; l.offset = off; l.width = w; l.writable = wr; l.is_int = is_int;
+		return true;
+	};
+	if (task < 0) {
+		using R = RobotL<N>;
+		switch (field) {
+			case OSC_F_Q: return set(0, R::Q, N, true);
+			case OSC_F_DQ: return set(0, R::DQ, N, true);
+			case OSC_F_TAU: return set(1, R::TAU, N, true);
+			case OSC_F_M: return set(1, R::M, N * N, false);
+			case OSC_F_MINV: return set(1, R::MINV, N * N, false);
+			case OSC_F_GRAVITY: return set(1, R::GRAV, N, false);
+			case OSC_F_STATUS: return set(2, R::STATUS, 1, true, true);
+			case OSC_F_N_TOTAL: {
+				if (b.tasks.empty()) return false;
+				const int last = (int)b.tasks.size() - 1;
+				l.owner = last;
+				return set(1, b.tasks[last].type == OSC_TASK_MOTION_FORCE ? MftL<N>::NTP : JtL<N>::NTP, N * N, false);
+			}
+		}
+		return false;
+	}
+	if (task >= (int)b.tasks.size()) return false;
+	const TaskH& t = b.tasks[task];
+	if (t.type == OSC_TASK_MOTION_FORCE) {
+		using L = MftL<N>;
+		constexpr int K = L::K;
+		switch (field) {
+			case OSC_F_TASK_TORQUES: return set(1, L::TASK_TAU, N, false);
+			case OSC_F_N_TASK: return set(1, L::NT, N * N, false);
+			case OSC_F_N_PREC: return set(1, L::NPREC, N * N, false);
+			case OSC_F_N_TASK_AND_PREC: return set(1, L::NTP, N * N, false);
+			case OSC_F_GOAL_POSITION: return set(0, L::GOAL_POS, 3, true);
+			case OSC_F_GOAL_ORIENTATION: return set(0, L::GOAL_ORI, 9, true);
+			case OSC_F_GOAL_LINEAR_VELOCITY: return set(0, L::GOAL_LINVEL, 3, true);
+			case OSC_F_GOAL_ANGULAR_VELOCITY: return set(0, L::GOAL_ANGVEL, 3, true);
+			case OSC_F_GOAL_LINEAR_ACCELERATION: return set(0, L::GOAL_LINACC, 3, true);
+			case OSC_F_GOAL_ANGULAR_ACCELERATION: return set(0, L::GOAL_ANGACC, 3, true);
+			case OSC_F_GOAL_FORCE: return set(0, L::GOAL_FORCE, 3, true);
+			case OSC_F_GOAL_MOMENT: return set(0, L::GOAL_MOMENT, 3, true);
+			case OSC_F_SENSED_FORCE_WORLD: return set(0, L::SENSED_F, 3, true);
+			case OSC_F_SENSED_MOMENT_WORLD: return set(0, L::SENSED_M, 3, true);
+			case OSC_F_CURRENT_POSITION: return set(0, L::CUR_POS, 3, false);
+			case OSC_F_CURRENT_ORIENTATION: return set(0, L::CUR_ORI, 9, false);
+			case OSC_F_CURRENT_LINEAR_VELOCITY: return set(1, L::CUR_V, 3, false);
+			case OSC_F_CURRENT_ANGULAR_VELOCITY: return set(1, L::CUR_W, 3, false);
+			case OSC_F_ORIENTATION_ERROR: return set(1, L::ORI_ERR, 3, false);
+			case OSC_F_UNIT_MASS_FORCE: return set(1, L::UMF, 6, false);
+			case OSC_F_JACOBIAN: return set(1, L::J, 6 * N, false);
+			case OSC_F_PROJECTED_JACOBIAN: return set(1, L::JP, 6 * N, false);
+			case OSC_F_LAMBDA_WORLD: l.special = 1; return set(1, 0, 36, false);
+			case OSC_F_LAMBDA_MODIFIED_WORLD: l.special = 2; return set(1, 0, 36, false);
+			case OSC_F_ALPHA: return set(1, L::ALPHA, 1, false);
+			case OSC_F_SINGULAR_VALUES: l.special = 5; return set(1, L::SV, 6, false);
+			case OSC_F_NS_RANK: return set(2, L::INS, 1, false, true);
+			case OSC_F_SINGULARITY_TYPES: l.special = 3; return set(2, 0, 6, false, true);
+			case OSC_F_SINGULARITY_COUNTERS: l.special = 4; return set(2, 0, 2, false, true);
+			case OSC_F_INTEGRATED_POSITION_ERROR: return set(0, L::INT_POS, 3, true);
+			case OSC_F_INTEGRATED_ORIENTATION_ERROR: return set(0, L::INT_ORI, 3, true);
+			case OSC_F_INTEGRATED_FORCE_ERROR: return set(0, L::INT_F, 3, true);
+			case OSC_F_INTEGRATED_MOMENT_ERROR: return set(0, L::INT_M, 3, true);
+			case OSC_F_POPC_RC: return set(0, L::POPC_RC, 1, false);
+			case OSC_F_POPC_OBSERVER: return set(0, L::POPC_PO, 1, false);
+			case OSC_F_Q_PRIOR: return set(0, L::Q_PRIOR, N, true);
+			case OSC_F_DESIRED_POSITION: return set(1, L::DES_POS, 3, false);
+			case OSC_F_DESIRED_ORIENTATION: return set(1, L::DES_ORI, 9, false);
+			case OSC_F_DESIRED_LINEAR_VELOCITY: return set(1, L::DES_LINVEL, 3, false);
+			case OSC_F_DESIRED_ANGULAR_VELOCITY: return set(1, L::DES_ANGVEL, 3, false);
+		}
+		(void)K;
+		return false;
+	}
+	using L = JtL<N>;
+	const int k = t.dof;
+	switch (field) {
+		case OSC_F_TASK_TORQUES: return set(1, L::TASK_TAU, N, false);
+		case OSC_F_N_TASK: return set(1, L::NT, N * N, false);
+		case OSC_F_N_PREC: return set(1, L::NPREC, N * N, false);
+		case OSC_F_N_TASK_AND_PREC: return set(1, L::NTP, N * N, false);
+		case OSC_F_JT_GOAL_POSITION: return set(0, L::GOAL_POS, k, true);
+		case OSC_F_JT_GOAL_VELOCITY: return set(0, L::GOAL_VEL, k, true);
+		case OSC_F_JT_GOAL_ACCELERATION: return set(0, L::GOAL_ACC, k, true);
+		case OSC_F_JT_CURRENT_POSITION: return set(1, L::CUR_POS, k, false);
+		case OSC_F_JT_CURRENT_VELOCITY: return set(1, L::CUR_VEL, k, false);
+		case OSC_F_JT_INTEGRATED_ERROR: return set(0, L::INTEG, k, true);
+		case OSC_F_JT_DESIRED_VELOCITY: return set(1, L::DES_VEL, k, false);
+		case OSC_F_JT_LAMBDA_WORLD: l.special = 6; return set(1, 0, k * k, false);
+		case OSC_F_JT_LAMBDA_MODIFIED_WORLD: l.special = 7; return set(1, 0, k * k, false);
+		case OSC_F_JT_RANGE_RANK: return set(2, L::RANK, 1, false, true);
+	}
+	return false;
+}
+
+// tmp: SoA [width][stride] of T (or int32)
+template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l, void* tmp) {
+	TaskH& t = b.tasks[l.owner];
+	constexpr int K = MftL<N>::K;
+	switch (l.special) {
+		case 1:
+		case 2:
+			k_pack_ulut<T, 6, K><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, MftL<N>::U_NS, l.special == 1 ? MftL<N>::L_NS : MftL<N>::L_NS_MOD,
+																		 (T*)tmp, b.B, b.stride, 6);
+			return done(b, "k_pack_ulut");
+		case 3:
+		case 4:
+			k_pack_types<N><<<grid(b), OSC_THREADS, 0, b.stream>>>(t.I, (int32_t*)tmp, b.B, b.stride, l.special == 3 ? 0 : 1);
+			return done(b, "k_pack_types");
+		case 5: {  // singular values zero padded to 6
+			cudaError_t e = cudaMemsetAsync(tmp, 0, (size_t)6 * b.stride * sizeof(T), b.stream);
+			if (e != cudaSuccess) return cuda_fail(e, "memset");
+			e = cudaMemcpyAsync(tmp, (const T*)t.S + (int64_t)MftL<N>::SV * b.stride, (size_t)K * b.stride * sizeof(T), cudaMemcpyDeviceToDevice, b.stream);
+			if (e != cudaSuccess) return cuda_fail(e, "memcpy");
+			return OSC_OK;
+		}
+		case 6:
+		case 7:
+			k_pack_ulut<T, N, N><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, JtL<N>::RANGE, l.special == 6 ? JtL<N>::LAM : JtL<N>::LAM_MOD,
+																		 (T*)tmp, b.B, b.stride, t.dof);
+			return done(b, "k_pack_ulut");
+	}
+	set_error("internal: unknown packed field");
+	return OSC_ERR_INVALID_ARGUMENT;
+}
+
+template <class T, int N> bool OpsImpl<T, N>::fused_supported(Batch& b) { return fused_tick_supported<T, N>(b); }
+template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
+	const int rc = fused_tick_launch<T, N>(b, ch, stacked);
+	if (rc != OSC_OK) return rc;
+	return done(b, "k_tick_fused");
+}

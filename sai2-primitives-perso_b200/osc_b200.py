@@ -1,0 +1,247 @@
+"""ctypes binding of libosc_b200.so (the C ABI of include/osc_b200.h) for tests, bench.py and Python users.
+
+The product is the shared library (hand-written sm_100a kernels behind a C ABI) and the C++ facade
+include/Sai2PrimitivesBatched.h; this module is only the thinnest possible Python view of the same entry points.
+There is NO CPU fallback: importing works without a GPU (so that the ABI can be inspected), but creating a batch
+without a CUDA device raises, and a missing library raises at import of `lib()`.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+import osc_abi as abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libosc_b200.so")
+_LIB = None
+
+
+class OscError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("osc_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class OscInvalidArgument(OscError, ValueError):
+    """the reference throws std::invalid_argument in this situation"""
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("libosc_b200.so is missing: run `python sai2-primitives-perso_b200/build.py` "
+                          "(there is no CPU fallback for the batched controller)")
+    L = C.CDLL(LIB_PATH)
+    vp, i, i64 = C.c_void_p, C.c_int, C.c_int64
+    sig = {
+        "osc_last_error": (C.c_char_p, []),
+        "osc_version": (i, []),
+        "osc_device_count": (i, []),
+        "osc_batch_create": (i, [C.POINTER(abi.ChainDesc), i64, i, i, C.POINTER(C.c_double), C.POINTER(vp)]),
+        "osc_batch_destroy": (None, [vp]),
+        "osc_batch_set_stream": (i, [vp, vp]),
+        "osc_synchronize": (i, [vp]),
+        "osc_batch_size": (i64, [vp]),
+        "osc_batch_dof": (i, [vp]),
+        "osc_batch_precision": (i, [vp]),
+        "osc_batch_add_motion_force_task": (i, [vp, C.POINTER(abi.MftDesc)]),
+        "osc_batch_add_joint_task": (i, [vp, C.POINTER(abi.JointTaskDesc)]),
+        "osc_batch_task_count": (i, [vp]),
+        "osc_batch_task_type": (i, [vp, i]),
+        "osc_batch_task_dof": (i, [vp, i]),
+        "osc_mft_default_params": (None, [C.POINTER(abi.MftParams)]),
+        "osc_joint_task_default_params": (None, [C.POINTER(abi.JointTaskParams), i]),
+        "osc_mft_get_params": (i, [vp, i, C.POINTER(abi.MftParams)]),
+        "osc_mft_set_params": (i, [vp, i, C.POINTER(abi.MftParams)]),
+        "osc_joint_task_get_params": (i, [vp, i, C.POINTER(abi.JointTaskParams)]),
+        "osc_joint_task_set_params": (i, [vp, i, C.POINTER(abi.JointTaskParams)]),
+        "osc_enable_gravity_compensation": (i, [vp, i]),
+        "osc_field_size": (i, [vp, i, i]),
+        "osc_set_field": (i, [vp, i, i, vp, i, i]),
+        "osc_get_field": (i, [vp, i, i, vp, i, i]),
+        "osc_mft_update_sensed_force_and_moment": (i, [vp, i, vp, vp, i, i]),
+        "osc_update_model": (i, [vp]),
+        "osc_update_kinematics": (i, [vp]),
+        "osc_task_update_model": (i, [vp, i, i]),
+        "osc_update_task_models": (i, [vp]),
+        "osc_task_compute_torques": (i, [vp, i, i]),
+        "osc_compute_torques": (i, [vp, i, vp, i, i]),
+        "osc_tick": (i, [vp, i, vp, i, i]),
+        "osc_tick_is_fused": (i, [vp]),
+        "osc_launch_count": (i64, [vp]),
+        "osc_reinitialize_tasks": (i, [vp, i]),
+        "osc_snapshot_bytes": (i64, [vp]),
+        "osc_snapshot": (i, [vp, vp, i]),
+        "osc_restore": (i, [vp, vp, i]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    _LIB = L
+    return L
+
+
+EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_create", "osc_batch_destroy",
+            "osc_batch_set_stream", "osc_synchronize", "osc_batch_size", "osc_batch_dof", "osc_batch_precision",
+            "osc_batch_add_motion_force_task", "osc_batch_add_joint_task", "osc_batch_task_count", "osc_batch_task_type",
+            "osc_batch_task_dof", "osc_mft_default_params", "osc_joint_task_default_params", "osc_mft_get_params",
+            "osc_mft_set_params", "osc_joint_task_get_params", "osc_joint_task_set_params",
+            "osc_enable_gravity_compensation", "osc_field_size", "osc_set_field", "osc_get_field",
+            "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
+            "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
+            "osc_tick", "osc_tick_is_fused", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
+            "osc_snapshot", "osc_restore"]
+
+
+class Batch:
+    """B robots on one GPU.  Method names follow the C ABI; host numpy arrays are AOS [B, k]."""
+
+    def __init__(self, chain: dict, n_robots: int, precision=abi.PRECISION_F64, device=0, q0=None):
+        self.L = lib()
+        self.chain = chain
+        self.n = chain["n"]
+        self.B = int(n_robots)
+        self.precision = precision
+        self.dtype = np.float64 if precision == abi.PRECISION_F64 else np.float32
+        self._cd = abi.chain_desc(chain)
+        h = C.c_void_p()
+        q0a = np.ascontiguousarray(q0, dtype=np.float64) if q0 is not None else None
+        rc = self.L.osc_batch_create(C.byref(self._cd), self.B, precision, device,
+                                     q0a.ctypes.data_as(C.POINTER(C.c_double)) if q0a is not None else None, C.byref(h))
+        self.h = None
+        self._chk(rc)
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.osc_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _chk(self, rc):
+        if rc < 0:
+            msg = self.L.osc_last_error().decode()
+            raise (OscInvalidArgument if rc == abi.ERR_INVALID_ARGUMENT else OscError)(rc, msg)
+        return rc
+
+    # ---- hierarchy ----
+    def add_motion_force_task(self, desc):
+        return self._chk(self.L.osc_batch_add_motion_force_task(self.h, C.byref(desc)))
+
+    def add_joint_task(self, desc):
+        return self._chk(self.L.osc_batch_add_joint_task(self.h, C.byref(desc)))
+
+    def task_dof(self, task):
+        return self._chk(self.L.osc_batch_task_dof(self.h, task))
+
+    def mft_params(self, task):
+        p = abi.MftParams()
+        self._chk(self.L.osc_mft_get_params(self.h, task, C.byref(p)))
+        return p
+
+    def set_mft_params(self, task, p):
+        return self._chk(self.L.osc_mft_set_params(self.h, task, C.byref(p)))
+
+    def joint_task_params(self, task):
+        p = abi.JointTaskParams()
+        self._chk(self.L.osc_joint_task_get_params(self.h, task, C.byref(p)))
+        return p
+
+    def set_joint_task_params(self, task, p):
+        return self._chk(self.L.osc_joint_task_set_params(self.h, task, C.byref(p)))
+
+    def enable_gravity_compensation(self, e=True):
+        self._chk(self.L.osc_enable_gravity_compensation(self.h, int(e)))
+
+    # ---- fields ----
+    def field_size(self, task, field):
+        return self._chk(self.L.osc_field_size(self.h, task, field))
+
+    def _dt(self, field):
+        return np.int32 if field in abi.INT_FIELDS else self.dtype
+
+    def get(self, field, task=-1):
+        w = self.field_size(task, field)
+        out = np.empty((self.B, w), dtype=self._dt(field))
+        self._chk(self.L.osc_get_field(self.h, task, field, out.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
+        return out
+
+    def set(self, field, data, task=-1):
+        w = self.field_size(task, field)
+        a = np.ascontiguousarray(data, dtype=self._dt(field))
+        if a.size == w and self.B != 1:
+            self._chk(self.L.osc_set_field(self.h, task, field, a.ctypes.data, abi.LAYOUT_UNIFORM, abi.MEM_HOST))
+        else:
+            a = np.ascontiguousarray(a.reshape(self.B, w))
+            self._chk(self.L.osc_set_field(self.h, task, field, a.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
+
+    def set_raw(self, field, ptr, layout, mem, task=-1):
+        self._chk(self.L.osc_set_field(self.h, task, field, ptr, layout, mem))
+
+    def get_raw(self, field, ptr, layout, mem, task=-1):
+        self._chk(self.L.osc_get_field(self.h, task, field, ptr, layout, mem))
+
+    def update_sensed_force_and_moment(self, task, f, m):
+        f = np.ascontiguousarray(f, dtype=self.dtype)
+        m = np.ascontiguousarray(m, dtype=self.dtype)
+        layout = abi.LAYOUT_UNIFORM if (f.size == 3 and self.B != 1) else abi.LAYOUT_AOS
+        self._chk(self.L.osc_mft_update_sensed_force_and_moment(self.h, task, f.ctypes.data, m.ctypes.data, layout, abi.MEM_HOST))
+
+    # ---- tick ----
+    def update_model(self):
+        self._chk(self.L.osc_update_model(self.h))
+
+    def update_kinematics(self):
+        self._chk(self.L.osc_update_kinematics(self.h))
+
+    def task_update_model(self, task, n_prec_task=-1):
+        self._chk(self.L.osc_task_update_model(self.h, task, n_prec_task))
+
+    def update_task_models(self):
+        self._chk(self.L.osc_update_task_models(self.h))
+
+    def task_compute_torques(self, task, with_tau_prec=False):
+        self._chk(self.L.osc_task_compute_torques(self.h, task, int(with_tau_prec)))
+
+    def compute_torques(self, stacked=True):
+        out = np.empty((self.B, self.n), dtype=self.dtype)
+        self._chk(self.L.osc_compute_torques(self.h, int(stacked), out.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
+        return out
+
+    def tick(self, stacked=True, fetch=True):
+        if not fetch:
+            self._chk(self.L.osc_tick(self.h, int(stacked), None, 0, 0))
+            return None
+        out = np.empty((self.B, self.n), dtype=self.dtype)
+        self._chk(self.L.osc_tick(self.h, int(stacked), out.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
+        return out
+
+    def tick_is_fused(self):
+        return bool(self.L.osc_tick_is_fused(self.h))
+
+    def launch_count(self):
+        return int(self.L.osc_launch_count(self.h))
+
+    def reinitialize_tasks(self, task=-1):
+        self._chk(self.L.osc_reinitialize_tasks(self.h, task))
+
+    def synchronize(self):
+        self._chk(self.L.osc_synchronize(self.h))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._chk(self.L.osc_batch_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def snapshot(self):
+        nbytes = int(self.L.osc_snapshot_bytes(self.h))
+        buf = np.empty(nbytes, dtype=np.uint8)
+        self._chk(self.L.osc_snapshot(self.h, buf.ctypes.data, abi.MEM_HOST))
+        return buf
+
+    def restore(self, buf):
+        self._chk(self.L.osc_restore(self.h, buf.ctypes.data, abi.MEM_HOST))

@@ -1,0 +1,64 @@
+"""GPU parity: Panda 6-DoF MotionForceTask + full JointTask through RobotController semantics (BASELINE config 2)
+and through the manual chaining of examples/04 (config 1 style, stack C), against the C++ oracle."""
+import numpy as np
+import pytest
+
+import osc_abi as abi
+from common import FP32_TOL, FP64_TOL, Pair, load_chain, random_q
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(chain, B, seed, precision=abi.PRECISION_F64):
+    rng = np.random.default_rng(seed)
+    p = Pair(chain, B, precision)
+    t0 = p.add_mft("end-effector", (0, 0, 0.07))
+    t1 = p.add_jt()
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-0.5, 0.5, (B, chain["n"]))
+    p.set(abi.F_Q, q)
+    p.set(abi.F_DQ, dq)
+    p.both("update_model")
+    p.both("update_task_models")
+    p.both("compute_torques", True)  # populates the current pose
+    x = p.ref.get(abi.F_CURRENT_POSITION, t0)
+    p.set(abi.F_GOAL_POSITION, x + rng.normal(0, 0.05, (B, 3)), t0)
+    p.set(abi.F_GOAL_LINEAR_VELOCITY, rng.normal(0, 0.05, (B, 3)), t0)
+    p.set(abi.F_GOAL_ANGULAR_VELOCITY, rng.normal(0, 0.05, (B, 3)), t0)
+    p.set(abi.F_JT_GOAL_POSITION, q + rng.normal(0, 0.1, (B, chain["n"])), t1)
+    return p, rng
+
+
+def test_panda_two_task_stacked_fp64(oracle_built):
+    chain = load_chain("panda")
+    p, rng = _setup(chain, 512, 2)
+    for tick in range(3):
+        tg, tr = p.both("tick", True)
+        errs = p.compare(FP64_TOL)
+    alpha = p.ref.get(abi.F_ALPHA, 0)
+    assert (alpha < 1).any() and (alpha == 1).any(), "the random batch should cover singular and non-singular robots"
+
+
+def test_panda_two_task_manual_chain_fp64(oracle_built):
+    chain = load_chain("panda")
+    p, rng = _setup(chain, 256, 3)
+    p.both("update_model")
+    p.both("task_update_model", 0, -1)
+    p.both("task_update_model", 1, 0)
+    p.both("task_compute_torques", 0, False)
+    p.both("task_compute_torques", 1, False)
+    p.compare(FP64_TOL, skip=(abi.F_TAU,))
+    p.both("compute_torques", False)
+    p.compare(FP64_TOL)
+
+
+def test_panda_two_task_fp32(oracle_built):
+    chain = load_chain("panda")
+    p, rng = _setup(chain, 256, 4, abi.PRECISION_F32)
+    tg, tr = p.both("tick", True)
+    alpha = p.ref.get(abi.F_ALPHA, 0)[:, 0]
+    sv = p.ref.get(abi.F_SINGULAR_VALUES, 0)
+    well = (alpha == 1) & (sv[:, 5] / sv[:, 0] > 0.1)
+    assert well.sum() > 20
+    err = np.abs(tg - tr).max(axis=1) / np.maximum(np.abs(tr).max(axis=1), 1e-2)
+    assert err[well].max() < FP32_TOL * 50, err[well].max()
