@@ -1,0 +1,314 @@
+#!/usr/bin/env python
+"""bench.py -- OSC control updates/s (robots x ticks / s) on N B200s, BASELINE.json config 2:
+Panda 7-DoF, 6-DoF MotionForceTask + full JointTask in its nullspace through RobotController semantics, 65,536 robots
+per GPU, FP64.  One "step" = one control tick of every robot of the batch (updateModel + updateControllerTaskModels +
+computeControlTorques).  Robots are independent: the batch shards over GPUs with no collective ("scaling": "weak").
+
+    python bench.py --gpus 1 --steps 50 --warmup 5            # this repo's CUDA path (through the C ABI)
+    python bench.py --impl reference --gpus 1 --steps 3 --warmup 1   # the reference algorithm on the host cores (oracle port)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "sai2-primitives-perso_b200"))
+
+METRIC = "OSC control updates/sec (robots x ticks/s)"
+UNIT = "robot-ticks/s"
+WORKLOAD = "Panda 7-DoF 6-DoF OSC + joint nullspace task, batch 65,536 robots per B200, FP64 (BASELINE config 2)"
+# algorithmic work per robot-tick, frozen from SURVEY.md 8(d) (the reference's own route: two Jacobi SVDs included)
+ALG_FLOP_PER_TICK = 3.6e4
+ALG_BYTES_PER_TICK = 416.0
+
+
+def load_chain(name="panda"):
+    with open(os.path.join(ROOT, "fixtures", name + ".chain.json")) as f:
+        return json.load(f)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)"""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.lines, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_batch(osc_b200, abi, chain, B, device, seed, precision):
+    import workloads
+    w = workloads.config2(chain, B, seed)
+    b = osc_b200.Batch(chain, B, precision=precision, device=device, q0=[j["q0"] for j in chain["joints"]])
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = b.add_joint_task(abi.joint_task_desc(chain["n"]))
+    b.set(abi.F_Q, w["q"]); b.set(abi.F_DQ, w["dq"])
+    b.update_model()
+    b.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); b.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
+    b.set(abi.F_GOAL_LINEAR_VELOCITY, w["goal_linvel"], t0); b.set(abi.F_GOAL_ANGULAR_VELOCITY, w["goal_angvel"], t0)
+    b.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
+    return b, w, t0, t1
+
+
+class CpuRef:
+    """The reference algorithm (oracle port of the reference path, g++ -O2, robots statically partitioned over the host
+    threads, one robot instance per thread at a time, each with its own model copy) on a bounded sample of config 2."""
+
+    def __init__(self, chain, nthreads, Bc=4096):
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        import osc_abi as abi
+        import workloads
+        self.Bc, self.nthreads = Bc, nthreads
+        w = workloads.config2(chain, Bc, seed=2)
+        o = orc.OracleBatch(chain, Bc, q0=[j["q0"] for j in chain["joints"]], nthreads=nthreads)
+        t0 = o.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+        t1 = o.add_joint_task(abi.joint_task_desc(chain["n"]))
+        o.set(abi.F_Q, w["q"]); o.set(abi.F_DQ, w["dq"]); o.update_model()
+        o.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); o.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
+        o.set(abi.F_GOAL_LINEAR_VELOCITY, w["goal_linvel"], t0); o.set(abi.F_GOAL_ANGULAR_VELOCITY, w["goal_angvel"], t0)
+        o.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
+        self.o = o
+
+    def run(self, ticks):
+        L, h = self.o.L, self.o.h
+        t = time.perf_counter()
+        for _ in range(ticks):
+            L.orc_tick(h, 1, self.nthreads)
+        return time.perf_counter() - t
+
+    def sample(self, ticks):
+        return "%d robots x %d ticks of config 2 (seed 2), %d threads, g++ -O2" % (self.Bc, ticks, self.nthreads)
+
+
+def cpu_baseline(chain, seconds=12.0):
+    nthreads = os.cpu_count() or 1
+    ref = CpuRef(chain, nthreads)
+    one = ref.run(1)
+    one = ref.run(1)
+    ticks = int(max(2, min(5000, seconds / max(one, 1e-6))))
+    el = ref.run(ticks)
+    return {"value": ref.Bc * ticks / el, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": ref.sample(ticks)}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the reference's CPU algorithm on this box's host cores.  The reference library itself cannot be
+    built here (needs Eigen3 + un-vendored sai2-model), so this is the oracle port ("kind": "port").
+    One step = 10 ticks of a 4096-robot sample."""
+    if rank != 0:
+        return
+    chain = load_chain()
+    nthreads = os.cpu_count() or 1
+    ref = CpuRef(chain, nthreads)
+    TICKS = 10
+    for _ in range(max(1, args.warmup)):
+        ref.run(1)
+    el = [ref.run(TICKS) for _ in range(args.steps)]
+    value = float(ref.Bc * TICKS * len(el) / sum(el))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": float(np.mean(el) * 1e3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "step_sample": "each step = %d ticks of a %d-robot sample on the host cores" % (TICKS, ref.Bc)},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": ref.sample(TICKS * len(el))},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=65536, help="robots per GPU")
+    ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_b200(args, rank, world, local_rank)
+
+
+def run_b200(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import osc_abi as abi
+    import osc_b200
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the batched controller has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    chain = load_chain()
+    n, B = chain["n"], args.batch
+    real = torch.float64 if args.precision == 64 else torch.float32
+    batch, w, t0, t1 = build_batch(osc_b200, abi, chain, B, local_rank, seed=2 + rank, precision=args.precision)
+    batch.set_stream(torch.cuda.current_stream().cuda_stream)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- device-resident tick: W warm-up + K timed steps, CUDA events on the launching stream, L2 flushed between steps
+    for _ in range(args.warmup):
+        batch.tick(True, fetch=False)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = batch.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for s, e in ev:
+        flush.zero_()
+        s.record()
+        batch.tick(True, fetch=False)
+        e.record()
+    barrier()
+    launches = batch.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    step_ms = np.array([s.elapsed_time(e) for s, e in ev])
+    total_ms = max_over_ranks(float(step_ms.sum()))
+    value = world * B * args.steps / (total_ms * 1e-3)
+
+    # ---- end to end through the C ABI with HOST buffers: H2D of this step's state + goals, tick, D2H of the torques
+    def pinned(a):
+        t = torch.from_numpy(np.ascontiguousarray(a.T)).to(real).pin_memory()  # SoA [k][B]
+        return t
+    h_in = [(abi.F_Q, -1, pinned(w["q"])), (abi.F_DQ, -1, pinned(w["dq"])), (abi.F_GOAL_POSITION, t0, pinned(w["goal_pos"])),
+            (abi.F_GOAL_ORIENTATION, t0, pinned(w["goal_ori"])), (abi.F_JT_GOAL_POSITION, t1, pinned(w["jt_goal"]))]
+    h_tau = torch.empty((n, B), dtype=real).pin_memory()
+    h2d = sum(t.numel() * t.element_size() for _, _, t in h_in)
+    d2h = h_tau.numel() * h_tau.element_size()
+    L, h = batch.L, batch.h
+
+    def e2e_step():
+        for f, task, t in h_in:
+            L.osc_set_field(h, task, f, t.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)
+        rc = L.osc_tick(h, 1, h_tau.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)  # returns after the torques landed
+        assert rc == 0
+    for _ in range(args.warmup):
+        e2e_step()
+    barrier()
+    t_e2e = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t_e2e)
+    barrier()
+    e2e_value = world * B * args.steps / e2e_s
+
+    # ---- roofline of the dominant kernel (its own launches timed with CUDA events, L2 flushed)
+    fused = batch.tick_is_fused()
+    stages = {}
+    if fused:
+        stages["k_tick_fused"] = float(np.mean(step_ms))
+    else:
+        calls = [("k_model", lambda: batch.update_model()), ("k_mft_update", lambda: batch.task_update_model(0, -1)),
+                 ("k_jt_update", lambda: batch.task_update_model(1, 0)), ("k_mft_compute", lambda: batch.task_compute_torques(0, False)),
+                 ("k_jt_compute", lambda: batch.task_compute_torques(1, True))]
+        for name, fn in calls:
+            ts = []
+            for _ in range(min(args.steps, 10)):
+                flush.zero_()
+                s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s.record(); fn(); e.record(); torch.cuda.synchronize()
+                ts.append(s.elapsed_time(e))
+            stages[name] = float(np.mean(ts))
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    fp64_peak = osc_b200.measure_fp64_peak(local_rank)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    top = max(stages, key=stages.get)
+    # algorithmic FLOP of each kernel per robot (whole tick = 3.6e4)
+    alg = {"k_tick_fused": ALG_FLOP_PER_TICK, "k_model": 504 + 84 + 1680 + 686, "k_mft_update": 10800 + 504 + 1314 + 1092 + 2000,
+           "k_jt_update": 15100 + 240, "k_mft_compute": 300 + 162 + 84 + 504, "k_jt_compute": 364}
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        traffic = json.load(open(tpath)).get(top)
+    t_top = stages[top] * 1e-3
+    roof = {"bound": "fp64", "kernel": top, "achieved": alg[top] * B / t_top / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": alg[top] * B / t_top / 1e12 / fp64_peak, "traffic": traffic,
+            "peak_source": "DFMA microbenchmark in this run (osc_measure_fp64_peak); nominal 148 SM x 64 DFMA/clk x 2 x 1.965 GHz = 37.2",
+            "alg_flop_per_robot": alg[top], "stage_ms": stages}
+    roof_hbm = {"bound": "hbm", "achieved": ALG_BYTES_PER_TICK * B / (float(np.mean(step_ms)) * 1e-3) / 1e9, "peak": hbm_peak,
+                "unit": "GB/s", "peak_source": hbm_src}
+    roof_hbm["frac"] = roof_hbm["achieved"] / hbm_peak
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "robots_per_gpu": B, "hierarchy": "MotionForceTask(6-DoF, end-effector + 0.07 m) > JointTask(full)",
+                       "stacked": True, "l2": "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
+            "p50_tick_us": float(np.median(step_ms) * 1e3), "p99_tick_us": float(np.percentile(step_ms, 99) * 1e3),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "path": "osc_set_field x5 + osc_tick with pinned HOST SoA buffers (C ABI)"},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_hbm": roof_hbm}
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(chain)
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -286,6 +286,10 @@ int64_t osc_launch_count(const osc_batch_t* batch);
 /* RobotController::reinitializeTasks / TemplateTask::reInitializeTask; task = -1 for all */
 int osc_reinitialize_tasks(osc_batch_t* batch, int task);
 
+/* ---- measurement helper: sustained FP64 FMA throughput of `device` in TFLOP/s (DFMA microbenchmark, 2 flop per FMA),
+ * the denominator of the FP64 roofline bench.py reports (MEASURED_PEAKS.json has no FP64 entry). ---- */
+int osc_measure_fp64_peak(int device, double* tflops, double* elapsed_ms);
+
 /* ---- controller-state snapshot (MPC rollouts: fork, roll out, restore) ---- */
 int64_t osc_snapshot_bytes(const osc_batch_t* batch);
 int osc_snapshot(osc_batch_t* batch, void* dst, int mem);

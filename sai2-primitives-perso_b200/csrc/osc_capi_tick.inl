@@ -135,3 +135,45 @@ int osc_restore(osc_batch_t* batch, const void* src, int mem) {
 }
 
 }  // extern "C"
+
+// ---- FP64 peak microbenchmark ----
+namespace osc {
+__global__ void __launch_bounds__(256) k_dfma_peak(double* out, int iters, double seed) {
+	double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+	const double m = 1.0000001, c = 1e-9;
+	for (int i = 0; i < iters; ++i) {
+		a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+		a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+	}
+	out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+}  // namespace osc
+
+extern "C" int osc_measure_fp64_peak(int device, double* tflops, double* elapsed_ms) {
+	if (!tflops) return invalid("null argument");
+	if (osc_device_count() == 0) { set_error("no CUDA device available"); return OSC_ERR_NO_DEVICE; }
+	OSC_CUDA(cudaSetDevice(device));
+	cudaDeviceProp prop;
+	OSC_CUDA(cudaGetDeviceProperties(&prop, device));
+	const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 16;
+	double* out = nullptr;
+	OSC_CUDA(cudaMalloc(&out, (size_t)blocks * threads * sizeof(double)));
+	cudaEvent_t e0, e1;
+	OSC_CUDA(cudaEventCreate(&e0));
+	OSC_CUDA(cudaEventCreate(&e1));
+	float best = 1e30f;
+	for (int rep = 0; rep < 4; ++rep) {
+		OSC_CUDA(cudaEventRecord(e0));
+		k_dfma_peak<<<blocks, threads>>>(out, iters, 1.0 + rep);
+		OSC_CUDA(cudaEventRecord(e1));
+		OSC_CUDA(cudaEventSynchronize(e1));
+		float ms = 0;
+		OSC_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+		if (rep > 0 && ms < best) best = ms;
+	}
+	cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+	const double flop = 2.0 * 8.0 * (double)iters * (double)blocks * threads;
+	*tflops = flop / (best * 1e-3) / 1e12;
+	if (elapsed_ms) *elapsed_ms = best;
+	return OSC_OK;
+}

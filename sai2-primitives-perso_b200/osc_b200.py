@@ -76,6 +76,7 @@ def lib():
         "osc_snapshot_bytes": (i64, [vp]),
         "osc_snapshot": (i, [vp, vp, i]),
         "osc_restore": (i, [vp, vp, i]),
+        "osc_measure_fp64_peak": (i, [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -94,7 +95,16 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
             "osc_tick", "osc_tick_is_fused", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
-            "osc_snapshot", "osc_restore"]
+            "osc_snapshot", "osc_restore", "osc_measure_fp64_peak"]
+
+
+def measure_fp64_peak(device=0):
+    """sustained DFMA throughput in TFLOP/s (2 flop per FMA) measured by the library's microbenchmark"""
+    t, ms = C.c_double(), C.c_double()
+    rc = lib().osc_measure_fp64_peak(device, C.byref(t), C.byref(ms))
+    if rc < 0:
+        raise OscError(rc, lib().osc_last_error().decode())
+    return t.value
 
 
 class Batch:
