@@ -280,6 +280,17 @@ int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layo
 int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
 /* 1 if osc_tick runs the fused kernel for the current hierarchy / parameters */
 int osc_tick_is_fused(const osc_batch_t* batch);
+/* What osc_tick leaves behind besides tau and the persistent controller state (integrators, observers, history):
+ *   OSC_TICK_OUTPUTS_LAZY (default)  vector-valued getters (task torques, poses, velocities, errors, unit-mass force, alpha)
+ *        are written by the tick; matrix-valued getters (M, M^-1, J, Lambda, N, singular values ...) are evaluated on
+ *        first use, at the batch's current q, by the per-call kernels -- every getter of the reference keeps working;
+ *   OSC_TICK_OUTPUTS_ALL             the tick is the per-call kernel sequence (updateModel, updateTaskModel x tasks,
+ *        computeTorques x tasks): every intermediate of the reference is materialised by the tick itself;
+ *   OSC_TICK_OUTPUTS_TAU             tau and persistent state only (MPC rollouts / parallel environments). */
+enum { OSC_TICK_OUTPUTS_ALL = 0, OSC_TICK_OUTPUTS_LAZY = 1, OSC_TICK_OUTPUTS_TAU = 2 };
+int osc_batch_set_tick_outputs(osc_batch_t* batch, int outputs);
+/* robots of the last fused tick that took the API-faithful route (singular / blend branch or not certifiable); synchronises */
+int64_t osc_tick_fallback_count(osc_batch_t* batch);
 /* number of kernels launched by this batch since creation (bench.py's gpu_launches) */
 int64_t osc_launch_count(const osc_batch_t* batch);
 

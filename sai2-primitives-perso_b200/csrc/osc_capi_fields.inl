@@ -1,5 +1,19 @@
 // osc_capi_fields.inl -- per-robot field access
 
+namespace osc {
+// fields the fused tick does not write (include/osc_b200.h, OSC_TICK_OUTPUTS_LAZY): model and task-model matrices
+static bool lazily_materialised(int task, int field) {
+	if (task < 0) return field == OSC_F_M || field == OSC_F_MINV || field == OSC_F_N_TOTAL;
+	switch (field) {
+		case OSC_F_N_TASK: case OSC_F_N_PREC: case OSC_F_N_TASK_AND_PREC: case OSC_F_JACOBIAN: case OSC_F_PROJECTED_JACOBIAN:
+		case OSC_F_LAMBDA_WORLD: case OSC_F_LAMBDA_MODIFIED_WORLD: case OSC_F_SINGULAR_VALUES:
+		case OSC_F_JT_LAMBDA_WORLD: case OSC_F_JT_LAMBDA_MODIFIED_WORLD: case OSC_F_JT_RANGE_RANK: case OSC_F_NS_RANK: case OSC_F_ALPHA:
+			return true;
+	}
+	return false;
+}
+}  // namespace osc
+
 extern "C" {
 
 int osc_field_size(const osc_batch_t* batch, int task, int field) {
@@ -26,6 +40,8 @@ int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout
 	Loc l;
 	if (!b->ops->locate(*b, task, field, l)) return invalid("unknown field for this task");
 	if (int rc = use_device(*b)) return rc;
+	if (b->stale && lazily_materialised(task, field))
+		if (int rc = b->ops->materialise(*b)) return rc;
 	const void* rows = nullptr;
 	if (l.special) {
 		void* tmp = b->ensure_stage2((size_t)l.width * b->stride * 8);
@@ -47,6 +63,7 @@ int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const v
 	if (!tmp) return invalid("out of device memory (staging)");
 	if (int rc = import_rows(*b, tmp, 3, false, force, layout, mem)) return rc;
 	if (int rc = import_rows(*b, tmp + (size_t)3 * b->stride * b->esz, 3, false, moment, layout, mem)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;  // the sensor-frame transform reads the kinematics of the last updateModel
 	return b->ops->update_sensed(*b, task, tmp);
 }
 

@@ -53,6 +53,7 @@ static int add_task_common(Batch& b, TaskH& t, double dt) {
 	if ((int)b.tasks.size() >= OSC_MAX_TASKS) return invalid("too many tasks (OSC_MAX_TASKS)");
 	if (!b.tasks.empty() && dt != b.dt) return invalid("All tasks must have the same loop timestep in RobotController");  // .cpp:23-27
 	if (int rc = use_device(b)) return rc;
+	if (int rc = b.ops->materialise(b)) return rc;
 	b.ops->task_rows(t.type, t.p_rows, t.s_rows, t.i_rows);
 	if (int rc = alloc_rows(b, &t.P, t.p_rows, b.esz)) return rc;
 	if (int rc = alloc_rows(b, &t.S, t.s_rows, b.esz)) return rc;

@@ -20,12 +20,14 @@ int osc_update_model(osc_batch_t* batch) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (int rc = use_device(*b)) return rc;
+	if (b->stale) return b->ops->materialise(*b);  // model + task models at the current q (see osc_batch_set_tick_outputs)
 	return b->ops->model(*b, 1);
 }
 int osc_update_kinematics(osc_batch_t* batch) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (int rc = use_device(*b)) return rc;
+	if (b->stale) return b->ops->materialise(*b);
 	return b->ops->model(*b, 0);
 }
 int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
@@ -34,6 +36,7 @@ int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
 	if (n_prec_task >= (int)b->tasks.size() || n_prec_task == task)
 		return invalid("N_prec matrix size not consistent with robot dof in updateTaskModel\n");
 	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
 	return b->ops->task_update(*b, task, n_prec_task < 0 ? -1 : n_prec_task);
 }
 int osc_update_task_models(osc_batch_t* batch) {  // RobotController.cpp:53-60
@@ -41,6 +44,7 @@ int osc_update_task_models(osc_batch_t* batch) {  // RobotController.cpp:53-60
 	if (!b) return invalid("null batch");
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
 	for (int t = 0; t < (int)b->tasks.size(); ++t)
 		if (int rc = b->ops->task_update(*b, t, t - 1)) return rc;
 	return OSC_OK;
@@ -49,6 +53,7 @@ int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
 	Batch* b = (Batch*)batch;
 	if (int rc = check_task(b, task)) return rc;
 	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
 	return b->ops->task_compute(*b, task, with_tau_prec, 0);
 }
 int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {  // RobotController.cpp:62-74
@@ -56,6 +61,7 @@ int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layo
 	if (!b) return invalid("null batch");
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
 	for (int t = 0; t < (int)b->tasks.size(); ++t)
 		if (int rc = b->ops->task_compute(*b, t, (stacked && t > 0) ? 1 : 0, t == 0 ? 1 : 2)) return rc;
 	if (b->gravity)
@@ -75,9 +81,27 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 		if (int rc = b->ops->tick_fused(*b, stacked)) return rc;
 		return emit_tau(*b, tau_out, layout, mem);
 	}
+	b->stale = false;
 	if (int rc = b->ops->model(*b, 1)) return rc;
 	if (int rc = osc_update_task_models(batch)) return rc;
 	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
+}
+int osc_batch_set_tick_outputs(osc_batch_t* batch, int outputs) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (outputs != OSC_TICK_OUTPUTS_ALL && outputs != OSC_TICK_OUTPUTS_LAZY && outputs != OSC_TICK_OUTPUTS_TAU)
+		return invalid("unknown tick output mode");
+	b->tick_outputs = outputs;
+	return OSC_OK;
+}
+int64_t osc_tick_fallback_count(osc_batch_t* batch) {
+	Batch* b = (Batch*)batch;
+	if (!b || !b->fb) return 0;
+	if (use_device(*b)) return -1;
+	int n = 0;
+	if (cudaMemcpyAsync(&n, b->fb + b->fb_last, sizeof(int), cudaMemcpyDeviceToHost, b->stream) != cudaSuccess) return -1;
+	if (cudaStreamSynchronize(b->stream) != cudaSuccess) return -1;
+	return n;
 }
 
 int osc_reinitialize_tasks(osc_batch_t* batch, int task) {
@@ -85,6 +109,7 @@ int osc_reinitialize_tasks(osc_batch_t* batch, int task) {
 	if (!b) return invalid("null batch");
 	if (task >= (int)b->tasks.size()) return invalid("task index out of range");
 	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
 	for (int t = 0; t < (int)b->tasks.size(); ++t)
 		if (task < 0 || t == task)
 			if (int rc = b->ops->task_reinit(*b, t)) return rc;

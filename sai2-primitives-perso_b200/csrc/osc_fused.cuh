@@ -1,10 +1,284 @@
-// osc_fused.cuh -- single-launch tick (updateModel + updateControllerTaskModels + computeControlTorques).
-// Placeholder until the fused kernel lands: osc_tick falls back to the API-faithful kernel sequence.
+// osc_fused.cuh -- single-launch control tick:  robot->updateModel(); controller->updateControllerTaskModels();
+// controller->computeControlTorques()  (examples/05-using_robot_controller/05-using_robot_controller.cpp:143-148,195;
+// src/RobotController.cpp:53-74) for the hierarchy [6-DoF MotionForceTask, full JointTask] (BASELINE configs 1, 2, 5).
+//
+// k_tick_fused: one robot per thread, everything between q and tau stays in registers.  It serves the robots that are
+// in the reference's NON-SINGULAR branch this tick (SingularityHandler.cpp:123-141, alpha = 1); in that branch the SVD
+// bases cancel out of every result the tick produces:
+//     tau_1 = J^T ( (J W J^T)^-1 F* + F_f )                   W = M^-1 or M_BIE^-1   (.cpp:307-309 with U_ns square)
+//     N_1   = I - M^-1 J^T (J M^-1 J^T)^-1 J                                          (.cpp:130-134)
+//     JointTask range basis R = orth(range(N_1)) (JointTask.cpp:233): with M = L L^T, Y = L^-1 J^T and u the unit vector
+//     orthogonal to range(Y):  N_1 = (L^-T u)(L u)^T,  R = L^-T u / |L^-T u|,  Lambda = 1 / |L^-T u|^2.
+// so the two Jacobi SVDs of the reference's route are replaced by (a) a CERTIFICATE that the robot is in the non-singular
+// branch -- sigma_0 >= s_abs_tol and lambda_min(J J^T) > s_max^2 * lambda_max, proven with an upper bound of lambda_max
+// (tr((JJ^T)^4)^(1/4)) and a Sylvester inertia test -- and (b) Cholesky factorisations.  A robot the certificate cannot
+// prove (singular, in the blend band, or within 25 % of it) is appended to a fallback list and gets the API-faithful
+// route (full Jacobi SVDs, every branch of SingularityHandler) from k_tick_tail in the same stream.  Results agree with
+// the reference route to O(eps * cond(J M^-1 J^T)): the parity tests hold both against the oracle at 1e-9.
 #pragma once
+#include "osc_aux_kernels.cuh"
 #include "osc_host.h"
-#include "osc_kernels.cuh"
 
 namespace osc {
-template <class T, int N> bool fused_tick_supported(Batch&) { return false; }
-template <class T, int N> int fused_tick_launch(Batch&, const ChainC<T, N>&, int) { return OSC_ERR_UNSUPPORTED; }
+
+#define OSC_FUSED_THREADS 64
+
+enum { OSC_EXPORT_VECTORS = 1 };
+
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_FUSED_THREADS) k_tick_fused(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+																   const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
+																   int64_t B, int64_t stride, int stacked, int gravity, int exports,
+																   int* __restrict__ fb_count, int* __restrict__ fb_list) {
+	static_assert(N == 6 || N == 7, "the fused tick covers n - 6 <= 1 (one-dimensional joint-task range)");
+	using ML = MftL<N>;
+	using JL = JtL<N>;
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
+	const Row<int32_t> mI{tk0.I, stride, r};
+	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
+	int status = 0;
+
+	// ---- robot->updateModel(): kinematics, Jacobian at the compliant frame, mass matrix ----
+	T q[N];
+	ld_vec<T, N>(rP, RobotL<N>::Q, q);
+	T J[6][N], x[3], Rc[3][3], M[N][N], grav[N];
+	{
+		Kin<T, N> kin;
+		forward_kinematics<T, N>(ch, q, kin);
+		mass_matrix<T, N>(ch, kin, M);
+		if (gravity) gravity_vector<T, N>(ch, kin, grav);
+		frame_pose<T, N>(kin, tc.body, tc.p_c, tc.R_c, x, Rc);
+		point_jacobian<T, N>(ch, kin, tc.body, x, J);
+	}
+
+	// ---- the branch certificate on G = J J^T (singular values of Jp = J: N_prec = I) ----
+	{
+		T G[6][6];
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(J[i][k], J[j][k], s);
+				G[i][j] = s; G[j][i] = s;
+			}
+		T f4 = T(0);  // tr(G^4) = |G^2|_F^2
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < 6; ++k) s = Num<T>::fma_(G[i][k], G[k][j], s);
+				f4 = Num<T>::fma_(i == j ? s : T(2) * s, s, f4);
+			}
+		const T lmax_hi = Num<T>::sqrt_(Num<T>::sqrt_(f4)) * T(1.0000001);  // lambda_max <= lmax_hi <= 6^(1/4) lambda_max
+		const T lmax_lo = lmax_hi * T(0.6389431);                            // 6^(-1/4)
+		const bool s0_ok = lmax_lo > tc.s_abs_tol * tc.s_abs_tol * T(1.001);
+		const bool sep_ok = spd_above<T, 6>(G, tc.s_max * tc.s_max * lmax_hi * T(1.001));
+		if (!(s0_ok && sep_ok)) {  // not provably non-singular: API-faithful route
+			fb_list[atomicAdd(fb_count, 1)] = (int)r;
+			return;
+		}
+	}
+
+	// ---- M = L L^T;  Y = L^-1 J^T (rows of J whitened);  A = J M^-1 J^T = Y^T Y ----
+	Chol<T, N> cm;
+	if (!chol_factor<T, N>(M, cm)) status |= 16;
+	T Y[6][N];  // Y[c][:] = L^-1 J[c][:]^T
+	OSC_UNROLL for (int c = 0; c < 6; ++c) {
+		OSC_UNROLL for (int i = 0; i < N; ++i) Y[c][i] = J[c][i];
+		chol_fwd<T, N>(cm, Y[c]);
+	}
+	Chol<T, 6> ca;
+	{
+		T A[6][6];
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(Y[i][k], Y[j][k], s);
+				A[i][j] = s;
+			}
+		if (!chol_factor<T, 6>(A, ca)) status |= 16;
+	}
+
+	// ---- Lambda_ns_modified F* (SingularityHandler.cpp:160-225, 307-309) ----
+	T dq[N];
+	ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
+	T Fstar[6], Ff[6];
+	mft_control_law<T, N>(tc, mP, mS, mI, stride, r, J, dq, x, Rc, Fstar, Ff, status, ex);
+	T f[6];
+	OSC_UNROLL for (int i = 0; i < 6; ++i) f[i] = Fstar[i];
+	Chol<T, N> cb;  // factor of M_BIE (bounded inertia estimates), shared with the joint task below
+	bool bie_any = false;
+	if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+		// both tasks use the same threshold by default; the (rare) different-threshold case is refused by fused_tick_supported
+		const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
+		OSC_UNROLL for (int i = 0; i < N; ++i)
+			if (M[i][i] < thr) { M[i][i] = thr; bie_any = true; }
+		if (bie_any) chol_factor<T, N>(M, cb);
+	}
+	if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && bie_any) {
+		T Yb[6][N], Ab[6][6];
+		OSC_UNROLL for (int c = 0; c < 6; ++c) {
+			OSC_UNROLL for (int i = 0; i < N; ++i) Yb[c][i] = J[c][i];
+			chol_fwd<T, N>(cb, Yb[c]);
+		}
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(Yb[i][k], Yb[j][k], s);
+				Ab[i][j] = s;
+			}
+		Chol<T, 6> cab;
+		chol_factor<T, 6>(Ab, cab);
+		chol_fwd<T, 6>(cab, f);
+		chol_bwd<T, 6>(cab, f);
+	} else if (tc.decoupling != OSC_IMPEDANCE) {
+		chol_fwd<T, 6>(ca, f);
+		chol_bwd<T, 6>(ca, f);
+	}
+	OSC_UNROLL for (int i = 0; i < 6; ++i) f[i] += Ff[i];
+	T tau1[N];
+	mtv<T, 6, N>(J, f, tau1);  // tau_1 = J^T (Lambda_mod F* + F_f)
+
+	// ---- classification state of a non-singular robot (SingularityHandler.cpp:237-244): history cleared ----
+	// and the q_prior latch (.cpp:233-236).  The latch of a non-singular robot is unobservable by the controller (it is
+	// re-latched on entry into a singularity before its first use), so the tau-only mode skips the store; _dq_prior is
+	// never read by the reference and is left alone.
+	{
+		const int ntypes = mI(ML::NTYPES);
+		bool latch = ntypes == 0;
+		if (ntypes != 0 || mI(ML::HIST_LEN) != 0) {
+			latch = latch || mI(ML::C2) > mI(ML::C1);
+			mI(ML::NTYPES) = 0; mI(ML::TYPES) = 0; mI(ML::C1) = 0; mI(ML::C2) = 0; mI(ML::HIST_LEN) = 0; mI(ML::HIST_HEAD) = 0;
+		}
+		if (ex && latch) st_vec<T, N>(mP, ML::Q_PRIOR, q);
+	}
+
+	// ---- JointTask in the nullspace (JointTask.cpp:218-356) ----
+	T tau[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) tau[i] = tau1[i];
+	T tau2[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) tau2[i] = T(0);
+	if constexpr (N == 7) {
+		// W = C^-1 Y (rows orthonormal); P = I - W^T W is the rank-1 orthogonal projector on range(Y)^perp
+		T W[6][N];
+		OSC_UNROLL for (int k = 0; k < N; ++k) {
+			T col[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) col[c] = Y[c][k];
+			chol_fwd<T, 6>(ca, col);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) W[c][k] = col[c];
+		}
+		// pick the unit vector e_k with the largest residual P_kk = 1 - |W[:,k]|^2
+		T best = T(-1);
+		int kb = 0;
+		OSC_UNROLL for (int k = 0; k < N; ++k) {
+			T s = T(1);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][k], W[c][k], s);
+			if (s > best) { best = s; kb = k; }
+		}
+		T u[N];
+		OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = (i == kb) ? T(1) : T(0);
+		OSC_UNROLL for (int pass = 0; pass < 2; ++pass) {  // project twice ("twice is enough")
+			T wu[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) {
+				T s = T(0);
+				OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(W[c][i], u[i], s);
+				wu[c] = s;
+			}
+			OSC_UNROLL for (int i = 0; i < N; ++i)
+				OSC_UNROLL for (int c = 0; c < 6; ++c) u[i] = Num<T>::fma_(-W[c][i], wu[c], u[i]);
+		}
+		{
+			T nu = T(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) nu = Num<T>::fma_(u[i], u[i], nu);
+			const T inv = Num<T>::rsqrt_(nu);
+			OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
+		}
+		T w[N], v[N];  // N_1 = v w^T with v = L^-T u, w = L u
+		chol_mul<T, N>(cm, u, w);
+		OSC_UNROLL for (int i = 0; i < N; ++i) v[i] = u[i];
+		chol_bwd<T, N>(cm, v);
+		T nv2 = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) nv2 = Num<T>::fma_(v[i], v[i], nv2);
+		const T lam = T(1) / nv2;              // Lambda = (R^T N_1 M^-1 N_1^T R)^-1 = 1 / |v|^2   (|L^-1 w| = |u| = 1)
+		T lam_mod = lam;                        // JointTask.cpp:253-267
+		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && bie_any) {
+			T t[N];
+			OSC_UNROLL for (int i = 0; i < N; ++i) t[i] = w[i];
+			chol_fwd<T, N>(cb, t);
+			T s = T(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(t[i], t[i], s);
+			lam_mod = T(1) / (nv2 * s);
+		} else if (jc.decoupling == OSC_IMPEDANCE) {
+			lam_mod = T(1);
+		}
+		T upd[N], acc[N];
+		jt_pd_law<T, N>(jc, jP, jS, q, dq, upd, acc, ex);
+		// R^T x = (v . x) / |v|;  tau_2 = N_1^T R s = w |v| s
+		T va = T(0), vu = T(0), vc = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<T>::fma_(v[i], acc[i], va); vu = Num<T>::fma_(v[i], upd[i], vu); }
+		if (stacked) {  // JointTask.cpp:285-292: - Jp^T R Lambda R^T S M^-1 tau_prec
+			T t[N];
+			OSC_UNROLL for (int i = 0; i < N; ++i) t[i] = tau1[i];
+			chol_fwd<T, N>(cm, t);
+			chol_bwd<T, N>(cm, t);
+			OSC_UNROLL for (int i = 0; i < N; ++i) vc = Num<T>::fma_(v[i], t[i], vc);
+		}
+		const T sc = lam * (va - vc) + lam_mod * vu;  // the 1/|v| of R^T and the |v| of N_1^T R cancel
+		OSC_UNROLL for (int i = 0; i < N; ++i) { tau2[i] = w[i] * sc; tau[i] += tau2[i]; }
+	}
+	if (ex) {
+		if constexpr (N == 7) tk1.I[(int64_t)JL::RANK * stride + r] = 1;
+		else tk1.I[(int64_t)JL::RANK * stride + r] = 0;
+		st_vec<T, N>(jS, JL::CUR_POS, q);
+		st_vec<T, N>(jS, JL::CUR_VEL, dq);
+		st_vec<T, N>(jS, JL::TASK_TAU, tau2);
+		st_vec<T, N>(mS, ML::TASK_TAU, tau1);
+		mS(ML::ALPHA) = T(1);
+		mI(ML::INS) = 6;
+	}
+	if (gravity) {
+		OSC_UNROLL for (int i = 0; i < N; ++i) tau[i] += grav[i];
+		if (ex) st_vec<T, N>(rS, RobotL<N>::GRAV, grav);
+	}
+	st_vec<T, N>(rS, RobotL<N>::TAU, tau);
+	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+}
+
+// The robots k_tick_fused could not certify: the API-faithful route (every branch of SingularityHandler, full Jacobi
+// SVDs), one robot per thread over the compacted list.  Also re-arms the other fallback counter for the next tick.
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+															const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1, int64_t stride,
+															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list) {
+	const int n = *fb_count;
+	if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count_next = 0;
+	for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+		const int64_t r = fb_list[idx];
+		model_robot<T, N>(ch, rob, stride, r, 1, gravity);
+		mft_update_robot<T, N>(ch, tc, rob, tk0, nullptr, stride, r, 0);
+		jt_update_robot<T, N>(jc, rob, tk1, tk0.S + (int64_t)MftL<N>::NTP * stride, stride, r);
+		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1);
+		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2);
+		if (gravity) {
+			const Row<T> rS{rob.S, stride, r};
+			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += rS(RobotL<N>::GRAV + i);
+		}
+	}
+}
+
+// hierarchy / parameter combinations the fused tick serves (everything else: the kernel sequence of osc_capi_tick.inl)
+template <class T, int N> bool fused_tick_supported(Batch& b) {
+	if constexpr (N != 6 && N != 7) return false;
+	if (b.tick_outputs == OSC_TICK_OUTPUTS_ALL) return false;
+	if (b.tasks.size() != 2) return false;
+	const TaskH &m = b.tasks[0], &j = b.tasks[1];
+	if (m.type != OSC_TASK_MOTION_FORCE || j.type != OSC_TASK_JOINT) return false;
+	if (m.md.partial || m.dof != 6 || !j.jd.full) return false;
+	if (m.mp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES && j.jp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES &&
+		m.mp.bie_threshold != j.jp.bie_threshold)
+		return false;
+	if (!(m.mp.s_max > 0) || !(m.mp.s_abs_tol > 0)) return false;
+	return true;
+}
+
 }  // namespace osc

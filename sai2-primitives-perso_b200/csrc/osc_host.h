@@ -48,7 +48,7 @@ struct Ops {
 	virtual int task_init(Batch& b, int t) = 0;
 	virtual int task_reinit(Batch& b, int t) = 0;
 	virtual int mft_reset(Batch& b, int t, int flags) = 0;  // 1 linear, 2 angular, 4 popc, 8 lin integrators, 16 ang integrators
-	virtual int task_update(Batch& b, int t, int src) = 0;
+	virtual int task_update(Batch& b, int t, int src, int no_history = 0) = 0;
 	virtual int task_compute(Batch& b, int t, int with_tau_prec, int accumulate) = 0;
 	virtual int add_gravity(Batch& b) = 0;
 	virtual int update_sensed(Batch& b, int t, const void* tmp6) = 0;
@@ -56,6 +56,7 @@ struct Ops {
 	virtual int pack_special(Batch& b, const Loc& loc, void* tmp) = 0;
 	virtual bool fused_supported(Batch& b) = 0;
 	virtual int tick_fused(Batch& b, int stacked) = 0;
+	virtual int materialise(Batch& b) = 0;  // after a fused tick: run the per-call model / task-model kernels (no state advance)
 };
 
 Ops* make_ops(int precision, int n);  // nullptr when that (precision, dof) pair was not compiled in
@@ -78,6 +79,11 @@ struct Batch {
 	bool gravity = false;
 	int64_t launches = 0;
 	Ops* ops = nullptr;
+	int tick_outputs = OSC_TICK_OUTPUTS_LAZY;
+	bool stale = false;        // a fused tick ran: the model / task-model scratch rows are older than tau
+	int* fb = nullptr;         // device: [2] fallback counters (ping-pong) + [stride] robot list
+	int fb_parity = 0;
+	int fb_last = 0;           // which counter the last fused tick filled
 	void* chain_dev = nullptr;  // ChainC<T,N> host copy owned by ops
 	// staging
 	void* stage = nullptr; size_t stage_bytes = 0;

@@ -6,12 +6,40 @@
 
 namespace osc {
 
+// The joint-space control law of JointTask::computeTorques (JointTask.cpp:319-346): integrates the error, returns the
+// PID (or velocity-saturated) command u and the feed-forward acceleration; rows >= k are zero.
 template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk,
-															const T* nprec_src, int64_t B, int64_t stride) {
+OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, const T (&cp)[N], const T (&cv)[N], T (&u)[N], T (&acc)[N],
+					   bool export_vectors) {
 	using L = JtL<N>;
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= B) return;
+	T dv[N];
+	const int k = jc.k;
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		const T e = cp[i] - tP(L::GOAL_POS + i);
+		T ie = tP(L::INTEG + i);
+		if (i < k) { ie += e * jc.dt; tP(L::INTEG + i) = ie; }  // JointTask.cpp:323-324
+		dv[i] = tP(L::GOAL_VEL + i);
+		acc[i] = (i < k) ? tP(L::GOAL_ACC + i) : T(0);
+		if (jc.use_vel_sat) {  // JointTask.cpp:327-340 (quirk Q7: loop to k)
+			T mx = T(0);
+			OSC_UNROLL for (int j = 0; j < N; ++j)
+				if (j < k) mx = Num<T>::abs_(jc.kv[j]) > mx ? Num<T>::abs_(jc.kv[j]) : mx;
+			const T kvi = Num<T>::abs_(jc.kv[i]) > T(1e-6) * mx ? T(1) / jc.kv[i] : T(0);
+			T d = -jc.kp[i] * kvi * e - jc.ki[i] * kvi * ie;
+			d = d > jc.sat[i] ? jc.sat[i] : (d < -jc.sat[i] ? -jc.sat[i] : d);
+			dv[i] = d;
+			u[i] = -jc.kv[i] * (cv[i] - d);
+		} else {
+			u[i] = -jc.kp[i] * e - jc.kv[i] * (cv[i] - dv[i]) - jc.ki[i] * ie;
+		}
+		if (i >= k) { u[i] = T(0); dv[i] = T(0); }
+	}
+	if (export_vectors) st_vec<T, N>(tS, L::DES_VEL, dv);
+}
+
+template <class T, int N>
+__device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<T>& rob, const Arena<T>& tk, const T* nprec_src, int64_t stride, int64_t r) {
+	using L = JtL<N>;
 	const Row<T> rS{rob.S, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
@@ -99,11 +127,17 @@ __global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant
 }
 
 template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk, int64_t B,
-															 int64_t stride, int with_tau_prec, int accumulate) {
-	using L = JtL<N>;
+__global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk,
+															const T* nprec_src, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
+	jt_update_robot<T, N>(jc, rob, tk, nprec_src, stride, r);
+}
+
+template <class T, int N>
+__device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r, int with_tau_prec,
+								 int accumulate) {
+	using L = JtL<N>;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	T q[N], dq[N], cp[N], cv[N];
@@ -121,29 +155,8 @@ __global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constan
 	T tau[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) tau[i] = T(0);
 	if (rank > 0) {
-		T u[N], acc[N], dv[N];
-		const int k = jc.k;
-		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			const T e = cp[i] - tP(L::GOAL_POS + i);
-			T ie = tP(L::INTEG + i);
-			if (i < k) { ie += e * jc.dt; tP(L::INTEG + i) = ie; }  // JointTask.cpp:323-324
-			dv[i] = tP(L::GOAL_VEL + i);
-			acc[i] = (i < k) ? tP(L::GOAL_ACC + i) : T(0);
-			if (jc.use_vel_sat) {  // JointTask.cpp:327-340 (quirk Q7: loop to k)
-				T mx = T(0);
-				OSC_UNROLL for (int j = 0; j < N; ++j)
-					if (j < k) mx = Num<T>::abs_(jc.kv[j]) > mx ? Num<T>::abs_(jc.kv[j]) : mx;
-				const T kvi = Num<T>::abs_(jc.kv[i]) > T(1e-6) * mx ? T(1) / jc.kv[i] : T(0);
-				T d = -jc.kp[i] * kvi * e - jc.ki[i] * kvi * ie;
-				d = d > jc.sat[i] ? jc.sat[i] : (d < -jc.sat[i] ? -jc.sat[i] : d);
-				dv[i] = d;
-				u[i] = -jc.kv[i] * (cv[i] - d);
-			} else {
-				u[i] = -jc.kp[i] * e - jc.kv[i] * (cv[i] - dv[i]) - jc.ki[i] * ie;
-			}
-			if (i >= k) { u[i] = T(0); dv[i] = T(0); }
-		}
-		st_vec<T, N>(tS, L::DES_VEL, dv);
+		T u[N], acc[N];
+		jt_pd_law<T, N>(jc, tP, tS, cp, cv, u, acc, true);
 		T Rg[N][N], Lam[N][N], Lm[N][N], Np[N][N];
 		ld_mat<T, N, N>(tS, L::RANGE, Rg);
 		ld_mat<T, N, N>(tS, L::LAM, Lam);
@@ -185,6 +198,14 @@ __global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constan
 	} else if (accumulate == 2) {
 		OSC_UNROLL for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += tau[i];
 	}
+}
+
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk, int64_t B,
+															 int64_t stride, int with_tau_prec, int accumulate) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	jt_compute_robot<T, N>(jc, rob, tk, stride, r, with_tau_prec, accumulate);
 }
 
 }  // namespace osc

@@ -79,9 +79,7 @@ template <class T, int N> OSC_DEV void ld_kin(const Row<T>& S, Kin<T, N>& k) {
 // robot->updateModel()
 // ------------------------------------------------------------------------------------------------------------------
 template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<T> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= B) return;
+__device__ void model_robot(const ChainC<T, N>& ch, const Arena<T>& rob, int64_t stride, int64_t r, int dynamics, int gravity) {
 	const Row<T> P{rob.P, stride, r}, S{rob.S, stride, r};
 	T q[N];
 	ld_vec<T, N>(P, RobotL<N>::Q, q);
@@ -106,6 +104,12 @@ __global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ C
 		gravity_vector<T, N>(ch, kin, g);
 		st_vec<T, N>(S, RobotL<N>::GRAV, g);
 	}
+}
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<T> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	model_robot<T, N>(ch, rob, stride, r, dynamics, gravity);
 }
 
 // bounded-inertia-estimate inverse: M with every diagonal entry raised to >= threshold, inverted

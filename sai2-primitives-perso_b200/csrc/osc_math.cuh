@@ -174,6 +174,73 @@ template <class T, int N> OSC_DEV bool spd_inverse_masked(T (&A)[N][N], unsigned
 	return ok;
 }
 
+// ---- triangular kernels of the fused tick (osc_fused.cuh) ----
+// Packed lower factor: A = L L^T with L[i][k] (k < i) as is, 1/L[i][i] in Li[i] and L[i][i] in Ld[i].
+template <class T, int N> struct Chol {
+	T L[N][N];  // strictly lower part used
+	T Li[N];    // 1 / L_ii
+	T Ld[N];    // L_ii
+};
+// A symmetric (lower triangle read).  Returns false when a pivot is not positive.
+template <class T, int N> OSC_DEV bool chol_factor(const T (&A)[N][N], Chol<T, N>& c) {
+	bool ok = true;
+	OSC_UNROLL for (int j = 0; j < N; ++j) {
+		T d = A[j][j];
+		OSC_UNROLL for (int k = 0; k < j; ++k) d = Num<T>::fma_(-c.L[j][k], c.L[j][k], d);
+		ok = ok && (d > T(0));
+		const T inv = Num<T>::rsqrt_(d);
+		c.Li[j] = inv;
+		c.Ld[j] = d * inv;
+		OSC_UNROLL for (int i = j + 1; i < N; ++i) {
+			T s = A[i][j];
+			OSC_UNROLL for (int k = 0; k < j; ++k) s = Num<T>::fma_(-c.L[i][k], c.L[j][k], s);
+			c.L[i][j] = s * inv;
+		}
+	}
+	return ok;
+}
+// x <- L^-1 x
+template <class T, int N> OSC_DEV void chol_fwd(const Chol<T, N>& c, T (&x)[N]) {
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		T s = x[i];
+		OSC_UNROLL for (int k = 0; k < i; ++k) s = Num<T>::fma_(-c.L[i][k], x[k], s);
+		x[i] = s * c.Li[i];
+	}
+}
+// x <- L^-T x
+template <class T, int N> OSC_DEV void chol_bwd(const Chol<T, N>& c, T (&x)[N]) {
+	OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
+		T s = x[i];
+		OSC_UNROLL for (int k = i + 1; k < N; ++k) s = Num<T>::fma_(-c.L[k][i], x[k], s);
+		x[i] = s * c.Li[i];
+	}
+}
+// y = L x
+template <class T, int N> OSC_DEV void chol_mul(const Chol<T, N>& c, const T (&x)[N], T (&y)[N]) {
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		T s = c.Ld[i] * x[i];
+		OSC_UNROLL for (int k = 0; k < i; ++k) s = Num<T>::fma_(c.L[i][k], x[k], s);
+		y[i] = s;
+	}
+}
+// true when A - shift * I is positive definite (pivots of its LDL^T all positive): a Sylvester-inertia test
+template <class T, int N> OSC_DEV bool spd_above(const T (&A)[N][N], T shift) {
+	T L[N][N], dinv[N];
+	bool ok = true;
+	OSC_UNROLL for (int j = 0; j < N; ++j) {
+		T d = A[j][j] - shift;
+		OSC_UNROLL for (int k = 0; k < j; ++k) d = Num<T>::fma_(-L[j][k] * L[j][k], dinv[k], d);  // L holds l_jk * d_k
+		ok = ok && (d > T(0));
+		dinv[j] = T(1) / d;
+		OSC_UNROLL for (int i = j + 1; i < N; ++i) {
+			T s = A[i][j];
+			OSC_UNROLL for (int k = 0; k < j; ++k) s = Num<T>::fma_(-L[i][k] * L[j][k], dinv[k], s);
+			L[i][j] = s;
+		}
+	}
+	return ok;
+}
+
 // ---- one-sided (Hestenes) Jacobi SVD of A[R][C], R >= C:  A = Q diag(s) W^T ----
 // On exit: A's columns hold Q (normalised, numerically-null columns completed to an orthonormal set), W[C][C] is
 // orthogonal, s[C] descending.  Stands in for Eigen::JacobiSVD (SingularityHandler.cpp:78, matrixRangeBasis).

@@ -98,7 +98,8 @@ OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>&
 // The control law: returns F* (unit mass force) and F_f (force feedback + feed-forward); updates integrators and caches.
 template <class T, int N>
 OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
-							 const T (&J)[6][N], const T (&dq)[N], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status) {
+							 const T (&J)[6][N], const T (&dq)[N], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status,
+							 bool export_vectors = true) {
 	using L = MftL<N>;
 	T v[3], w[3];
 	OSC_UNROLL for (int a = 0; a < 3; ++a) {
@@ -111,9 +112,11 @@ OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& 
 	ld_vec<T, 3>(tP, L::GOAL_POS, xg);
 	T oe[3];
 	orientation_error<T>(Rg, R, oe);  // .cpp:291-292 (_orientation_error, for getters)
-	st_vec<T, 3>(tS, L::ORI_ERR, oe);
-	st_vec<T, 3>(tS, L::CUR_V, v);
-	st_vec<T, 3>(tS, L::CUR_W, w);
+	if (export_vectors) {
+		st_vec<T, 3>(tS, L::ORI_ERR, oe);
+		st_vec<T, 3>(tS, L::CUR_V, v);
+		st_vec<T, 3>(tS, L::CUR_W, w);
+	}
 	st_vec<T, 3>(tP, L::CUR_POS, x);
 	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
 
@@ -229,10 +232,12 @@ OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& 
 		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = bd[a] - tc.kp_ori[a] * eo[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io[a];
 		mv3(So, raw, Fo);
 	}
-	st_vec<T, 3>(tS, L::DES_POS, xg);
-	st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
-	st_vec<T, 3>(tS, L::DES_LINVEL, vd);
-	st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+	if (export_vectors) {
+		st_vec<T, 3>(tS, L::DES_POS, xg);
+		st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
+		st_vec<T, 3>(tS, L::DES_LINVEL, vd);
+		st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+	}
 	// assemble (.cpp:470-487; quirk Q3: the moment feed-forward is scaled under the *force* flag)
 	T ffh[3], fft[3];
 	mv3(Sf, gf, ffh);
@@ -244,7 +249,7 @@ OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& 
 		Fstar[a] = Fp[a]; Fstar[3 + a] = Fo[a];
 		Ff[a] = Ffb[a] + ffh[a]; Ff[3 + a] = Mfb[a] + fft[a];
 	}
-	st_vec<T, 6>(tS, L::UMF, Fstar);
+	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
 }
 
 }  // namespace osc

@@ -26,12 +26,10 @@ OSC_DEV void range_torque(const Row<T>& tS, int offU, int offJ, int offL, const 
 }
 
 template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_mft_compute(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-															  Arena<T> rob, Arena<T> tk, int64_t B, int64_t stride, int with_tau_prec, int accumulate) {
+__device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r,
+								  int with_tau_prec, int accumulate) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= B) return;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
@@ -150,6 +148,14 @@ __global__ void __launch_bounds__(OSC_THREADS) k_mft_compute(const __grid_consta
 		OSC_UNROLL for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += tau[i];
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+}
+
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_mft_compute(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+															  Arena<T> rob, Arena<T> tk, int64_t B, int64_t stride, int with_tau_prec, int accumulate) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	mft_compute_robot<T, N>(ch, tc, rob, tk, stride, r, with_tau_prec, accumulate);
 }
 
 }  // namespace osc

@@ -20,13 +20,13 @@ OSC_DEV void task_jacobian(const ChainC<T, N>& ch, const MftC<T>& tc, const Kin<
 	}
 }
 
+// One robot.  `no_history` re-evaluates the task model without pushing a classification sample (lazy materialisation
+// of the getters after a fused tick: the history was already advanced by the tick itself).
 template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-															 Arena<T> rob, Arena<T> tk, const T* nprec_src, int64_t B, int64_t stride) {
+__device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<T>& rob, const Arena<T>& tk, const T* nprec_src,
+								 int64_t stride, int64_t r, int no_history) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= B) return;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constan
 	T q[N];
 	ld_vec<T, N>(rP, RobotL<N>::Q, q);
 	int c1 = tI(L::C1), c2 = tI(L::C2);
-	if (tI(L::NTYPES) == 0 || c2 > c1) {
+	if (!no_history && (tI(L::NTYPES) == 0 || c2 > c1)) {
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			tP(L::Q_PRIOR + i) = q[i];
 			tP(L::DQ_PRIOR + i) = rP(RobotL<N>::DQ + i);
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constan
 	}
 	if (mask_s == 0u) {
 		tI(L::NTYPES) = 0; tI(L::TYPES) = 0; tI(L::C1) = 0; tI(L::C2) = 0; tI(L::HIST_LEN) = 0; tI(L::HIST_HEAD) = 0;
-	} else {
+	} else if (!no_history) {
 		int types = 0, ntypes = 0;
 		bool any1 = false;
 		const int first = fully ? 0 : ins;
@@ -252,6 +252,14 @@ __global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constan
 		tI(L::HIST_LEN) = len; tI(L::HIST_HEAD) = head; tI(L::C1) = c1; tI(L::C2) = c2;
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+}
+
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+															 Arena<T> rob, Arena<T> tk, const T* nprec_src, int64_t B, int64_t stride, int no_history) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	mft_update_robot<T, N>(ch, tc, rob, tk, nprec_src, stride, r, no_history);
 }
 
 }  // namespace osc

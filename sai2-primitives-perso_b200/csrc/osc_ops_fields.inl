@@ -130,7 +130,44 @@ template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l
 
 template <class T, int N> bool OpsImpl<T, N>::fused_supported(Batch& b) { return fused_tick_supported<T, N>(b); }
 template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
-	const int rc = fused_tick_launch<T, N>(b, ch, stacked);
-	if (rc != OSC_OK) return rc;
-	return done(b, "k_tick_fused");
+	if constexpr (N == 6 || N == 7) {
+		if (!b.fb) {
+			cudaError_t e = cudaMalloc((void**)&b.fb, (size_t)(b.stride + 2) * sizeof(int));
+			if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(fallback list)");
+			e = cudaMemsetAsync(b.fb, 0, 2 * sizeof(int), b.stream);
+			if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(fallback counters)");
+			b.fb_parity = 0;
+		}
+		TaskH &m = b.tasks[0], &j = b.tasks[1];
+		int* cnt = b.fb + b.fb_parity;
+		int* nxt = b.fb + (b.fb_parity ^ 1);
+		int* list = b.fb + 2;
+		const int exports = b.tick_outputs == OSC_TICK_OUTPUTS_TAU ? 0 : OSC_EXPORT_VECTORS;
+		const dim3 g((unsigned)((b.B + OSC_FUSED_THREADS - 1) / OSC_FUSED_THREADS));
+		const MftC<T> tc = mftc(m);
+		const JtC<T, N> jc = jtc(b, j);
+		k_tick_fused<T, N><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list);
+		if (int rc = done(b, "k_tick_fused")) return rc;
+		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
+		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list);
+		if (int rc = done(b, "k_tick_tail")) return rc;
+		b.fb_last = b.fb_parity;
+		b.fb_parity ^= 1;
+		b.stale = true;
+		return OSC_OK;
+	} else {
+		(void)stacked;
+		set_error("the fused tick is not built for this dof");
+		return OSC_ERR_UNSUPPORTED;
+	}
+}
+// The getters of the reference that the fused tick did not write: recompute the model and the task models with the
+// per-call kernels at the current q.  No persistent state advances (k_mft_update runs with no_history while b.stale).
+template <class T, int N> int OpsImpl<T, N>::materialise(Batch& b) {
+	if (!b.stale) return OSC_OK;
+	if (int rc = model(b, 1)) return rc;
+	for (int t = 0; t < (int)b.tasks.size(); ++t)
+		if (int rc = task_update(b, t, t - 1, 1)) return rc;
+	b.stale = false;
+	return OSC_OK;
 }

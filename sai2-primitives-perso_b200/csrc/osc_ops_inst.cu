@@ -137,10 +137,10 @@ template <class T, int N> struct OpsImpl : Ops {
 		const int off = s.type == OSC_TASK_MOTION_FORCE ? MftL<N>::NTP : JtL<N>::NTP;
 		return (const T*)s.S + (int64_t)off * b.stride;
 	}
-	int task_update(Batch& b, int t, int src) override {
+	int task_update(Batch& b, int t, int src, int no_history) override {
 		TaskH& th = b.tasks[t];
 		if (th.type == OSC_TASK_MOTION_FORCE) {
-			k_mft_update<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, mftc(th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride);
+			k_mft_update<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, mftc(th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride, no_history);
 			return done(b, "k_mft_update");
 		}
 		k_jt_update<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtc(b, th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride);
@@ -169,6 +169,7 @@ template <class T, int N> struct OpsImpl : Ops {
 	int pack_special(Batch& b, const Loc& l, void* tmp) override;
 	bool fused_supported(Batch& b) override;
 	int tick_fused(Batch& b, int stacked) override;
+	int materialise(Batch& b) override;
 };
 
 #include "osc_ops_fields.inl"

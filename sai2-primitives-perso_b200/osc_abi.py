@@ -19,6 +19,8 @@ TASK_UNDEFINED, TASK_JOINT, TASK_MOTION_FORCE = 0, 1, 2
 FULL_DYNAMIC_DECOUPLING, BOUNDED_INERTIA_ESTIMATES, IMPEDANCE = 0, 1, 2
 NO_SINGULARITY, TYPE_1_SINGULARITY, TYPE_2_SINGULARITY = 0, 1, 2
 
+TICK_OUTPUTS_ALL, TICK_OUTPUTS_LAZY, TICK_OUTPUTS_TAU = 0, 1, 2
+
 STATUS_NAN_TORQUE = 1 << 0
 STATUS_POPC_RING_OVERFLOW = 1 << 1
 STATUS_POPC_RC_NAN = 1 << 2

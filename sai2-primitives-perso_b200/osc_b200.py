@@ -71,6 +71,8 @@ def lib():
         "osc_compute_torques": (i, [vp, i, vp, i, i]),
         "osc_tick": (i, [vp, i, vp, i, i]),
         "osc_tick_is_fused": (i, [vp]),
+        "osc_batch_set_tick_outputs": (i, [vp, i]),
+        "osc_tick_fallback_count": (i64, [vp]),
         "osc_launch_count": (i64, [vp]),
         "osc_reinitialize_tasks": (i, [vp, i]),
         "osc_snapshot_bytes": (i64, [vp]),
@@ -94,7 +96,7 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_enable_gravity_compensation", "osc_field_size", "osc_set_field", "osc_get_field",
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
-            "osc_tick", "osc_tick_is_fused", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
+            "osc_tick", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak"]
 
 
@@ -234,6 +236,12 @@ class Batch:
 
     def tick_is_fused(self):
         return bool(self.L.osc_tick_is_fused(self.h))
+
+    def set_tick_outputs(self, outputs):
+        self._chk(self.L.osc_batch_set_tick_outputs(self.h, int(outputs)))
+
+    def tick_fallback_count(self):
+        return int(self.L.osc_tick_fallback_count(self.h))
 
     def launch_count(self):
         return int(self.L.osc_launch_count(self.h))

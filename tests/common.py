@@ -67,7 +67,7 @@ JT_FIELDS = [(abi.F_JT_CURRENT_POSITION, None), (abi.F_JT_CURRENT_VELOCITY, None
 JT_INT_FIELDS = [abi.F_JT_RANGE_RANK]
 
 
-def compare(gpu, orc, task_types, tol, skip=(), report=None):
+def compare(gpu, orc, task_types, tol, skip=(), report=None, loose=None):
     """Compare every exported field of both batches; returns {name: err}; asserts err <= tol."""
     names = {v: k for k, v in vars(abi).items() if k.startswith("F_")}
     errs = {}
@@ -78,7 +78,7 @@ def compare(gpu, orc, task_types, tol, skip=(), report=None):
         a, b = gpu.get(field, task), orc.get(field, task)
         e, where = rel_err(a, b, floor)
         errs["%s[t%d]" % (names[field], task)] = e
-        assert e <= tol, "%s task %d: rel err %.3e > %.1e at robot %d\n gpu=%s\n ref=%s" % (
+        assert e <= (loose or {}).get(field, tol), "%s task %d: rel err %.3e > %.1e at robot %d\n gpu=%s\n ref=%s" % (
             names[field], task, e, tol, where, a[where], b[where])
 
     def one_int(field, task):
@@ -169,5 +169,5 @@ class Pair:
                     setattr(p, k, v)
             b.set_joint_task_params(task, p)
 
-    def compare(self, tol, skip=(), report=None):
-        return compare(self.gpu, self.ref, self.types, tol, skip, report)
+    def compare(self, tol, skip=(), report=None, loose=None):
+        return compare(self.gpu, self.ref, self.types, tol, skip, report, loose)
