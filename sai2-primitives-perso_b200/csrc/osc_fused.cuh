@@ -25,8 +25,8 @@ namespace osc {
 
 enum { OSC_EXPORT_VECTORS = 1 };
 
-template <class T, int N>
-__global__ void __launch_bounds__(OSC_FUSED_THREADS) k_tick_fused(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+template <class T, int N, int MINB>
+__global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 																   const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
 																   int64_t B, int64_t stride, int stacked, int gravity, int exports,
 																   int* __restrict__ fb_count, int* __restrict__ fb_list) {

@@ -146,7 +146,12 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 		const dim3 g((unsigned)((b.B + OSC_FUSED_THREADS - 1) / OSC_FUSED_THREADS));
 		const MftC<T> tc = mftc(m);
 		const JtC<T, N> jc = jtc(b, j);
-		k_tick_fused<T, N><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list);
+		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : 8; }();  // 8 blocks of 64 = 128 registers: 65,536 robots are ONE wave on 148 SMs (profiles/README.md)
+#define OSC_LAUNCH_FUSED(MB) k_tick_fused<T, N, MB><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list)
+		if (minb >= 8) OSC_LAUNCH_FUSED(8);
+		else if (minb >= 6) OSC_LAUNCH_FUSED(6);
+		else OSC_LAUNCH_FUSED(4);
+#undef OSC_LAUNCH_FUSED
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
 		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list);

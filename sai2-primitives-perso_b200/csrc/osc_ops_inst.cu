@@ -1,5 +1,9 @@
 // osc_ops_inst.cu -- one instantiation of the kernel set.  Compiled once per (OSC_T, OSC_N) pair:
 //   nvcc -DOSC_T=double -DOSC_TNAME=f64 -DOSC_N=7 -c osc_ops_inst.cu -o ops_f64_7.o
+#include <stdlib.h>
+
+#include <algorithm>
+
 #include "osc_aux_kernels.cuh"
 #include "osc_fused.cuh"
 #include "osc_host.h"
