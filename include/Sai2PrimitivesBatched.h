@@ -164,3 +164,313 @@ protected:
 	double _dt;
 	int _index = -1;
 };
+
+// ---- src/tasks/MotionForceTask.h ----
+class MotionForceTask : public TemplateTask {
+public:
+	// MotionForceTask(robot, link_name, compliant_frame, task_name, is_force_motion_parametrization_in_compliant_frame,
+	//                 loop_timestep)   src/tasks/MotionForceTask.h:96-101, MotionForceTask.cpp:16-31
+	MotionForceTask(const std::shared_ptr<RobotBatch>& robot, const Link& link, const Affine3& compliant_frame = Affine3::Identity(),
+					const std::string& task_name = "motion_force_task", bool is_force_motion_parametrization_in_compliant_frame = false,
+					double loop_timestep = 0.001)
+		: TemplateTask(robot, task_name, MOTION_FORCE_TASK, loop_timestep) {
+		attach(link, compliant_frame, nullptr, nullptr, is_force_motion_parametrization_in_compliant_frame);
+	}
+	// partial task: controlled translation / rotation directions   MotionForceTask.h:103-110, MotionForceTask.cpp:33-90
+	MotionForceTask(const std::shared_ptr<RobotBatch>& robot, const Link& link, const std::vector<std::array<double, 3>>& controlled_directions_translation,
+					const std::vector<std::array<double, 3>>& controlled_directions_rotation, const Affine3& compliant_frame = Affine3::Identity(),
+					const std::string& task_name = "partial_motion_force_task", bool is_force_motion_parametrization_in_compliant_frame = false,
+					double loop_timestep = 0.001)
+		: TemplateTask(robot, task_name, MOTION_FORCE_TASK, loop_timestep) {
+		attach(link, compliant_frame, &controlled_directions_translation, &controlled_directions_rotation, is_force_motion_parametrization_in_compliant_frame);
+	}
+
+	// ---- goals (MotionForceTask.h:211-247, 362, 376) ----
+	void setGoalPosition(const In& v) { _robot->set(_index, OSC_F_GOAL_POSITION, v); }
+	void setGoalOrientation(const In& R) { _robot->set(_index, OSC_F_GOAL_ORIENTATION, R); }
+	void setGoalLinearVelocity(const In& v) { _robot->set(_index, OSC_F_GOAL_LINEAR_VELOCITY, v); }
+	void setGoalAngularVelocity(const In& v) { _robot->set(_index, OSC_F_GOAL_ANGULAR_VELOCITY, v); }
+	void setGoalLinearAcceleration(const In& v) { _robot->set(_index, OSC_F_GOAL_LINEAR_ACCELERATION, v); }
+	void setGoalAngularAcceleration(const In& v) { _robot->set(_index, OSC_F_GOAL_ANGULAR_ACCELERATION, v); }
+	void setGoalForce(const In& v) { _robot->set(_index, OSC_F_GOAL_FORCE, v); }
+	void setGoalMoment(const In& v) { _robot->set(_index, OSC_F_GOAL_MOMENT, v); }
+	void getGoalPosition(const Out& o) { _robot->get(_index, OSC_F_GOAL_POSITION, o); }
+	void getGoalOrientation(const Out& o) { _robot->get(_index, OSC_F_GOAL_ORIENTATION, o); }
+	void getGoalLinearVelocity(const Out& o) { _robot->get(_index, OSC_F_GOAL_LINEAR_VELOCITY, o); }
+	void getGoalAngularVelocity(const Out& o) { _robot->get(_index, OSC_F_GOAL_ANGULAR_VELOCITY, o); }
+	// ---- state getters (MotionForceTask.h:121-205, 508-522) ----
+	void getCurrentPosition(const Out& o) { _robot->get(_index, OSC_F_CURRENT_POSITION, o); }
+	void getCurrentOrientation(const Out& o) { _robot->get(_index, OSC_F_CURRENT_ORIENTATION, o); }
+	void getCurrentLinearVelocity(const Out& o) { _robot->get(_index, OSC_F_CURRENT_LINEAR_VELOCITY, o); }
+	void getCurrentAngularVelocity(const Out& o) { _robot->get(_index, OSC_F_CURRENT_ANGULAR_VELOCITY, o); }
+	void getDesiredPosition(const Out& o) { _robot->get(_index, OSC_F_DESIRED_POSITION, o); }
+	void getDesiredOrientation(const Out& o) { _robot->get(_index, OSC_F_DESIRED_ORIENTATION, o); }
+	void getDesiredLinearVelocity(const Out& o) { _robot->get(_index, OSC_F_DESIRED_LINEAR_VELOCITY, o); }
+	void getDesiredAngularVelocity(const Out& o) { _robot->get(_index, OSC_F_DESIRED_ANGULAR_VELOCITY, o); }
+	void getOrientationError(const Out& o) { _robot->get(_index, OSC_F_ORIENTATION_ERROR, o); }
+	void getUnitMassForce(const Out& o) { _robot->get(_index, OSC_F_UNIT_MASS_FORCE, o); }
+	void getSensedForceControlWorldFrame(const Out& o) { _robot->get(_index, OSC_F_SENSED_FORCE_WORLD, o); }
+	void getSensedMomentControlWorldFrame(const Out& o) { _robot->get(_index, OSC_F_SENSED_MOMENT_WORLD, o); }
+	void getJacobian(const Out& o) { _robot->get(_index, OSC_F_JACOBIAN, o); }
+	void getProjectedJacobian(const Out& o) { _robot->get(_index, OSC_F_PROJECTED_JACOBIAN, o); }
+	void getLambdaWorldFrame(const Out& o) { _robot->get(_index, OSC_F_LAMBDA_WORLD, o); }
+	void getLambdaModifiedWorldFrame(const Out& o) { _robot->get(_index, OSC_F_LAMBDA_MODIFIED_WORLD, o); }
+	void getSingularityBlendingCoefficient(const Out& o) { _robot->get(_index, OSC_F_ALPHA, o); }
+	void getSingularValues(const Out& o) { _robot->get(_index, OSC_F_SINGULAR_VALUES, o); }
+	void getSingularityTypes(const Out& o) { _robot->get(_index, OSC_F_SINGULARITY_TYPES, o); }
+	int getTaskDof() const { return osc_batch_task_dof(_robot->handle(), _index); }
+
+	// ---- gains (MotionForceTask.h:272-355) ----
+	void setPosControlGains(const PIDGains& g) { setPosControlGains(g.kp, g.kv, g.ki); }
+	void setPosControlGains(double kp, double kv, double ki = 0) { setPosControlGains({kp, kp, kp}, {kv, kv, kv}, {ki, ki, ki}); }
+	void setPosControlGains(const std::array<double, 3>& kp, const std::array<double, 3>& kv, const std::array<double, 3>& ki = {0, 0, 0}) {
+		edit([&](osc_mft_params& p) { for (int a = 0; a < 3; ++a) { p.kp_pos[a] = kp[a]; p.kv_pos[a] = kv[a]; p.ki_pos[a] = ki[a]; } });
+	}
+	void setOriControlGains(const PIDGains& g) { setOriControlGains(g.kp, g.kv, g.ki); }
+	void setOriControlGains(double kp, double kv, double ki = 0) { setOriControlGains({kp, kp, kp}, {kv, kv, kv}, {ki, ki, ki}); }
+	void setOriControlGains(const std::array<double, 3>& kp, const std::array<double, 3>& kv, const std::array<double, 3>& ki = {0, 0, 0}) {
+		edit([&](osc_mft_params& p) { for (int a = 0; a < 3; ++a) { p.kp_ori[a] = kp[a]; p.kv_ori[a] = kv[a]; p.ki_ori[a] = ki[a]; } });
+	}
+	void setForceControlGains(const PIDGains& g) { setForceControlGains(g.kp, g.kv, g.ki); }
+	void setForceControlGains(double kp, double kv, double ki) { edit([&](osc_mft_params& p) { p.kp_force = kp; p.kv_force = kv; p.ki_force = ki; }); }
+	void setMomentControlGains(const PIDGains& g) { setMomentControlGains(g.kp, g.kv, g.ki); }
+	void setMomentControlGains(double kp, double kv, double ki) { edit([&](osc_mft_params& p) { p.kp_moment = kp; p.kv_moment = kv; p.ki_moment = ki; }); }
+	void setFeedforwardForceGain(double k) { edit([&](osc_mft_params& p) { p.kff_force = k; }); }
+	void setFeedforwardMomentGain(double k) { edit([&](osc_mft_params& p) { p.kff_moment = k; }); }
+	void setMaxForceControlFeedbackOutput(double v) { edit([&](osc_mft_params& p) { p.max_force_control_feedback_output = v; }); }
+	void setMaxMomentControlFeedbackOutput(double v) { edit([&](osc_mft_params& p) { p.max_moment_control_feedback_output = v; }); }
+
+	// ---- force / motion space parametrisation (MotionForceTask.h:576-623, MotionForceTask.cpp:830-890, 973-986) ----
+	// returns true when the parametrisation changed (goal <- current pose, integrators reset: .cpp:850-856)
+	bool parametrizeForceMotionSpaces(int force_space_dimension, const std::array<double, 3>& force_or_motion_single_axis = {0, 0, 0}) {
+		const int mask = edit([&](osc_mft_params& p) {
+			p.force_space_dimension = force_space_dimension;
+			for (int a = 0; a < 3; ++a) p.force_or_motion_axis[a] = force_or_motion_single_axis[a];
+		});
+		return (mask & 1) != 0;
+	}
+	bool parametrizeMomentRotMotionSpaces(int moment_space_dimension, const std::array<double, 3>& moment_or_rot_motion_single_axis = {0, 0, 0}) {
+		const int mask = edit([&](osc_mft_params& p) {
+			p.moment_space_dimension = moment_space_dimension;
+			for (int a = 0; a < 3; ++a) p.moment_or_rotmotion_axis[a] = moment_or_rot_motion_single_axis[a];
+		});
+		return (mask & 2) != 0;
+	}
+	void setClosedLoopForceControl(bool closed_loop = true) { edit([&](osc_mft_params& p) { p.closed_loop_force_control = closed_loop; }); }
+	void setClosedLoopMomentControl(bool closed_loop = true) { edit([&](osc_mft_params& p) { p.closed_loop_moment_control = closed_loop; }); }
+	void enablePassivity() { edit([&](osc_mft_params& p) { p.passivity_enabled = 1; }); }
+	void disablePassivity() { edit([&](osc_mft_params& p) { p.passivity_enabled = 0; }); }
+	// MotionForceTask::setForceSensorFrame (.cpp:794-803): the sensor pose IN THE CONTROL LINK; stored relative to the compliant frame
+	void setForceSensorFrame(const Affine3& transformation_in_link) {
+		Affine3 inv;  // compliant_frame^-1
+		for (int i = 0; i < 3; ++i) {
+			for (int j = 0; j < 3; ++j) inv.rot[3 * i + j] = _compliant_frame.rot[3 * j + i];
+		}
+		for (int i = 0; i < 3; ++i) {
+			inv.xyz[i] = 0;
+			for (int k = 0; k < 3; ++k) inv.xyz[i] -= inv.rot[3 * i + k] * _compliant_frame.xyz[k];
+		}
+		const Affine3 T = inv * transformation_in_link;
+		edit([&](osc_mft_params& p) {
+			for (int k = 0; k < 9; ++k) p.sensor_rot[k] = T.rot[k];
+			for (int k = 0; k < 3; ++k) p.sensor_xyz[k] = T.xyz[k];
+		});
+	}
+	// MotionForceTask::updateSensedForceAndMoment (.cpp:805-828): sensor-frame wrench of every robot
+	void updateSensedForceAndMoment(const In& sensed_force_sensor_frame, const In& sensed_moment_sensor_frame) {
+		if (sensed_force_sensor_frame.layout != sensed_moment_sensor_frame.layout || sensed_force_sensor_frame.mem != sensed_moment_sensor_frame.mem)
+			throw std::invalid_argument("force and moment must use the same layout and memory space in MotionForceTask::updateSensedForceAndMoment\n");
+		check(osc_mft_update_sensed_force_and_moment(_robot->handle(), _index, sensed_force_sensor_frame.ptr, sensed_moment_sensor_frame.ptr,
+													 sensed_force_sensor_frame.layout, sensed_force_sensor_frame.mem));
+	}
+
+	// ---- velocity saturation, decoupling, singularity handling (MotionForceTask.h:430-432, 669-753) ----
+	void enableVelocitySaturation(double linear_vel_sat = 0.3, double angular_vel_sat = 3.14159265358979323846 / 3) {
+		if (linear_vel_sat <= 0 || angular_vel_sat <= 0)
+			throw std::invalid_argument("Velocity saturation values should be strictly positive or zero in MotionForceTask::enableVelocitySaturation\n");
+		edit([&](osc_mft_params& p) { p.use_velocity_saturation = 1; p.linear_saturation_velocity = linear_vel_sat; p.angular_saturation_velocity = angular_vel_sat; });
+	}
+	void disableVelocitySaturation() { edit([&](osc_mft_params& p) { p.use_velocity_saturation = 0; }); }
+	void setDynamicDecouplingType(DynamicDecouplingType type) { edit([&](osc_mft_params& p) { p.dynamic_decoupling_type = type; }); }
+	void setBoundedInertiaEstimateThreshold(double threshold) { edit([&](osc_mft_params& p) { p.bie_threshold = threshold; }); }
+	void handleAllSingularitiesAsType1(bool flag) { edit([&](osc_mft_params& p) { p.enforce_type_1_strategy = flag; }); }
+	void setType1Posture(const In& q_prior) { _robot->set(_index, OSC_F_Q_PRIOR, q_prior); }
+	void enableSingularityHandling() { edit([&](osc_mft_params& p) { p.singularity_handling_enabled = 1; }); }
+	void disableSingularityHandling() { edit([&](osc_mft_params& p) { p.singularity_handling_enabled = 0; }); }
+	void setSingularityHandlingBounds(double s_min, double s_max) { edit([&](osc_mft_params& p) { p.s_min = s_min; p.s_max = s_max; }); }
+	void setSingularityHandlingGains(double kp_type_1, double kv_type_1, double kv_type_2) {
+		edit([&](osc_mft_params& p) { p.kp_type_1 = kp_type_1; p.kv_type_1 = kv_type_1; p.kv_type_2 = kv_type_2; });
+	}
+	// the internal OTG of the reference is the "next" row f-1: the batched task runs with it disabled (04...cpp:115)
+	void disableInternalOtg() {}
+	void resetIntegrators() {
+		const std::array<double, 3> z = {0, 0, 0};
+		_robot->set(_index, OSC_F_INTEGRATED_POSITION_ERROR, z);
+		_robot->set(_index, OSC_F_INTEGRATED_ORIENTATION_ERROR, z);
+		_robot->set(_index, OSC_F_INTEGRATED_FORCE_ERROR, z);
+		_robot->set(_index, OSC_F_INTEGRATED_MOMENT_ERROR, z);
+	}
+	osc_mft_params getParams() const { osc_mft_params p; check(osc_mft_get_params(_robot->handle(), _index, &p)); return p; }
+
+private:
+	template <class F> int edit(F f) {
+		osc_mft_params p = getParams();
+		f(p);
+		const int rc = osc_mft_set_params(_robot->handle(), _index, &p);
+		check(rc);
+		return rc;
+	}
+	void attach(const Link& link, const Affine3& compliant_frame, const std::vector<std::array<double, 3>>* dt, const std::vector<std::array<double, 3>>* dr,
+				bool in_compliant_frame) {
+		_compliant_frame = compliant_frame;
+		const Affine3 f = link.in_body * compliant_frame;
+		osc_mft_desc d{};
+		d.body = link.body;
+		for (int k = 0; k < 3; ++k) d.frame_xyz[k] = f.xyz[k];
+		for (int k = 0; k < 9; ++k) d.frame_rot[k] = f.rot[k];
+		d.partial = dt != nullptr;
+		if (dt) {
+			if (dt->size() > 3 || dr->size() > 3) throw std::invalid_argument("at most 3 controlled directions per block in MotionForceTask\n");
+			d.n_dirs_translation = (int)dt->size();
+			d.n_dirs_rotation = (int)dr->size();
+			for (size_t c = 0; c < dt->size(); ++c) for (int k = 0; k < 3; ++k) d.dirs_translation[c][k] = (*dt)[c][k];
+			for (size_t c = 0; c < dr->size(); ++c) for (int k = 0; k < 3; ++k) d.dirs_rotation[c][k] = (*dr)[c][k];
+		}
+		d.parametrization_in_compliant_frame = in_compliant_frame;
+		d.loop_timestep = _dt;
+		_index = osc_batch_add_motion_force_task(_robot->handle(), &d);
+		check(_index);
+	}
+	Affine3 _compliant_frame;
+};
+
+// ---- src/tasks/JointTask.h ----
+class JointTask : public TemplateTask {
+public:
+	// JointTask(robot, task_name, loop_timestep)   JointTask.h:56-60, JointTask.cpp:14-21
+	JointTask(const std::shared_ptr<RobotBatch>& robot, const std::string& task_name = "joint_task", double loop_timestep = 0.001)
+		: TemplateTask(robot, task_name, JOINT_TASK, loop_timestep) {
+		osc_joint_task_desc d{};
+		d.full = 1; d.k = robot->dof(); d.loop_timestep = loop_timestep;
+		_k = d.k;
+		_index = osc_batch_add_joint_task(_robot->handle(), &d);
+		check(_index);
+	}
+	// JointTask(robot, joint_selection_matrix (k x n, row-major, full row rank), task_name, loop_timestep)   JointTask.h:70-75, .cpp:23-43
+	JointTask(const std::shared_ptr<RobotBatch>& robot, const std::vector<double>& joint_selection_matrix, int task_dof,
+			  const std::string& task_name = "partial_joint_task", double loop_timestep = 0.001)
+		: TemplateTask(robot, task_name, JOINT_TASK, loop_timestep) {
+		const int n = robot->dof();
+		if (task_dof < 1 || task_dof > n || (int)joint_selection_matrix.size() != task_dof * n)
+			throw std::invalid_argument("joint selection matrix size not consistent with robot dof in JointTask constructor\n");
+		osc_joint_task_desc d{};
+		d.full = 0; d.k = task_dof; d.loop_timestep = loop_timestep;
+		for (int i = 0; i < task_dof * n; ++i) d.selection[i] = joint_selection_matrix[i];
+		_k = task_dof;
+		_index = osc_batch_add_joint_task(_robot->handle(), &d);
+		check(_index);
+	}
+	bool isFullJointTask() const { return _k == _robot->dof(); }  // JointTask.h:123
+	int getTaskDof() const { return _k; }
+
+	// goals (JointTask.h:137-172)
+	void setGoalPosition(const In& v) { _robot->set(_index, OSC_F_JT_GOAL_POSITION, v); }
+	void setGoalVelocity(const In& v) { _robot->set(_index, OSC_F_JT_GOAL_VELOCITY, v); }
+	void setGoalAcceleration(const In& v) { _robot->set(_index, OSC_F_JT_GOAL_ACCELERATION, v); }
+	void getGoalPosition(const Out& o) { _robot->get(_index, OSC_F_JT_GOAL_POSITION, o); }
+	void getCurrentPosition(const Out& o) { _robot->get(_index, OSC_F_JT_CURRENT_POSITION, o); }
+	void getCurrentVelocity(const Out& o) { _robot->get(_index, OSC_F_JT_CURRENT_VELOCITY, o); }
+	void getDesiredVelocity(const Out& o) { _robot->get(_index, OSC_F_JT_DESIRED_VELOCITY, o); }
+	void getLambdaJointFrame(const Out& o) { _robot->get(_index, OSC_F_JT_LAMBDA_WORLD, o); }
+	// gains (JointTask.h:234-254)
+	void setGains(const PIDGains& g) { setGains(g.kp, g.kv, g.ki); }
+	void setGains(double kp, double kv, double ki = 0) {
+		edit([&](osc_joint_task_params& p) { for (int i = 0; i < _k; ++i) { p.kp[i] = kp; p.kv[i] = kv; p.ki[i] = ki; } });
+	}
+	void setGains(const std::vector<double>& kp, const std::vector<double>& kv, const std::vector<double>& ki = {}) {
+		if ((int)kp.size() != _k || (int)kv.size() != _k || (!ki.empty() && (int)ki.size() != _k))
+			throw std::invalid_argument("size of gain vectors inconsistent with number of task dofs in JointTask::setGains\n");
+		edit([&](osc_joint_task_params& p) { for (int i = 0; i < _k; ++i) { p.kp[i] = kp[i]; p.kv[i] = kv[i]; p.ki[i] = ki.empty() ? 0 : ki[i]; } });
+	}
+	void enableVelocitySaturation(double saturation_velocity = 3.14159265358979323846 / 3) {
+		edit([&](osc_joint_task_params& p) { p.use_velocity_saturation = 1; for (int i = 0; i < _k; ++i) p.saturation_velocity[i] = saturation_velocity; });
+	}
+	void enableVelocitySaturation(const std::vector<double>& saturation_velocity) {
+		if ((int)saturation_velocity.size() != _k)
+			throw std::invalid_argument("saturation velocity vector does not have the correct size in JointTask::enableVelocitySaturation\n");
+		edit([&](osc_joint_task_params& p) { p.use_velocity_saturation = 1; for (int i = 0; i < _k; ++i) p.saturation_velocity[i] = saturation_velocity[i]; });
+	}
+	void disableVelocitySaturation() { edit([&](osc_joint_task_params& p) { p.use_velocity_saturation = 0; }); }
+	void setDynamicDecouplingType(DynamicDecouplingType type) { edit([&](osc_joint_task_params& p) { p.dynamic_decoupling_type = type; }); }
+	void setBoundedInertiaEstimateThreshold(double threshold) { edit([&](osc_joint_task_params& p) { p.bie_threshold = threshold; }); }
+	void disableInternalOtg() {}
+	void resetIntegrators() { _robot->set(_index, OSC_F_JT_INTEGRATED_ERROR, std::vector<double>((size_t)_k, 0.0)); }  // JointTask.h:394
+	osc_joint_task_params getParams() const { osc_joint_task_params p; check(osc_joint_task_get_params(_robot->handle(), _index, &p)); return p; }
+
+private:
+	template <class F> void edit(F f) {
+		osc_joint_task_params p = getParams();
+		f(p);
+		check(osc_joint_task_set_params(_robot->handle(), _index, &p));
+	}
+	int _k = 0;
+};
+
+// ---- src/RobotController.h:22-51 ----
+class RobotController {
+public:
+	// RobotController(robot, tasks): the rules of RobotController.cpp:8-51.  Same-dt and nothing-after-a-full-joint-task are
+	// enforced by the batch when the tasks are constructed; here: at least one task, same robot, unique names, priority
+	// order = construction order.
+	RobotController(const std::shared_ptr<RobotBatch>& robot, const std::vector<std::shared_ptr<TemplateTask>>& tasks) : _robot(robot), _tasks(tasks) {
+		if (tasks.empty()) throw std::invalid_argument("RobotController must have at least one task");
+		for (size_t i = 0; i < tasks.size(); ++i) {
+			if (tasks[i]->robot() != robot) throw std::invalid_argument("All tasks must have the same robot model in RobotController");
+			if (tasks[i]->getLoopTimestep() != tasks[0]->getLoopTimestep()) throw std::invalid_argument("All tasks must have the same loop timestep in RobotController");
+			for (size_t j = 0; j < i; ++j)
+				if (tasks[j]->getTaskName() == tasks[i]->getTaskName()) throw std::invalid_argument("Tasks in RobotController must have unique names");
+			if (tasks[i]->index() != (int)i)
+				throw std::invalid_argument("tasks must be given to RobotController in the order they were constructed on the robot batch (priority order)");
+		}
+		if ((int)tasks.size() != osc_batch_task_count(robot->handle()))
+			throw std::invalid_argument("every task constructed on the robot batch must be given to RobotController");
+	}
+	void updateControllerTaskModels() { check(osc_update_task_models(_robot->handle())); }  // RobotController.cpp:53-60
+	// VectorXd computeControlTorques()   RobotController.cpp:62-74
+	void computeControlTorques(const Out& tau) { check(osc_compute_torques(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem)); }
+	void computeControlTorques() { check(osc_compute_torques(_robot->handle(), 1, nullptr, 0, 0)); }
+	// robot->updateModel(); updateControllerTaskModels(); computeControlTorques() in one (fused) launch
+	void tick(const Out& tau) { check(osc_tick(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem)); }
+	void tick() { check(osc_tick(_robot->handle(), 1, nullptr, 0, 0)); }
+	void getControlTorques(const Out& tau) { _robot->get(-1, OSC_F_TAU, tau); }
+	void enableGravityCompensation(bool enable) { check(osc_enable_gravity_compensation(_robot->handle(), enable)); }  // RobotController.h:31-33
+	void reinitializeTasks() { check(osc_reinitialize_tasks(_robot->handle(), -1)); }
+	std::vector<std::string> getTaskNames() const {
+		std::vector<std::string> n;
+		for (auto& t : _tasks) n.push_back(t->getTaskName());
+		return n;
+	}
+	std::shared_ptr<JointTask> getJointTaskByName(const std::string& name) const {
+		for (auto& t : _tasks)
+			if (t->getTaskName() == name) {
+				if (t->getTaskType() != JOINT_TASK) throw std::invalid_argument("Task [" + name + "] is not a JointTask");
+				return std::static_pointer_cast<JointTask>(t);
+			}
+		throw std::invalid_argument("Task [" + name + "] not found");
+	}
+	std::shared_ptr<MotionForceTask> getMotionForceTaskByName(const std::string& name) const {
+		for (auto& t : _tasks)
+			if (t->getTaskName() == name) {
+				if (t->getTaskType() != MOTION_FORCE_TASK) throw std::invalid_argument("Task [" + name + "] is not a MotionForceTask");
+				return std::static_pointer_cast<MotionForceTask>(t);
+			}
+		throw std::invalid_argument("Task [" + name + "] not found");
+	}
+
+private:
+	std::shared_ptr<RobotBatch> _robot;
+	std::vector<std::shared_ptr<TemplateTask>> _tasks;
+};
+
+}  // namespace Sai2PrimitivesBatched
+#endif  // SAI2_PRIMITIVES_BATCHED_H_

@@ -1,0 +1,82 @@
+"""The C++ facade (include/Sai2PrimitivesBatched.h): compiles against the C ABI with plain g++ (CPU check), refuses to run
+without a CUDA device (no CPU fallback), and on the GPU reproduces the oracle through the reference's method names."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import osc_abi as abi
+from common import FP64_TOL, ROOT, load_chain, q0_of, random_q, rel_err
+
+PKG = os.path.join(ROOT, "sai2-primitives-perso_b200")
+EXE = os.path.join(ROOT, "tests", "cpp", "_build", "facade_demo")
+
+
+def _build():
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    src = os.path.join(ROOT, "tests", "cpp", "facade_demo.cpp")
+    if not os.path.exists(EXE) or os.path.getmtime(EXE) < max(os.path.getmtime(src), os.path.getmtime(os.path.join(ROOT, "include", "Sai2PrimitivesBatched.h"))):
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), src, "-o", EXE,
+                               "-L", PKG, "-losc_b200", "-Wl,-rpath," + PKG])
+    return EXE
+
+
+def _inputs(tmp_path, chain, B, seed):
+    rng = np.random.default_rng(seed)
+    n = chain["n"]
+    import workloads
+    w = workloads.config2(chain, B, seed)
+    (tmp_path / "chain.bin").write_bytes(bytes(abi.chain_desc(chain)))
+    with open(tmp_path / "in.bin", "wb") as f:
+        for a in (w["q"], w["dq"], w["goal_pos"], w["goal_ori"], w["jt_goal"]):
+            f.write(np.ascontiguousarray(a, np.float64).tobytes())
+    return w
+
+
+def test_facade_compiles_and_refuses_cpu(tmp_path):
+    import osc_b200
+    osc_b200.lib()
+    exe = _build()
+    if osc_b200.lib().osc_device_count() > 0:
+        pytest.skip("a CUDA device is present: covered by the gpu test")
+    chain = load_chain("panda")
+    _inputs(tmp_path, chain, 8, 1)
+    r = subprocess.run([exe, str(tmp_path / "chain.bin"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "8", "1", "0"],
+                       capture_output=True, text=True)
+    assert r.returncode == 10, (r.returncode, r.stderr)
+    assert "no CUDA device" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_facade_matches_oracle(tmp_path, oracle_built, mode):
+    orc = oracle_built
+    exe = _build()
+    chain = load_chain("panda")
+    B, ticks = 256, 3
+    w = _inputs(tmp_path, chain, B, 40 + mode)
+    r = subprocess.run([exe, str(tmp_path / "chain.bin"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), str(B), str(ticks), str(mode)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stderr)
+    out = np.fromfile(tmp_path / "out.bin", dtype=np.float64)
+    tau, x = out[:B * 7].reshape(B, 7), out[B * 7:].reshape(B, 3)
+    o = orc.OracleBatch(chain, B, q0=q0_of(chain))
+    o.set(abi.F_Q, w["q"]); o.set(abi.F_DQ, w["dq"]); o.update_model()
+    t0 = o.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = o.add_joint_task(abi.joint_task_desc(7))
+    p = o.mft_params(t0)
+    for a in range(3):
+        p.kp_pos[a], p.kv_pos[a], p.kp_ori[a], p.kv_ori[a] = 120.0, 22.0, 210.0, 29.0
+    o.set_mft_params(t0, p)
+    jp = o.joint_task_params(t1)
+    for a in range(7):
+        jp.kp[a], jp.kv[a] = 55.0, 15.0
+    o.set_joint_task_params(t1, jp)
+    o.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); o.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
+    o.set(abi.F_GOAL_LINEAR_VELOCITY, np.array([0.01, -0.02, 0.03]), t0); o.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
+    for _ in range(ticks):
+        ref = o.tick(mode != 2)
+    assert rel_err(tau, ref)[0] <= FP64_TOL
+    assert rel_err(x, o.get(abi.F_CURRENT_POSITION, t0))[0] <= FP64_TOL
