@@ -1,0 +1,431 @@
+// osc_fused2.cuh -- second generation of the single-launch tick (see osc_fused.cuh for the algebra and the contract).
+//
+// Same mathematics as k_tick_fused, re-engineered around what ncu showed on B200 (profiles/README.md, r1b/r1c):
+// the first version was a 124 KB straight-line kernel with 1.7-2.2 KB of local-memory spills per thread; at 16 warps/SM
+// the spills miss L1 (36 % hit rate) and the warps sit on the long scoreboard, at 8 warps/SM on instruction fetch.
+//   * no local memory: a 57-slot per-thread stash in SHARED memory (slot-major, conflict free) holds, in turn,
+//     sin/cos -> F*, F_f | M -> L, 1/L_ii | chol(J M^-1 J^T); registers hold J (overwritten in place by Y = L^-1 J^T);
+//   * the mass matrix comes from a ROLLED body-frame composite-rigid-body recursion (needs only sin/cos, 250 instructions
+//     instead of 2,500); forward kinematics is unrolled but calls one out-of-line sincos;
+//   * bounded inertia estimates without a second factorisation: when only the last diagonal entry of M is clamped (always
+//     for the Panda: M_77 = 0.08 < 0.1) L_BIE differs from L in its last pivot only, so A_BIE = A - beta y y^T and
+//     A_BIE^-1 F* follows from Sherman-Morrison; any other clamp pattern takes the API-faithful route;
+//   * the branch certificate runs in FP32 on the FP32 pipe (it is a bound with a 2 % margin, not a result);
+//   * M^-1 tau_1 = L^-T (Y f): the Jacobian is not needed after Y is formed (tau_1 = L (Y f)).
+#pragma once
+#include "osc_fused.cuh"
+
+namespace osc {
+
+template <int N> struct F2 {
+	static constexpr int SC = 0;                          // sin/cos (2N), later F* (6) and F_f (6)
+	static constexpr int MM = 2 * N;                      // M lower triangle (N(N+1)/2), later L strictly lower + 1/L_ii
+	static constexpr int LL = MM;                         // L[i][j], j < i at LL + i(i-1)/2 + j
+	static constexpr int LI = MM + N * (N - 1) / 2;       // 1 / L_ii
+	static constexpr int CC = MM + N * (N + 1) / 2;       // chol(A) strictly lower (15)
+	static constexpr int SLOTS = CC + 15;
+};
+
+template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c) { Num<T>::sincos_(x, s, c); }
+
+template <class T, int N, int MINB>
+__global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+																		 const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
+																		 int64_t B, int64_t stride, int stacked, int gravity, int exports,
+																		 int* __restrict__ fb_count, int* __restrict__ fb_list) {
+	static_assert(N == 6 || N == 7, "the fused tick covers n - 6 <= 1");
+	using ML = MftL<N>;
+	using JL = JtL<N>;
+	using F = F2<N>;
+	__shared__ T sm[F::SLOTS * OSC_FUSED_THREADS];
+#define SM(slot) sm[(slot) * OSC_FUSED_THREADS + threadIdx.x]
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
+	const Row<int32_t> mI{tk0.I, stride, r};
+	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
+	int status = 0;
+
+	// ---- P1: sin/cos of every joint (one out-of-line sincos) ----
+	_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
+		T s, c;
+		sincos_outlined<T>(rP(RobotL<N>::Q + i), &s, &c);
+		SM(F::SC + 2 * i) = s;
+		SM(F::SC + 2 * i + 1) = c;
+	}
+
+	// ---- P2: mass matrix, composite rigid body recursion in BODY frames, tip to base (Sai2Model::updateModel) ----
+	// composite of bodies >= i in frame i: mass cm, first moment h, inertia about the frame origin I (xx xy xz yy yz zz).
+	// column i: momentum (p, l) of the composite under the unit joint twist (omega = z, v = 0), carried down the chain;
+	// M[i][j] = z . l in frame j.  Frame change child -> parent: x_parent = xyz + rot * Rz(q) * x_child.
+	{
+		T cm = T(0), h0 = T(0), h1 = T(0), h2 = T(0), Ixx = T(0), Ixy = T(0), Ixz = T(0), Iyy = T(0), Iyz = T(0), Izz = T(0);
+		_Pragma("unroll 1") for (int i = N - 1; i >= 0; --i) {
+			cm += ch.mass[i];
+			h0 += ch.hb[i][0]; h1 += ch.hb[i][1]; h2 += ch.hb[i][2];
+			Ixx += ch.Ib[i][0]; Ixy += ch.Ib[i][1]; Ixz += ch.Ib[i][2]; Iyy += ch.Ib[i][3]; Iyz += ch.Ib[i][4]; Izz += ch.Ib[i][5];
+			T p0 = -h1, p1 = h0, p2 = T(0), l0 = Ixz, l1 = Iyz, l2 = Izz;
+			const int row = F::MM + i * (i + 1) / 2;
+			SM(row + i) = l2;
+			_Pragma("unroll 1") for (int j = i; j >= 1; --j) {
+				const T s = SM(F::SC + 2 * j), c = SM(F::SC + 2 * j + 1);
+				const T a0 = c * p0 - s * p1, a1 = s * p0 + c * p1, b0 = c * l0 - s * l1, b1 = s * l0 + c * l1;
+				p0 = ch.rot[j][0][0] * a0 + ch.rot[j][0][1] * a1 + ch.rot[j][0][2] * p2;
+				p1 = ch.rot[j][1][0] * a0 + ch.rot[j][1][1] * a1 + ch.rot[j][1][2] * p2;
+				p2 = ch.rot[j][2][0] * a0 + ch.rot[j][2][1] * a1 + ch.rot[j][2][2] * p2;
+				const T m0 = ch.rot[j][0][0] * b0 + ch.rot[j][0][1] * b1 + ch.rot[j][0][2] * l2;
+				const T m1 = ch.rot[j][1][0] * b0 + ch.rot[j][1][1] * b1 + ch.rot[j][1][2] * l2;
+				const T m2 = ch.rot[j][2][0] * b0 + ch.rot[j][2][1] * b1 + ch.rot[j][2][2] * l2;
+				l0 = m0 + ch.xyz[j][1] * p2 - ch.xyz[j][2] * p1;
+				l1 = m1 + ch.xyz[j][2] * p0 - ch.xyz[j][0] * p2;
+				l2 = m2 + ch.xyz[j][0] * p1 - ch.xyz[j][1] * p0;
+				SM(row + j - 1) = l2;
+			}
+			if (i > 0) {  // express the composite in the parent frame
+				const T s = SM(F::SC + 2 * i), c = SM(F::SC + 2 * i + 1);
+				T E[3][3];
+				OSC_UNROLL for (int a = 0; a < 3; ++a) {
+					E[a][0] = ch.rot[i][a][0] * c + ch.rot[i][a][1] * s;
+					E[a][1] = ch.rot[i][a][1] * c - ch.rot[i][a][0] * s;
+					E[a][2] = ch.rot[i][a][2];
+				}
+				const T I3[3][3] = {{Ixx, Ixy, Ixz}, {Ixy, Iyy, Iyz}, {Ixz, Iyz, Izz}};
+				T EI[3][3];
+				mm3(E, I3, EI);
+				const T g0 = E[0][0] * h0 + E[0][1] * h1 + E[0][2] * h2, g1 = E[1][0] * h0 + E[1][1] * h1 + E[1][2] * h2,
+						g2 = E[2][0] * h0 + E[2][1] * h1 + E[2][2] * h2;
+				const T r0 = ch.xyz[i][0], r1 = ch.xyz[i][1], r2 = ch.xyz[i][2];
+				const T iso = cm * (r0 * r0 + r1 * r1 + r2 * r2) + T(2) * (r0 * g0 + r1 * g1 + r2 * g2);
+				Ixx = EI[0][0] * E[0][0] + EI[0][1] * E[0][1] + EI[0][2] * E[0][2] + iso - cm * r0 * r0 - T(2) * r0 * g0;
+				Iyy = EI[1][0] * E[1][0] + EI[1][1] * E[1][1] + EI[1][2] * E[1][2] + iso - cm * r1 * r1 - T(2) * r1 * g1;
+				Izz = EI[2][0] * E[2][0] + EI[2][1] * E[2][1] + EI[2][2] * E[2][2] + iso - cm * r2 * r2 - T(2) * r2 * g2;
+				Ixy = EI[0][0] * E[1][0] + EI[0][1] * E[1][1] + EI[0][2] * E[1][2] - cm * r0 * r1 - r0 * g1 - g0 * r1;
+				Ixz = EI[0][0] * E[2][0] + EI[0][1] * E[2][1] + EI[0][2] * E[2][2] - cm * r0 * r2 - r0 * g2 - g0 * r2;
+				Iyz = EI[1][0] * E[2][0] + EI[1][1] * E[2][1] + EI[1][2] * E[2][2] - cm * r1 * r2 - r1 * g2 - g1 * r2;
+				h0 = g0 + cm * r0; h1 = g1 + cm * r1; h2 = g2 + cm * r2;
+			}
+		}
+	}
+
+	// ---- P3: M = L L^T in registers, then parked in the stash; bounded-inertia clamp pattern ----
+	T rho2 = T(1), beta = T(0);  // BIE: L_BIE = L except its last pivot; rho = L_nn / L_BIE,nn, beta = 1 - rho^2
+	{
+		T Mx[N][N];
+		OSC_UNROLL for (int i = 0; i < N; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) Mx[i][j] = SM(F::MM + i * (i + 1) / 2 + j);
+		T delta = T(0);
+		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+			const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
+			bool other = false;
+			OSC_UNROLL for (int i = 0; i < N - 1; ++i) other = other || (Mx[i][i] < thr);
+			if (other) {  // a clamp that is not confined to the last joint: API-faithful route (nothing was written yet)
+				fb_list[atomicAdd(fb_count, 1)] = (int)r;
+				return;
+			}
+			if (Mx[N - 1][N - 1] < thr) delta = thr - Mx[N - 1][N - 1];
+		}
+		Chol<T, N> cm;
+		if (!chol_factor<T, N>(Mx, cm)) status |= 16;
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::LL + i * (i - 1) / 2 + j) = cm.L[i][j];
+			SM(F::LI + i) = cm.Li[i];
+		}
+		if (delta > T(0)) {
+			const T d = cm.Ld[N - 1] * cm.Ld[N - 1];
+			rho2 = d / (d + delta);
+			beta = T(1) - rho2;
+		}
+	}
+
+	// ---- P4: forward kinematics (revolute chain, control link on the last body) and the Jacobian at the compliant frame ----
+	T J[6][N], x[3], Rc[3][3];
+	{
+		T Rp[3][3], pp[3], Jz[N][3], Jo[N][3];
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			pp[a] = ch.world_xyz[a];
+			OSC_UNROLL for (int b = 0; b < 3; ++b) Rp[a][b] = ch.world_rot[a][b];
+		}
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T pre[3][3], d[3];
+			mm3(Rp, ch.rot[i], pre);
+			mv3(Rp, ch.xyz[i], d);
+			const T s = SM(F::SC + 2 * i), c = SM(F::SC + 2 * i + 1);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) {
+				pp[a] += d[a];
+				Rp[a][0] = c * pre[a][0] + s * pre[a][1];
+				Rp[a][1] = c * pre[a][1] - s * pre[a][0];
+				Rp[a][2] = pre[a][2];
+				Jz[i][a] = pre[a][2];
+				Jo[i][a] = pp[a];
+			}
+		}
+		T d[3];
+		mv3(Rp, tc.p_c, d);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) x[a] = pp[a] + d[a];
+		mm3(Rp, tc.R_c, Rc);
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			const T e[3] = {x[0] - Jo[i][0], x[1] - Jo[i][1], x[2] - Jo[i][2]};
+			T l[3];
+			cross3(Jz[i], e, l);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) { J[a][i] = l[a]; J[3 + a][i] = Jz[i][a]; }
+		}
+	}
+
+	// ---- P5: branch certificate in FP32 (a bound with a 2 % margin; see osc_fused.cuh) ----
+	{
+		float G[6][6];
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				float s = 0.f;
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = fmaf((float)J[i][k], (float)J[j][k], s);
+				G[i][j] = s; G[j][i] = s;
+			}
+		float f4 = 0.f;  // tr(G^4) = |G^2|_F^2
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				float s = 0.f;
+				OSC_UNROLL for (int k = 0; k < 6; ++k) s = fmaf(G[i][k], G[k][j], s);
+				f4 = fmaf(i == j ? s : 2.f * s, s, f4);
+			}
+		const float lmax_hi = sqrtf(sqrtf(f4)) * 1.001f;  // lambda_max <= lmax_hi <= 6^(1/4) lambda_max
+		const float tol = (float)tc.s_abs_tol, smax = (float)tc.s_max;
+		const bool s0_ok = lmax_hi * 0.6389431f > tol * tol * 1.02f;
+		const bool sep_ok = spd_above<float, 6>(G, smax * smax * lmax_hi * 1.02f);
+		if (!(s0_ok && sep_ok)) {  // not provably non-singular: API-faithful route (nothing was written yet)
+			fb_list[atomicAdd(fb_count, 1)] = (int)r;
+			return;
+		}
+	}
+
+	// ---- P6: control law (MotionForceTask.cpp:278-509) -> F*, F_f, parked in the sin/cos slots ----
+	{
+		T dq[N];
+		ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
+		T Fstar[6], Ff[6];
+		mft_control_law<T, N>(tc, mP, mS, mI, stride, r, J, dq, x, Rc, Fstar, Ff, status, ex);
+		OSC_UNROLL for (int i = 0; i < 6; ++i) { SM(F::SC + i) = Fstar[i]; SM(F::SC + 6 + i) = Ff[i]; }
+	}
+
+	// ---- P7: Y = L^-1 J^T in place (J[c][:] <- L^-1 J[c][:]), L streamed row by row from the stash ----
+	OSC_UNROLL for (int k = 0; k < N; ++k) {
+		T Lk[N];
+		OSC_UNROLL for (int m = 0; m < k; ++m) Lk[m] = SM(F::LL + k * (k - 1) / 2 + m);
+		const T li = SM(F::LI + k);
+		OSC_UNROLL for (int c = 0; c < 6; ++c) {
+			T s = J[c][k];
+			OSC_UNROLL for (int m = 0; m < k; ++m) s = Num<T>::fma_(-Lk[m], J[c][m], s);
+			J[c][k] = s * li;
+		}
+	}
+	T (&Y)[6][N] = J;
+
+	// ---- P8: A = J M^-1 J^T = Y Y^T, C = chol(A): strictly lower part to the stash, 1/C_ii in registers ----
+	T cli[6];
+	{
+		T A[6][6];
+		OSC_UNROLL for (int i = 0; i < 6; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(Y[i][k], Y[j][k], s);
+				A[i][j] = s;
+			}
+		Chol<T, 6> ca;
+		if (!chol_factor<T, 6>(A, ca)) status |= 16;
+		OSC_UNROLL for (int i = 0; i < 6; ++i) {
+			cli[i] = ca.Li[i];
+			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::CC + i * (i - 1) / 2 + j) = ca.L[i][j];
+		}
+	}
+#define OSC_CFWD(t)                                                                                     \
+	OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) {                                                         \
+		T s_ = t[i_];                                                                                   \
+		OSC_UNROLL for (int m_ = 0; m_ < i_; ++m_) s_ = Num<T>::fma_(-SM(F::CC + i_ * (i_ - 1) / 2 + m_), t[m_], s_); \
+		t[i_] = s_ * cli[i_];                                                                           \
+	}
+#define OSC_CBWD(t)                                                                                     \
+	OSC_UNROLL for (int i_ = 5; i_ >= 0; --i_) {                                                        \
+		T s_ = t[i_];                                                                                   \
+		OSC_UNROLL for (int m_ = i_ + 1; m_ < 6; ++m_) s_ = Num<T>::fma_(-SM(F::CC + m_ * (m_ - 1) / 2 + i_), t[m_], s_); \
+		t[i_] = s_ * cli[i_];                                                                           \
+	}
+
+	// ---- P9: u = unit vector orthogonal to range(Y^T) (n = 7): N_1 = (L^-T u)(L u)^T ----
+	T u[N], t_last[6];  // t_last = C^-1 y_last (y_k = column k of Y), for the BIE correction
+	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
+	{
+		T best = T(-1);
+		int kb = 0;
+		OSC_UNROLL for (int k = (N == 7 ? 0 : N - 1); k < N; ++k) {  // residual of e_k: P_kk = 1 - |C^-1 y_k|^2
+			T t[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) t[c] = Y[c][k];
+			OSC_CFWD(t)
+			T s = T(1);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-t[c], t[c], s);
+			if (s > best) { best = s; kb = k; }
+			if (k == N - 1) {
+				OSC_UNROLL for (int c = 0; c < 6; ++c) t_last[c] = t[c];
+			}
+		}
+		if constexpr (N == 7) {
+			T a[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) {
+				T s = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? Y[c][k] : s;
+				a[c] = s;
+			}
+			OSC_CFWD(a)
+			OSC_CBWD(a)
+			OSC_UNROLL for (int i = 0; i < N; ++i) {
+				T s = (i == kb) ? T(1) : T(0);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+				u[i] = s;
+			}
+			// second projection ("twice is enough")
+			OSC_UNROLL for (int c = 0; c < 6; ++c) {
+				T s = T(0);
+				OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(Y[c][i], u[i], s);
+				a[c] = s;
+			}
+			OSC_CFWD(a)
+			OSC_CBWD(a)
+			T nu = T(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) {
+				T s = u[i];
+				OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+				u[i] = s;
+				nu = Num<T>::fma_(s, s, nu);
+			}
+			const T inv = Num<T>::rsqrt_(nu);
+			OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
+		}
+	}
+
+	// ---- P10: f = Lambda_mod F* + F_f (SingularityHandler.cpp:160-225, 307-309); h = Y^T f; tau_1 = J^T f = L h ----
+	T h[N];
+	{
+		T f[6];
+		OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = SM(F::SC + c);
+		if (tc.decoupling != OSC_IMPEDANCE) {
+			OSC_CFWD(f)
+			OSC_CBWD(f)
+			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
+				// A_BIE = A - beta y y^T (y = last column of Y):  A_BIE^-1 F = A^-1 F + beta z (z . F) / (1 - beta y . z),  z = A^-1 y
+				T yz = T(0), zF = T(0);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) yz = Num<T>::fma_(t_last[c], t_last[c], yz);
+				OSC_CBWD(t_last)  // z
+				OSC_UNROLL for (int c = 0; c < 6; ++c) zF = Num<T>::fma_(t_last[c], SM(F::SC + c), zF);
+				const T coef = beta * zF / (T(1) - beta * yz);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = Num<T>::fma_(coef, t_last[c], f[c]);
+			}
+		}
+		OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] += SM(F::SC + 6 + c);
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T s = T(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(Y[c][i], f[c], s);
+			h[i] = s;
+		}
+	}
+	// Y (= J) is dead from here on.
+
+	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
+	{
+		const int ntypes = mI(ML::NTYPES);
+		bool latch = ntypes == 0;
+		if (ntypes != 0 || mI(ML::HIST_LEN) != 0) {
+			latch = latch || mI(ML::C2) > mI(ML::C1);
+			mI(ML::NTYPES) = 0; mI(ML::TYPES) = 0; mI(ML::C1) = 0; mI(ML::C2) = 0; mI(ML::HIST_LEN) = 0; mI(ML::HIST_HEAD) = 0;
+		}
+		if (ex && latch) {
+			OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = rP(RobotL<N>::Q + i);
+		}
+	}
+
+	// ---- P11: tau_1 = L h, w = L u;  v = L^-T u, M^-1 tau_1 = L^-T h  (two sweeps over L, shared by both vectors) ----
+	T tau1[N], w[N], v[N], mt[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		const T ld = T(1) / SM(F::LI + i);
+		T s1 = ld * h[i], sw = ld * u[i];
+		OSC_UNROLL for (int m = 0; m < i; ++m) {
+			const T l = SM(F::LL + i * (i - 1) / 2 + m);
+			s1 = Num<T>::fma_(l, h[m], s1);
+			sw = Num<T>::fma_(l, u[m], sw);
+		}
+		tau1[i] = s1; w[i] = sw;
+	}
+	T tau2[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) tau2[i] = T(0);
+	if constexpr (N == 7) {
+		OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
+			T sv = u[i], st = h[i];
+			OSC_UNROLL for (int k = i + 1; k < N; ++k) {
+				const T l = SM(F::LL + k * (k - 1) / 2 + i);
+				sv = Num<T>::fma_(-l, v[k], sv);
+				st = Num<T>::fma_(-l, mt[k], st);
+			}
+			const T li = SM(F::LI + i);
+			v[i] = sv * li; mt[i] = st * li;
+		}
+		// JointTask in the nullspace (JointTask.cpp:218-356): R = v / |v|, Lambda = 1 / |v|^2, tau_2 = w [Lambda (v.a - v.M^-1 tau_1) + Lambda_mod v.u_pd]
+		T nv2 = T(0), vc = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) { nv2 = Num<T>::fma_(v[i], v[i], nv2); vc = Num<T>::fma_(v[i], mt[i], vc); }
+		const T lam = T(1) / nv2;
+		T lam_mod = lam;  // JointTask.cpp:253-267
+		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u[N - 1] * u[N - 1]));  // |L_BIE^-1 L u|^2
+		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = T(1);
+		T q[N], dq[N], upd[N], acc[N];
+		ld_vec<T, N>(rP, RobotL<N>::Q, q);
+		ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
+		jt_pd_law<T, N>(jc, jP, jS, q, dq, upd, acc, ex);
+		T va = T(0), vu = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<T>::fma_(v[i], acc[i], va); vu = Num<T>::fma_(v[i], upd[i], vu); }
+		const T sc = lam * (va - (stacked ? vc : T(0))) + lam_mod * vu;
+		OSC_UNROLL for (int i = 0; i < N; ++i) tau2[i] = w[i] * sc;
+		if (ex) {
+			st_vec<T, N>(jS, JL::CUR_POS, q);
+			st_vec<T, N>(jS, JL::CUR_VEL, dq);
+		}
+	} else if (ex) {
+		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); }
+	}
+	if (ex) {
+		tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;
+		st_vec<T, N>(jS, JL::TASK_TAU, tau2);
+		st_vec<T, N>(mS, ML::TASK_TAU, tau1);
+		mS(ML::ALPHA) = T(1);
+		mI(ML::INS) = 6;
+	}
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		T t = tau1[i] + tau2[i];
+		if (gravity) t += rS(RobotL<N>::GRAV + i);  // written by k_gravity ahead of this kernel
+		rS(RobotL<N>::TAU + i) = t;
+	}
+	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+#undef OSC_CFWD
+#undef OSC_CBWD
+#undef SM
+}
+
+// jointGravityVector for the fused tick when gravity compensation is on (default off, RobotController.cpp:10): a small
+// separate launch ahead of k_tick_fused2 keeps the gravity recursion out of the hot kernel's register budget.
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_gravity(const __grid_constant__ ChainC<T, N> ch, Arena<T> rob, int64_t B, int64_t stride) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T> P{rob.P, stride, r}, S{rob.S, stride, r};
+	T q[N], g[N];
+	ld_vec<T, N>(P, RobotL<N>::Q, q);
+	Kin<T, N> kin;
+	forward_kinematics<T, N>(ch, q, kin);
+	gravity_vector<T, N>(ch, kin, g);
+	st_vec<T, N>(S, RobotL<N>::GRAV, g);
+}
+
+// what the second-generation kernel adds to fused_tick_supported: a revolute chain with the control link on the last body
+inline bool fused2_supported(Batch& b) {
+	if (b.tasks.empty() || b.tasks[0].md.body != b.n - 1) return false;
+	for (int i = 0; i < b.n; ++i)
+		if (b.chain.joint_type[i] != OSC_JOINT_REVOLUTE) return false;
+	return true;
+}
+
+}  // namespace osc

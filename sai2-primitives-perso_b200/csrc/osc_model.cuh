@@ -17,6 +17,8 @@ template <class T, int N> struct ChainC {
 	T mass[N];
 	T com[N][3];
 	T inertia[N][6];  // xx xy xz yy yz zz about the com, body frame
+	T hb[N][3];       // first moment m * com about the body (= joint) origin, body frame
+	T Ib[N][6];       // inertia about the body origin, body frame: inertia + m (|c|^2 1 - c c^T)   (body-frame CRBA of osc_fused2.cuh)
 	T q_lower[N], q_upper[N], effort[N];
 	T world_rot[3][3], world_xyz[3], gravity[3];
 };

@@ -146,12 +146,24 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 		const dim3 g((unsigned)((b.B + OSC_FUSED_THREADS - 1) / OSC_FUSED_THREADS));
 		const MftC<T> tc = mftc(m);
 		const JtC<T, N> jc = jtc(b, j);
-		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : 8; }();  // 8 blocks of 64 = 128 registers: 65,536 robots are ONE wave on 148 SMs (profiles/README.md)
-#define OSC_LAUNCH_FUSED(MB) k_tick_fused<T, N, MB><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list)
-		if (minb >= 8) OSC_LAUNCH_FUSED(8);
-		else if (minb >= 6) OSC_LAUNCH_FUSED(6);
-		else OSC_LAUNCH_FUSED(4);
-#undef OSC_LAUNCH_FUSED
+		// OSC_FUSED_V=1 selects the first-generation kernel (osc_fused.cuh), OSC_FUSED_MINB its occupancy variant: experiment knobs
+		static const int ver = [] { const char* e = getenv("OSC_FUSED_V"); return e ? atoi(e) : 2; }();
+		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : (ver == 2 ? 7 : 8); }();
+#define OSC_FUSED_ARGS ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list
+		if (ver == 2 && fused2_supported(b)) {
+			if (b.gravity) {
+				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
+				if (int rc = done(b, "k_gravity")) return rc;
+			}
+			if (minb >= 8) k_tick_fused2<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else if (minb >= 7) k_tick_fused2<T, N, 7><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else k_tick_fused2<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+		} else {
+			if (minb >= 8) k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else if (minb >= 6) k_tick_fused<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else k_tick_fused<T, N, 4><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+		}
+#undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
 		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list);

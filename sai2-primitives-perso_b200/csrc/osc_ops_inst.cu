@@ -5,7 +5,7 @@
 #include <algorithm>
 
 #include "osc_aux_kernels.cuh"
-#include "osc_fused.cuh"
+#include "osc_fused2.cuh"
 #include "osc_host.h"
 
 #ifndef OSC_T
@@ -54,6 +54,13 @@ template <class T, int N> struct OpsImpl : Ops {
 			ch.inertia[i][0] = (T)I[0]; ch.inertia[i][1] = (T)I[1]; ch.inertia[i][2] = (T)I[2];
 			ch.inertia[i][3] = (T)I[4]; ch.inertia[i][4] = (T)I[5]; ch.inertia[i][5] = (T)I[8];
 			ch.q_lower[i] = (T)c.q_lower[i]; ch.q_upper[i] = (T)c.q_upper[i]; ch.effort[i] = (T)c.effort[i];
+			const double m = c.mass[i], *cm = c.com[i];
+			const double cc = cm[0] * cm[0] + cm[1] * cm[1] + cm[2] * cm[2];
+			int e = 0;
+			for (int a = 0; a < 3; ++a) {
+				ch.hb[i][a] = (T)(m * cm[a]);
+				for (int k = a; k < 3; ++k) ch.Ib[i][e++] = (T)(I[3 * a + k] + m * ((a == k ? cc : 0.0) - cm[a] * cm[k]));
+			}
 		}
 		for (int a = 0; a < 3; ++a) {
 			ch.world_xyz[a] = (T)c.world_xyz[a]; ch.gravity[a] = (T)c.gravity[a];

@@ -124,16 +124,25 @@ def test_fused_force_axis_closed_loop(oracle_built):
     p.compare(FP64_TOL)
 
 
-def test_fused_puma_six_dof(oracle_built):
-    """n = 6: the joint task has an empty range below a 6-DoF task (JointTask.cpp:234-239)"""
+@pytest.mark.parametrize("decoupling", [abi.FULL_DYNAMIC_DECOUPLING, abi.BOUNDED_INERTIA_ESTIMATES])
+def test_fused_puma_six_dof(oracle_built, decoupling):
+    """n = 6: the joint task has an empty range below a 6-DoF task (JointTask.cpp:234-239).  With bounded inertia estimates
+    the PUMA clamps its three wrist joints: k_tick_fused2 serves only the last-joint clamp pattern, so every robot takes
+    the API-faithful route; with full decoupling the certified ones stay in the fused kernel."""
     chain = load_chain("puma560_synthetic")
     p, q, dq, rng = _two_task(chain, 512, 31, p_c=(0, 0, 0))
+    p.set_mft_params(0, dynamic_decoupling_type=decoupling)
+    p.set_jt_params(1, dynamic_decoupling_type=decoupling)
     assert p.gpu.tick_is_fused()
     for _ in range(2):
         tg, tr = p.both("tick", True)
         assert _tau_err(tg, tr) <= FP64_TOL
     blend = int((p.ref.get(abi.F_ALPHA, 0)[:, 0] < 1).sum())
-    assert blend <= p.gpu.tick_fallback_count() <= blend + 512 // 20
+    fb = p.gpu.tick_fallback_count()
+    if decoupling == abi.FULL_DYNAMIC_DECOUPLING:
+        assert blend <= fb <= blend + 512 // 20
+    else:
+        assert blend <= fb <= 512
     # nullspace projectors of blend-branch robots: N = I - Jbar J cancels to O(eps |Jbar| |J|); |Jbar| reaches 1e7 for the
     # near-singular PUMA draws, so their absolute accuracy is 1e-8, not 1e-9 (same for the oracle vs LAPACK)
     nfields = {abi.F_N_TOTAL: 1e-6, abi.F_N_TASK: 1e-6, abi.F_N_TASK_AND_PREC: 1e-6, abi.F_N_PREC: 1e-6}
