@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __
 template <class T, int N>
 __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1, int64_t stride,
-															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list) {
+															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law) {
 	const int n = *fb_count;
 	if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count_next = 0;
 	for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 		model_robot<T, N>(ch, rob, stride, r, 1, gravity);
 		mft_update_robot<T, N>(ch, tc, rob, tk0, nullptr, stride, r, 0);
 		jt_update_robot<T, N>(jc, rob, tk1, tk0.S + (int64_t)MftL<N>::NTP * stride, stride, r);
-		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1);
+		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1, reuse_law);
 		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2);
 		if (gravity) {
 			const Row<T> rS{rob.S, stride, r};

@@ -28,8 +28,8 @@ template <int N> struct F2 {
 
 template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c) { Num<T>::sincos_(x, s, c); }
 
-template <class T, int N, int MINB>
-__global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+template <class T, int N, int MAXREG>
+__global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 																		 const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
 																		 int64_t B, int64_t stride, int stacked, int gravity, int exports,
 																		 int* __restrict__ fb_count, int* __restrict__ fb_list) {
@@ -49,11 +49,58 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 	// ---- P1: sin/cos of every joint (one out-of-line sincos) ----
 	_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
 		T s, c;
-		sincos_outlined<T>(rP(RobotL<N>::Q + i), &s, &c);
+		Num<T>::sincos_(rP(RobotL<N>::Q + i), &s, &c);
 		SM(F::SC + 2 * i) = s;
 		SM(F::SC + 2 * i + 1) = c;
 	}
 
+	OSC_FENCE();
+	// ---- P1b: a ROLLED forward-kinematics pass for what the control law needs: x, R of the compliant frame and its twist
+	// v = w x x - sum_i dq_i (z_i x o_i), w = sum_i dq_i z_i (= J dq, MotionForceTask.cpp:293-298) -- then the control law itself
+	// (MotionForceTask.cpp:278-509) while nothing else is live.  F*, F_f are parked in the C slots until sin/cos are dead.
+	// The control law runs BEFORE the branch certificate: a robot that later falls back hands F*, F_f to k_tick_tail
+	// (ML::UMF, ML::FFB) instead of running the law a second time.
+	{
+		T Rp[3][3], pp[3], w[3] = {T(0), T(0), T(0)}, mo[3] = {T(0), T(0), T(0)};
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			pp[a] = ch.world_xyz[a];
+			OSC_UNROLL for (int b = 0; b < 3; ++b) Rp[a][b] = ch.world_rot[a][b];
+		}
+		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
+			T pre[3][3], d[3];
+			mm3(Rp, ch.rot[i], pre);
+			mv3(Rp, ch.xyz[i], d);
+			const T s = SM(F::SC + 2 * i), c = SM(F::SC + 2 * i + 1), dqi = rP(RobotL<N>::DQ + i);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) {
+				pp[a] += d[a];
+				Rp[a][0] = c * pre[a][0] + s * pre[a][1];
+				Rp[a][1] = c * pre[a][1] - s * pre[a][0];
+				Rp[a][2] = pre[a][2];
+			}
+			const T z[3] = {pre[0][2], pre[1][2], pre[2][2]};
+			T zxo[3];
+			cross3(z, pp, zxo);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) { w[a] = Num<T>::fma_(dqi, z[a], w[a]); mo[a] = Num<T>::fma_(dqi, zxo[a], mo[a]); }
+		}
+		T x[3], Rc[3][3], d[3], v[3];
+		mv3(Rp, tc.p_c, d);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) x[a] = pp[a] + d[a];
+		mm3(Rp, tc.R_c, Rc);
+		cross3(w, x, v);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) v[a] -= mo[a];
+		T Fstar[6], Ff[6];
+		mft_control_law_vw<T, N, true>(tc, mP, mS, mI, stride, r, v, w, x, Rc, Fstar, Ff, status, ex);
+		OSC_UNROLL for (int i = 0; i < 6; ++i) { SM(F::CC + i) = Fstar[i]; SM(F::CC + 6 + i) = Ff[i]; }
+	}
+#define OSC_FALL_BACK()                                                                      \
+	{                                                                                        \
+		OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) { mS(ML::UMF + i_) = SM(F::CC + i_); mS(ML::FFB + i_) = SM(F::CC + 6 + i_); } \
+		if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);       \
+		fb_list[atomicAdd(fb_count, 1)] = (int)r;                                            \
+		return;                                                                              \
+	}
+
+	OSC_FENCE();
 	// ---- P2: mass matrix, composite rigid body recursion in BODY frames, tip to base (Sai2Model::updateModel) ----
 	// composite of bodies >= i in frame i: mass cm, first moment h, inertia about the frame origin I (xx xy xz yy yz zz).
 	// column i: momentum (p, l) of the composite under the unit joint twist (omega = z, v = 0), carried down the chain;
@@ -107,10 +154,11 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		}
 	}
 
-	// ---- P3: M = L L^T in registers, then parked in the stash; bounded-inertia clamp pattern ----
+	OSC_FENCE();
+	// ---- P3: M = L L^T in place in registers, then parked in the stash; bounded-inertia clamp pattern ----
 	T rho2 = T(1), beta = T(0);  // BIE: L_BIE = L except its last pivot; rho = L_nn / L_BIE,nn, beta = 1 - rho^2
 	{
-		T Mx[N][N];
+		T Mx[N][N], li[N];
 		OSC_UNROLL for (int i = 0; i < N; ++i)
 			OSC_UNROLL for (int j = 0; j <= i; ++j) Mx[i][j] = SM(F::MM + i * (i + 1) / 2 + j);
 		T delta = T(0);
@@ -118,29 +166,26 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 			const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
 			OSC_UNROLL for (int i = 0; i < N - 1; ++i) other = other || (Mx[i][i] < thr);
-			if (other) {  // a clamp that is not confined to the last joint: API-faithful route (nothing was written yet)
-				fb_list[atomicAdd(fb_count, 1)] = (int)r;
-				return;
-			}
+			if (other) OSC_FALL_BACK()  // a clamp that is not confined to the last joint: API-faithful route
 			if (Mx[N - 1][N - 1] < thr) delta = thr - Mx[N - 1][N - 1];
 		}
-		Chol<T, N> cm;
-		if (!chol_factor<T, N>(Mx, cm)) status |= 16;
+		if (!chol_inplace<T, N>(Mx, li)) status |= 16;
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::LL + i * (i - 1) / 2 + j) = cm.L[i][j];
-			SM(F::LI + i) = cm.Li[i];
+			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::LL + i * (i - 1) / 2 + j) = Mx[i][j];
+			SM(F::LI + i) = li[i];
 		}
 		if (delta > T(0)) {
-			const T d = cm.Ld[N - 1] * cm.Ld[N - 1];
+			const T d = Mx[N - 1][N - 1] * Mx[N - 1][N - 1];
 			rho2 = d / (d + delta);
 			beta = T(1) - rho2;
 		}
 	}
 
+	OSC_FENCE();
 	// ---- P4: forward kinematics (revolute chain, control link on the last body) and the Jacobian at the compliant frame ----
-	T J[6][N], x[3], Rc[3][3];
+	T J[6][N];
 	{
-		T Rp[3][3], pp[3], Jz[N][3], Jo[N][3];
+		T Rp[3][3], pp[3], Jz[N][3], Jo[N][3], x[3];
 		OSC_UNROLL for (int a = 0; a < 3; ++a) {
 			pp[a] = ch.world_xyz[a];
 			OSC_UNROLL for (int b = 0; b < 3; ++b) Rp[a][b] = ch.world_rot[a][b];
@@ -162,7 +207,6 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		T d[3];
 		mv3(Rp, tc.p_c, d);
 		OSC_UNROLL for (int a = 0; a < 3; ++a) x[a] = pp[a] + d[a];
-		mm3(Rp, tc.R_c, Rc);
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			const T e[3] = {x[0] - Jo[i][0], x[1] - Jo[i][1], x[2] - Jo[i][2]};
 			T l[3];
@@ -171,6 +215,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		}
 	}
 
+	OSC_FENCE();
 	// ---- P5: branch certificate in FP32 (a bound with a 2 % margin; see osc_fused.cuh) ----
 	{
 		float G[6][6];
@@ -191,21 +236,12 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		const float tol = (float)tc.s_abs_tol, smax = (float)tc.s_max;
 		const bool s0_ok = lmax_hi * 0.6389431f > tol * tol * 1.02f;
 		const bool sep_ok = spd_above<float, 6>(G, smax * smax * lmax_hi * 1.02f);
-		if (!(s0_ok && sep_ok)) {  // not provably non-singular: API-faithful route (nothing was written yet)
-			fb_list[atomicAdd(fb_count, 1)] = (int)r;
-			return;
-		}
+		if (!(s0_ok && sep_ok)) OSC_FALL_BACK()  // not provably non-singular: API-faithful route
 	}
+	// sin/cos are dead: move F*, F_f into their slots (the C slots are needed by P8)
+	OSC_UNROLL for (int i = 0; i < 12; ++i) SM(F::SC + i) = SM(F::CC + i);
 
-	// ---- P6: control law (MotionForceTask.cpp:278-509) -> F*, F_f, parked in the sin/cos slots ----
-	{
-		T dq[N];
-		ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
-		T Fstar[6], Ff[6];
-		mft_control_law<T, N>(tc, mP, mS, mI, stride, r, J, dq, x, Rc, Fstar, Ff, status, ex);
-		OSC_UNROLL for (int i = 0; i < 6; ++i) { SM(F::SC + i) = Fstar[i]; SM(F::SC + 6 + i) = Ff[i]; }
-	}
-
+	OSC_FENCE();
 	// ---- P7: Y = L^-1 J^T in place (J[c][:] <- L^-1 J[c][:]), L streamed row by row from the stash ----
 	OSC_UNROLL for (int k = 0; k < N; ++k) {
 		T Lk[N];
@@ -219,6 +255,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 	}
 	T (&Y)[6][N] = J;
 
+	OSC_FENCE();
 	// ---- P8: A = J M^-1 J^T = Y Y^T, C = chol(A): strictly lower part to the stash, 1/C_ii in registers ----
 	T cli[6];
 	{
@@ -249,6 +286,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		t[i_] = s_ * cli[i_];                                                                           \
 	}
 
+	OSC_FENCE();
 	// ---- P9: u = unit vector orthogonal to range(Y^T) (n = 7): N_1 = (L^-T u)(L u)^T ----
 	T u[N], t_last[6];  // t_last = C^-1 y_last (y_k = column k of Y), for the BIE correction
 	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
@@ -300,6 +338,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		}
 	}
 
+	OSC_FENCE();
 	// ---- P10: f = Lambda_mod F* + F_f (SingularityHandler.cpp:160-225, 307-309); h = Y^T f; tau_1 = J^T f = L h ----
 	T h[N];
 	{
@@ -327,6 +366,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 	}
 	// Y (= J) is dead from here on.
 
+	OSC_FENCE();
 	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
 	{
 		const int ntypes = mI(ML::NTYPES);
@@ -340,6 +380,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		}
 	}
 
+	OSC_FENCE();
 	// ---- P11: tau_1 = L h, w = L u;  v = L^-T u, M^-1 tau_1 = L^-T h  (two sweeps over L, shared by both vectors) ----
 	T tau1[N], w[N], v[N], mt[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
@@ -400,6 +441,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused2(const _
 		rS(RobotL<N>::TAU + i) = t;
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+#undef OSC_FALL_BACK
 #undef OSC_CFWD
 #undef OSC_CBWD
 #undef SM

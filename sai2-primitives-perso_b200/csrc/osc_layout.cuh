@@ -37,7 +37,8 @@ template <int N> struct MftL {
 						 U_NS = NTP + N * N, J_NS = U_NS + 6 * K, L_NS = J_NS + K * N, L_NS_MOD = L_NS + K * K,
 						 U_S = L_NS_MOD + K * K, V_S = U_S + 6 * K, J_S = V_S + N * K, L_S_MOD = J_S + K * N,
 						 J_POST = L_S_MOD + K * K, L_JS_MOD = J_POST + K * N, ALPHA = L_JS_MOD + K * K, SV = ALPHA + 1,
-						 S_SIZE = SV + K;
+						 FFB = SV + K,  // F_f of the control law, handed from k_tick_fused2 to k_tick_tail for robots that fall back
+						 S_SIZE = FFB + 6;
 };
 
 template <int N> struct JtL {

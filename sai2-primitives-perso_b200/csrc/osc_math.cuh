@@ -199,6 +199,24 @@ template <class T, int N> OSC_DEV bool chol_factor(const T (&A)[N][N], Chol<T, N
 	}
 	return ok;
 }
+// In-place Cholesky of the lower triangle of A: on exit A[i][j] (j < i) = L[i][j], li[i] = 1 / L_ii, A[i][i] = L_ii.
+template <class T, int N> OSC_DEV bool chol_inplace(T (&A)[N][N], T (&li)[N]) {
+	bool ok = true;
+	OSC_UNROLL for (int j = 0; j < N; ++j) {
+		T d = A[j][j];
+		OSC_UNROLL for (int k = 0; k < j; ++k) d = Num<T>::fma_(-A[j][k], A[j][k], d);
+		ok = ok && (d > T(0));
+		const T inv = Num<T>::rsqrt_(d);
+		li[j] = inv;
+		A[j][j] = d * inv;
+		OSC_UNROLL for (int i = j + 1; i < N; ++i) {
+			T s = A[i][j];
+			OSC_UNROLL for (int k = 0; k < j; ++k) s = Num<T>::fma_(-A[i][k], A[j][k], s);
+			A[i][j] = s * inv;
+		}
+	}
+	return ok;
+}
 // x <- L^-1 x
 template <class T, int N> OSC_DEV void chol_fwd(const Chol<T, N>& c, T (&x)[N]) {
 	OSC_UNROLL for (int i = 0; i < N; ++i) {

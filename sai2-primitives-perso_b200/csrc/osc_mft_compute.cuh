@@ -95,161 +95,162 @@ OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>&
 	tI(L::POPC_COUNTER) = counter; tI(L::POPC_HEAD) = head; tI(L::POPC_LEN) = len;
 }
 
+#define OSC_FENCE() asm volatile("" ::: "memory")  // keeps ptxas from interleaving independent phases (register pressure)
+
+// One 3-dof half of the motion law (MotionForceTask.cpp:411-437 linear / 441-468 angular): integrates Sigma e, returns
+// Sigma (a_des - kp e - kv (v - v_des) - ki int) or its velocity-saturated variant; vd is the desired velocity (in/out).
+template <class T>
+OSC_DEV void motion_half(const T (&Sg)[3][3], const T (&err)[3], bool err_is_projected, const T (&vel)[3], T (&vd)[3], const T (&acc)[3],
+						 const T (&kp)[3], const T (&kv)[3], const T (&ki)[3], bool use_sat, T sat, T dt, const Row<T>& tP, int off_int, T (&out)[3]) {
+	T se[3], ip[3], raw[3];
+	mv3(Sg, err, se);
+	OSC_UNROLL for (int a = 0; a < 3; ++a) { ip[a] = tP(off_int + a) + se[a] * dt; tP(off_int + a) = ip[a]; }
+	if (use_sat) {
+		T mx = T(0);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) mx = Num<T>::abs_(kv[a]) > mx ? Num<T>::abs_(kv[a]) : mx;
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			const T kvi = Num<T>::abs_(kv[a]) > T(1e-6) * mx ? T(1) / kv[a] : T(0);  // computePseudoInverse of the diagonal gain
+			vd[a] = -kp[a] * kvi * se[a] - ki[a] * kvi * ip[a];
+		}
+		const T nv = norm3(vd);
+		if (nv > sat) {
+			const T sc = sat / nv;
+			OSC_UNROLL for (int a = 0; a < 3; ++a) vd[a] *= sc;
+		}
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = acc[a] - kv[a] * (vel[a] - vd[a]);
+	} else {
+		// the linear law uses the UNPROJECTED error in the kp term (.cpp:431-434), the angular one the projected error (.cpp:443)
+		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = acc[a] - kp[a] * (err_is_projected ? se[a] : err[a]) - kv[a] * (vel[a] - vd[a]) - ki[a] * ip[a];
+	}
+	mv3(Sg, raw, out);
+}
+
 // The control law: returns F* (unit mass force) and F_f (force feedback + feed-forward); updates integrators and caches.
+// The linear half (force space + position) is finished before the angular half starts, so that only one pair of
+// selection matrices is live at a time.  FULL = the task controls all six directions (P = I).
+template <class T, int N, bool FULL = false>
+OSC_DEV void mft_control_law_vw(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
+								const T (&v)[3], const T (&w)[3], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status,
+								bool export_vectors = true) {
+	using L = MftL<N>;
+	if (export_vectors) {
+		st_vec<T, 3>(tS, L::CUR_V, v);
+		st_vec<T, 3>(tS, L::CUR_W, w);
+	}
+	st_vec<T, 3>(tP, L::CUR_POS, x);
+	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
+	T rot[3][3];
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) rot[i][j] = tc.in_compliant_frame ? R[i][j] : (i == j ? T(1) : T(0));
+	const T Id[3][3] = {{T(1), T(0), T(0)}, {T(0), T(1), T(0)}, {T(0), T(0), T(1)}};
+
+	{  // ---- linear half: force space (.cpp:327-354) and position (.cpp:411-437) ----
+		T Sf[3][3], gf_[3], gf[3], Ffb[3];
+		if constexpr (FULL) sigma_matrix<T>(tc.force_dim, Id, rot, tc.force_axis, Sf);
+		else sigma_matrix<T>(tc.force_dim, tc.Pt, rot, tc.force_axis, Sf);
+		ld_vec<T, 3>(tP, L::GOAL_FORCE, gf_);
+		mv3(rot, gf_, gf);  // getGoalForce, .cpp:755-761
+		if (tc.closed_loop_force) {
+			T fs[3], e[3], se[3], ie[3], raw[3], fb[3];
+			ld_vec<T, 3>(tP, L::SENSED_F, fs);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = fs[a] - gf[a];
+			mv3(Sf, e, se);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_F + a) + se[a] * tc.dt; tP(L::INT_F + a) = ie[a]; }
+			OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_force * e[a] - tc.ki_force * ie[a];
+			mv3(Sf, raw, fb);
+			const T nf = norm3(fb);
+			if (nf > tc.max_force_fb) {
+				const T sc = tc.max_force_fb / nf;
+				OSC_UNROLL for (int a = 0; a < 3; ++a) fb[a] *= sc;
+			}
+			T a1[3], a2[3], a3[3], a4[3];
+			mv3(Sf, gf, a1); mv3(Sf, fs, a2); mv3(Sf, fb, a3); mv3(Sf, v, a4);
+			popc_force<T, N>(tc, tP, tI, stride, r, a1, a2, a3, a4, Ffb, status);
+		} else {  // .cpp:352-353
+			T raw[3];
+			OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_force * v[a];
+			mv3(Sf, raw, Ffb);
+		}
+		T ffh[3];
+		mv3(Sf, gf, ffh);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) Ff[a] = Ffb[a] + (tc.closed_loop_force ? tc.kff_force * ffh[a] : ffh[a]);
+		T Sp[3][3];
+		if constexpr (FULL) sigma_complement<T>(Id, Sf, Sp);
+		else sigma_complement<T>(tc.Pt, Sf, Sp);
+		T xg[3], vd[3], ad[3], ex[3], Fp[3];
+		ld_vec<T, 3>(tP, L::GOAL_POS, xg);
+		ld_vec<T, 3>(tP, L::GOAL_LINVEL, vd);
+		ld_vec<T, 3>(tP, L::GOAL_LINACC, ad);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) ex[a] = x[a] - xg[a];
+		motion_half<T>(Sp, ex, false, v, vd, ad, tc.kp_pos, tc.kv_pos, tc.ki_pos, tc.use_vel_sat != 0, tc.lin_sat, tc.dt, tP, L::INT_POS, Fp);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) Fstar[a] = Fp[a];
+		if (export_vectors) {
+			st_vec<T, 3>(tS, L::DES_POS, xg);
+			st_vec<T, 3>(tS, L::DES_LINVEL, vd);
+		}
+	}
+	OSC_FENCE();
+	{  // ---- angular half: moment space (.cpp:357-383) and orientation (.cpp:441-468) ----
+		T Sm[3][3], gm_[3], gm[3], Mfb[3];
+		if constexpr (FULL) sigma_matrix<T>(tc.moment_dim, Id, rot, tc.moment_axis, Sm);
+		else sigma_matrix<T>(tc.moment_dim, tc.Pr, rot, tc.moment_axis, Sm);
+		ld_vec<T, 3>(tP, L::GOAL_MOMENT, gm_);
+		mv3(rot, gm_, gm);
+		if (tc.closed_loop_moment) {
+			T ms[3], e[3], se[3], ie[3], raw[3], mb[3];
+			ld_vec<T, 3>(tP, L::SENSED_M, ms);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = ms[a] - gm[a];
+			mv3(Sm, e, se);
+			OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_M + a) + se[a] * tc.dt; tP(L::INT_M + a) = ie[a]; }
+			OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_moment * e[a] - tc.ki_moment * ie[a];
+			mv3(Sm, raw, mb);
+			const T nm = norm3(mb);
+			if (nm > tc.max_moment_fb) {
+				const T sc = tc.max_moment_fb / nm;
+				OSC_UNROLL for (int a = 0; a < 3; ++a) mb[a] *= sc;
+			}
+			OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = mb[a] - tc.kv_moment * w[a];
+			mv3(Sm, raw, Mfb);
+		} else {  // .cpp:381-382
+			T raw[3];
+			OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_moment * w[a];
+			mv3(Sm, raw, Mfb);
+		}
+		T fft[3];
+		mv3(Sm, gm, fft);
+		// quirk Q3 (.cpp:484-487): the moment feed-forward is scaled under the *force* flag
+		OSC_UNROLL for (int a = 0; a < 3; ++a) Ff[3 + a] = Mfb[a] + (tc.closed_loop_force ? tc.kff_moment * fft[a] : fft[a]);
+		T So[3][3];
+		if constexpr (FULL) sigma_complement<T>(Id, Sm, So);
+		else sigma_complement<T>(tc.Pr, Sm, So);
+		T Rg[3][3], oe[3], wd[3], bd[3], Fo[3];
+		ld_mat<T, 3, 3>(tP, L::GOAL_ORI, Rg);
+		orientation_error<T>(Rg, R, oe);  // .cpp:291-292 (_orientation_error, for getters); desired orientation == goal
+		ld_vec<T, 3>(tP, L::GOAL_ANGVEL, wd);
+		ld_vec<T, 3>(tP, L::GOAL_ANGACC, bd);
+		motion_half<T>(So, oe, true, w, wd, bd, tc.kp_ori, tc.kv_ori, tc.ki_ori, tc.use_vel_sat != 0, tc.ang_sat, tc.dt, tP, L::INT_ORI, Fo);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) Fstar[3 + a] = Fo[a];
+		if (export_vectors) {
+			st_vec<T, 3>(tS, L::ORI_ERR, oe);
+			st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
+			st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+		}
+	}
+	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
+}
+
+// same, from the task Jacobian: v = J[0:3] dq, w = J[3:6] dq (MotionForceTask.cpp:293-298)
 template <class T, int N>
 OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
 							 const T (&J)[6][N], const T (&dq)[N], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status,
 							 bool export_vectors = true) {
-	using L = MftL<N>;
 	T v[3], w[3];
 	OSC_UNROLL for (int a = 0; a < 3; ++a) {
 		T sv = T(0), sw = T(0);
 		OSC_UNROLL for (int j = 0; j < N; ++j) { sv = Num<T>::fma_(J[a][j], dq[j], sv); sw = Num<T>::fma_(J[3 + a][j], dq[j], sw); }
 		v[a] = sv; w[a] = sw;
 	}
-	T Rg[3][3], xg[3];
-	ld_mat<T, 3, 3>(tP, L::GOAL_ORI, Rg);
-	ld_vec<T, 3>(tP, L::GOAL_POS, xg);
-	T oe[3];
-	orientation_error<T>(Rg, R, oe);  // .cpp:291-292 (_orientation_error, for getters)
-	if (export_vectors) {
-		st_vec<T, 3>(tS, L::ORI_ERR, oe);
-		st_vec<T, 3>(tS, L::CUR_V, v);
-		st_vec<T, 3>(tS, L::CUR_W, w);
-	}
-	st_vec<T, 3>(tP, L::CUR_POS, x);
-	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
-
-	T rot[3][3];
-	OSC_UNROLL for (int i = 0; i < 3; ++i)
-		OSC_UNROLL for (int j = 0; j < 3; ++j) rot[i][j] = tc.in_compliant_frame ? R[i][j] : (i == j ? T(1) : T(0));
-	T Sf[3][3], Sm[3][3], Sp[3][3], So[3][3];
-	sigma_matrix<T>(tc.force_dim, tc.Pt, rot, tc.force_axis, Sf);
-	sigma_matrix<T>(tc.moment_dim, tc.Pr, rot, tc.moment_axis, Sm);
-	sigma_complement<T>(tc.Pt, Sf, Sp);
-	sigma_complement<T>(tc.Pr, Sm, So);
-	T gf_[3], gm_[3], gf[3], gm[3], fs[3], ms[3];
-	ld_vec<T, 3>(tP, L::GOAL_FORCE, gf_);
-	ld_vec<T, 3>(tP, L::GOAL_MOMENT, gm_);
-	mv3(rot, gf_, gf);  // getGoalForce / getGoalMoment, .cpp:755-769
-	mv3(rot, gm_, gm);
-	ld_vec<T, 3>(tP, L::SENSED_F, fs);
-	ld_vec<T, 3>(tP, L::SENSED_M, ms);
-
-	T Ffb[3], Mfb[3];
-	if (tc.closed_loop_force) {  // .cpp:327-349
-		T e[3], se[3], ie[3], raw[3], fb[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = fs[a] - gf[a];
-		mv3(Sf, e, se);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_F + a) + se[a] * tc.dt; tP(L::INT_F + a) = ie[a]; }
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_force * e[a] - tc.ki_force * ie[a];
-		mv3(Sf, raw, fb);
-		const T nf = norm3(fb);
-		if (nf > tc.max_force_fb) {
-			const T sc = tc.max_force_fb / nf;
-			OSC_UNROLL for (int a = 0; a < 3; ++a) fb[a] *= sc;
-		}
-		T a1[3], a2[3], a3[3], a4[3];
-		mv3(Sf, gf, a1); mv3(Sf, fs, a2); mv3(Sf, fb, a3); mv3(Sf, v, a4);
-		popc_force<T, N>(tc, tP, tI, stride, r, a1, a2, a3, a4, Ffb, status);
-	} else {  // .cpp:352-353
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_force * v[a];
-		mv3(Sf, raw, Ffb);
-	}
-	if (tc.closed_loop_moment) {  // .cpp:357-378
-		T e[3], se[3], ie[3], raw[3], mb[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) e[a] = ms[a] - gm[a];
-		mv3(Sm, e, se);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) { ie[a] = tP(L::INT_M + a) + se[a] * tc.dt; tP(L::INT_M + a) = ie[a]; }
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kp_moment * e[a] - tc.ki_moment * ie[a];
-		mv3(Sm, raw, mb);
-		const T nm = norm3(mb);
-		if (nm > tc.max_moment_fb) {
-			const T sc = tc.max_moment_fb / nm;
-			OSC_UNROLL for (int a = 0; a < 3; ++a) mb[a] *= sc;
-		}
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = mb[a] - tc.kv_moment * w[a];
-		mv3(Sm, raw, Mfb);
-	} else {  // .cpp:381-382
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = -tc.kv_moment * w[a];
-		mv3(Sm, raw, Mfb);
-	}
-
-	// desired <- goal (.cpp:387-392; the internal OTG is the "next" row f-1)
-	T vd[3], wd[3], ad[3], bd[3];
-	ld_vec<T, 3>(tP, L::GOAL_LINVEL, vd);
-	ld_vec<T, 3>(tP, L::GOAL_ANGVEL, wd);
-	ld_vec<T, 3>(tP, L::GOAL_LINACC, ad);
-	ld_vec<T, 3>(tP, L::GOAL_ANGACC, bd);
-	// linear motion (.cpp:411-437)
-	T ex[3], sex[3], ip[3], Fp[3], Fo[3];
-	OSC_UNROLL for (int a = 0; a < 3; ++a) ex[a] = x[a] - xg[a];
-	mv3(Sp, ex, sex);
-	OSC_UNROLL for (int a = 0; a < 3; ++a) { ip[a] = tP(L::INT_POS + a) + sex[a] * tc.dt; tP(L::INT_POS + a) = ip[a]; }
-	if (tc.use_vel_sat) {
-		T mx = T(0);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) mx = Num<T>::abs_(tc.kv_pos[a]) > mx ? Num<T>::abs_(tc.kv_pos[a]) : mx;
-		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			const T kvi = Num<T>::abs_(tc.kv_pos[a]) > T(1e-6) * mx ? T(1) / tc.kv_pos[a] : T(0);  // computePseudoInverse
-			vd[a] = -tc.kp_pos[a] * kvi * sex[a] - tc.ki_pos[a] * kvi * ip[a];
-		}
-		const T nv = norm3(vd);
-		if (nv > tc.lin_sat) {
-			const T sc = tc.lin_sat / nv;
-			OSC_UNROLL for (int a = 0; a < 3; ++a) vd[a] *= sc;
-		}
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = ad[a] - tc.kv_pos[a] * (v[a] - vd[a]);
-		mv3(Sp, raw, Fp);
-	} else {
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = ad[a] - tc.kp_pos[a] * ex[a] - tc.kv_pos[a] * (v[a] - vd[a]) - tc.ki_pos[a] * ip[a];
-		mv3(Sp, raw, Fp);
-	}
-	// angular motion (.cpp:441-468)
-	T eo[3], io[3];
-	mv3(So, oe, eo);  // desired orientation == goal orientation
-	OSC_UNROLL for (int a = 0; a < 3; ++a) { io[a] = tP(L::INT_ORI + a) + eo[a] * tc.dt; tP(L::INT_ORI + a) = io[a]; }
-	if (tc.use_vel_sat) {
-		T mx = T(0);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) mx = Num<T>::abs_(tc.kv_ori[a]) > mx ? Num<T>::abs_(tc.kv_ori[a]) : mx;
-		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			const T kvi = Num<T>::abs_(tc.kv_ori[a]) > T(1e-6) * mx ? T(1) / tc.kv_ori[a] : T(0);
-			wd[a] = -tc.kp_ori[a] * kvi * eo[a] - tc.ki_ori[a] * kvi * io[a];
-		}
-		const T nw = norm3(wd);
-		if (nw > tc.ang_sat) {
-			const T sc = tc.ang_sat / nw;
-			OSC_UNROLL for (int a = 0; a < 3; ++a) wd[a] *= sc;
-		}
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = bd[a] - tc.kv_ori[a] * (w[a] - wd[a]);
-		mv3(So, raw, Fo);
-	} else {
-		T raw[3];
-		OSC_UNROLL for (int a = 0; a < 3; ++a) raw[a] = bd[a] - tc.kp_ori[a] * eo[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io[a];
-		mv3(So, raw, Fo);
-	}
-	if (export_vectors) {
-		st_vec<T, 3>(tS, L::DES_POS, xg);
-		st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
-		st_vec<T, 3>(tS, L::DES_LINVEL, vd);
-		st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
-	}
-	// assemble (.cpp:470-487; quirk Q3: the moment feed-forward is scaled under the *force* flag)
-	T ffh[3], fft[3];
-	mv3(Sf, gf, ffh);
-	mv3(Sm, gm, fft);
-	if (tc.closed_loop_force) {
-		OSC_UNROLL for (int a = 0; a < 3; ++a) { ffh[a] *= tc.kff_force; fft[a] *= tc.kff_moment; }
-	}
-	OSC_UNROLL for (int a = 0; a < 3; ++a) {
-		Fstar[a] = Fp[a]; Fstar[3 + a] = Fo[a];
-		Ff[a] = Ffb[a] + ffh[a]; Ff[3 + a] = Mfb[a] + fft[a];
-	}
-	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
+	mft_control_law_vw<T, N>(tc, tP, tS, tI, stride, r, v, w, x, R, Fstar, Ff, status, export_vectors);
 }
 
 }  // namespace osc

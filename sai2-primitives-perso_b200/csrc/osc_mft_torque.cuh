@@ -27,7 +27,7 @@ OSC_DEV void range_torque(const Row<T>& tS, int offU, int offJ, int offL, const 
 
 template <class T, int N>
 __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r,
-								  int with_tau_prec, int accumulate) {
+								  int with_tau_prec, int accumulate, int reuse_law = 0) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
@@ -52,7 +52,12 @@ __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, con
 	ld_vec<T, N>(rP, RobotL<N>::Q, q);
 	ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
 	T Fstar[6], Ff[6];
-	mft_control_law<T, N>(tc, tP, tS, tI, stride, r, J, dq, x, R, Fstar, Ff, status);
+	if (reuse_law) {  // k_tick_tail: the fused kernel already ran the control law (and advanced its state) for this robot
+		ld_vec<T, 6>(tS, L::UMF, Fstar);
+		ld_vec<T, 6>(tS, L::FFB, Ff);
+	} else {
+		mft_control_law<T, N>(tc, tP, tS, tI, stride, r, J, dq, x, R, Fstar, Ff, status);
+	}
 
 	// ---- SingularityHandler::computeTorques ----
 	T tau[N];

@@ -148,16 +148,18 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 		const JtC<T, N> jc = jtc(b, j);
 		// OSC_FUSED_V=1 selects the first-generation kernel (osc_fused.cuh), OSC_FUSED_MINB its occupancy variant: experiment knobs
 		static const int ver = [] { const char* e = getenv("OSC_FUSED_V"); return e ? atoi(e) : 2; }();
-		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : (ver == 2 ? 7 : 8); }();
+		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : 8; }();
 #define OSC_FUSED_ARGS ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list
+		int reuse_law = 0;
 		if (ver == 2 && fused2_supported(b)) {
+			reuse_law = 1;
 			if (b.gravity) {
 				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
-			if (minb >= 8) k_tick_fused2<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else if (minb >= 7) k_tick_fused2<T, N, 7><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else k_tick_fused2<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			if (minb >= 8) k_tick_fused2<T, N, 128><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else if (minb >= 7) k_tick_fused2<T, N, 144><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			else k_tick_fused2<T, N, 168><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 		} else {
 			if (minb >= 8) k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 			else if (minb >= 6) k_tick_fused<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
@@ -166,7 +168,7 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 #undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
-		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list);
+		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list, reuse_law);
 		if (int rc = done(b, "k_tick_tail")) return rc;
 		b.fb_last = b.fb_parity;
 		b.fb_parity ^= 1;
