@@ -23,12 +23,17 @@ template <int N> struct F2 {
 	static constexpr int LL = MM;                         // L[i][j], j < i at LL + i(i-1)/2 + j
 	static constexpr int LI = MM + N * (N - 1) / 2;       // 1 / L_ii
 	static constexpr int CC = MM + N * (N + 1) / 2;       // chol(A) strictly lower (15)
-	static constexpr int SLOTS = CC + 15;
+	// 1 / C_ii: the spare slots behind F*, F_f first (2N - 12), the rest behind C
+	static constexpr int SPARE = 2 * N - 12;
+	__host__ __device__ static constexpr int cli(int i) { return i < SPARE ? SC + 12 + i : CC + 15 + (i - SPARE); }
+	static constexpr int SLOTS = CC + 15 + (6 - SPARE);
 };
 
 template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c) { Num<T>::sincos_(x, s, c); }
 
-template <class T, int N, int MAXREG>
+// SIMPLE = plain motion task over a plain joint task (no force / moment space, open loop, no velocity saturation): the
+// host selects this instantiation from the uniform task parameters; F_f is identically zero there.
+template <class T, int N, int MAXREG, bool SIMPLE>
 __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 																		 const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
 																		 int64_t B, int64_t stride, int stacked, int gravity, int exports,
@@ -89,7 +94,12 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		cross3(w, x, v);
 		OSC_UNROLL for (int a = 0; a < 3; ++a) v[a] -= mo[a];
 		T Fstar[6], Ff[6];
-		mft_control_law_vw<T, N, true>(tc, mP, mS, mI, stride, r, v, w, x, Rc, Fstar, Ff, status, ex);
+		if constexpr (SIMPLE) {
+			mft_control_law_motion_only<T, N>(tc, mP, mS, v, w, x, Rc, Fstar, ex);
+			OSC_UNROLL for (int i = 0; i < 6; ++i) Ff[i] = T(0);
+		} else {
+			mft_control_law_vw<T, N, true>(tc, mP, mS, mI, stride, r, v, w, x, Rc, Fstar, Ff, status, ex);
+		}
 		OSC_UNROLL for (int i = 0; i < 6; ++i) { SM(F::CC + i) = Fstar[i]; SM(F::CC + 6 + i) = Ff[i]; }
 	}
 #define OSC_FALL_BACK()                                                                      \
@@ -256,86 +266,80 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	T (&Y)[6][N] = J;
 
 	OSC_FENCE();
-	// ---- P8: A = J M^-1 J^T = Y Y^T, C = chol(A): strictly lower part to the stash, 1/C_ii in registers ----
-	T cli[6];
+	// ---- P8: A = J M^-1 J^T = Y Y^T, C = chol(A) in place: strictly lower part and 1/C_ii to the stash ----
 	{
-		T A[6][6];
+		T A[6][6], cli[6];
 		OSC_UNROLL for (int i = 0; i < 6; ++i)
 			OSC_UNROLL for (int j = 0; j <= i; ++j) {
 				T s = T(0);
 				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(Y[i][k], Y[j][k], s);
 				A[i][j] = s;
 			}
-		Chol<T, 6> ca;
-		if (!chol_factor<T, 6>(A, ca)) status |= 16;
+		if (!chol_inplace<T, 6>(A, cli)) status |= 16;
 		OSC_UNROLL for (int i = 0; i < 6; ++i) {
-			cli[i] = ca.Li[i];
-			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::CC + i * (i - 1) / 2 + j) = ca.L[i][j];
+			SM(F::cli(i)) = cli[i];
+			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::CC + i * (i - 1) / 2 + j) = A[i][j];
 		}
 	}
 #define OSC_CFWD(t)                                                                                     \
 	OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) {                                                         \
 		T s_ = t[i_];                                                                                   \
 		OSC_UNROLL for (int m_ = 0; m_ < i_; ++m_) s_ = Num<T>::fma_(-SM(F::CC + i_ * (i_ - 1) / 2 + m_), t[m_], s_); \
-		t[i_] = s_ * cli[i_];                                                                           \
+		t[i_] = s_ * SM(F::cli(i_));                                                                    \
 	}
 #define OSC_CBWD(t)                                                                                     \
 	OSC_UNROLL for (int i_ = 5; i_ >= 0; --i_) {                                                        \
 		T s_ = t[i_];                                                                                   \
 		OSC_UNROLL for (int m_ = i_ + 1; m_ < 6; ++m_) s_ = Num<T>::fma_(-SM(F::CC + m_ * (m_ - 1) / 2 + i_), t[m_], s_); \
-		t[i_] = s_ * cli[i_];                                                                           \
+		t[i_] = s_ * SM(F::cli(i_));                                                                    \
 	}
 
 	OSC_FENCE();
 	// ---- P9: u = unit vector orthogonal to range(Y^T) (n = 7): N_1 = (L^-T u)(L u)^T ----
-	T u[N], t_last[6];  // t_last = C^-1 y_last (y_k = column k of Y), for the BIE correction
+	T u[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
-	{
+	if constexpr (N == 7) {
 		T best = T(-1);
 		int kb = 0;
-		OSC_UNROLL for (int k = (N == 7 ? 0 : N - 1); k < N; ++k) {  // residual of e_k: P_kk = 1 - |C^-1 y_k|^2
+		OSC_UNROLL for (int k = 0; k < N; ++k) {  // residual of e_k: P_kk = 1 - |C^-1 y_k|^2  (y_k = column k of Y)
 			T t[6];
 			OSC_UNROLL for (int c = 0; c < 6; ++c) t[c] = Y[c][k];
 			OSC_CFWD(t)
 			T s = T(1);
 			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-t[c], t[c], s);
 			if (s > best) { best = s; kb = k; }
-			if (k == N - 1) {
-				OSC_UNROLL for (int c = 0; c < 6; ++c) t_last[c] = t[c];
-			}
 		}
-		if constexpr (N == 7) {
-			T a[6];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) {
-				T s = T(0);
-				OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? Y[c][k] : s;
-				a[c] = s;
-			}
-			OSC_CFWD(a)
-			OSC_CBWD(a)
-			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				T s = (i == kb) ? T(1) : T(0);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
-				u[i] = s;
-			}
-			// second projection ("twice is enough")
-			OSC_UNROLL for (int c = 0; c < 6; ++c) {
-				T s = T(0);
-				OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(Y[c][i], u[i], s);
-				a[c] = s;
-			}
-			OSC_CFWD(a)
-			OSC_CBWD(a)
-			T nu = T(0);
-			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				T s = u[i];
-				OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
-				u[i] = s;
-				nu = Num<T>::fma_(s, s, nu);
-			}
-			const T inv = Num<T>::rsqrt_(nu);
-			OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
+		OSC_FENCE();
+		T a[6];
+		OSC_UNROLL for (int c = 0; c < 6; ++c) {
+			T s = T(0);
+			OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? Y[c][k] : s;
+			a[c] = s;
 		}
+		OSC_CFWD(a)
+		OSC_CBWD(a)
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T s = (i == kb) ? T(1) : T(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+			u[i] = s;
+		}
+		// second projection ("twice is enough")
+		OSC_UNROLL for (int c = 0; c < 6; ++c) {
+			T s = T(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(Y[c][i], u[i], s);
+			a[c] = s;
+		}
+		OSC_CFWD(a)
+		OSC_CBWD(a)
+		T nu = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T s = u[i];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+			u[i] = s;
+			nu = Num<T>::fma_(s, s, nu);
+		}
+		const T inv = Num<T>::rsqrt_(nu);
+		OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
 	}
 
 	OSC_FENCE();
@@ -349,15 +353,19 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 			OSC_CBWD(f)
 			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
 				// A_BIE = A - beta y y^T (y = last column of Y):  A_BIE^-1 F = A^-1 F + beta z (z . F) / (1 - beta y . z),  z = A^-1 y
-				T yz = T(0), zF = T(0);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) yz = Num<T>::fma_(t_last[c], t_last[c], yz);
-				OSC_CBWD(t_last)  // z
-				OSC_UNROLL for (int c = 0; c < 6; ++c) zF = Num<T>::fma_(t_last[c], SM(F::SC + c), zF);
+				T z[6], yz = T(0), zF = T(0);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) z[c] = Y[c][N - 1];
+				OSC_CFWD(z)
+				OSC_UNROLL for (int c = 0; c < 6; ++c) yz = Num<T>::fma_(z[c], z[c], yz);
+				OSC_CBWD(z)
+				OSC_UNROLL for (int c = 0; c < 6; ++c) zF = Num<T>::fma_(z[c], SM(F::SC + c), zF);
 				const T coef = beta * zF / (T(1) - beta * yz);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = Num<T>::fma_(coef, t_last[c], f[c]);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = Num<T>::fma_(coef, z[c], f[c]);
 			}
 		}
-		OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] += SM(F::SC + 6 + c);
+		if constexpr (!SIMPLE) {
+			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] += SM(F::SC + 6 + c);
+		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			T s = T(0);
 			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(Y[c][i], f[c], s);
@@ -381,8 +389,8 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 
 	OSC_FENCE();
-	// ---- P11: tau_1 = L h, w = L u;  v = L^-T u, M^-1 tau_1 = L^-T h  (two sweeps over L, shared by both vectors) ----
-	T tau1[N], w[N], v[N], mt[N];
+	// ---- P11: tau_1 = L h and w = L u (one sweep over L), parked in the dead C slots ----
+	constexpr int TAU1 = F::CC, WW = F::CC + N;  // N = 7: 14 of the 15 C slots
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		const T ld = T(1) / SM(F::LI + i);
 		T s1 = ld * h[i], sw = ld * u[i];
@@ -391,54 +399,72 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 			s1 = Num<T>::fma_(l, h[m], s1);
 			sw = Num<T>::fma_(l, u[m], sw);
 		}
-		tau1[i] = s1; w[i] = sw;
+		if (ex) mS(ML::TASK_TAU + i) = s1;
+		if constexpr (N == 7) { SM(TAU1 + i) = s1; SM(WW + i) = sw; }
+		else rS(RobotL<N>::TAU + i) = gravity ? s1 + rS(RobotL<N>::GRAV + i) : s1;
 	}
-	T tau2[N];
-	OSC_UNROLL for (int i = 0; i < N; ++i) tau2[i] = T(0);
 	if constexpr (N == 7) {
+		OSC_FENCE();
+		// v = L^-T u, M^-1 tau_1 = L^-T h: in place (u -> v, h -> mt), one backward sweep over L
+		const T u_last = u[N - 1];
 		OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
 			T sv = u[i], st = h[i];
 			OSC_UNROLL for (int k = i + 1; k < N; ++k) {
 				const T l = SM(F::LL + k * (k - 1) / 2 + i);
-				sv = Num<T>::fma_(-l, v[k], sv);
-				st = Num<T>::fma_(-l, mt[k], st);
+				sv = Num<T>::fma_(-l, u[k], sv);
+				st = Num<T>::fma_(-l, h[k], st);
 			}
 			const T li = SM(F::LI + i);
-			v[i] = sv * li; mt[i] = st * li;
+			u[i] = sv * li; h[i] = st * li;
 		}
-		// JointTask in the nullspace (JointTask.cpp:218-356): R = v / |v|, Lambda = 1 / |v|^2, tau_2 = w [Lambda (v.a - v.M^-1 tau_1) + Lambda_mod v.u_pd]
+		T (&v)[N] = u;
+		// JointTask in the nullspace (JointTask.cpp:218-356): R = v / |v|, Lambda = 1 / |v|^2,
+		// tau_2 = w [Lambda (v.a - v.M^-1 tau_1) + Lambda_mod v.u_pd]
 		T nv2 = T(0), vc = T(0);
-		OSC_UNROLL for (int i = 0; i < N; ++i) { nv2 = Num<T>::fma_(v[i], v[i], nv2); vc = Num<T>::fma_(v[i], mt[i], vc); }
+		OSC_UNROLL for (int i = 0; i < N; ++i) { nv2 = Num<T>::fma_(v[i], v[i], nv2); vc = Num<T>::fma_(v[i], h[i], vc); }
 		const T lam = T(1) / nv2;
 		T lam_mod = lam;  // JointTask.cpp:253-267
-		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u[N - 1] * u[N - 1]));  // |L_BIE^-1 L u|^2
+		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u_last * u_last));  // |L_BIE^-1 L u|^2
 		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = T(1);
-		T q[N], dq[N], upd[N], acc[N];
-		ld_vec<T, N>(rP, RobotL<N>::Q, q);
-		ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
-		jt_pd_law<T, N>(jc, jP, jS, q, dq, upd, acc, ex);
 		T va = T(0), vu = T(0);
-		OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<T>::fma_(v[i], acc[i], va); vu = Num<T>::fma_(v[i], upd[i], vu); }
+		if constexpr (SIMPLE) {  // joint PID, one joint at a time (JointTask.cpp:319-346 without velocity saturation)
+			OSC_UNROLL for (int i = 0; i < N; ++i) {
+				const T qi = rP(RobotL<N>::Q + i), dqi = rP(RobotL<N>::DQ + i);
+				const T e = qi - jP(JL::GOAL_POS + i);
+				const T ie = jP(JL::INTEG + i) + e * jc.dt;
+				jP(JL::INTEG + i) = ie;
+				const T dv = jP(JL::GOAL_VEL + i);
+				const T upd = -jc.kp[i] * e - jc.kv[i] * (dqi - dv) - jc.ki[i] * ie;
+				va = Num<T>::fma_(v[i], jP(JL::GOAL_ACC + i), va);
+				vu = Num<T>::fma_(v[i], upd, vu);
+				if (ex) { jS(JL::CUR_POS + i) = qi; jS(JL::CUR_VEL + i) = dqi; jS(JL::DES_VEL + i) = dv; }
+			}
+		} else {
+			T q[N], dq[N], upd[N], acc[N];
+			ld_vec<T, N>(rP, RobotL<N>::Q, q);
+			ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
+			jt_pd_law<T, N>(jc, jP, jS, q, dq, upd, acc, ex);
+			OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<T>::fma_(v[i], acc[i], va); vu = Num<T>::fma_(v[i], upd[i], vu); }
+			if (ex) {
+				st_vec<T, N>(jS, JL::CUR_POS, q);
+				st_vec<T, N>(jS, JL::CUR_VEL, dq);
+			}
+		}
 		const T sc = lam * (va - (stacked ? vc : T(0))) + lam_mod * vu;
-		OSC_UNROLL for (int i = 0; i < N; ++i) tau2[i] = w[i] * sc;
-		if (ex) {
-			st_vec<T, N>(jS, JL::CUR_POS, q);
-			st_vec<T, N>(jS, JL::CUR_VEL, dq);
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			const T t2 = SM(WW + i) * sc;
+			T t = SM(TAU1 + i) + t2;
+			if (gravity) t += rS(RobotL<N>::GRAV + i);  // written by k_gravity ahead of this kernel
+			rS(RobotL<N>::TAU + i) = t;
+			if (ex) jS(JL::TASK_TAU + i) = t2;
 		}
 	} else if (ex) {
-		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); }
+		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); jS(JL::TASK_TAU + i) = T(0); }
 	}
 	if (ex) {
 		tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;
-		st_vec<T, N>(jS, JL::TASK_TAU, tau2);
-		st_vec<T, N>(mS, ML::TASK_TAU, tau1);
 		mS(ML::ALPHA) = T(1);
 		mI(ML::INS) = 6;
-	}
-	OSC_UNROLL for (int i = 0; i < N; ++i) {
-		T t = tau1[i] + tau2[i];
-		if (gravity) t += rS(RobotL<N>::GRAV + i);  // written by k_gravity ahead of this kernel
-		rS(RobotL<N>::TAU + i) = t;
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 #undef OSC_FALL_BACK
@@ -463,6 +489,11 @@ __global__ void __launch_bounds__(OSC_THREADS) k_gravity(const __grid_constant__
 }
 
 // what the second-generation kernel adds to fused_tick_supported: a revolute chain with the control link on the last body
+inline bool fused2_simple(const Batch& b) {
+	const osc_mft_params& p = b.tasks[0].mp;
+	return p.force_space_dimension == 0 && p.moment_space_dimension == 0 && !p.closed_loop_force_control && !p.closed_loop_moment_control &&
+		   !p.use_velocity_saturation && !b.tasks[1].jp.use_velocity_saturation;
+}
 inline bool fused2_supported(Batch& b) {
 	if (b.tasks.empty() || b.tasks[0].md.body != b.n - 1) return false;
 	for (int i = 0; i < b.n; ++i)

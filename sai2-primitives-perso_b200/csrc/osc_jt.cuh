@@ -8,7 +8,7 @@ namespace osc {
 
 // The joint-space control law of JointTask::computeTorques (JointTask.cpp:319-346): integrates the error, returns the
 // PID (or velocity-saturated) command u and the feed-forward acceleration; rows >= k are zero.
-template <class T, int N>
+template <class T, int N, bool NOSAT = false>
 OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, const T (&cp)[N], const T (&cv)[N], T (&u)[N], T (&acc)[N],
 					   bool export_vectors) {
 	using L = JtL<N>;
@@ -20,7 +20,7 @@ OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, 
 		if (i < k) { ie += e * jc.dt; tP(L::INTEG + i) = ie; }  // JointTask.cpp:323-324
 		dv[i] = tP(L::GOAL_VEL + i);
 		acc[i] = (i < k) ? tP(L::GOAL_ACC + i) : T(0);
-		if (jc.use_vel_sat) {  // JointTask.cpp:327-340 (quirk Q7: loop to k)
+		if (!NOSAT && jc.use_vel_sat) {  // JointTask.cpp:327-340 (quirk Q7: loop to k)
 			T mx = T(0);
 			OSC_UNROLL for (int j = 0; j < N; ++j)
 				if (j < k) mx = Num<T>::abs_(jc.kv[j]) > mx ? Num<T>::abs_(jc.kv[j]) : mx;

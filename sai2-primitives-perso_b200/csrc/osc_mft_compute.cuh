@@ -239,6 +239,55 @@ OSC_DEV void mft_control_law_vw(const MftC<T>& tc, const Row<T>& tP, const Row<T
 	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
 }
 
+// The law for the plain motion task: no force / moment space (dimension 0), open loop, no velocity saturation, all six
+// directions controlled.  Then Sigma_force = Sigma_moment = 0, Sigma_position = Sigma_orientation = I and F_f = 0
+// (MotionForceTask.cpp:306-309, 352-353, 381-382, 427-467): F* = a_des - kp e - kv (v - v_des) - ki int e.
+template <class T, int N>
+OSC_DEV void mft_control_law_motion_only(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const T (&v)[3], const T (&w)[3], const T (&x)[3],
+										 const T (&R)[3][3], T (&Fstar)[6], bool export_vectors) {
+	using L = MftL<N>;
+	if (export_vectors) {
+		st_vec<T, 3>(tS, L::CUR_V, v);
+		st_vec<T, 3>(tS, L::CUR_W, w);
+	}
+	st_vec<T, 3>(tP, L::CUR_POS, x);
+	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
+	{
+		T xg[3], vd[3], ad[3];
+		ld_vec<T, 3>(tP, L::GOAL_POS, xg);
+		ld_vec<T, 3>(tP, L::GOAL_LINVEL, vd);
+		ld_vec<T, 3>(tP, L::GOAL_LINACC, ad);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			const T e = x[a] - xg[a];
+			const T ip = tP(L::INT_POS + a) + e * tc.dt;
+			tP(L::INT_POS + a) = ip;
+			Fstar[a] = ad[a] - tc.kp_pos[a] * e - tc.kv_pos[a] * (v[a] - vd[a]) - tc.ki_pos[a] * ip;
+		}
+		if (export_vectors) {
+			st_vec<T, 3>(tS, L::DES_POS, xg);
+			st_vec<T, 3>(tS, L::DES_LINVEL, vd);
+		}
+	}
+	{
+		T Rg[3][3], oe[3], wd[3], bd[3];
+		ld_mat<T, 3, 3>(tP, L::GOAL_ORI, Rg);
+		orientation_error<T>(Rg, R, oe);
+		ld_vec<T, 3>(tP, L::GOAL_ANGVEL, wd);
+		ld_vec<T, 3>(tP, L::GOAL_ANGACC, bd);
+		OSC_UNROLL for (int a = 0; a < 3; ++a) {
+			const T io = tP(L::INT_ORI + a) + oe[a] * tc.dt;
+			tP(L::INT_ORI + a) = io;
+			Fstar[3 + a] = bd[a] - tc.kp_ori[a] * oe[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io;
+		}
+		if (export_vectors) {
+			st_vec<T, 3>(tS, L::ORI_ERR, oe);
+			st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
+			st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+		}
+	}
+	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
+}
+
 // same, from the task Jacobian: v = J[0:3] dq, w = J[3:6] dq (MotionForceTask.cpp:293-298)
 template <class T, int N>
 OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,

@@ -157,9 +157,14 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
-			if (minb >= 8) k_tick_fused2<T, N, 128><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else if (minb >= 7) k_tick_fused2<T, N, 144><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else k_tick_fused2<T, N, 168><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			const bool simple = fused2_simple(b) && !getenv("OSC_FUSED_NOSIMPLE");
+			if (minb >= 8) {
+				if (simple) k_tick_fused2<T, N, 128, true><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+				else k_tick_fused2<T, N, 128, false><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			} else {
+				if (simple) k_tick_fused2<T, N, 168, true><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+				else k_tick_fused2<T, N, 168, false><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			}
 		} else {
 			if (minb >= 8) k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 			else if (minb >= 6) k_tick_fused<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
