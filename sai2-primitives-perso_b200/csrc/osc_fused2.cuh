@@ -51,7 +51,19 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
 	int status = 0;
 
-	// ---- P1: sin/cos of every joint (one out-of-line sincos) ----
+	// ---- P0: the tick is latency bound at 3.5 warps per scheduler: pull every input row of this robot towards L2 now, so
+	// that the loads of the control law (P1b) and of the joint task (P11) do not pay a DRAM round trip each ----
+	{
+		auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
+		_Pragma("unroll 1") for (int e = 0; e < N; ++e) pf(&rP(RobotL<N>::DQ + e));
+		_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
+		_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
+		_Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+		pf(&mI(ML::NTYPES));
+		pf(&mI(ML::HIST_LEN));
+	}
+
+	// ---- P1: sin/cos of every joint ----
 	_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
 		T s, c;
 		Num<T>::sincos_(rP(RobotL<N>::Q + i), &s, &c);
@@ -266,75 +278,58 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	T (&Y)[6][N] = J;
 
 	OSC_FENCE();
-	// ---- P8: A = J M^-1 J^T = Y Y^T, C = chol(A) in place: strictly lower part and 1/C_ii to the stash ----
-	{
-		T A[6][6], cli[6];
-		OSC_UNROLL for (int i = 0; i < 6; ++i)
-			OSC_UNROLL for (int j = 0; j <= i; ++j) {
-				T s = T(0);
-				OSC_UNROLL for (int k = 0; k < N; ++k) s = Num<T>::fma_(Y[i][k], Y[j][k], s);
-				A[i][j] = s;
-			}
-		if (!chol_inplace<T, 6>(A, cli)) status |= 16;
-		OSC_UNROLL for (int i = 0; i < 6; ++i) {
-			SM(F::cli(i)) = cli[i];
-			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::CC + i * (i - 1) / 2 + j) = A[i][j];
+	// ---- P8: orthonormalise the rows of Y in place (modified Gram-Schmidt): Y = C W with W W^T = I and C lower triangular,
+	// i.e. C = chol(A) for A = Y Y^T = J M^-1 J^T without ever forming A (and without squaring its condition number).
+	// C goes to the stash (strictly lower part + 1/C_cc); W stays in the registers of Y. ----
+	OSC_UNROLL for (int c = 0; c < 6; ++c) {
+		T nn = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) nn = Num<T>::fma_(Y[c][i], Y[c][i], nn);
+		if (!(nn > T(0))) status |= 16;
+		const T inv = Num<T>::rsqrt_(nn);
+		SM(F::cli(c)) = inv;
+		OSC_UNROLL for (int i = 0; i < N; ++i) Y[c][i] *= inv;
+		OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) {
+			T rr = T(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) rr = Num<T>::fma_(Y[c][i], Y[c2][i], rr);
+			SM(F::CC + c2 * (c2 - 1) / 2 + c) = rr;
+			OSC_UNROLL for (int i = 0; i < N; ++i) Y[c2][i] = Num<T>::fma_(-rr, Y[c][i], Y[c2][i]);
 		}
 	}
-#define OSC_CFWD(t)                                                                                     \
-	OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) {                                                         \
-		T s_ = t[i_];                                                                                   \
-		OSC_UNROLL for (int m_ = 0; m_ < i_; ++m_) s_ = Num<T>::fma_(-SM(F::CC + i_ * (i_ - 1) / 2 + m_), t[m_], s_); \
-		t[i_] = s_ * SM(F::cli(i_));                                                                    \
-	}
-#define OSC_CBWD(t)                                                                                     \
-	OSC_UNROLL for (int i_ = 5; i_ >= 0; --i_) {                                                        \
-		T s_ = t[i_];                                                                                   \
-		OSC_UNROLL for (int m_ = i_ + 1; m_ < 6; ++m_) s_ = Num<T>::fma_(-SM(F::CC + m_ * (m_ - 1) / 2 + i_), t[m_], s_); \
-		t[i_] = s_ * SM(F::cli(i_));                                                                    \
-	}
+	T (&W)[6][N] = Y;
 
 	OSC_FENCE();
-	// ---- P9: u = unit vector orthogonal to range(Y^T) (n = 7): N_1 = (L^-T u)(L u)^T ----
+	// ---- P9: u = unit vector orthogonal to the rows of W (n = 7): P = I - W^T W = u u^T, N_1 = (L^-T u)(L u)^T ----
 	T u[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
 	if constexpr (N == 7) {
 		T best = T(-1);
 		int kb = 0;
-		OSC_UNROLL for (int k = 0; k < N; ++k) {  // residual of e_k: P_kk = 1 - |C^-1 y_k|^2  (y_k = column k of Y)
-			T t[6];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) t[c] = Y[c][k];
-			OSC_CFWD(t)
+		OSC_UNROLL for (int k = 0; k < N; ++k) {  // residual of e_k: P_kk = 1 - |W[:,k]|^2
 			T s = T(1);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-t[c], t[c], s);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][k], W[c][k], s);
 			if (s > best) { best = s; kb = k; }
 		}
-		OSC_FENCE();
 		T a[6];
 		OSC_UNROLL for (int c = 0; c < 6; ++c) {
 			T s = T(0);
-			OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? Y[c][k] : s;
+			OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? W[c][k] : s;
 			a[c] = s;
 		}
-		OSC_CFWD(a)
-		OSC_CBWD(a)
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			T s = (i == kb) ? T(1) : T(0);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][i], a[c], s);
 			u[i] = s;
 		}
 		// second projection ("twice is enough")
 		OSC_UNROLL for (int c = 0; c < 6; ++c) {
 			T s = T(0);
-			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(Y[c][i], u[i], s);
+			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(W[c][i], u[i], s);
 			a[c] = s;
 		}
-		OSC_CFWD(a)
-		OSC_CBWD(a)
 		T nu = T(0);
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			T s = u[i];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-Y[c][i], a[c], s);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][i], a[c], s);
 			u[i] = s;
 			nu = Num<T>::fma_(s, s, nu);
 		}
@@ -343,32 +338,38 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 
 	OSC_FENCE();
-	// ---- P10: f = Lambda_mod F* + F_f (SingularityHandler.cpp:160-225, 307-309); h = Y^T f; tau_1 = J^T f = L h ----
+	// ---- P10: tau_1 = J^T (Lambda_mod F* + F_f) = L h with h = W^T g,  g = C^T (Lambda_mod F* + F_f)
+	// (SingularityHandler.cpp:160-225, 307-309).  Lambda = A^-1 = C^-T C^-1, so C^T Lambda F* = C^-1 F*: one forward solve. ----
 	T h[N];
 	{
-		T f[6];
-		OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = SM(F::SC + c);
+		T g[6];
+		OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::SC + c);
 		if (tc.decoupling != OSC_IMPEDANCE) {
-			OSC_CFWD(f)
-			OSC_CBWD(f)
+			OSC_UNROLL for (int i = 0; i < 6; ++i) {  // g <- C^-1 F*
+				T s = g[i];
+				OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<T>::fma_(-SM(F::CC + i * (i - 1) / 2 + m), g[m], s);
+				g[i] = s * SM(F::cli(i));
+			}
 			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
-				// A_BIE = A - beta y y^T (y = last column of Y):  A_BIE^-1 F = A^-1 F + beta z (z . F) / (1 - beta y . z),  z = A^-1 y
-				T z[6], yz = T(0), zF = T(0);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) z[c] = Y[c][N - 1];
-				OSC_CFWD(z)
-				OSC_UNROLL for (int c = 0; c < 6; ++c) yz = Num<T>::fma_(z[c], z[c], yz);
-				OSC_CBWD(z)
-				OSC_UNROLL for (int c = 0; c < 6; ++c) zF = Num<T>::fma_(z[c], SM(F::SC + c), zF);
-				const T coef = beta * zF / (T(1) - beta * yz);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = Num<T>::fma_(coef, z[c], f[c]);
+				// A_BIE = A - beta y y^T with y = C w (w = last column of W):  C^T A_BIE^-1 F* = g + beta w (w . g) / (1 - beta |w|^2)
+				T ww = T(0), wg = T(0);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) { ww = Num<T>::fma_(W[c][N - 1], W[c][N - 1], ww); wg = Num<T>::fma_(W[c][N - 1], g[c], wg); }
+				const T coef = beta * wg / (T(1) - beta * ww);
+				OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = Num<T>::fma_(coef, W[c][N - 1], g[c]);
 			}
 		}
-		if constexpr (!SIMPLE) {
-			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] += SM(F::SC + 6 + c);
+		if (!SIMPLE || tc.decoupling == OSC_IMPEDANCE) {  // + C^T F_f (and C^T F* when Lambda_mod = I)
+			T f[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = (SIMPLE ? T(0) : SM(F::SC + 6 + c)) + (tc.decoupling == OSC_IMPEDANCE ? g[c] : T(0));
+			OSC_UNROLL for (int c = 0; c < 6; ++c) {
+				T s = f[c] / SM(F::cli(c));
+				OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) s = Num<T>::fma_(SM(F::CC + c2 * (c2 - 1) / 2 + c), f[c2], s);
+				g[c] = (tc.decoupling == OSC_IMPEDANCE ? T(0) : g[c]) + s;
+			}
 		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			T s = T(0);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(Y[c][i], f[c], s);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(W[c][i], g[c], s);
 			h[i] = s;
 		}
 	}
@@ -468,8 +469,6 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 #undef OSC_FALL_BACK
-#undef OSC_CFWD
-#undef OSC_CBWD
 #undef SM
 }
 
