@@ -55,7 +55,6 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	// that the loads of the control law (P1b) and of the joint task (P11) do not pay a DRAM round trip each ----
 	{
 		auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
-		_Pragma("unroll 1") for (int e = 0; e < N; ++e) pf(&rP(RobotL<N>::DQ + e));
 		_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
 		_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
 		_Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
@@ -63,10 +62,16 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		pf(&mI(ML::HIST_LEN));
 	}
 
-	// ---- P1: sin/cos of every joint ----
+	// ---- P1: sin/cos of every joint.  q and dq are fetched as ONE batch of independent loads into the stash (a load per
+	// rolled iteration would pay a DRAM round trip each: profiles/README.md r1f) ----
+	{
+		T q[N], dq[N];
+		OSC_UNROLL for (int i = 0; i < N; ++i) { q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i); }
+		OSC_UNROLL for (int i = 0; i < N; ++i) { SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i]; }
+	}
 	_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
 		T s, c;
-		Num<T>::sincos_(rP(RobotL<N>::Q + i), &s, &c);
+		Num<T>::sincos_(SM(F::SC + 2 * i), &s, &c);
 		SM(F::SC + 2 * i) = s;
 		SM(F::SC + 2 * i + 1) = c;
 	}
@@ -87,7 +92,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 			T pre[3][3], d[3];
 			mm3(Rp, ch.rot[i], pre);
 			mv3(Rp, ch.xyz[i], d);
-			const T s = SM(F::SC + 2 * i), c = SM(F::SC + 2 * i + 1), dqi = rP(RobotL<N>::DQ + i);
+			const T s = SM(F::SC + 2 * i), c = SM(F::SC + 2 * i + 1), dqi = SM(F::MM + i);
 			OSC_UNROLL for (int a = 0; a < 3; ++a) {
 				pp[a] += d[a];
 				Rp[a][0] = c * pre[a][0] + s * pre[a][1];
@@ -378,14 +383,14 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	OSC_FENCE();
 	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
 	{
-		const int ntypes = mI(ML::NTYPES);
+		const int ntypes = mI(ML::NTYPES), hist_len = mI(ML::HIST_LEN);
 		bool latch = ntypes == 0;
-		if (ntypes != 0 || mI(ML::HIST_LEN) != 0) {
+		if (ntypes != 0 || hist_len != 0) {
 			latch = latch || mI(ML::C2) > mI(ML::C1);
 			mI(ML::NTYPES) = 0; mI(ML::TYPES) = 0; mI(ML::C1) = 0; mI(ML::C2) = 0; mI(ML::HIST_LEN) = 0; mI(ML::HIST_HEAD) = 0;
 		}
 		if (ex && latch) {
-			OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = rP(RobotL<N>::Q + i);
+			OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = rP.ro(RobotL<N>::Q + i);
 		}
 	}
 
@@ -428,17 +433,23 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u_last * u_last));  // |L_BIE^-1 L u|^2
 		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = T(1);
 		T va = T(0), vu = T(0);
-		if constexpr (SIMPLE) {  // joint PID, one joint at a time (JointTask.cpp:319-346 without velocity saturation)
+		if constexpr (SIMPLE) {  // joint PID (JointTask.cpp:319-346 without velocity saturation): every load first, then the stores
+			T q[N], dq[N], gp[N], gv[N], ga[N], ig[N];
 			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				const T qi = rP(RobotL<N>::Q + i), dqi = rP(RobotL<N>::DQ + i);
-				const T e = qi - jP(JL::GOAL_POS + i);
-				const T ie = jP(JL::INTEG + i) + e * jc.dt;
-				jP(JL::INTEG + i) = ie;
-				const T dv = jP(JL::GOAL_VEL + i);
-				const T upd = -jc.kp[i] * e - jc.kv[i] * (dqi - dv) - jc.ki[i] * ie;
-				va = Num<T>::fma_(v[i], jP(JL::GOAL_ACC + i), va);
+				q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i);
+				gp[i] = jP.ro(JL::GOAL_POS + i); gv[i] = jP.ro(JL::GOAL_VEL + i); ga[i] = jP.ro(JL::GOAL_ACC + i);
+				ig[i] = jP(JL::INTEG + i);
+			}
+			OSC_UNROLL for (int i = 0; i < N; ++i) {
+				const T e = q[i] - gp[i];
+				ig[i] = Num<T>::fma_(e, jc.dt, ig[i]);
+				const T upd = -jc.kp[i] * e - jc.kv[i] * (dq[i] - gv[i]) - jc.ki[i] * ig[i];
+				va = Num<T>::fma_(v[i], ga[i], va);
 				vu = Num<T>::fma_(v[i], upd, vu);
-				if (ex) { jS(JL::CUR_POS + i) = qi; jS(JL::CUR_VEL + i) = dqi; jS(JL::DES_VEL + i) = dv; }
+			}
+			OSC_UNROLL for (int i = 0; i < N; ++i) jP(JL::INTEG + i) = ig[i];
+			if (ex) {
+				OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = q[i]; jS(JL::CUR_VEL + i) = dq[i]; jS(JL::DES_VEL + i) = gv[i]; }
 			}
 		} else {
 			T q[N], dq[N], upd[N], acc[N];

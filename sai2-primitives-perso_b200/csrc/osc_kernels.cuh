@@ -49,6 +49,8 @@ template <class T> struct Row {
 	T* base;
 	int64_t stride, r;
 	OSC_DEV T& operator()(int e) const { return base[(int64_t)e * stride + r]; }
+	// read-only load (ld.global.nc): ONLY for rows the running kernel never writes; lets the compiler hoist it over stores
+	OSC_DEV T ro(int e) const { return __ldg(base + (int64_t)e * stride + r); }
 };
 template <class T, int R, int C> OSC_DEV void ld_mat(const Row<T>& a, int off, T (&A)[R][C]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i)

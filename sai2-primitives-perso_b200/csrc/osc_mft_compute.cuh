@@ -246,46 +246,38 @@ template <class T, int N>
 OSC_DEV void mft_control_law_motion_only(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const T (&v)[3], const T (&w)[3], const T (&x)[3],
 										 const T (&R)[3][3], T (&Fstar)[6], bool export_vectors) {
 	using L = MftL<N>;
+	// every load first (goals are read-only rows of this kernel, the integrators are read-modify-write), then the arithmetic,
+	// then the stores: a load placed after a store through the same arena cannot be hoisted by the compiler and costs a
+	// serialised memory round trip (profiles/README.md r1f)
+	T xg[3], vd[3], ad[3], Rg[3][3], wd[3], bd[3], ip[3], io[3], oe[3];
+	OSC_UNROLL for (int a = 0; a < 3; ++a) {
+		xg[a] = tP.ro(L::GOAL_POS + a); vd[a] = tP.ro(L::GOAL_LINVEL + a); ad[a] = tP.ro(L::GOAL_LINACC + a);
+		wd[a] = tP.ro(L::GOAL_ANGVEL + a); bd[a] = tP.ro(L::GOAL_ANGACC + a);
+		OSC_UNROLL for (int b = 0; b < 3; ++b) Rg[a][b] = tP.ro(L::GOAL_ORI + 3 * a + b);
+		ip[a] = tP(L::INT_POS + a); io[a] = tP(L::INT_ORI + a);
+	}
+	orientation_error<T>(Rg, R, oe);
+	OSC_UNROLL for (int a = 0; a < 3; ++a) {
+		const T e = x[a] - xg[a];
+		ip[a] = ip[a] + e * tc.dt;
+		Fstar[a] = ad[a] - tc.kp_pos[a] * e - tc.kv_pos[a] * (v[a] - vd[a]) - tc.ki_pos[a] * ip[a];
+		io[a] = io[a] + oe[a] * tc.dt;
+		Fstar[3 + a] = bd[a] - tc.kp_ori[a] * oe[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io[a];
+	}
+	st_vec<T, 3>(tP, L::INT_POS, ip);
+	st_vec<T, 3>(tP, L::INT_ORI, io);
+	st_vec<T, 3>(tP, L::CUR_POS, x);
+	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
 	if (export_vectors) {
 		st_vec<T, 3>(tS, L::CUR_V, v);
 		st_vec<T, 3>(tS, L::CUR_W, w);
+		st_vec<T, 3>(tS, L::DES_POS, xg);
+		st_vec<T, 3>(tS, L::DES_LINVEL, vd);
+		st_vec<T, 3>(tS, L::ORI_ERR, oe);
+		st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
+		st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
+		st_vec<T, 6>(tS, L::UMF, Fstar);
 	}
-	st_vec<T, 3>(tP, L::CUR_POS, x);
-	st_mat<T, 3, 3>(tP, L::CUR_ORI, R);
-	{
-		T xg[3], vd[3], ad[3];
-		ld_vec<T, 3>(tP, L::GOAL_POS, xg);
-		ld_vec<T, 3>(tP, L::GOAL_LINVEL, vd);
-		ld_vec<T, 3>(tP, L::GOAL_LINACC, ad);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			const T e = x[a] - xg[a];
-			const T ip = tP(L::INT_POS + a) + e * tc.dt;
-			tP(L::INT_POS + a) = ip;
-			Fstar[a] = ad[a] - tc.kp_pos[a] * e - tc.kv_pos[a] * (v[a] - vd[a]) - tc.ki_pos[a] * ip;
-		}
-		if (export_vectors) {
-			st_vec<T, 3>(tS, L::DES_POS, xg);
-			st_vec<T, 3>(tS, L::DES_LINVEL, vd);
-		}
-	}
-	{
-		T Rg[3][3], oe[3], wd[3], bd[3];
-		ld_mat<T, 3, 3>(tP, L::GOAL_ORI, Rg);
-		orientation_error<T>(Rg, R, oe);
-		ld_vec<T, 3>(tP, L::GOAL_ANGVEL, wd);
-		ld_vec<T, 3>(tP, L::GOAL_ANGACC, bd);
-		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			const T io = tP(L::INT_ORI + a) + oe[a] * tc.dt;
-			tP(L::INT_ORI + a) = io;
-			Fstar[3 + a] = bd[a] - tc.kp_ori[a] * oe[a] - tc.kv_ori[a] * (w[a] - wd[a]) - tc.ki_ori[a] * io;
-		}
-		if (export_vectors) {
-			st_vec<T, 3>(tS, L::ORI_ERR, oe);
-			st_mat<T, 3, 3>(tS, L::DES_ORI, Rg);
-			st_vec<T, 3>(tS, L::DES_ANGVEL, wd);
-		}
-	}
-	if (export_vectors) st_vec<T, 6>(tS, L::UMF, Fstar);
 }
 
 // same, from the task Jacobian: v = J[0:3] dq, w = J[3:6] dq (MotionForceTask.cpp:293-298)
