@@ -250,6 +250,9 @@ template <class T, int N>
 __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1, int64_t stride,
 															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law) {
+	// launched with programmatic stream serialisation behind the fused kernel: its launch latency overlaps the fused kernel's
+	// run; the fallback list is complete (and visible) once the wait returns.  A no-op under a plain launch.
+	asm volatile("griddepcontrol.wait;" ::: "memory");
 	const int n = *fb_count;
 	if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count_next = 0;
 	for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {

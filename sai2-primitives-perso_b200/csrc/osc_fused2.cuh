@@ -62,6 +62,8 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		pf(&mI(ML::HIST_LEN));
 	}
 
+	asm volatile("griddepcontrol.launch_dependents;");  // lets the launch of k_tick_tail proceed under this kernel
+
 	// ---- P1: sin/cos of every joint.  q and dq are fetched as ONE batch of independent loads into the stash (a load per
 	// rolled iteration would pay a DRAM round trip each: profiles/README.md r1f) ----
 	{

@@ -173,7 +173,21 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 #undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
-		k_tick_tail<T, N><<<tail_blocks, OSC_THREADS, 0, b.stream>>>(ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0, cnt, nxt, list, reuse_law);
+		{
+			cudaLaunchConfig_t cfg = {};
+			cfg.gridDim = dim3(tail_blocks);
+			cfg.blockDim = dim3(OSC_THREADS);
+			cfg.stream = b.stream;
+			cudaLaunchAttribute at[1];
+			at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+			at[0].val.programmaticStreamSerializationAllowed = 1;
+			static const bool pdl = !getenv("OSC_NO_PDL");
+			cfg.attrs = at;
+			cfg.numAttrs = pdl ? 1 : 0;
+			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<T, N>, ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
+											   (const int*)cnt, nxt, (const int*)list, reuse_law);
+			if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_tick_tail)");
+		}
 		if (int rc = done(b, "k_tick_tail")) return rc;
 		b.fb_last = b.fb_parity;
 		b.fb_parity ^= 1;
