@@ -48,6 +48,16 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	if (r >= B) return;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
 	const Row<int32_t> mI{tk0.I, stride, r};
+	// Row addresses are pure functions of r: left alone, the compiler computes them once at the top and SPILLS the 64-bit
+	// addresses across the whole kernel (r1g: LDL of addresses ahead of every late load/store).  Each memory phase therefore
+	// re-derives its rows from a laundered copy of r.
+#define OSC_FRESH_ROWS()                                                                                                            \
+	int64_t r_ = r;                                                                                                                 \
+	asm volatile("" : "+l"(r_));                                                                                                    \
+	const Row<T> rP{rob.P, stride, r_}, rS{rob.S, stride, r_}, mP{tk0.P, stride, r_}, mS{tk0.S, stride, r_}, jP{tk1.P, stride, r_}, \
+		jS{tk1.S, stride, r_};                                                                                                      \
+	const Row<int32_t> mI{tk0.I, stride, r_};                                                                                       \
+	(void)rP; (void)rS; (void)mP; (void)mS; (void)jP; (void)jS; (void)mI
 	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
 	int status = 0;
 
@@ -113,6 +123,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		cross3(w, x, v);
 		OSC_UNROLL for (int a = 0; a < 3; ++a) v[a] -= mo[a];
 		T Fstar[6], Ff[6];
+		OSC_FRESH_ROWS();
 		if constexpr (SIMPLE) {
 			mft_control_law_motion_only<T, N>(tc, mP, mS, v, w, x, Rc, Fstar, ex);
 			OSC_UNROLL for (int i = 0; i < 6; ++i) Ff[i] = T(0);
@@ -383,6 +394,8 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	// Y (= J) is dead from here on.
 
 	OSC_FENCE();
+	{  // fresh rows for the closing memory phases
+	OSC_FRESH_ROWS();
 	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
 	{
 		const int ntypes = mI(ML::NTYPES), hist_len = mI(ML::HIST_LEN);
@@ -481,6 +494,8 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		mI(ML::INS) = 6;
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
+	}
+#undef OSC_FRESH_ROWS
 #undef OSC_FALL_BACK
 #undef SM
 }
