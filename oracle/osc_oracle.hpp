@@ -255,6 +255,12 @@ inline Svd jacobi_svd(const Mat& A) {
 	Mat W = tr ? A.T() : A;  // rows >= cols
 	const int m = W.r, n = W.c;
 	Mat R = Mat::Identity(n);
+	// Eigen's JacobiSVD stops on an ABSOLUTE threshold tied to the largest diagonal entry (precision x maxDiagEntry): columns at
+	// rounding-noise level are not rotated against each other.  Same here: columns below 1e-14 |A|_F are numerically null.
+	double negl = 0;
+	for (int i = 0; i < m; ++i)
+		for (int j = 0; j < n; ++j) negl += W(i, j) * W(i, j);
+	negl *= 1e-28;
 	for (int sweep = 0; sweep < 60; ++sweep) {
 		bool rotated = false;
 		for (int p = 0; p < n - 1; ++p)
@@ -265,7 +271,7 @@ inline Svd jacobi_svd(const Mat& A) {
 					be += W(i, q) * W(i, q);
 					ga += W(i, p) * W(i, q);
 				}
-				if (ga == 0.0 || std::fabs(ga) <= 1e-16 * std::sqrt(al * be)) continue;
+				if (ga == 0.0 || al <= negl || be <= negl || std::fabs(ga) <= 1e-15 * std::sqrt(al * be)) continue;
 				rotated = true;
 				double zeta = (be - al) / (2.0 * ga);
 				double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));

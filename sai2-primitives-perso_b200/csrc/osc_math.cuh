@@ -22,7 +22,7 @@ template <> struct Num<double> {
 	static OSC_DEV void sincos_(double x, double* s, double* c) { ::sincos(x, s, c); }
 	static OSC_DEV double fma_(double a, double b, double c) { return ::fma(a, b, c); }
 	static OSC_DEV double eps() { return 2.220446049250313e-16; }
-	static OSC_DEV double jacobi_tol() { return 1e-16; }
+	static OSC_DEV double jacobi_tol() { return 1e-15; }  // ~ sqrt(rows) eps (LAPACK dgesvj); below eps the test can never pass
 	static OSC_DEV double tiny_sv() { return 1e-14; }
 };
 template <> struct Num<float> {
@@ -32,7 +32,7 @@ template <> struct Num<float> {
 	static OSC_DEV void sincos_(float x, float* s, float* c) { ::sincosf(x, s, c); }
 	static OSC_DEV float fma_(float a, float b, float c) { return ::fmaf(a, b, c); }
 	static OSC_DEV float eps() { return 1.1920929e-7f; }
-	static OSC_DEV float jacobi_tol() { return 6e-8f; }
+	static OSC_DEV float jacobi_tol() { return 5e-7f; }
 	static OSC_DEV float tiny_sv() { return 1e-6f; }
 };
 
@@ -266,6 +266,13 @@ template <class T, int N> OSC_DEV bool spd_above(const T (&A)[N][N], T shift) {
 template <class T, int R, int C> OSC_DEV bool svd_onesided(T (&A)[R][C], T (&W)[C][C], T (&s)[C]) {
 	OSC_UNROLL for (int i = 0; i < C; ++i)
 		OSC_UNROLL for (int j = 0; j < C; ++j) W[i][j] = (i == j) ? T(1) : T(0);
+	// columns below tiny_sv x |A|_F are numerically null: they are replaced by the Gram-Schmidt completion below, and
+	// rotating rounding noise against rounding noise never meets the relative test (a rank-deficient N_prec would spin
+	// through all 40 sweeps and raise OSC_STATUS_SVD_NOT_CONVERGED for nothing)
+	T negl = T(0);
+	OSC_UNROLL for (int i = 0; i < R; ++i)
+		OSC_UNROLL for (int j = 0; j < C; ++j) negl = Num<T>::fma_(A[i][j], A[i][j], negl);
+	negl *= Num<T>::tiny_sv() * Num<T>::tiny_sv();
 	bool converged = false;
 	for (int sweep = 0; sweep < 40 && !converged; ++sweep) {
 		bool rotated = false;
@@ -277,7 +284,7 @@ template <class T, int R, int C> OSC_DEV bool svd_onesided(T (&A)[R][C], T (&W)[
 					be = Num<T>::fma_(A[i][q], A[i][q], be);
 					ga = Num<T>::fma_(A[i][p], A[i][q], ga);
 				}
-				const bool skip = (ga == T(0)) || (Num<T>::abs_(ga) <= Num<T>::jacobi_tol() * Num<T>::sqrt_(al * be));
+				const bool skip = (ga == T(0)) || al <= negl || be <= negl || (Num<T>::abs_(ga) <= Num<T>::jacobi_tol() * Num<T>::sqrt_(al * be));
 				if (!skip) {
 					rotated = true;
 					const T zeta = (be - al) / (T(2) * ga);
