@@ -260,8 +260,8 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 		model_robot<T, N>(ch, rob, stride, r, 1, gravity);
 		mft_update_robot<T, N>(ch, tc, rob, tk0, nullptr, stride, r, 0);
 		jt_update_robot<T, N>(jc, rob, tk1, tk0.S + (int64_t)MftL<N>::NTP * stride, stride, r);
-		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1, reuse_law);
-		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2);
+		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1, reuse_law & 1);
+		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2, reuse_law & 2);
 		if (gravity) {
 			const Row<T> rS{rob.S, stride, r};
 			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += rS(RobotL<N>::GRAV + i);

@@ -26,7 +26,11 @@ template <int N> struct F2 {
 	// 1 / C_ii: the spare slots behind F*, F_f first (2N - 12), the rest behind C
 	static constexpr int SPARE = 2 * N - 12;
 	__host__ __device__ static constexpr int cli(int i) { return i < SPARE ? SC + 12 + i : CC + 15 + (i - SPARE); }
-	static constexpr int SLOTS = CC + 15 + (6 - SPARE);
+	// SIMPLE kernel (no C stored): F* at CC..CC+5, the joint PID command u_pd (N) and the joint goal acceleration (N) behind it
+	static constexpr int UPD = CC + 6;
+	static constexpr int GAC = CC + 6 + N;
+	static constexpr int SLOTS_GENERAL = CC + 15 + (6 - SPARE);
+	static constexpr int SLOTS = SLOTS_GENERAL > GAC + N ? SLOTS_GENERAL : GAC + N;
 };
 
 template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c) { Num<T>::sincos_(x, s, c); }
@@ -67,7 +71,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
 		_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
 		_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
-		_Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+		if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
 		pf(&mI(ML::NTYPES));
 		pf(&mI(ML::HIST_LEN));
 	}
@@ -76,7 +80,28 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 
 	// ---- P1: sin/cos of every joint.  q and dq are fetched as ONE batch of independent loads into the stash (a load per
 	// rolled iteration would pay a DRAM round trip each: profiles/README.md r1f) ----
-	{
+	if constexpr (SIMPLE && N == 7) {
+		// ... together with every input of the joint task: its PID command u_pd and the goal acceleration wait in the stash for
+		// the range basis (P11), so that the kernel ends without a load phase.  The integrated error is stored here; a robot
+		// that falls back tells k_tick_tail not to integrate again (reuse_law bit 1).
+		T q[N], dq[N], gp[N], gv[N], ga[N], ig[N];
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i);
+			gp[i] = jP.ro(JL::GOAL_POS + i); gv[i] = jP.ro(JL::GOAL_VEL + i); ga[i] = jP.ro(JL::GOAL_ACC + i);
+			ig[i] = jP(JL::INTEG + i);
+		}
+		OSC_UNROLL for (int i = 0; i < N; ++i) {  // JointTask.cpp:319-346 without velocity saturation
+			SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i];
+			const T e = q[i] - gp[i];
+			ig[i] = Num<T>::fma_(e, jc.dt, ig[i]);
+			SM(F::UPD + i) = -jc.kp[i] * e - jc.kv[i] * (dq[i] - gv[i]) - jc.ki[i] * ig[i];
+			SM(F::GAC + i) = ga[i];
+		}
+		OSC_UNROLL for (int i = 0; i < N; ++i) jP(JL::INTEG + i) = ig[i];
+		if (ex) {
+			OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = q[i]; jS(JL::CUR_VEL + i) = dq[i]; jS(JL::DES_VEL + i) = gv[i]; }
+		}
+	} else {
 		T q[N], dq[N];
 		OSC_UNROLL for (int i = 0; i < N; ++i) { q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i); }
 		OSC_UNROLL for (int i = 0; i < N; ++i) { SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i]; }
@@ -130,11 +155,14 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		} else {
 			mft_control_law_vw<T, N, true>(tc, mP, mS, mI, stride, r, v, w, x, Rc, Fstar, Ff, status, ex);
 		}
-		OSC_UNROLL for (int i = 0; i < 6; ++i) { SM(F::CC + i) = Fstar[i]; SM(F::CC + 6 + i) = Ff[i]; }
+		OSC_UNROLL for (int i = 0; i < 6; ++i) {
+			SM(F::CC + i) = Fstar[i];
+			if constexpr (!SIMPLE) SM(F::CC + 6 + i) = Ff[i];
+		}
 	}
 #define OSC_FALL_BACK()                                                                      \
 	{                                                                                        \
-		OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) { mS(ML::UMF + i_) = SM(F::CC + i_); mS(ML::FFB + i_) = SM(F::CC + 6 + i_); } \
+		OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) { mS(ML::UMF + i_) = SM(F::CC + i_); mS(ML::FFB + i_) = SIMPLE ? T(0) : SM(F::CC + 6 + i_); } \
 		if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);       \
 		fb_list[atomicAdd(fb_count, 1)] = (int)r;                                            \
 		return;                                                                              \
@@ -278,8 +306,10 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		const bool sep_ok = spd_above<float, 6>(G, smax * smax * lmax_hi * 1.02f);
 		if (!(s0_ok && sep_ok)) OSC_FALL_BACK()  // not provably non-singular: API-faithful route
 	}
-	// sin/cos are dead: move F*, F_f into their slots (the C slots are needed by P8)
-	OSC_UNROLL for (int i = 0; i < 12; ++i) SM(F::SC + i) = SM(F::CC + i);
+	// sin/cos are dead: move F*, F_f into their slots (the C slots are needed by P8; the SIMPLE kernel stores no C)
+	if constexpr (!SIMPLE) {
+		OSC_UNROLL for (int i = 0; i < 12; ++i) SM(F::SC + i) = SM(F::CC + i);
+	}
 
 	OSC_FENCE();
 	// ---- P7: Y = L^-1 J^T in place (J[c][:] <- L^-1 J[c][:]), L streamed row by row from the stash ----
@@ -299,17 +329,25 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	// ---- P8: orthonormalise the rows of Y in place (modified Gram-Schmidt): Y = C W with W W^T = I and C lower triangular,
 	// i.e. C = chol(A) for A = Y Y^T = J M^-1 J^T without ever forming A (and without squaring its condition number).
 	// C goes to the stash (strictly lower part + 1/C_cc); W stays in the registers of Y. ----
+	// The SIMPLE kernel carries F* through the same row operations as an extra column: C^-1 [Y | F*] = [W | g] with
+	// g = C^-1 F* = C^T Lambda F*, which is all P10 needs of C -- so C is not stored at all there.
+	T g[6];
+	if constexpr (SIMPLE) {
+		OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::CC + c);
+	}
 	OSC_UNROLL for (int c = 0; c < 6; ++c) {
 		T nn = T(0);
 		OSC_UNROLL for (int i = 0; i < N; ++i) nn = Num<T>::fma_(Y[c][i], Y[c][i], nn);
 		if (!(nn > T(0))) status |= 16;
 		const T inv = Num<T>::rsqrt_(nn);
-		SM(F::cli(c)) = inv;
+		if constexpr (SIMPLE) g[c] *= inv;
+		else SM(F::cli(c)) = inv;
 		OSC_UNROLL for (int i = 0; i < N; ++i) Y[c][i] *= inv;
 		OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) {
 			T rr = T(0);
 			OSC_UNROLL for (int i = 0; i < N; ++i) rr = Num<T>::fma_(Y[c][i], Y[c2][i], rr);
-			SM(F::CC + c2 * (c2 - 1) / 2 + c) = rr;
+			if constexpr (SIMPLE) g[c2] = Num<T>::fma_(-rr, g[c], g[c2]);
+			else SM(F::CC + c2 * (c2 - 1) / 2 + c) = rr;
 			OSC_UNROLL for (int i = 0; i < N; ++i) Y[c2][i] = Num<T>::fma_(-rr, Y[c][i], Y[c2][i]);
 		}
 	}
@@ -360,25 +398,26 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	// (SingularityHandler.cpp:160-225, 307-309).  Lambda = A^-1 = C^-T C^-1, so C^T Lambda F* = C^-1 F*: one forward solve. ----
 	T h[N];
 	{
-		T g[6];
-		OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::SC + c);
-		if (tc.decoupling != OSC_IMPEDANCE) {
-			OSC_UNROLL for (int i = 0; i < 6; ++i) {  // g <- C^-1 F*
-				T s = g[i];
-				OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<T>::fma_(-SM(F::CC + i * (i - 1) / 2 + m), g[m], s);
-				g[i] = s * SM(F::cli(i));
-			}
-			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
-				// A_BIE = A - beta y y^T with y = C w (w = last column of W):  C^T A_BIE^-1 F* = g + beta w (w . g) / (1 - beta |w|^2)
-				T ww = T(0), wg = T(0);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) { ww = Num<T>::fma_(W[c][N - 1], W[c][N - 1], ww); wg = Num<T>::fma_(W[c][N - 1], g[c], wg); }
-				const T coef = beta * wg / (T(1) - beta * ww);
-				OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = Num<T>::fma_(coef, W[c][N - 1], g[c]);
+		if constexpr (!SIMPLE) {
+			OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::SC + c);
+			if (tc.decoupling != OSC_IMPEDANCE) {
+				OSC_UNROLL for (int i = 0; i < 6; ++i) {  // g <- C^-1 F*
+					T s = g[i];
+					OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<T>::fma_(-SM(F::CC + i * (i - 1) / 2 + m), g[m], s);
+					g[i] = s * SM(F::cli(i));
+				}
 			}
 		}
-		if (!SIMPLE || tc.decoupling == OSC_IMPEDANCE) {  // + C^T F_f (and C^T F* when Lambda_mod = I)
+		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
+			// A_BIE = A - beta y y^T with y = C w (w = last column of W):  C^T A_BIE^-1 F* = g + beta w (w . g) / (1 - beta |w|^2)
+			T ww = T(0), wg = T(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) { ww = Num<T>::fma_(W[c][N - 1], W[c][N - 1], ww); wg = Num<T>::fma_(W[c][N - 1], g[c], wg); }
+			const T coef = beta * wg / (T(1) - beta * ww);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = Num<T>::fma_(coef, W[c][N - 1], g[c]);
+		}
+		if constexpr (!SIMPLE) {  // + C^T F_f (and C^T F* when Lambda_mod = I)
 			T f[6];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = (SIMPLE ? T(0) : SM(F::SC + 6 + c)) + (tc.decoupling == OSC_IMPEDANCE ? g[c] : T(0));
+			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = SM(F::SC + 6 + c) + (tc.decoupling == OSC_IMPEDANCE ? g[c] : T(0));
 			OSC_UNROLL for (int c = 0; c < 6; ++c) {
 				T s = f[c] / SM(F::cli(c));
 				OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) s = Num<T>::fma_(SM(F::CC + c2 * (c2 - 1) / 2 + c), f[c2], s);
@@ -411,7 +450,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 
 	OSC_FENCE();
 	// ---- P11: tau_1 = L h and w = L u (one sweep over L), parked in the dead C slots ----
-	constexpr int TAU1 = F::CC, WW = F::CC + N;  // N = 7: 14 of the 15 C slots
+	constexpr int TAU1 = SIMPLE ? F::SC : F::CC, WW = TAU1 + N;  // dead slots: sin/cos (SIMPLE, F* lives in registers) or C
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		const T ld = T(1) / SM(F::LI + i);
 		T s1 = ld * h[i], sw = ld * u[i];
@@ -448,23 +487,10 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u_last * u_last));  // |L_BIE^-1 L u|^2
 		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = T(1);
 		T va = T(0), vu = T(0);
-		if constexpr (SIMPLE) {  // joint PID (JointTask.cpp:319-346 without velocity saturation): every load first, then the stores
-			T q[N], dq[N], gp[N], gv[N], ga[N], ig[N];
+		if constexpr (SIMPLE) {  // u_pd and the goal acceleration were staged by P1
 			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i);
-				gp[i] = jP.ro(JL::GOAL_POS + i); gv[i] = jP.ro(JL::GOAL_VEL + i); ga[i] = jP.ro(JL::GOAL_ACC + i);
-				ig[i] = jP(JL::INTEG + i);
-			}
-			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				const T e = q[i] - gp[i];
-				ig[i] = Num<T>::fma_(e, jc.dt, ig[i]);
-				const T upd = -jc.kp[i] * e - jc.kv[i] * (dq[i] - gv[i]) - jc.ki[i] * ig[i];
-				va = Num<T>::fma_(v[i], ga[i], va);
-				vu = Num<T>::fma_(v[i], upd, vu);
-			}
-			OSC_UNROLL for (int i = 0; i < N; ++i) jP(JL::INTEG + i) = ig[i];
-			if (ex) {
-				OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = q[i]; jS(JL::CUR_VEL + i) = dq[i]; jS(JL::DES_VEL + i) = gv[i]; }
+				va = Num<T>::fma_(v[i], SM(F::GAC + i), va);
+				vu = Num<T>::fma_(v[i], SM(F::UPD + i), vu);
 			}
 		} else {
 			T q[N], dq[N], upd[N], acc[N];
@@ -518,7 +544,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_gravity(const __grid_constant__
 // what the second-generation kernel adds to fused_tick_supported: a revolute chain with the control link on the last body
 inline bool fused2_simple(const Batch& b) {
 	const osc_mft_params& p = b.tasks[0].mp;
-	return p.force_space_dimension == 0 && p.moment_space_dimension == 0 && !p.closed_loop_force_control && !p.closed_loop_moment_control &&
+	return p.dynamic_decoupling_type != OSC_IMPEDANCE && p.force_space_dimension == 0 && p.moment_space_dimension == 0 && !p.closed_loop_force_control && !p.closed_loop_moment_control &&
 		   !p.use_velocity_saturation && !b.tasks[1].jp.use_velocity_saturation;
 }
 inline bool fused2_supported(Batch& b) {

@@ -10,14 +10,14 @@ namespace osc {
 // PID (or velocity-saturated) command u and the feed-forward acceleration; rows >= k are zero.
 template <class T, int N, bool NOSAT = false>
 OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, const T (&cp)[N], const T (&cv)[N], T (&u)[N], T (&acc)[N],
-					   bool export_vectors) {
+					   bool export_vectors, bool integrate = true) {
 	using L = JtL<N>;
 	T dv[N];
 	const int k = jc.k;
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		const T e = cp[i] - tP(L::GOAL_POS + i);
 		T ie = tP(L::INTEG + i);
-		if (i < k) { ie += e * jc.dt; tP(L::INTEG + i) = ie; }  // JointTask.cpp:323-324
+		if (i < k && integrate) { ie += e * jc.dt; tP(L::INTEG + i) = ie; }  // JointTask.cpp:323-324
 		dv[i] = tP(L::GOAL_VEL + i);
 		acc[i] = (i < k) ? tP(L::GOAL_ACC + i) : T(0);
 		if (!NOSAT && jc.use_vel_sat) {  // JointTask.cpp:327-340 (quirk Q7: loop to k)
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant
 
 template <class T, int N>
 __device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r, int with_tau_prec,
-								 int accumulate) {
+								 int accumulate, int integrated_already = 0) {
 	using L = JtL<N>;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
@@ -156,7 +156,7 @@ __device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<T>& rob, const
 	OSC_UNROLL for (int i = 0; i < N; ++i) tau[i] = T(0);
 	if (rank > 0) {
 		T u[N], acc[N];
-		jt_pd_law<T, N>(jc, tP, tS, cp, cv, u, acc, true);
+		jt_pd_law<T, N>(jc, tP, tS, cp, cv, u, acc, true, !integrated_already);  // k_tick_fused2 integrates before it can fall back
 		T Rg[N][N], Lam[N][N], Lm[N][N], Np[N][N];
 		ld_mat<T, N, N>(tS, L::RANGE, Rg);
 		ld_mat<T, N, N>(tS, L::LAM, Lam);

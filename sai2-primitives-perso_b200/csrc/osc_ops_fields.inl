@@ -158,6 +158,12 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
 			const bool simple = fused2_simple(b) && !getenv("OSC_FUSED_NOSIMPLE");
+			if (simple && N == 7) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
+			if (getenv("OSC_DEBUG_OCC")) {
+				int nb = 0;
+				cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_tick_fused2<T, N, 128, true>, OSC_FUSED_THREADS, 0);
+				fprintf(stderr, "k_tick_fused2<%d,128,simple>: %d blocks/SM, %d stash slots\n", N, nb, F2<N>::SLOTS);
+			}
 			if (minb >= 8) {
 				if (simple) k_tick_fused2<T, N, 128, true><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 				else k_tick_fused2<T, N, 128, false><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
