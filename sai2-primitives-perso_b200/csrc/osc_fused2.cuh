@@ -175,14 +175,14 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	// M[i][j] = z . l in frame j.  Frame change child -> parent: x_parent = xyz + rot * Rz(q) * x_child.
 	{
 		T cm = T(0), h0 = T(0), h1 = T(0), h2 = T(0), Ixx = T(0), Ixy = T(0), Ixz = T(0), Iyy = T(0), Iyz = T(0), Izz = T(0);
-		_Pragma("unroll 1") for (int i = N - 1; i >= 0; --i) {
+		OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
 			cm += ch.mass[i];
 			h0 += ch.hb[i][0]; h1 += ch.hb[i][1]; h2 += ch.hb[i][2];
 			Ixx += ch.Ib[i][0]; Ixy += ch.Ib[i][1]; Ixz += ch.Ib[i][2]; Iyy += ch.Ib[i][3]; Iyz += ch.Ib[i][4]; Izz += ch.Ib[i][5];
 			T p0 = -h1, p1 = h0, p2 = T(0), l0 = Ixz, l1 = Iyz, l2 = Izz;
 			const int row = F::MM + i * (i + 1) / 2;
 			SM(row + i) = l2;
-			_Pragma("unroll 1") for (int j = i; j >= 1; --j) {
+			OSC_UNROLL for (int j = i; j >= 1; --j) {
 				const T s = SM(F::SC + 2 * j), c = SM(F::SC + 2 * j + 1);
 				const T a0 = c * p0 - s * p1, a1 = s * p0 + c * p1, b0 = c * l0 - s * l1, b1 = s * l0 + c * l1;
 				p0 = ch.rot[j][0][0] * a0 + ch.rot[j][0][1] * a1 + ch.rot[j][0][2] * p2;
