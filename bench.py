@@ -187,6 +187,8 @@ def main():
     ap.add_argument("--batch", type=int, default=65536, help="robots per GPU")
     ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tick-outputs", default="lazy", choices=["lazy", "tau"],
+                    help="lazy (default): the tick also writes every vector-valued getter of the reference; tau: torques only")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -212,6 +214,8 @@ def run_b200(args, rank, world, local_rank):
     real = torch.float64 if args.precision == 64 else torch.float32
     batch, w, t0, t1 = build_batch(osc_b200, abi, chain, B, local_rank, seed=2 + rank, precision=args.precision)
     batch.set_stream(torch.cuda.current_stream().cuda_stream)
+    if args.tick_outputs == "tau":
+        batch.set_tick_outputs(abi.TICK_OUTPUTS_TAU)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def barrier():
@@ -336,7 +340,7 @@ def run_b200(args, rank, world, local_rank):
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "robots_per_gpu": B, "hierarchy": "MotionForceTask(6-DoF, end-effector + 0.07 m) > JointTask(full)",
-                       "stacked": True, "l2": "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
+                       "stacked": True, "tick_outputs": args.tick_outputs, "l2": "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
             "p50_tick_us": float(np.median(step_ms) * 1e3), "p99_tick_us": float(np.percentile(step_ms, 99) * 1e3),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "path": "osc_set_field x5 + osc_tick with pinned HOST SoA buffers (C ABI)"},
