@@ -240,8 +240,10 @@ def run_b200(args, rank, world, local_rank):
         sampler.start()
     l0 = batch.launch_count()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    noflush = bool(os.environ.get("OSC_BENCH_NOFLUSH"))  # diagnosis only: a line measured this way is not a bench value
     for s, e in ev:
-        flush.zero_()
+        if not noflush:
+            flush.zero_()
         s.record()
         batch.tick(True, fetch=False)
         e.record()
@@ -340,7 +342,7 @@ def run_b200(args, rank, world, local_rank):
             "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "robots_per_gpu": B, "hierarchy": "MotionForceTask(6-DoF, end-effector + 0.07 m) > JointTask(full)",
-                       "stacked": True, "tick_outputs": args.tick_outputs, "l2": "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
+                       "stacked": True, "tick_outputs": args.tick_outputs, "l2": "NOT FLUSHED (diagnostic run)" if noflush else "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
             "p50_tick_us": float(np.median(step_ms) * 1e3), "p99_tick_us": float(np.percentile(step_ms, 99) * 1e3),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "path": "osc_set_field x5 + osc_tick with pinned HOST SoA buffers (C ABI)"},

@@ -37,8 +37,10 @@ template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c)
 
 // SIMPLE = plain motion task over a plain joint task (no force / moment space, open loop, no velocity saturation): the
 // host selects this instantiation from the uniform task parameters; F_f is identically zero there.
-template <class T, int N, int MAXREG, bool SIMPLE>
-__global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+// BT threads per block; SYNC: block-wide barriers at the phase boundaries keep the warps of a block inside the same stretch of
+// this 100 KB straight-line kernel, so that they share instruction-cache lines (r1k: instruction fetch was the top stall).
+template <class T, int N, int MAXREG, bool SIMPLE, int BT = OSC_FUSED_THREADS, bool SYNC = false>
+__global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 																		 const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
 																		 int64_t B, int64_t stride, int stacked, int gravity, int exports,
 																		 int* __restrict__ fb_count, int* __restrict__ fb_list) {
@@ -46,8 +48,12 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	using ML = MftL<N>;
 	using JL = JtL<N>;
 	using F = F2<N>;
-	__shared__ T sm[F::SLOTS * OSC_FUSED_THREADS];
-#define SM(slot) sm[(slot) * OSC_FUSED_THREADS + threadIdx.x]
+	extern __shared__ __align__(16) unsigned char osc_stash_raw[];
+	T* const sm = reinterpret_cast<T*>(osc_stash_raw);
+#define SM(slot) sm[(slot) * BT + threadIdx.x]
+#define OSC_PHASE()                       \
+	OSC_FENCE();                          \
+	if constexpr (SYNC) __syncthreads()
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
@@ -113,7 +119,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		SM(F::SC + 2 * i + 1) = c;
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P1b: a ROLLED forward-kinematics pass for what the control law needs: x, R of the compliant frame and its twist
 	// v = w x x - sum_i dq_i (z_i x o_i), w = sum_i dq_i z_i (= J dq, MotionForceTask.cpp:293-298) -- then the control law itself
 	// (MotionForceTask.cpp:278-509) while nothing else is live.  F*, F_f are parked in the C slots until sin/cos are dead.
@@ -168,7 +174,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		return;                                                                              \
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P2: mass matrix, composite rigid body recursion in BODY frames, tip to base (Sai2Model::updateModel) ----
 	// composite of bodies >= i in frame i: mass cm, first moment h, inertia about the frame origin I (xx xy xz yy yz zz).
 	// column i: momentum (p, l) of the composite under the unit joint twist (omega = z, v = 0), carried down the chain;
@@ -222,7 +228,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		}
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P3: M = L L^T in place in registers, then parked in the stash; bounded-inertia clamp pattern ----
 	T rho2 = T(1), beta = T(0);  // BIE: L_BIE = L except its last pivot; rho = L_nn / L_BIE,nn, beta = 1 - rho^2
 	{
@@ -249,7 +255,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		}
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P4: forward kinematics (revolute chain, control link on the last body) and the Jacobian at the compliant frame ----
 	T J[6][N];
 	{
@@ -283,7 +289,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		}
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P5: branch certificate in FP32 (a bound with a 2 % margin; see osc_fused.cuh) ----
 	{
 		float G[6][6];
@@ -311,7 +317,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		OSC_UNROLL for (int i = 0; i < 12; ++i) SM(F::SC + i) = SM(F::CC + i);
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P7: Y = L^-1 J^T in place (J[c][:] <- L^-1 J[c][:]), L streamed row by row from the stash ----
 	OSC_UNROLL for (int k = 0; k < N; ++k) {
 		T Lk[N];
@@ -325,7 +331,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 	T (&Y)[6][N] = J;
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P8: orthonormalise the rows of Y in place (modified Gram-Schmidt): Y = C W with W W^T = I and C lower triangular,
 	// i.e. C = chol(A) for A = Y Y^T = J M^-1 J^T without ever forming A (and without squaring its condition number).
 	// C goes to the stash (strictly lower part + 1/C_cc); W stays in the registers of Y. ----
@@ -353,7 +359,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 	T (&W)[6][N] = Y;
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P9: u = unit vector orthogonal to the rows of W (n = 7): P = I - W^T W = u u^T, N_1 = (L^-T u)(L u)^T ----
 	T u[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
@@ -393,7 +399,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P10: tau_1 = J^T (Lambda_mod F* + F_f) = L h with h = W^T g,  g = C^T (Lambda_mod F* + F_f)
 	// (SingularityHandler.cpp:160-225, 307-309).  Lambda = A^-1 = C^-T C^-1, so C^T Lambda F* = C^-1 F*: one forward solve. ----
 	T h[N];
@@ -432,7 +438,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	}
 	// Y (= J) is dead from here on.
 
-	OSC_FENCE();
+	OSC_PHASE();
 	{  // fresh rows for the closing memory phases
 	OSC_FRESH_ROWS();
 	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
@@ -448,7 +454,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 		}
 	}
 
-	OSC_FENCE();
+	OSC_PHASE();
 	// ---- P11: tau_1 = L h and w = L u (one sweep over L), parked in the dead C slots ----
 	constexpr int TAU1 = SIMPLE ? F::SC : F::CC, WW = TAU1 + N;  // dead slots: sin/cos (SIMPLE, F* lives in registers) or C
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
@@ -522,6 +528,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS) __maxnreg__(MAXREG) k_tick_
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 	}
 #undef OSC_FRESH_ROWS
+#undef OSC_PHASE
 #undef OSC_FALL_BACK
 #undef SM
 }

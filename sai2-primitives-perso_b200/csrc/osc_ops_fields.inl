@@ -159,18 +159,31 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			}
 			const bool simple = fused2_simple(b) && !getenv("OSC_FUSED_NOSIMPLE");
 			if (simple && N == 7) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
-			if (getenv("OSC_DEBUG_OCC")) {
-				int nb = 0;
-				cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_tick_fused2<T, N, 128, true>, OSC_FUSED_THREADS, 0);
-				fprintf(stderr, "k_tick_fused2<%d,128,simple>: %d blocks/SM, %d stash slots\n", N, nb, F2<N>::SLOTS);
-			}
-			if (minb >= 8) {
-				if (simple) k_tick_fused2<T, N, 128, true><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-				else k_tick_fused2<T, N, 128, false><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			} else {
-				if (simple) k_tick_fused2<T, N, 168, true><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-				else k_tick_fused2<T, N, 168, false><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			}
+			// block shape: 224 threads with phase barriers once the batch fills two such blocks per SM (r1l: 44.7 us against
+			// 45.7 us for 64-thread blocks at 65,536 robots), 64-thread blocks below that so that small batches still spread
+			// over the SMs.  OSC_FUSED_BT = 64 | 65 (64 + barriers) | 224 | 448 overrides (experiment knob).
+			static const int bt_env = [] { const char* e = getenv("OSC_FUSED_BT"); return e ? atoi(e) : 0; }();
+			const int bt = bt_env ? bt_env : (b.B >= 224 * 148 ? 224 : 64);
+			auto go = [&](auto kern, int threads) -> int {
+				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(T);
+				cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+				if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused2)");
+				if (getenv("OSC_DEBUG_OCC")) {
+					int nb = 0;
+					cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, threads, smem);
+					fprintf(stderr, "k_tick_fused2<%d>: %d threads/block, %d blocks/SM, %d stash slots\n", N, threads, nb, F2<N>::SLOTS);
+				}
+				const dim3 gg((unsigned)((b.B + threads - 1) / threads));
+				kern<<<gg, threads, smem, b.stream>>>(OSC_FUSED_ARGS);
+				return OSC_OK;
+			};
+			int rc = OSC_OK;
+			if (minb < 8) rc = simple ? go(k_tick_fused2<T, N, 168, true>, 64) : go(k_tick_fused2<T, N, 168, false>, 64);
+			else if (bt == 65) rc = simple ? go(k_tick_fused2<T, N, 128, true, 64, true>, 64) : go(k_tick_fused2<T, N, 128, false, 64, true>, 64);
+			else if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true>, 224);
+			else if (bt == 448) rc = simple ? go(k_tick_fused2<T, N, 128, true, 448, true>, 448) : go(k_tick_fused2<T, N, 128, false, 448, true>, 448);
+			else rc = simple ? go(k_tick_fused2<T, N, 128, true>, 64) : go(k_tick_fused2<T, N, 128, false>, 64);
+			if (rc) return rc;
 		} else {
 			if (minb >= 8) k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 			else if (minb >= 6) k_tick_fused<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);

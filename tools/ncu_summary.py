@@ -49,6 +49,25 @@ def main():
               for k in d if k.startswith("smsp__pcsamp_warps_issue_stalled_") and "not_issued" not in k}
     tot = sum(stalls.values()) or 1
     out["stall samples"] = {k: "%d (%.0f%%)" % (n, 100.0 * n / tot) for k, n in sorted(stalls.items(), key=lambda kv: -kv[1]) if n * 50 >= tot}
+    # executed FP64 work from the report's own SASS listing (thread instructions of DFMA/DADD/DMUL; an FMA counts 2 FLOP)
+    src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+    srows = list(csv.reader(io.StringIO(src)))
+    hi = next((i for i, r in enumerate(srows) if r and r[0] == "Address"), None)
+    if hi is not None:
+        col = {n: i for i, n in enumerate(srows[hi])}
+        ops = {"DFMA": 0, "DADD": 0, "DMUL": 0}
+        n_inst = 0
+        for r in srows[hi + 1:]:
+            if len(r) != len(srows[hi]):
+                continue
+            n_inst += 1
+            ins = r[col["Source"]].split()
+            op = (ins[1] if ins and ins[0].startswith("@") and len(ins) > 1 else (ins[0] if ins else "")).split(".")[0]
+            if op in ops:
+                ops[op] += int(r[col["Thread Instructions Executed"]] or 0)
+        out["SASS instructions in the kernel"] = n_inst
+        out["FP64 thread instructions"] = ops
+        out["executed FP64 FLOP per launch"] = 2 * ops["DFMA"] + ops["DADD"] + ops["DMUL"]
     if "--json" in sys.argv:
         print(json.dumps(out, indent=1))
     else:
