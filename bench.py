@@ -187,7 +187,7 @@ def main():
     ap.add_argument("--batch", type=int, default=65536, help="robots per GPU")
     ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--tick-outputs", default="lazy", choices=["lazy", "tau"],
+    ap.add_argument("--tick-outputs", default="lazy", choices=["lazy", "tau", "all"],
                     help="lazy (default): the tick also writes every vector-valued getter of the reference; tau: torques only")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -216,6 +216,8 @@ def run_b200(args, rank, world, local_rank):
     batch.set_stream(torch.cuda.current_stream().cuda_stream)
     if args.tick_outputs == "tau":
         batch.set_tick_outputs(abi.TICK_OUTPUTS_TAU)
+    elif args.tick_outputs == "all":  # the per-call (API-faithful) kernel sequence: every getter written every tick
+        batch.set_tick_outputs(abi.TICK_OUTPUTS_ALL)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def barrier():
