@@ -13,7 +13,7 @@ import numpy as np
 import osc_abi as abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libosc_b200.so")
+LIB_PATH = os.environ.get("OSC_B200_LIB") or os.path.join(_HERE, "libosc_b200.so")  # override: A/B runs of two builds
 _LIB = None
 
 
