@@ -70,17 +70,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	(void)rP; (void)rS; (void)mP; (void)mS; (void)jP; (void)jS; (void)mI
 	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
 	int status = 0;
-
-	// ---- P0: the tick is latency bound at 3.5 warps per scheduler: pull every input row of this robot towards L2 now, so
-	// that the loads of the control law (P1b) and of the joint task (P11) do not pay a DRAM round trip each ----
-	{
-		auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); };
-		_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
-		_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
-		if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
-		pf(&mI(ML::NTYPES));
-		pf(&mI(ML::HIST_LEN));
-	}
+	constexpr int CLS_RESET = 1 << 30, CLS_LATCH = 1 << 29;  // private flags riding in `status`, masked out before it is published
 
 	asm volatile("griddepcontrol.launch_dependents;");  // lets the launch of k_tick_tail proceed under this kernel
 
@@ -90,14 +80,35 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 		// ... together with every input of the joint task: its PID command u_pd and the goal acceleration wait in the stash for
 		// the range basis (P11), so that the kernel ends without a load phase.  The integrated error is stored here; a robot
 		// that falls back tells k_tick_tail not to integrate again (reuse_law bit 1).
+		// All 44 loads are issued back to back (a 22 MB burst over the whole grid: 3-4 us of pure HBM time since every warp
+		// starts in lock step); q comes first and the sin/cos loop runs while the rest of the burst is still in flight.
 		T q[N], dq[N], gp[N], gv[N], ga[N], ig[N];
+		OSC_UNROLL for (int i = 0; i < N; ++i) q[i] = rP.ro(RobotL<N>::Q + i);
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i);
+			dq[i] = rP.ro(RobotL<N>::DQ + i);
 			gp[i] = jP.ro(JL::GOAL_POS + i); gv[i] = jP.ro(JL::GOAL_VEL + i); ga[i] = jP.ro(JL::GOAL_ACC + i);
 			ig[i] = jP(JL::INTEG + i);
 		}
+		{
+			const int ntypes = mI(ML::NTYPES), hist_len = mI(ML::HIST_LEN);  // classification state: decided here, used after P10
+			if (ntypes != 0 || hist_len != 0) status |= CLS_RESET;
+			if (ntypes == 0) status |= CLS_LATCH;
+		}
+		{  // P0 (issued BEHIND the loads above so that q is not queued after them): pull the control-law rows towards L2
+			auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); };
+			_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
+			_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
+			if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+		}
+		OSC_UNROLL for (int i = 0; i < N; ++i) SM(F::SC + 2 * i) = q[i];
+		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
+			T s, c;
+			Num<T>::sincos_(SM(F::SC + 2 * i), &s, &c);
+			SM(F::SC + 2 * i) = s;
+			SM(F::SC + 2 * i + 1) = c;
+		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) {  // JointTask.cpp:319-346 without velocity saturation
-			SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i];
+			SM(F::MM + i) = dq[i];
 			const T e = q[i] - gp[i];
 			ig[i] = Num<T>::fma_(e, jc.dt, ig[i]);
 			SM(F::UPD + i) = -jc.kp[i] * e - jc.kv[i] * (dq[i] - gv[i]) - jc.ki[i] * ig[i];
@@ -110,13 +121,24 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	} else {
 		T q[N], dq[N];
 		OSC_UNROLL for (int i = 0; i < N; ++i) { q[i] = rP.ro(RobotL<N>::Q + i); dq[i] = rP.ro(RobotL<N>::DQ + i); }
+		{
+			const int ntypes = mI(ML::NTYPES), hist_len = mI(ML::HIST_LEN);
+			if (ntypes != 0 || hist_len != 0) status |= CLS_RESET;
+			if (ntypes == 0) status |= CLS_LATCH;
+		}
+		{  // P0 (issued BEHIND the loads above so that q is not queued after them): pull the control-law rows towards L2
+			auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); };
+			_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
+			_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
+			if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) { SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i]; }
-	}
-	_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
-		T s, c;
-		Num<T>::sincos_(SM(F::SC + 2 * i), &s, &c);
-		SM(F::SC + 2 * i) = s;
-		SM(F::SC + 2 * i + 1) = c;
+		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
+			T s, c;
+			Num<T>::sincos_(SM(F::SC + 2 * i), &s, &c);
+			SM(F::SC + 2 * i) = s;
+			SM(F::SC + 2 * i + 1) = c;
+		}
 	}
 
 	OSC_PHASE();
@@ -169,7 +191,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 #define OSC_FALL_BACK()                                                                      \
 	{                                                                                        \
 		OSC_UNROLL for (int i_ = 0; i_ < 6; ++i_) { mS(ML::UMF + i_) = SM(F::CC + i_); mS(ML::FFB + i_) = SIMPLE ? T(0) : SM(F::CC + 6 + i_); } \
-		if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);       \
+		if (status & ~(CLS_RESET | CLS_LATCH)) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status & ~(CLS_RESET | CLS_LATCH)); \
 		fb_list[atomicAdd(fb_count, 1)] = (int)r;                                            \
 		return;                                                                              \
 	}
@@ -442,17 +464,14 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	{  // fresh rows for the closing memory phases
 	OSC_FRESH_ROWS();
 	// ---- classification state of a non-singular robot (SingularityHandler.cpp:233-244); see osc_fused.cuh ----
-	{
-		const int ntypes = mI(ML::NTYPES), hist_len = mI(ML::HIST_LEN);
-		bool latch = ntypes == 0;
-		if (ntypes != 0 || hist_len != 0) {
-			latch = latch || mI(ML::C2) > mI(ML::C1);
-			mI(ML::NTYPES) = 0; mI(ML::TYPES) = 0; mI(ML::C1) = 0; mI(ML::C2) = 0; mI(ML::HIST_LEN) = 0; mI(ML::HIST_HEAD) = 0;
-		}
-		if (ex && latch) {
-			OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = rP.ro(RobotL<N>::Q + i);
-		}
+	bool latch = (status & CLS_LATCH) != 0;
+	if (status & CLS_RESET) {
+		latch = latch || mI(ML::C2) > mI(ML::C1);
+		mI(ML::NTYPES) = 0; mI(ML::TYPES) = 0; mI(ML::C1) = 0; mI(ML::C2) = 0; mI(ML::HIST_LEN) = 0; mI(ML::HIST_HEAD) = 0;
 	}
+	latch = latch && ex;
+	T qq[N];  // q_prior latch: loaded here, stored at the very end (the loads ride under P11)
+	OSC_UNROLL for (int i = 0; i < N; ++i) qq[i] = latch ? rP.ro(RobotL<N>::Q + i) : T(0);
 
 	OSC_PHASE();
 	// ---- P11: tau_1 = L h and w = L u (one sweep over L), parked in the dead C slots ----
@@ -525,6 +544,10 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 		mS(ML::ALPHA) = T(1);
 		mI(ML::INS) = 6;
 	}
+	if (latch) {
+		OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = qq[i];
+	}
+	status &= ~(CLS_RESET | CLS_LATCH);
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 	}
 #undef OSC_FRESH_ROWS
