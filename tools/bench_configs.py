@@ -1,0 +1,117 @@
+#!/usr/bin/env python3
+"""Throughput of BASELINE configs 3, 4 and 5 on one B200 (config 2 is bench.py).  One JSON line per measurement.
+
+    python tools/bench_configs.py [--max-batch 3000000]
+
+Device-resident timing with CUDA events around the control calls only (inputs already on the device), after warm-up ticks.
+These are companion numbers for BASELINE.md section 3; the headline contract lives in bench.py.
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "sai2-primitives-perso_b200"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import osc_abi as abi  # noqa: E402
+import osc_b200  # noqa: E402
+import workloads  # noqa: E402
+
+
+def chain_of(name):
+    with open(os.path.join(ROOT, "fixtures", name + ".chain.json")) as f:
+        return json.load(f)
+
+
+def timed(torch, fn, ticks, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(ticks)]
+    for s, e in ev:
+        s.record(); fn(); e.record()
+    torch.cuda.synchronize()
+    return np.array([s.elapsed_time(e) for s, e in ev])
+
+
+def config5(torch, chain, B):
+    w = workloads.config2(chain, min(B, 65536), seed=5)
+    rep = (B + len(w["q"]) - 1) // len(w["q"])
+    tile = lambda a: np.tile(a, (rep, 1))[:B]
+    b = osc_b200.Batch(chain, B, q0=[j["q0"] for j in chain["joints"]])
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = b.add_joint_task(abi.joint_task_desc(chain["n"]))
+    b.set_stream(torch.cuda.current_stream().cuda_stream)
+    b.set(abi.F_Q, tile(w["q"])); b.set(abi.F_DQ, tile(w["dq"])); b.update_model()
+    b.set(abi.F_GOAL_POSITION, tile(w["goal_pos"]), t0); b.set(abi.F_GOAL_ORIENTATION, tile(w["goal_ori"]), t0)
+    b.set(abi.F_JT_GOAL_POSITION, tile(w["jt_goal"]), t1)
+    ms = timed(torch, lambda: b.tick(True, fetch=False), 20)
+    fb = b.tick_fallback_count()
+    del b
+    return {"config": 5, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+            "robot_ticks_per_s": B / (ms.mean() * 1e-3), "fallback_robots": int(fb)}
+
+
+def config3(torch, chain, B=262144, ticks=100):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_config3_force_popc_gpu as T
+    from common import q0_of, random_q
+    rng = np.random.default_rng(3)
+    q = random_q(chain, B, rng, 0.3); dq = rng.uniform(-0.5, 0.5, (B, 7)); gq = q + rng.normal(0, 0.1, (B, 7))
+    b = osc_b200.Batch(chain, B, q0=q0_of(chain))
+    b.set_stream(torch.cuda.current_stream().cuda_stream)
+    t0, _ = T._configure(b, chain, q, dq, 3, gq)
+    f, _ = workloads.config3_wrench(B, 0)
+    fd = torch.from_numpy(np.ascontiguousarray(f.T)).cuda(); md = torch.zeros_like(fd)
+    L, h = b.L, b.h
+
+    def step():
+        L.osc_update_model(h); L.osc_update_task_models(h)
+        L.osc_mft_update_sensed_force_and_moment(h, t0, fd.data_ptr(), md.data_ptr(), abi.LAYOUT_SOA, abi.MEM_DEVICE)
+        L.osc_compute_torques(h, 1, None, abi.LAYOUT_SOA, abi.MEM_DEVICE)
+    ms = timed(torch, step, ticks)
+    return {"config": 3, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+            "robot_ticks_per_s": B / (ms.mean() * 1e-3), "route": "per-call kernels (partial task + force axes + POPC)"}
+
+
+def config4(torch, name, B=65536, ticks=50):
+    import test_singular_gpu as S
+    from common import q0_of
+    chain = chain_of(name)
+    rng = np.random.default_rng(4)
+    base = S._panda_q(rng) if name == "panda" else S._puma_q(rng)
+    q = np.tile(base, ((B + len(base) - 1) // len(base), 1))[:B]
+    n = chain["n"]
+    b = osc_b200.Batch(chain, B, q0=q0_of(chain))
+    b.set_stream(torch.cuda.current_stream().cuda_stream)
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0)))
+    if n > 6:
+        b.add_joint_task(abi.joint_task_desc(n))
+    b.set(abi.F_Q, q); b.set(abi.F_DQ, np.zeros((B, n))); b.update_model(); b.reinitialize_tasks()
+    ms = timed(torch, lambda: b.tick(n > 6, fetch=False), ticks)
+    return {"config": 4, "chain": name, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+            "robot_ticks_per_s": B / (ms.mean() * 1e-3), "fallback_robots": int(b.tick_fallback_count()),
+            "route": "fused tick; robots in the blend branch go through k_tick_tail"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--max-batch", type=int, default=3000000)
+    args = ap.parse_args()
+    import torch
+    panda = chain_of("panda")
+    for B in (10000, 30000, 100000, 300000, 1000000, 3000000, 10000000):
+        if B <= args.max_batch:
+            print(json.dumps(config5(torch, panda, B)), flush=True)
+            torch.cuda.empty_cache()
+    print(json.dumps(config3(torch, panda)), flush=True)
+    print(json.dumps(config4(torch, "panda")), flush=True)
+    print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
+
+
+if __name__ == "__main__":
+    main()
