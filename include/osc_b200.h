@@ -67,7 +67,10 @@ enum {
 	OSC_STATUS_SVD_NOT_CONVERGED = 1 << 3,
 	OSC_STATUS_NOT_POSITIVE_DEFINITE = 1 << 4, /* a Cholesky pivot was <= 0 (the reference's llt() would return garbage) */
 	OSC_STATUS_SINGULAR_BRANCH = 1 << 5,     /* informational: robot is in the blend / fully singular branch */
-	OSC_STATUS_BAD_GOAL_ORIENTATION = 1 << 6 /* orientationError would throw (Appendix B): goal not orthonormal */
+	OSC_STATUS_BAD_GOAL_ORIENTATION = 1 << 6, /* orientationError would throw (Appendix B): goal not orthonormal */
+	OSC_STATUS_OTG_ERROR = 1 << 7            /* the internal OTG returned an error this tick (the reference prints a warning,
+	                                            keeps the previous output and zeroes the trajectory velocity:
+	                                            OTG_joints.cpp:143-149, OTG_6dof_cartesian.cpp:229-235) */
 };
 
 /* ---- robot model: stands in for Sai2Model::Sai2Model(urdf) (un-vendored sai2-model) ----
@@ -202,6 +205,8 @@ enum {
 	OSC_F_DESIRED_ORIENTATION = 73,       /* 9 out */
 	OSC_F_DESIRED_LINEAR_VELOCITY = 74,   /* 3 out */
 	OSC_F_DESIRED_ANGULAR_VELOCITY = 75,  /* 3 out */
+	OSC_F_DESIRED_LINEAR_ACCELERATION = 76, /* 3 out */
+	OSC_F_DESIRED_ANGULAR_ACCELERATION = 77, /* 3 out */
 	/* JointTask (k = task dof) */
 	OSC_F_JT_GOAL_POSITION = 80,     /* k in/out */
 	OSC_F_JT_GOAL_VELOCITY = 81,     /* k */
@@ -212,7 +217,12 @@ enum {
 	OSC_F_JT_LAMBDA_WORLD = 86,      /* k*k out R Lambda R^T : basis-independent form of _M_partial */
 	OSC_F_JT_LAMBDA_MODIFIED_WORLD = 87, /* k*k out */
 	OSC_F_JT_RANGE_RANK = 88,        /* 1 (int32) out cols(_current_task_range), 0 when the range is empty */
-	OSC_F_JT_DESIRED_VELOCITY = 89   /* k out */
+	OSC_F_JT_DESIRED_VELOCITY = 89,  /* k out */
+	OSC_F_JT_DESIRED_POSITION = 90,  /* k out */
+	OSC_F_JT_DESIRED_ACCELERATION = 91, /* k out */
+	/* internal OTG of a task (either type), valid once it has been enabled */
+	OSC_F_OTG_FLAGS = 100,  /* 1 (int32) out: bit 0 = isGoalReached() (OTG_joints.h, OTG_6dof_cartesian.h) */
+	OSC_F_OTG_RESULT = 101  /* 1 (int32) out: ruckig::Result of the last update (0 working, 1 finished, < 0 error) */
 };
 
 typedef struct osc_batch osc_batch_t;
@@ -248,6 +258,23 @@ int osc_mft_get_params(const osc_batch_t* batch, int task, osc_mft_params* out);
 int osc_mft_set_params(osc_batch_t* batch, int task, const osc_mft_params* p);
 int osc_joint_task_get_params(const osc_batch_t* batch, int task, osc_joint_task_params* out);
 int osc_joint_task_set_params(osc_batch_t* batch, int task, const osc_joint_task_params* p);
+/* ---- internal online trajectory generation (Ruckig), acceleration-limited ----
+ * JointTask::enableInternalOtgAccelerationLimited (src/tasks/JointTask.cpp:358-381): count = 1 (same limit for every task
+ * dof, JointTask.h:262-271) or count = task dof; limits[0..count) = max velocity, limits[count..2*count) = max acceleration.
+ * MotionForceTask::enableInternalOtgAccelerationLimited (src/tasks/MotionForceTask.cpp:511-523): count = 2 and
+ * limits = {max_linear_velocity, max_angular_velocity, max_linear_acceleration, max_angular_acceleration}.
+ * The reference constructs its tasks with the OTG ON (JointTask.h:38, MotionForceTask.h:67); a batch task starts with it
+ * OFF (= after disableInternalOtg(), what every BASELINE config runs) and the C++ facade restores the reference default.
+ * While it is on, the goal fields (OSC_F_GOAL_*, OSC_F_JT_GOAL_*) are the OTG's targets and the control law follows
+ * OSC_F_DESIRED_* / OSC_F_JT_DESIRED_*.  The jerk-limited variant (enableInternalOtgJerkLimited) returns
+ * OSC_ERR_UNSUPPORTED. */
+int osc_task_enable_internal_otg_acceleration_limited(osc_batch_t* batch, int task, const double* limits, int count);
+int osc_task_enable_internal_otg_jerk_limited(osc_batch_t* batch, int task, const double* limits, int count);
+/* disableInternalOtg(), JointTask.h:320 / MotionForceTask.h:423 */
+int osc_task_disable_internal_otg(osc_batch_t* batch, int task);
+/* getInternalOtgEnabled() */
+int osc_task_internal_otg_enabled(const osc_batch_t* batch, int task);
+
 /* RobotController::enableGravityCompensation, src/RobotController.h:31-33 */
 int osc_enable_gravity_compensation(osc_batch_t* batch, int enable);
 

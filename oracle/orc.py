@@ -58,8 +58,113 @@ def lib():
         L.orc_tick.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.orc_reinitialize_tasks.argtypes = [C.c_void_p, C.c_int]
         L.orc_hardware_threads.restype = C.c_int
+        # internal OTG (otg_oracle.hpp)
+        L.orc_otg_use_reference.restype = C.c_int
+        L.orc_otg_use_reference.argtypes = [C.c_char_p]
+        L.orc_task_enable_internal_otg_acceleration_limited.restype = C.c_int
+        L.orc_task_enable_internal_otg_acceleration_limited.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int]
+        L.orc_task_disable_internal_otg.restype = C.c_int
+        L.orc_task_disable_internal_otg.argtypes = [C.c_void_p, C.c_int]
+        for name in ("orc_rk_create", "orc_otgj_create", "orc_otgc_create"):
+            getattr(L, name).restype = C.c_void_p
+        L.orc_rk_create.argtypes = [C.c_int, C.c_double]
+        L.orc_otgj_create.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_void_p, C.c_void_p]
+        L.orc_otgc_create.argtypes = [C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double]
+        for name in ("orc_rk_destroy", "orc_otgj_destroy", "orc_otgc_destroy"):
+            getattr(L, name).restype = None
+            getattr(L, name).argtypes = [C.c_void_p]
+        L.orc_rk_update.restype = C.c_int
+        L.orc_rk_update.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_otgj_step.restype = C.c_int
+        L.orc_otgj_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_otgc_step.restype = C.c_int
+        L.orc_otgc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         _LIB = L
     return _LIB
+
+
+REF_RUCKIG = os.path.join(_HERE, "_ref", "libruckig_ref.so")
+
+
+def have_reference_ruckig():
+    """oracle/_ref/libruckig_ref.so = the UNMODIFIED Ruckig of /root/reference/ruckig behind oracle/ruckig_ref_capi.cpp"""
+    return os.path.exists(REF_RUCKIG)
+
+
+def otg_use_reference(on=True):
+    """Every OTG object created afterwards runs on the real Ruckig (on=True) or on the restatement (on=False)."""
+    rc = lib().orc_otg_use_reference(REF_RUCKIG.encode() if on else None)
+    if rc != 0:
+        raise RuntimeError(lib().orc_last_error().decode())
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Ruckig2:
+    """One Ruckig instance (second order, phase synchronisation): restatement or reference backend."""
+
+    def __init__(self, n, dt):
+        self.L, self.n = lib(), n
+        self.h = self.L.orc_rk_create(n, dt)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_rk_destroy(self.h)
+            self.h = None
+
+    def update(self, cur_p, cur_v, cur_a, tgt_p, tgt_v, max_v, max_a):
+        io = _f64(np.concatenate([_f64(x).ravel() for x in (cur_p, cur_v, cur_a, tgt_p, tgt_v, max_v, max_a)]))
+        out = np.full(3 * self.n, np.nan)
+        info = np.zeros(3)
+        r = self.L.orc_rk_update(self.h, io.ctypes.data, out.ctypes.data, info.ctypes.data)
+        return r, out.reshape(3, self.n), info
+
+
+class OtgJoints:
+    """src/helper_modules/OTG_joints.cpp, acceleration limited"""
+
+    def __init__(self, p0, dt, max_v, max_a):
+        self.L, self.n = lib(), len(p0)
+        p0, mv, ma = _f64(p0), _f64(np.broadcast_to(max_v, (self.n,))), _f64(np.broadcast_to(max_a, (self.n,)))
+        self.h = self.L.orc_otgj_create(p0.ctypes.data, self.n, dt, mv.ctypes.data, ma.ctypes.data)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_otgj_destroy(self.h)
+            self.h = None
+
+    def step(self, goal_p, goal_v=None):
+        gp = _f64(goal_p)
+        gv = _f64(goal_v) if goal_v is not None else np.zeros(self.n)
+        out = np.zeros(3 * self.n)
+        fl = np.zeros(1, dtype=np.int32)
+        r = self.L.orc_otgj_step(self.h, gp.ctypes.data, gv.ctypes.data, out.ctypes.data, fl.ctypes.data)
+        return r, out.reshape(3, self.n), int(fl[0])
+
+
+class OtgCartesian:
+    """src/helper_modules/OTG_6dof_cartesian.cpp, acceleration limited"""
+
+    def __init__(self, p0, R0, dt, lin_v, lin_a, ang_v, ang_a):
+        self.L = lib()
+        p0, R0 = _f64(p0), _f64(R0)
+        self.h = self.L.orc_otgc_create(p0.ctypes.data, R0.ctypes.data, dt, lin_v, lin_a, ang_v, ang_a)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_otgc_destroy(self.h)
+            self.h = None
+
+    def step(self, gp, gR, gv=None, gw=None):
+        gp, gR = _f64(gp), _f64(gR)
+        gv = _f64(gv) if gv is not None else np.zeros(3)
+        gw = _f64(gw) if gw is not None else np.zeros(3)
+        out = np.zeros(24)
+        fl = np.zeros(1, dtype=np.int32)
+        r = self.L.orc_otgc_step(self.h, gp.ctypes.data, gR.ctypes.data, gv.ctypes.data, gw.ctypes.data, out.ctypes.data, fl.ctypes.data)
+        return r, out, int(fl[0])
 
 
 class OracleBatch:
@@ -164,3 +269,12 @@ class OracleBatch:
 
     def reinitialize_tasks(self, task=-1):
         self.L.orc_reinitialize_tasks(self.h, task)
+
+    def enable_internal_otg(self, task, max_velocity, max_acceleration):
+        """JointTask: scalars or length-k vectors.  MotionForceTask: (lin, ang) pairs."""
+        mv, ma = np.atleast_1d(_f64(max_velocity)), np.atleast_1d(_f64(max_acceleration))
+        lim = _f64(np.concatenate([mv, ma]))
+        self._chk(self.L.orc_task_enable_internal_otg_acceleration_limited(self.h, task, lim.ctypes.data, len(mv)))
+
+    def disable_internal_otg(self, task):
+        self.L.orc_task_disable_internal_otg(self.h, task)

@@ -19,6 +19,8 @@
 
 #include "../include/osc_b200.h"
 
+#include "otg_oracle.hpp"
+
 namespace orc {
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -814,6 +816,10 @@ struct MotionForceTask : Task {
 	V3 sensed_force, sensed_moment;
 	V3 integ_pos, integ_ori, integ_force, integ_moment;
 	double unit_mass_force[6];
+	// internal OTG (MotionForceTask.h:812-815).  The reference enables it by default (MotionForceTask.h:67, .cpp:173-188);
+	// here it starts disabled (every BASELINE config runs with OTG off) and enableInternalOtgAccelerationLimited turns it on.
+	bool use_internal_otg = false;
+	otg::OtgCartesian* otg_ = nullptr;
 
 	MotionForceTask(Model* r, const osc_mft_desc& d) : desc(d), body(d.body), p_c(d.frame_xyz), R_c(d.frame_rot), popc(d.loop_timestep) {
 		robot = r; type = OSC_TASK_MOTION_FORCE; dt = d.loop_timestep;
@@ -840,7 +846,7 @@ struct MotionForceTask : Task {
 		}
 		initialSetup();
 	}
-	~MotionForceTask() override { delete handler; }
+	~MotionForceTask() override { delete handler; delete otg_; }
 
 	static void default_params(osc_mft_params* p) {  // MotionForceTask.h:40-75; SingularityHandler.cpp:10-20; MotionForceTask.cpp:197
 		std::memset(p, 0, sizeof *p);
@@ -889,7 +895,27 @@ struct MotionForceTask : Task {
 		goal_force = goal_moment = sensed_force = sensed_moment = V3();
 		integ_force = integ_moment = V3();
 		for (double& u : unit_mass_force) u = 0;
+		if (otg_) otgReInitialize();  // .cpp:244
 	}
+	void otgReInitialize() {
+		double p0[3] = {x.x, x.y, x.z}, R0[9];
+		for (int i = 0; i < 9; ++i) R0[i] = R.m[i / 3][i % 3];
+		otg_->reInitialize(p0, R0);
+	}
+	// MotionForceTask.cpp:511-523
+	void enableInternalOtgAccelerationLimited(double max_lin_v, double max_lin_a, double max_ang_v, double max_ang_a) {
+		if (max_lin_v <= 0 || max_lin_a <= 0 || max_ang_v <= 0 || max_ang_a <= 0)  // OTG_6dof_cartesian.cpp:88-129
+			throw std::invalid_argument("max velocity / acceleration set to 0 or negative value in OTG_6dof_cartesian\n");
+		if (!otg_) {  // constructor, .cpp:171-172
+			double p0[3] = {x.x, x.y, x.z}, R0[9];
+			for (int i = 0; i < 9; ++i) R0[i] = R.m[i / 3][i % 3];
+			otg_ = new otg::OtgCartesian(p0, R0, dt);
+		}
+		if (!use_internal_otg) otgReInitialize();
+		otg_->setLimits(max_lin_v, max_lin_a, max_ang_v, max_ang_a);
+		use_internal_otg = true;
+	}
+	void disableInternalOtg() { use_internal_otg = false; }  // MotionForceTask.h:423
 
 	// applies the side effects of parametrizeForceMotionSpaces (.cpp:830-858), parametrizeMomentRotMotionSpaces
 	// (.cpp:860-890), setClosedLoopForce/MomentControl (.cpp:973-986), enable/disablePassivity
@@ -918,11 +944,13 @@ struct MotionForceTask : Task {
 		} else std::memcpy(p.moment_or_rotmotion_axis, prm.moment_or_rotmotion_axis, sizeof p.moment_or_rotmotion_axis);
 		if (reset_lin) {
 			goal_pos = x; goal_linvel = V3(); goal_linacc = V3();
+			if (otg_) { double p0[3] = {x.x, x.y, x.z}; otg_->reInitializeLinear(p0); }  // .cpp:854
 			integ_pos = V3(); integ_force = V3();
 			resets |= 1;
 		}
 		if (reset_ang) {
 			goal_ori = R; goal_angvel = V3(); goal_angacc = V3();
+			if (otg_) { double R0[9]; for (int i = 0; i < 9; ++i) R0[i] = R.m[i / 3][i % 3]; otg_->reInitializeAngular(R0); }  // .cpp:886
 			integ_ori = V3(); integ_moment = V3();
 			resets |= 2;
 		}
@@ -1019,10 +1047,25 @@ struct MotionForceTask : Task {
 		} else {
 			M_fb = Sm * (-1.0 * cwise(kv_m, w));
 		}
-		// .cpp:387-392 (internal OTG: "next" row f-1, disabled like examples/04...cpp:115)
+		// .cpp:387-392
 		des_pos = goal_pos; des_ori = goal_ori;
 		des_linvel = goal_linvel; des_angvel = goal_angvel;
 		des_linacc = goal_linacc; des_angacc = goal_angacc;
+		if (use_internal_otg) {  // .cpp:394-407
+			const double gp[3] = {goal_pos.x, goal_pos.y, goal_pos.z}, gv[3] = {goal_linvel.x, goal_linvel.y, goal_linvel.z},
+						 gw[3] = {goal_angvel.x, goal_angvel.y, goal_angvel.z};
+			double gR[9], Rn[9], wn[3], an[3];
+			for (int i = 0; i < 9; ++i) gR[i] = goal_ori.m[i / 3][i % 3];
+			otg_->setGoalPositionAndLinearVelocity(gp, gv);
+			if (!otg_->setGoalOrientationAndAngularVelocity(gR, gw))
+				throw std::invalid_argument("goal orientation is not a valid rotation matrix OTG_6dof_cartesian::setGoalOrientationAndAngularVelocity\n");
+			otg_->update();
+			des_pos = V3(otg_->out_p); des_linvel = V3(otg_->out_v); des_linacc = V3(otg_->out_a);
+			otg_->getNextOrientation(Rn);
+			des_ori = M3(Rn);
+			otg_->getNextAngularVelocity(wn); otg_->getNextAngularAcceleration(an);
+			des_angvel = V3(wn); des_angacc = V3(an);
+		}
 		integ_pos = integ_pos + (Sp * (x - des_pos)) * dt;  // .cpp:411-413
 		if (prm.use_velocity_saturation) {                  // .cpp:416-429
 			double kvi[3];
@@ -1068,6 +1111,20 @@ struct JointTask : Task {
 	int k;
 	Mat Jp, range, Lam, Lam_mod;
 	double cur_pos[8], cur_vel[8], goal_pos[8], goal_vel[8], goal_acc[8], des_pos[8], des_vel[8], des_acc[8], integ[8];
+	bool use_internal_otg = false;  // JointTask.h:440 (reference default: on; here off until enabled, see MotionForceTask)
+	otg::OtgJoints* otg_ = nullptr;
+	~JointTask() override { delete otg_; }
+	// JointTask.cpp:358-381
+	void enableInternalOtgAccelerationLimited(const double* max_v, const double* max_a) {
+		for (int i = 0; i < k; ++i)
+			if (max_v[i] <= 0 || max_a[i] <= 0) throw std::invalid_argument("max velocity / acceleration cannot be 0 or negative in OTG_joints\n");
+		if (!otg_) otg_ = new otg::OtgJoints(cur_pos, k, dt);  // constructor, .cpp:71-72
+		if (!use_internal_otg) otg_->reInitialize(cur_pos);
+		otg_->setLimits(max_v, max_a);
+		otg_->disableJerkLimits();
+		use_internal_otg = true;
+	}
+	void disableInternalOtg() { use_internal_otg = false; }  // JointTask.h:320
 
 	static void default_params(osc_joint_task_params* p, int k) {  // JointTask.h:31-45
 		std::memset(p, 0, sizeof *p);
@@ -1104,6 +1161,7 @@ struct JointTask : Task {
 			cur_pos[i] = goal_pos[i] = des_pos[i] = s;
 			cur_vel[i] = goal_vel[i] = goal_acc[i] = des_vel[i] = des_acc[i] = integ[i] = 0;
 		}
+		if (otg_) otg_->reInitialize(cur_pos);  // .cpp:106
 	}
 
 	void updateTaskModel(const Mat& N_prec_) override {  // JointTask.cpp:218-283
@@ -1149,6 +1207,11 @@ struct JointTask : Task {
 		if (range.norm() == 0) { tau = Mat::Zero(dof, 1); return tau; }
 		Mat u(k, 1), acc(k, 1);
 		for (int i = 0; i < k; ++i) { des_pos[i] = goal_pos[i]; des_vel[i] = goal_vel[i]; des_acc[i] = goal_acc[i]; }
+		if (use_internal_otg) {  // .cpp:313-320
+			otg_->setGoalPositionAndVelocity(goal_pos, goal_vel);
+			otg_->update();
+			for (int i = 0; i < k; ++i) { des_pos[i] = otg_->out_p[i]; des_vel[i] = otg_->out_v[i]; des_acc[i] = otg_->out_a[i]; }
+		}
 		for (int i = 0; i < k; ++i) integ[i] += (cur_pos[i] - des_pos[i]) * dt;
 		if (prm.use_velocity_saturation) {
 			double kvi[8];

@@ -158,6 +158,10 @@ static int field_io(orc_batch* b, Robot& r, int task, int field, double* o, cons
 			M3FIELD(OSC_F_DESIRED_ORIENTATION, des_ori)
 			V3FIELD(OSC_F_DESIRED_LINEAR_VELOCITY, des_linvel)
 			V3FIELD(OSC_F_DESIRED_ANGULAR_VELOCITY, des_angvel)
+			V3FIELD(OSC_F_DESIRED_LINEAR_ACCELERATION, des_linacc)
+			V3FIELD(OSC_F_DESIRED_ANGULAR_ACCELERATION, des_angacc)
+			case OSC_F_OTG_FLAGS: if (!m->otg_) return -1; if (o) o[0] = m->otg_->goal_reached ? 1 : 0; return 1;
+			case OSC_F_OTG_RESULT: if (!m->otg_) return -1; if (o) o[0] = m->otg_->result_value; return 1;
 			case OSC_F_UNIT_MASS_FORCE: if (o) for (int i = 0; i < 6; ++i) o[i] = m->unit_mass_force[i]; return 6;
 			case OSC_F_JACOBIAN: if (o) putMat(o, m->J, 6, n); return 6 * n;
 			case OSC_F_PROJECTED_JACOBIAN: if (o) putMat(o, m->Jp, 6, n); return 6 * n;
@@ -190,6 +194,10 @@ static int field_io(orc_batch* b, Robot& r, int task, int field, double* o, cons
 		KFIELD(OSC_F_JT_CURRENT_VELOCITY, cur_vel)
 		KFIELD(OSC_F_JT_INTEGRATED_ERROR, integ)
 		KFIELD(OSC_F_JT_DESIRED_VELOCITY, des_vel)
+		KFIELD(OSC_F_JT_DESIRED_POSITION, des_pos)
+		KFIELD(OSC_F_JT_DESIRED_ACCELERATION, des_acc)
+		case OSC_F_OTG_FLAGS: if (!j->otg_) return -1; if (o) o[0] = j->otg_->goal_reached ? 1 : 0; return 1;
+		case OSC_F_OTG_RESULT: if (!j->otg_) return -1; if (o) o[0] = j->otg_->result_value; return 1;
 		case OSC_F_JT_LAMBDA_WORLD:
 		case OSC_F_JT_LAMBDA_MODIFIED_WORLD:
 			if (o) {
@@ -254,6 +262,95 @@ int orc_reinitialize_tasks(orc_batch* b, int task) {
 			if (task < 0 || t == task) r->tasks[t]->reInitializeTask();
 	return 0;
 }
+// ---- internal OTG (otg_oracle.hpp) ----
+// 1 = run the wrappers on the REAL Ruckig (oracle/_ref/libruckig_ref.so) for every OTG created afterwards; 0 = restatement
+int orc_otg_use_reference(const char* path) {
+	if (!path) { otg::use_reference_backend() = false; return 0; }
+	if (!otg::RefLib::get().load(path)) { g_err = std::string("cannot load ") + path; return OSC_ERR_INVALID_ARGUMENT; }
+	otg::use_reference_backend() = true;
+	return 0;
+}
+// same argument convention as osc_task_enable_internal_otg_acceleration_limited (include/osc_b200.h)
+int orc_task_enable_internal_otg_acceleration_limited(orc_batch* b, int task, const double* limits, int count) {
+	try {
+		for (Robot* r : b->robots) {
+			Task* t = r->tasks[task];
+			if (t->type == OSC_TASK_MOTION_FORCE) {
+				if (count != 2) throw std::invalid_argument("MotionForceTask OTG limits: 4 numbers");
+				static_cast<MotionForceTask*>(t)->enableInternalOtgAccelerationLimited(limits[0], limits[2], limits[1], limits[3]);
+			} else {
+				auto* j = static_cast<JointTask*>(t);
+				if (count != 1 && count != j->k) throw std::invalid_argument("max velocity or max acceleration vector size not consistent with task dof in JointTask::enableInternalOtgAccelerationLimited\n");
+				double mv[8], ma[8];
+				for (int i = 0; i < j->k; ++i) { mv[i] = limits[count == 1 ? 0 : i]; ma[i] = limits[count + (count == 1 ? 0 : i)]; }
+				j->enableInternalOtgAccelerationLimited(mv, ma);
+			}
+		}
+	} catch (std::exception& e) { g_err = e.what(); return OSC_ERR_INVALID_ARGUMENT; }
+	return 0;
+}
+int orc_task_disable_internal_otg(orc_batch* b, int task) {
+	for (Robot* r : b->robots) {
+		Task* t = r->tasks[task];
+		if (t->type == OSC_TASK_MOTION_FORCE) static_cast<MotionForceTask*>(t)->disableInternalOtg();
+		else static_cast<JointTask*>(t)->disableInternalOtg();
+	}
+	return 0;
+}
+
+// stand-alone objects for the pinning tests (tests/test_otg_oracle.py)
+void* orc_rk_create(int n, double dt) { return new otg::Engine(n, dt); }
+void orc_rk_destroy(void* h) { delete (otg::Engine*)h; }
+// one Ruckig::update; io = [cur_p cur_v cur_a tgt_p tgt_v max_v max_a] (7 x n), out = [new_p new_v new_a] (3 x n, left
+// untouched on an error), info = {time, duration, new_calculation}
+int orc_rk_update(void* h, const double* io, double* out, double* info) {
+	otg::Engine* e = (otg::Engine*)h;
+	const int n = e->n;
+	otg::Input in;
+	for (int i = 0; i < n; ++i) {
+		in.cur_p[i] = io[i]; in.cur_v[i] = io[n + i]; in.cur_a[i] = io[2 * n + i]; in.tgt_p[i] = io[3 * n + i]; in.tgt_v[i] = io[4 * n + i];
+		in.max_v[i] = io[5 * n + i]; in.max_a[i] = io[6 * n + i];
+	}
+	const int r = e->update(in, out, out + n, out + 2 * n);
+	info[0] = e->last_time; info[1] = e->last_duration; info[2] = e->last_new_calculation ? 1 : 0;
+	return r;
+}
+void* orc_otgj_create(const double* p0, int n, double dt, const double* max_v, const double* max_a) {
+	auto* o = new otg::OtgJoints(p0, n, dt);
+	o->setLimits(max_v, max_a);
+	o->disableJerkLimits();
+	return o;
+}
+void orc_otgj_destroy(void* h) { delete (otg::OtgJoints*)h; }
+// setGoalPositionAndVelocity + update; out = [p v a] (3 x n); returns result_value, flags[0] = goal reached
+int orc_otgj_step(void* h, const double* goal_p, const double* goal_v, double* out, int* flags) {
+	auto* o = (otg::OtgJoints*)h;
+	o->setGoalPositionAndVelocity(goal_p, goal_v);
+	o->update();
+	for (int i = 0; i < o->dim; ++i) { out[i] = o->out_p[i]; out[o->dim + i] = o->out_v[i]; out[2 * o->dim + i] = o->out_a[i]; }
+	flags[0] = o->goal_reached ? 1 : 0;
+	return o->result_value;
+}
+void* orc_otgc_create(const double* p0, const double* R0, double dt, double lin_v, double lin_a, double ang_v, double ang_a) {
+	auto* o = new otg::OtgCartesian(p0, R0, dt);
+	o->setLimits(lin_v, lin_a, ang_v, ang_a);
+	return o;
+}
+void orc_otgc_destroy(void* h) { delete (otg::OtgCartesian*)h; }
+// out = [pos 3, R 9, linvel 3, angvel 3, linacc 3, angacc 3] = 24; returns result_value, or -1000 for an invalid goal rotation
+int orc_otgc_step(void* h, const double* gp, const double* gR, const double* gv, const double* gw, double* out, int* flags) {
+	auto* o = (otg::OtgCartesian*)h;
+	o->setGoalPositionAndLinearVelocity(gp, gv);
+	if (!o->setGoalOrientationAndAngularVelocity(gR, gw)) return -1000;
+	o->update();
+	for (int i = 0; i < 3; ++i) { out[i] = o->out_p[i]; out[12 + i] = o->out_v[i]; out[18 + i] = o->out_a[i]; }
+	o->getNextOrientation(out + 3);
+	o->getNextAngularVelocity(out + 15);
+	o->getNextAngularAcceleration(out + 21);
+	flags[0] = o->goal_reached ? 1 : 0;
+	return o->result_value;
+}
+
 int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
 
 }  // extern "C"

@@ -227,8 +227,69 @@ int osc_mft_set_params(osc_batch_t* batch, int task, const osc_mft_params* np) {
 	t.mp = p;
 	if (flags) {
 		if (int rc = b->ops->mft_reset(*b, task, flags)) return rc;
+		if (t.otgO && (flags & 3))  // _otg->reInitializeLinear / reInitializeAngular, MotionForceTask.cpp:854,886
+			if (int rc = b->ops->otg_reinit(*b, task, ((flags & 1) ? 2 : 0) | ((flags & 2) ? 4 : 0) | (t.otg_on ? 64 : 0))) return rc;
 	}
 	return ret;
+}
+
+int osc_task_enable_internal_otg_acceleration_limited(osc_batch_t* batch, int task, const double* limits, int count) {
+	Batch* b = (Batch*)batch;
+	if (!b || !limits || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
+	TaskH& t = b->tasks[task];
+	double mv[8] = {0}, ma[8] = {0};
+	if (t.type == OSC_TASK_MOTION_FORCE) {
+		if (count != 2) return invalid("MotionForceTask OTG limits: {max_linear_velocity, max_angular_velocity, max_linear_acceleration, max_angular_acceleration}");
+		for (int i = 0; i < 3; ++i) { mv[i] = limits[0]; mv[3 + i] = limits[1]; ma[i] = limits[2]; ma[3 + i] = limits[3]; }
+		for (int i = 0; i < 6; ++i)  // OTG_6dof_cartesian.cpp:86-129
+			if (!(mv[i] > 0) || !(ma[i] > 0)) return invalid("max velocity or acceleration set to 0 or negative value in some directions in OTG_6dof_cartesian\n");
+	} else {
+		if (count != 1 && count != t.dof)  // JointTask.cpp:366-372
+			return invalid("max velocity or max acceleration vector size not consistent with task dof in JointTask::enableInternalOtgAccelerationLimited\n");
+		for (int i = 0; i < t.dof; ++i) { mv[i] = limits[count == 1 ? 0 : i]; ma[i] = limits[count + (count == 1 ? 0 : i)]; }
+		for (int i = 0; i < t.dof; ++i)  // OTG_joints.cpp:49-53,63-67
+			if (!(mv[i] > 0) || !(ma[i] > 0)) return invalid("max velocity or acceleration cannot be 0 or negative in any directions in OTG_joints\n");
+	}
+	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->materialise(*b)) return rc;
+	bool fresh = false;
+	if (!t.otgO) {
+		b->ops->otg_rows(*b, task, t.otg_o_rows, t.otg_i_rows, t.otg_g_rows);
+		if (int rc = alloc_rows(*b, (void**)&t.otgO, t.otg_o_rows, 8)) return rc;
+		if (int rc = alloc_rows(*b, (void**)&t.otgI, t.otg_i_rows, 4)) return rc;
+		if (int rc = alloc_rows(*b, &t.otgG, t.otg_g_rows, b->esz)) return rc;
+		fresh = true;
+	}
+	const bool limits_changed = memcmp(t.otg_max_v, mv, sizeof mv) != 0 || memcmp(t.otg_max_a, ma, sizeof ma) != 0;
+	memcpy(t.otg_max_v, mv, sizeof mv);
+	memcpy(t.otg_max_a, ma, sizeof ma);
+	if (t.otg_on && limits_changed)
+		if (int rc = b->ops->otg_reinit(*b, task, 128)) return rc;
+	if (!t.otg_on) {  // reInitialize(_current_position) when it was off (JointTask.cpp:373-375); the user's goals move to G
+		if (int rc = b->ops->otg_reinit(*b, task, 1 | 8 | (fresh ? 32 : 0))) return rc;
+	}
+	t.otg_on = true;
+	return OSC_OK;
+}
+int osc_task_enable_internal_otg_jerk_limited(osc_batch_t* batch, int task, const double* limits, int count) {
+	(void)batch; (void)task; (void)limits; (void)count;
+	set_error("jerk-limited internal OTG (third-order Ruckig profiles) is not built; use the acceleration-limited mode");
+	return OSC_ERR_UNSUPPORTED;
+}
+int osc_task_disable_internal_otg(osc_batch_t* batch, int task) {
+	Batch* b = (Batch*)batch;
+	if (!b || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
+	TaskH& t = b->tasks[task];
+	if (!t.otg_on) return OSC_OK;
+	if (int rc = use_device(*b)) return rc;
+	if (int rc = b->ops->otg_reinit(*b, task, 16)) return rc;  // the goal rows are the user's goals again
+	t.otg_on = false;
+	return OSC_OK;
+}
+int osc_task_internal_otg_enabled(const osc_batch_t* batch, int task) {
+	const Batch* b = (const Batch*)batch;
+	if (!b || task < 0 || task >= (int)b->tasks.size()) return 0;
+	return b->tasks[task].otg_on ? 1 : 0;
 }
 
 int osc_joint_task_get_params(const osc_batch_t* batch, int task, osc_joint_task_params* out) {

@@ -54,6 +54,8 @@ int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
 	if (int rc = check_task(b, task)) return rc;
 	if (int rc = use_device(*b)) return rc;
 	if (int rc = b->ops->materialise(*b)) return rc;
+	if (b->tasks[task].otg_on)
+		if (int rc = b->ops->otg_tick(*b, task)) return rc;
 	return b->ops->task_compute(*b, task, with_tau_prec, 0);
 }
 int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {  // RobotController.cpp:62-74
@@ -62,8 +64,11 @@ int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layo
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (int rc = use_device(*b)) return rc;
 	if (int rc = b->ops->materialise(*b)) return rc;
-	for (int t = 0; t < (int)b->tasks.size(); ++t)
+	for (int t = 0; t < (int)b->tasks.size(); ++t) {
+		if (b->tasks[t].otg_on)
+			if (int rc = b->ops->otg_tick(*b, t)) return rc;
 		if (int rc = b->ops->task_compute(*b, t, (stacked && t > 0) ? 1 : 0, t == 0 ? 1 : 2)) return rc;
+	}
 	if (b->gravity)
 		if (int rc = b->ops->add_gravity(*b)) return rc;
 	return emit_tau(*b, tau_out, layout, mem);
@@ -78,6 +83,9 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (int rc = use_device(*b)) return rc;
 	if (b->ops->fused_supported(*b)) {
+		for (int t = 0; t < (int)b->tasks.size(); ++t)  // the desired state of this tick, before the control law reads it
+			if (b->tasks[t].otg_on)
+				if (int rc = b->ops->otg_tick(*b, t)) return rc;
 		if (int rc = b->ops->tick_fused(*b, stacked)) return rc;
 		return emit_tau(*b, tau_out, layout, mem);
 	}
@@ -111,8 +119,11 @@ int osc_reinitialize_tasks(osc_batch_t* batch, int task) {
 	if (int rc = use_device(*b)) return rc;
 	if (int rc = b->ops->materialise(*b)) return rc;
 	for (int t = 0; t < (int)b->tasks.size(); ++t)
-		if (task < 0 || t == task)
+		if (task < 0 || t == task) {
 			if (int rc = b->ops->task_reinit(*b, t)) return rc;
+			if (b->tasks[t].otgO)  // _otg->reInitialize(...), JointTask.cpp:106 / MotionForceTask.cpp:244
+				if (int rc = b->ops->otg_reinit(*b, t, 1 | (b->tasks[t].otg_on ? 64 : 0))) return rc;
+		}
 	return OSC_OK;
 }
 
@@ -134,6 +145,11 @@ static int64_t snapshot_walk(Batch& b, char* buf, int mem, int dir) {
 		if (seg(t.P, (size_t)t.p_rows * b.stride * b.esz)) return -1;
 		if (seg(t.I, (size_t)t.i_rows * b.stride * 4)) return -1;
 		if (t.popc_ring && seg(t.popc_ring, (size_t)OSC_POPC_RING_CAPACITY * b.stride * b.esz)) return -1;
+		if (t.otgO) {
+			if (seg(t.otgO, (size_t)t.otg_o_rows * b.stride * 8)) return -1;
+			if (seg(t.otgI, (size_t)t.otg_i_rows * b.stride * 4)) return -1;
+			if (seg(t.otgG, (size_t)t.otg_g_rows * b.stride * b.esz)) return -1;
+		}
 	}
 	return off;
 }

@@ -139,6 +139,8 @@ template <class E> __global__ void k_broadcast(const __grid_constant__ Uniform64
 inline void* arena_base(Batch& b, const Loc& l) {
 	if (l.owner < 0) return l.arena == 0 ? b.P : (l.arena == 1 ? b.S : (void*)b.I);
 	TaskH& t = b.tasks[l.owner];
+	if (l.arena == 3) return t.otgG;
+	if (l.arena == 4) return (void*)t.otgI;
 	return l.arena == 0 ? t.P : (l.arena == 1 ? t.S : (void*)t.I);
 }
 inline void* row_ptr(Batch& b, const Loc& l) {

@@ -25,10 +25,17 @@ struct TaskH {
 	int32_t* I = nullptr;
 	int64_t p_rows = 0, s_rows = 0, i_rows = 0;
 	void* popc_ring = nullptr;
+	// internal OTG (osc_otg.cuh), allocated when first enabled: O = double state rows, OI = int rows, G = user goals (T)
+	bool otg_on = false;
+	double *otgO = nullptr;
+	int32_t* otgI = nullptr;
+	void* otgG = nullptr;
+	int64_t otg_o_rows = 0, otg_i_rows = 0, otg_g_rows = 0;
+	double otg_max_v[8]{}, otg_max_a[8]{};
 };
 
 struct Loc {
-	int arena = 0;   // 0 P, 1 S, 2 I
+	int arena = 0;   // 0 P, 1 S, 2 I, 3 G (user goals while the internal OTG is on), 4 OTG ints
 	int offset = 0;
 	int width = 0;
 	bool is_int = false;
@@ -56,7 +63,10 @@ struct Ops {
 	virtual int pack_special(Batch& b, const Loc& loc, void* tmp) = 0;
 	virtual bool fused_supported(Batch& b) = 0;
 	virtual int tick_fused(Batch& b, int stacked) = 0;
-	virtual int materialise(Batch& b) = 0;  // after a fused tick: run the per-call model / task-model kernels (no state advance)
+	virtual int materialise(Batch& b) = 0;
+	virtual void otg_rows(Batch& b, int t, int64_t& o, int64_t& i, int64_t& g) = 0;
+	virtual int otg_reinit(Batch& b, int t, int mode) = 0;  // k_otg_reinit modes (osc_otg.cuh)
+	virtual int otg_tick(Batch& b, int t) = 0;              // goal filter + update() + desired rows of task t  // after a fused tick: run the per-call model / task-model kernels (no state advance)
 };
 
 Ops* make_ops(int precision, int n);  // nullptr when that (precision, dof) pair was not compiled in

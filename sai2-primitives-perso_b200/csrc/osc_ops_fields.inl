@@ -36,12 +36,12 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 			case OSC_F_N_TASK: return set(1, L::NT, N * N, false);
 			case OSC_F_N_PREC: return set(1, L::NPREC, N * N, false);
 			case OSC_F_N_TASK_AND_PREC: return set(1, L::NTP, N * N, false);
-			case OSC_F_GOAL_POSITION: return set(0, L::GOAL_POS, 3, true);
-			case OSC_F_GOAL_ORIENTATION: return set(0, L::GOAL_ORI, 9, true);
-			case OSC_F_GOAL_LINEAR_VELOCITY: return set(0, L::GOAL_LINVEL, 3, true);
-			case OSC_F_GOAL_ANGULAR_VELOCITY: return set(0, L::GOAL_ANGVEL, 3, true);
-			case OSC_F_GOAL_LINEAR_ACCELERATION: return set(0, L::GOAL_LINACC, 3, true);
-			case OSC_F_GOAL_ANGULAR_ACCELERATION: return set(0, L::GOAL_ANGACC, 3, true);
+			case OSC_F_GOAL_POSITION: return set(t.otg_on ? 3 : 0, L::GOAL_POS, 3, true);
+			case OSC_F_GOAL_ORIENTATION: return set(t.otg_on ? 3 : 0, L::GOAL_ORI, 9, true);
+			case OSC_F_GOAL_LINEAR_VELOCITY: return set(t.otg_on ? 3 : 0, L::GOAL_LINVEL, 3, true);
+			case OSC_F_GOAL_ANGULAR_VELOCITY: return set(t.otg_on ? 3 : 0, L::GOAL_ANGVEL, 3, true);
+			case OSC_F_GOAL_LINEAR_ACCELERATION: return set(t.otg_on ? 3 : 0, L::GOAL_LINACC, 3, true);
+			case OSC_F_GOAL_ANGULAR_ACCELERATION: return set(t.otg_on ? 3 : 0, L::GOAL_ANGACC, 3, true);
 			case OSC_F_GOAL_FORCE: return set(0, L::GOAL_FORCE, 3, true);
 			case OSC_F_GOAL_MOMENT: return set(0, L::GOAL_MOMENT, 3, true);
 			case OSC_F_SENSED_FORCE_WORLD: return set(0, L::SENSED_F, 3, true);
@@ -72,6 +72,10 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 			case OSC_F_DESIRED_ORIENTATION: return set(1, L::DES_ORI, 9, false);
 			case OSC_F_DESIRED_LINEAR_VELOCITY: return set(1, L::DES_LINVEL, 3, false);
 			case OSC_F_DESIRED_ANGULAR_VELOCITY: return set(1, L::DES_ANGVEL, 3, false);
+			case OSC_F_DESIRED_LINEAR_ACCELERATION: return set(0, L::GOAL_LINACC, 3, false);
+			case OSC_F_DESIRED_ANGULAR_ACCELERATION: return set(0, L::GOAL_ANGACC, 3, false);
+			case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<6>::FLAGS, 1, false, true);
+			case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<6>::RESULT, 1, false, true);
 		}
 		(void)K;
 		return false;
@@ -83,9 +87,9 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 		case OSC_F_N_TASK: return set(1, L::NT, N * N, false);
 		case OSC_F_N_PREC: return set(1, L::NPREC, N * N, false);
 		case OSC_F_N_TASK_AND_PREC: return set(1, L::NTP, N * N, false);
-		case OSC_F_JT_GOAL_POSITION: return set(0, L::GOAL_POS, k, true);
-		case OSC_F_JT_GOAL_VELOCITY: return set(0, L::GOAL_VEL, k, true);
-		case OSC_F_JT_GOAL_ACCELERATION: return set(0, L::GOAL_ACC, k, true);
+		case OSC_F_JT_GOAL_POSITION: return set(t.otg_on ? 3 : 0, L::GOAL_POS, k, true);
+		case OSC_F_JT_GOAL_VELOCITY: return set(t.otg_on ? 3 : 0, L::GOAL_VEL, k, true);
+		case OSC_F_JT_GOAL_ACCELERATION: return set(t.otg_on ? 3 : 0, L::GOAL_ACC, k, true);
 		case OSC_F_JT_CURRENT_POSITION: return set(1, L::CUR_POS, k, false);
 		case OSC_F_JT_CURRENT_VELOCITY: return set(1, L::CUR_VEL, k, false);
 		case OSC_F_JT_INTEGRATED_ERROR: return set(0, L::INTEG, k, true);
@@ -93,6 +97,11 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 		case OSC_F_JT_LAMBDA_WORLD: l.special = 6; return set(1, 0, k * k, false);
 		case OSC_F_JT_LAMBDA_MODIFIED_WORLD: l.special = 7; return set(1, 0, k * k, false);
 		case OSC_F_JT_RANGE_RANK: return set(2, L::RANK, 1, false, true);
+		// _desired_position / _desired_acceleration: the rows the control law reads (= the goal rows while the OTG is off)
+		case OSC_F_JT_DESIRED_POSITION: return set(0, L::GOAL_POS, k, false);
+		case OSC_F_JT_DESIRED_ACCELERATION: return set(0, L::GOAL_ACC, k, false);
+		case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<N>::FLAGS, 1, false, true);
+		case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<N>::RESULT, 1, false, true);
 	}
 	return false;
 }

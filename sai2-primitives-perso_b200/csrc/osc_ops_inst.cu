@@ -6,6 +6,7 @@
 
 #include "osc_aux_kernels.cuh"
 #include "osc_fused2.cuh"
+#include "osc_otg.cuh"
 #include "osc_host.h"
 
 #ifndef OSC_T
@@ -174,6 +175,39 @@ template <class T, int N> struct OpsImpl : Ops {
 		TaskH& th = b.tasks[t];
 		k_mft_sensed<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride);
 		return done(b, "k_mft_sensed");
+	}
+
+	// ---- internal OTG (osc_otg.cuh) ----
+	OtgJob otg_job(Batch& b, TaskH& th) {
+		OtgJob j{};
+		j.O = th.otgO; j.OI = th.otgI; j.G = th.otgG; j.P = th.P;
+		j.status = b.I + (int64_t)RobotL<N>::STATUS * b.stride;
+		j.k = th.type == OSC_TASK_MOTION_FORCE ? 6 : th.dof;
+		j.rank = th.type == OSC_TASK_MOTION_FORCE ? nullptr : th.I + (int64_t)JtL<N>::RANK * b.stride;
+		j.dt = b.dt;
+		for (int i = 0; i < 8; ++i) { j.max_v[i] = th.otg_max_v[i]; j.max_a[i] = th.otg_max_a[i]; }
+		return j;
+	}
+	void otg_rows(Batch& b, int t, int64_t& o, int64_t& i, int64_t& g) override {
+		if (b.tasks[t].type == OSC_TASK_MOTION_FORCE) { o = OtgL<6>::O_SIZE; i = OtgL<6>::I_SIZE; g = MftL<N>::GOAL_FORCE; }
+		else { o = OtgL<N>::O_SIZE; i = OtgL<N>::I_SIZE; g = 3 * N; }
+	}
+	int otg_reinit(Batch& b, int t, int mode) override {
+		TaskH& th = b.tasks[t];
+		const dim3 g((unsigned)((b.B + 127) / 128));
+		if (th.type == OSC_TASK_MOTION_FORCE)
+			k_otg_reinit<T, 6, true><<<g, 128, 0, b.stream>>>(otg_job(b, th), (const T*)th.P, b.B, b.stride, mode, (int)th.otg_g_rows);
+		else
+			k_otg_reinit<T, N, false><<<g, 128, 0, b.stream>>>(otg_job(b, th), (const T*)th.S + (int64_t)JtL<N>::CUR_POS * b.stride, b.B, b.stride, mode,
+															   (int)th.otg_g_rows);
+		return done(b, "k_otg_reinit");
+	}
+	int otg_tick(Batch& b, int t) override {
+		TaskH& th = b.tasks[t];
+		const dim3 g((unsigned)((b.B + 127) / 128));
+		if (th.type == OSC_TASK_MOTION_FORCE) k_otg_tick<T, 6, true><<<g, 128, 0, b.stream>>>(otg_job(b, th), b.B, b.stride);
+		else k_otg_tick<T, N, false><<<g, 128, 0, b.stream>>>(otg_job(b, th), b.B, b.stride);
+		return done(b, "k_otg_tick");
 	}
 
 	bool locate(Batch& b, int task, int field, Loc& l) override;

@@ -28,6 +28,7 @@ STATUS_SVD_NOT_CONVERGED = 1 << 3
 STATUS_NOT_POSITIVE_DEFINITE = 1 << 4
 STATUS_SINGULAR_BRANCH = 1 << 5
 STATUS_BAD_GOAL_ORIENTATION = 1 << 6
+STATUS_OTG_ERROR = 1 << 7
 
 # field ids (enum in osc_b200.h)
 F_Q, F_DQ, F_TAU, F_M, F_MINV, F_N_TOTAL, F_STATUS, F_GRAVITY = 0, 1, 2, 3, 4, 5, 6, 7
@@ -43,11 +44,14 @@ F_INTEGRATED_POSITION_ERROR, F_INTEGRATED_ORIENTATION_ERROR = 65, 66
 F_INTEGRATED_FORCE_ERROR, F_INTEGRATED_MOMENT_ERROR = 67, 68
 F_POPC_RC, F_POPC_OBSERVER, F_Q_PRIOR = 69, 70, 71
 F_DESIRED_POSITION, F_DESIRED_ORIENTATION, F_DESIRED_LINEAR_VELOCITY, F_DESIRED_ANGULAR_VELOCITY = 72, 73, 74, 75
+F_DESIRED_LINEAR_ACCELERATION, F_DESIRED_ANGULAR_ACCELERATION = 76, 77
 F_JT_GOAL_POSITION, F_JT_GOAL_VELOCITY, F_JT_GOAL_ACCELERATION = 80, 81, 82
 F_JT_CURRENT_POSITION, F_JT_CURRENT_VELOCITY, F_JT_INTEGRATED_ERROR = 83, 84, 85
 F_JT_LAMBDA_WORLD, F_JT_LAMBDA_MODIFIED_WORLD, F_JT_RANGE_RANK, F_JT_DESIRED_VELOCITY = 86, 87, 88, 89
+F_JT_DESIRED_POSITION, F_JT_DESIRED_ACCELERATION = 90, 91
+F_OTG_FLAGS, F_OTG_RESULT = 100, 101
 
-INT_FIELDS = {F_STATUS, F_NS_RANK, F_SINGULARITY_TYPES, F_SINGULARITY_COUNTERS, F_JT_RANGE_RANK}
+INT_FIELDS = {F_STATUS, F_NS_RANK, F_SINGULARITY_TYPES, F_SINGULARITY_COUNTERS, F_JT_RANGE_RANK, F_OTG_FLAGS, F_OTG_RESULT}
 
 d = C.c_double
 i32 = C.c_int32

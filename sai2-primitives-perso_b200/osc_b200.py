@@ -79,6 +79,10 @@ def lib():
         "osc_snapshot": (i, [vp, vp, i]),
         "osc_restore": (i, [vp, vp, i]),
         "osc_measure_fp64_peak": (i, [i, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "osc_task_enable_internal_otg_acceleration_limited": (i, [vp, i, vp, i]),
+        "osc_task_enable_internal_otg_jerk_limited": (i, [vp, i, vp, i]),
+        "osc_task_disable_internal_otg": (i, [vp, i]),
+        "osc_task_internal_otg_enabled": (i, [vp, i]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -97,7 +101,8 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
             "osc_tick", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
-            "osc_snapshot", "osc_restore", "osc_measure_fp64_peak"]
+            "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",
+            "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled"]
 
 
 def measure_fp64_peak(device=0):
@@ -248,6 +253,19 @@ class Batch:
 
     def reinitialize_tasks(self, task=-1):
         self._chk(self.L.osc_reinitialize_tasks(self.h, task))
+
+    def enable_internal_otg(self, task, max_velocity, max_acceleration):
+        """enableInternalOtgAccelerationLimited.  JointTask: scalars or length-k vectors; MotionForceTask: (lin, ang) pairs."""
+        mv = np.atleast_1d(np.asarray(max_velocity, dtype=np.float64))
+        ma = np.atleast_1d(np.asarray(max_acceleration, dtype=np.float64))
+        lim = np.ascontiguousarray(np.concatenate([mv, ma]))
+        self._chk(self.L.osc_task_enable_internal_otg_acceleration_limited(self.h, task, lim.ctypes.data, len(mv)))
+
+    def disable_internal_otg(self, task):
+        self._chk(self.L.osc_task_disable_internal_otg(self.h, task))
+
+    def internal_otg_enabled(self, task):
+        return bool(self.L.osc_task_internal_otg_enabled(self.h, task))
 
     def synchronize(self):
         self._chk(self.L.osc_synchronize(self.h))

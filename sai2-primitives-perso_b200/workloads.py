@@ -75,3 +75,52 @@ def config3_wrench(B, tick, seed=3, goal_force=(0.0, 0.0, -5.0), dt=0.001):
     g = np.asarray(goal_force, float)
     f = g[None] * (1 + 0.3 * np.sin(2 * np.pi * 3 * tick * dt + phase))[:, None] + rng.normal(0, 0.2, (B, 3))
     return f, np.zeros((B, 3))
+
+
+def otg_rollout(batch, w, t0, t1, ticks, abi, every=10, per_call=True):
+    """Roll-out with the internal OTGs on, shared by tools/make_otg_golden.py (CPU oracle on the
+    real Ruckig) and tests/test_otg_gpu.py (CUDA path): the robots stay at the config-2 state (q, dq of `w`: no simulator
+    here, and the OTG does not read the robot state), the goals change at ticks 0, 120 (new pose + joint goal), 200
+    (goal velocity on half of the robots) and 300 (back to the first goals).  `batch` is an osc_b200.Batch or an
+    orc.OracleBatch (same method names).  Records, every `every` ticks: torques, desired pose / joint positions, OTG flags."""
+    B, n = w["q"].shape
+    rng = np.random.default_rng(1234)
+    goals2 = dict(pos=w["goal_pos"] + rng.uniform(-0.08, 0.08, (B, 3)), jt=w["jt_goal"] + rng.uniform(-0.4, 0.4, (B, n)))
+    half = (np.arange(B) % 2 == 0)[:, None]
+    rec = dict(tau=[], des_pos=[], des_ori=[], des_linvel=[], des_angvel=[], jt_des_pos=[], jt_des_vel=[], jt_des_acc=[], flags0=[], flags1=[])
+    for t in range(ticks):
+        if t == 0:
+            batch.set(abi.F_GOAL_POSITION, w["goal_pos"], t0)
+            batch.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
+            batch.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
+        elif t == 120:
+            batch.set(abi.F_GOAL_POSITION, goals2["pos"], t0)
+            batch.set(abi.F_JT_GOAL_POSITION, goals2["jt"], t1)
+        elif t == 200:
+            batch.set(abi.F_GOAL_LINEAR_VELOCITY, np.where(half, w["goal_linvel"], 0.0), t0)
+            batch.set(abi.F_GOAL_ANGULAR_VELOCITY, np.where(half, w["goal_angvel"], 0.0), t0)
+            batch.set(abi.F_JT_GOAL_VELOCITY, np.where(half, 0.05, 0.0) * np.ones((B, n)), t1)
+        elif t == 300:
+            batch.set(abi.F_GOAL_LINEAR_VELOCITY, np.zeros((B, 3)), t0)
+            batch.set(abi.F_GOAL_ANGULAR_VELOCITY, np.zeros((B, 3)), t0)
+            batch.set(abi.F_JT_GOAL_VELOCITY, np.zeros((B, n)), t1)
+            batch.set(abi.F_GOAL_POSITION, w["goal_pos"], t0)
+            batch.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
+        if per_call:
+            batch.update_model()
+            batch.update_task_models()
+            tau = batch.compute_torques(True)
+        else:
+            tau = batch.tick(True)
+        if t % every == 0 or t == ticks - 1:
+            rec["tau"].append(np.asarray(tau, dtype=np.float64))
+            rec["des_pos"].append(np.asarray(batch.get(abi.F_DESIRED_POSITION, t0), dtype=np.float64))
+            rec["des_ori"].append(np.asarray(batch.get(abi.F_DESIRED_ORIENTATION, t0), dtype=np.float64))
+            rec["des_linvel"].append(np.asarray(batch.get(abi.F_DESIRED_LINEAR_VELOCITY, t0), dtype=np.float64))
+            rec["des_angvel"].append(np.asarray(batch.get(abi.F_DESIRED_ANGULAR_VELOCITY, t0), dtype=np.float64))
+            rec["jt_des_pos"].append(np.asarray(batch.get(abi.F_JT_DESIRED_POSITION, t1), dtype=np.float64))
+            rec["jt_des_vel"].append(np.asarray(batch.get(abi.F_JT_DESIRED_VELOCITY, t1), dtype=np.float64))
+            rec["jt_des_acc"].append(np.asarray(batch.get(abi.F_JT_DESIRED_ACCELERATION, t1), dtype=np.float64))
+            rec["flags0"].append(np.asarray(batch.get(abi.F_OTG_FLAGS, t0)).astype(np.int32) & 1)
+            rec["flags1"].append(np.asarray(batch.get(abi.F_OTG_FLAGS, t1)).astype(np.int32) & 1)
+    return {k: np.stack(v) for k, v in rec.items()}
