@@ -222,7 +222,8 @@ enum {
 	OSC_F_JT_DESIRED_ACCELERATION = 91, /* k out */
 	/* internal OTG of a task (either type), valid once it has been enabled */
 	OSC_F_OTG_FLAGS = 100,  /* 1 (int32) out: bit 0 = isGoalReached() (OTG_joints.h, OTG_6dof_cartesian.h) */
-	OSC_F_OTG_RESULT = 101  /* 1 (int32) out: ruckig::Result of the last update (0 working, 1 finished, < 0 error) */
+	OSC_F_OTG_RESULT = 101, /* 1 (int32) out: ruckig::Result of the last update (0 working, 1 finished, < 0 error) */
+	OSC_F_OTG_STATE = 102   /* diagnostic, FP64 batches only: the raw state rows of the OTG (layout OtgL<D> in csrc/osc_otg.cuh) */
 };
 
 typedef struct osc_batch osc_batch_t;

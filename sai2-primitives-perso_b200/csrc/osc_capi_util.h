@@ -141,6 +141,7 @@ inline void* arena_base(Batch& b, const Loc& l) {
 	TaskH& t = b.tasks[l.owner];
 	if (l.arena == 3) return t.otgG;
 	if (l.arena == 4) return (void*)t.otgI;
+	if (l.arena == 5) return (void*)t.otgO;
 	return l.arena == 0 ? t.P : (l.arena == 1 ? t.S : (void*)t.I);
 }
 inline void* row_ptr(Batch& b, const Loc& l) {

@@ -76,6 +76,7 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 			case OSC_F_DESIRED_ANGULAR_ACCELERATION: return set(0, L::GOAL_ANGACC, 3, false);
 			case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<6>::FLAGS, 1, false, true);
 			case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<6>::RESULT, 1, false, true);
+			case OSC_F_OTG_STATE: if (!t.otgO || sizeof(T) != 8) return false; return set(5, 0, OtgL<6>::O_SIZE, false);
 		}
 		(void)K;
 		return false;
@@ -102,6 +103,7 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 		case OSC_F_JT_DESIRED_ACCELERATION: return set(0, L::GOAL_ACC, k, false);
 		case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<N>::FLAGS, 1, false, true);
 		case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<N>::RESULT, 1, false, true);
+		case OSC_F_OTG_STATE: if (!t.otgO || sizeof(T) != 8) return false; return set(5, 0, OtgL<N>::O_SIZE, false);
 	}
 	return false;
 }

@@ -91,7 +91,7 @@ struct OtgBlock {  // ruckig/include/ruckig/block.hpp: fastest profile + at most
 
 // PositionSecondOrderStep1::get_profile (ruckig/src/ruckig/position-second-step1.cpp:92-136) + Block::calculate_block
 // (block.hpp:58-131).  `base` carries the boundary and the brake segment.
-__device__ inline bool otg_step1(const OtgProf& base, double vMax_, double aMax_, OtgBlock& blk) {
+static __device__ __noinline__ bool otg_step1(const OtgProf& base, double vMax_, double aMax_, OtgBlock& blk) {
 	const double vMin_ = -vMax_, aMin_ = -aMax_;
 	const double v0 = base.v0, vf = base.vf, pd = base.pf - base.p0;
 	OtgProf cand[4];
@@ -170,7 +170,7 @@ __device__ inline bool otg_step1(const OtgProf& base, double vMax_, double aMax_
 }
 
 // PositionSecondOrderStep2::get_profile (ruckig/src/ruckig/position-second-step2.cpp:109-117): profile of duration tf
-__device__ inline bool otg_step2(OtgProf& p, double tf, double vMax_, double aMax_) {
+static __device__ __noinline__ bool otg_step2(OtgProf& p, double tf, double vMax_, double aMax_) {
 	const double v0 = p.v0, vf = p.vf, pd = p.pf - p.p0, vd = p.vf - p.v0;
 	auto all = [&](double vMax, double vMin, double aMax, double aMin) -> bool {
 		{  // time_acc0, UD, :16-31
@@ -218,8 +218,11 @@ __device__ inline bool otg_step2(OtgProf& p, double tf, double vMax_, double aMa
 
 // TargetCalculator::calculate for the second-order position interface (calculator_target.hpp:227-523).
 // in: current p, v, a; target p, v; limits.  out: one profile per DoF + the synchronised duration.
+// __noinline__ (also otg_step1 / otg_step2): this is the rare, divergent path; kept out of line it costs the steady-state
+// advance no registers, and the fully inlined 255-register build of nvcc 12.9 overlapped the caller's cp[] with prof[] in
+// the local frame for D = 6 (caught by tests/test_otg_gpu.py against the golden vectors; the out-of-line build is correct).
 template <int D>
-__device__ int otg_calculate(int n, const double* cp, const double* cv, const double* ca, const double* tp, const double* tv, const double* mv,
+__device__ __noinline__ int otg_calculate(int n, const double* cp, const double* cv, const double* ca, const double* tp, const double* tv, const double* mv,
 							 const double* ma, OtgProf* prof, double& duration) {
 	const double eps = 2.220446049250313e-16;
 	OtgBlock blk[D];
@@ -565,7 +568,13 @@ __global__ void __launch_bounds__(128) k_otg_tick(const __grid_constant__ OtgJob
 				if (isnan(cp[i]) || isnan(cv[i]) || isnan(ca[i]) || isnan(tgt_p[i]) || isnan(tgt_v[i])) result = OTG_ERR_INPUT;
 				if (tgt_v[i] > job.max_v[i] || tgt_v[i] < -job.max_v[i]) result = OTG_ERR_INPUT;
 			}
+#ifdef OSC_OTG_DEBUG
+		if (r == 0) printf("otg dbg CART=%d flags=%d cp=%g %g %g %g %g %g out_p=%g %g %g have_out=%d\n", (int)CART, flags, cp[0], cp[1], cp[2], cp[3], cp[4], cp[5], out_p[0], out_p[1], out_p[2], (int)have_out);
+#endif
 		if (result == OTG_WORKING) result = otg_calculate<D>(k, cp, cv, ca, tgt_p, tgt_v, job.max_v, job.max_a, prof, duration);
+#ifdef OSC_OTG_DEBUG
+		if (r == 0) printf("otg dbg after calc res=%d dur=%g pS=%g %g %g\n", result, duration, prof[0].pS, prof[1].pS, prof[2].pS);
+#endif
 		if (result != OTG_WORKING) {
 			// the wrappers keep the previous output and zero the input velocity / acceleration (OTG_joints.cpp:144-149)
 			if (flags & OTG_IN_SYNCED) {

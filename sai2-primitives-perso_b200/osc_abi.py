@@ -49,7 +49,7 @@ F_JT_GOAL_POSITION, F_JT_GOAL_VELOCITY, F_JT_GOAL_ACCELERATION = 80, 81, 82
 F_JT_CURRENT_POSITION, F_JT_CURRENT_VELOCITY, F_JT_INTEGRATED_ERROR = 83, 84, 85
 F_JT_LAMBDA_WORLD, F_JT_LAMBDA_MODIFIED_WORLD, F_JT_RANGE_RANK, F_JT_DESIRED_VELOCITY = 86, 87, 88, 89
 F_JT_DESIRED_POSITION, F_JT_DESIRED_ACCELERATION = 90, 91
-F_OTG_FLAGS, F_OTG_RESULT = 100, 101
+F_OTG_FLAGS, F_OTG_RESULT, F_OTG_STATE = 100, 101, 102
 
 INT_FIELDS = {F_STATUS, F_NS_RANK, F_SINGULARITY_TYPES, F_SINGULARITY_COUNTERS, F_JT_RANGE_RANK, F_OTG_FLAGS, F_OTG_RESULT}
 

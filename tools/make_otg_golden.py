@@ -162,7 +162,7 @@ def main():
     import osc_abi as abi
     import workloads
     chain = json.load(open(os.path.join(ROOT, "fixtures", "panda.chain.json")))
-    B, T = 48, 400
+    B, T = 48, 1000
     w = workloads.config2(chain, B, seed=31)
     q0 = [j["q0"] for j in chain["joints"]]
     o = orc.OracleBatch(chain, B, q0=q0)
