@@ -26,6 +26,10 @@ WORKLOAD = "Panda 7-DoF 6-DoF OSC + joint nullspace task, batch 65,536 robots pe
 # algorithmic work per robot-tick, frozen from SURVEY.md 8(d) (the reference's own route: two Jacobi SVDs included)
 ALG_FLOP_PER_TICK = 3.6e4
 ALG_BYTES_PER_TICK = 416.0
+# internal OTG state advance, both tasks: per DoF the current segment (p, v, a, end time) read and the
+# desired (p, v, a) written, plus the trajectory clock; the cartesian OTG also writes the 9 entries of the desired orientation
+# joints (n = 7): (4*7 + 1 + 3*7) * 8 = 400 B; cartesian: (4*6 + 1 + 24) * 8 = 392 B
+OTG_BYTES_PER_TICK = 792.0
 
 
 def load_chain(name="panda"):
@@ -187,6 +191,7 @@ def main():
     ap.add_argument("--batch", type=int, default=65536, help="robots per GPU")
     ap.add_argument("--precision", type=int, default=64, choices=[64, 32])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-otg", action="store_true", help="skip the extra measurement with the internal OTGs enabled")
     ap.add_argument("--tick-outputs", default="lazy", choices=["lazy", "tau", "all"],
                     help="lazy (default): the tick also writes every vector-valued getter of the reference; tau: torques only")
     args = ap.parse_args()
@@ -301,6 +306,35 @@ def run_b200(args, rank, world, local_rank):
                 s.record(); fn(); e.record(); torch.cuda.synchronize()
                 ts.append(s.elapsed_time(e))
             stages[name] = float(np.mean(ts))
+    # ---- the same tick with the reference's default internal OTGs on: k_otg_tick x2 ahead of the fused
+    # kernel.  First tick after a goal change = every robot recalculates its trajectory; then the steady state-advance.
+    otg = None
+    if not args.no_otg and fused:
+        batch.enable_internal_otg(t0, [0.3, np.pi / 3], [2.0, 2 * np.pi])   # MotionForceTask.h:68-71
+        batch.enable_internal_otg(t1, np.pi / 3, 2 * np.pi)                  # JointTask.h:40-41
+        rng = np.random.default_rng(99)
+        batch.set(abi.F_GOAL_POSITION, w["goal_pos"] + rng.uniform(-0.2, 0.2, (B, 3)), t0)
+        batch.set(abi.F_JT_GOAL_POSITION, w["jt_goal"] + rng.uniform(-1.0, 1.0, (B, n)), t1)
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush.zero_(); s.record(); batch.tick(True, fetch=False); e.record(); torch.cuda.synchronize()
+        recalc_ms = s.elapsed_time(e)
+        for _ in range(args.warmup):
+            batch.tick(True, fetch=False)
+        ts = []
+        for _ in range(args.steps):
+            flush.zero_()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record(); batch.tick(True, fetch=False); e.record(); torch.cuda.synchronize()
+            ts.append(s.elapsed_time(e))
+        reached = (np.asarray(batch.get(abi.F_OTG_FLAGS, t1))[:, 0] & 1).mean()
+        otg_ms = float(np.mean(ts))
+        extra_ms = otg_ms - float(np.mean(step_ms))
+        otg = {"ms_per_step": otg_ms, "value": B / (otg_ms * 1e-3), "unit": UNIT, "first_tick_all_robots_recalculate_ms": recalc_ms,
+               "k_otg_tick_x2_ms": extra_ms, "alg_bytes_per_robot_tick": OTG_BYTES_PER_TICK,
+               "hbm_frac_of_otg_kernels": OTG_BYTES_PER_TICK * B / max(extra_ms * 1e-3, 1e-9) / 1e9 / (
+                   json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0),
+               "robots_at_goal_after": float(reached), "limits": "reference defaults (MotionForceTask.h:68-71, JointTask.h:40-41)"}
+        batch.disable_internal_otg(t0); batch.disable_internal_otg(t1)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -349,6 +383,8 @@ def run_b200(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "path": "osc_set_field x5 + osc_tick with pinned HOST SoA buffers (C ABI)"},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_hbm": roof_hbm}
+    if otg:
+        line["otg_on"] = otg
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(chain)
     print(json.dumps(line))

@@ -301,8 +301,20 @@ public:
 	void setSingularityHandlingGains(double kp_type_1, double kv_type_1, double kv_type_2) {
 		edit([&](osc_mft_params& p) { p.kp_type_1 = kp_type_1; p.kv_type_1 = kv_type_1; p.kv_type_2 = kv_type_2; });
 	}
-	// the internal OTG of the reference is the "next" row f-1: the batched task runs with it disabled (04...cpp:115)
-	void disableInternalOtg() {}
+	// ---- internal OTG (MotionForceTask.h:387-427, MotionForceTask.cpp:511-538): on by default, acceleration limited ----
+	void enableInternalOtgAccelerationLimited(double max_linear_velocity, double max_linear_acceleration, double max_angular_velocity,
+											  double max_angular_acceleration) {
+		const double lim[4] = {max_linear_velocity, max_angular_velocity, max_linear_acceleration, max_angular_acceleration};
+		check(osc_task_enable_internal_otg_acceleration_limited(_robot->handle(), _index, lim, 2));
+	}
+	// third-order (jerk-limited) profiles are not built: OSC_ERR_UNSUPPORTED -> std::runtime_error
+	void enableInternalOtgJerkLimited(double, double, double, double, double, double) {
+		check(osc_task_enable_internal_otg_jerk_limited(_robot->handle(), _index, nullptr, 0));
+	}
+	void disableInternalOtg() { check(osc_task_disable_internal_otg(_robot->handle(), _index)); }
+	bool getInternalOtgEnabled() const { return osc_task_internal_otg_enabled(_robot->handle(), _index) != 0; }
+	void getDesiredLinearAcceleration(const Out& o) { _robot->get(_index, OSC_F_DESIRED_LINEAR_ACCELERATION, o); }
+	void getDesiredAngularAcceleration(const Out& o) { _robot->get(_index, OSC_F_DESIRED_ANGULAR_ACCELERATION, o); }
 	void resetIntegrators() {
 		const std::array<double, 3> z = {0, 0, 0};
 		_robot->set(_index, OSC_F_INTEGRATED_POSITION_ERROR, z);
@@ -340,6 +352,8 @@ private:
 		d.loop_timestep = _dt;
 		_index = osc_batch_add_motion_force_task(_robot->handle(), &d);
 		check(_index);
+		// DefaultParameters::use_internal_otg = true, acceleration limited (MotionForceTask.h:67-72, MotionForceTask.cpp:173-188)
+		enableInternalOtgAccelerationLimited(0.3, 2.0, 3.14159265358979323846 / 3, 2 * 3.14159265358979323846);
 	}
 	Affine3 _compliant_frame;
 };
@@ -355,6 +369,7 @@ public:
 		_k = d.k;
 		_index = osc_batch_add_joint_task(_robot->handle(), &d);
 		check(_index);
+		enableInternalOtgAccelerationLimited(3.14159265358979323846 / 3, 2 * 3.14159265358979323846);  // JointTask.h:38-41, JointTask.cpp:73-83
 	}
 	// JointTask(robot, joint_selection_matrix (k x n, row-major, full row rank), task_name, loop_timestep)   JointTask.h:70-75, .cpp:23-43
 	JointTask(const std::shared_ptr<RobotBatch>& robot, const std::vector<double>& joint_selection_matrix, int task_dof,
@@ -369,6 +384,7 @@ public:
 		_k = task_dof;
 		_index = osc_batch_add_joint_task(_robot->handle(), &d);
 		check(_index);
+		enableInternalOtgAccelerationLimited(3.14159265358979323846 / 3, 2 * 3.14159265358979323846);  // JointTask.h:38-41, JointTask.cpp:73-83
 	}
 	bool isFullJointTask() const { return _k == _robot->dof(); }  // JointTask.h:123
 	int getTaskDof() const { return _k; }
@@ -403,7 +419,24 @@ public:
 	void disableVelocitySaturation() { edit([&](osc_joint_task_params& p) { p.use_velocity_saturation = 0; }); }
 	void setDynamicDecouplingType(DynamicDecouplingType type) { edit([&](osc_joint_task_params& p) { p.dynamic_decoupling_type = type; }); }
 	void setBoundedInertiaEstimateThreshold(double threshold) { edit([&](osc_joint_task_params& p) { p.bie_threshold = threshold; }); }
-	void disableInternalOtg() {}
+	// ---- internal OTG (JointTask.h:262-324, JointTask.cpp:358-406): on by default, acceleration limited ----
+	void enableInternalOtgAccelerationLimited(double max_velocity, double max_acceleration) {
+		const double lim[2] = {max_velocity, max_acceleration};
+		check(osc_task_enable_internal_otg_acceleration_limited(_robot->handle(), _index, lim, 1));
+	}
+	void enableInternalOtgAccelerationLimited(const std::vector<double>& max_velocity, const std::vector<double>& max_acceleration) {
+		if (max_velocity.size() == 1 && max_acceleration.size() == 1 && _k != 1) return enableInternalOtgAccelerationLimited(max_velocity[0], max_acceleration[0]);
+		if ((int)max_velocity.size() != _k || (int)max_acceleration.size() != _k)
+			throw std::invalid_argument("max velocity or max acceleration vector size not consistent with task dof in JointTask::enableInternalOtgAccelerationLimited\n");
+		std::vector<double> lim(max_velocity);
+		lim.insert(lim.end(), max_acceleration.begin(), max_acceleration.end());
+		check(osc_task_enable_internal_otg_acceleration_limited(_robot->handle(), _index, lim.data(), _k));
+	}
+	void enableInternalOtgJerkLimited(double, double, double) { check(osc_task_enable_internal_otg_jerk_limited(_robot->handle(), _index, nullptr, 0)); }
+	void disableInternalOtg() { check(osc_task_disable_internal_otg(_robot->handle(), _index)); }
+	bool getInternalOtgEnabled() const { return osc_task_internal_otg_enabled(_robot->handle(), _index) != 0; }
+	void getDesiredPosition(const Out& o) { _robot->get(_index, OSC_F_JT_DESIRED_POSITION, o); }
+	void getDesiredAcceleration(const Out& o) { _robot->get(_index, OSC_F_JT_DESIRED_ACCELERATION, o); }
 	void resetIntegrators() { _robot->set(_index, OSC_F_JT_INTEGRATED_ERROR, std::vector<double>((size_t)_k, 0.0)); }  // JointTask.h:394
 	osc_joint_task_params getParams() const { osc_joint_task_params p; check(osc_joint_task_get_params(_robot->handle(), _index, &p)); return p; }
 

@@ -67,7 +67,7 @@ void osc_batch_destroy(osc_batch_t* batch) {
 	if (!b) return;
 	cudaSetDevice(b->device);
 	cudaStreamSynchronize(b->stream);
-	for (TaskH& t : b->tasks) { cudaFree(t.P); cudaFree(t.S); cudaFree(t.I); cudaFree(t.popc_ring); cudaFree(t.otgO); cudaFree(t.otgI); cudaFree(t.otgG); }
+	for (TaskH& t : b->tasks) { cudaFree(t.P); cudaFree(t.S); cudaFree(t.I); cudaFree(t.popc_ring); cudaFree(t.otgO); cudaFree(t.otgI); cudaFree(t.otgG); cudaFree(t.otg_slow); }
 	cudaFree(b->P); cudaFree(b->S); cudaFree(b->I); cudaFree(b->stage); cudaFree(b->stage2); cudaFree(b->fb);
 	delete b->ops;
 	delete b;

@@ -31,6 +31,7 @@ int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int
 	if (!b->ops->locate(*b, task, field, l)) return invalid("unknown field for this task");
 	if (!l.writable || l.special) return invalid("field is read-only");
 	if (int rc = use_device(*b)) return rc;
+	if (l.arena == 3) b->tasks[l.owner].otg_goals_dirty = true;  // the next k_otg_advance runs the goal filter
 	return import_rows(*b, row_ptr(*b, l), l.width, l.is_int, data, layout, mem);
 }
 

@@ -269,6 +269,7 @@ int osc_task_enable_internal_otg_acceleration_limited(osc_batch_t* batch, int ta
 		if (int rc = b->ops->otg_reinit(*b, task, 1 | 8 | (fresh ? 32 : 0))) return rc;
 	}
 	t.otg_on = true;
+	t.otg_goals_dirty = true;
 	return OSC_OK;
 }
 int osc_task_enable_internal_otg_jerk_limited(osc_batch_t* batch, int task, const double* limits, int count) {

@@ -83,9 +83,7 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (int rc = use_device(*b)) return rc;
 	if (b->ops->fused_supported(*b)) {
-		for (int t = 0; t < (int)b->tasks.size(); ++t)  // the desired state of this tick, before the control law reads it
-			if (b->tasks[t].otg_on)
-				if (int rc = b->ops->otg_tick(*b, t)) return rc;
+		if (int rc = b->ops->otg_tick(*b, -1)) return rc;  // the desired state of this tick, before the control law reads it
 		if (int rc = b->ops->tick_fused(*b, stacked)) return rc;
 		return emit_tau(*b, tau_out, layout, mem);
 	}
@@ -171,6 +169,7 @@ int osc_restore(osc_batch_t* batch, const void* src, int mem) {
 	if (!b || !src) return invalid("null argument");
 	if (int rc = use_device(*b)) return rc;
 	if (snapshot_walk(*b, (char*)src, mem, 1) < 0) return OSC_ERR_CUDA;
+	for (TaskH& t : b->tasks) t.otg_goals_dirty = true;
 	if (mem == OSC_MEM_HOST) OSC_CUDA(cudaStreamSynchronize(b->stream));
 	return OSC_OK;
 }

@@ -32,6 +32,9 @@ struct TaskH {
 	void* otgG = nullptr;
 	int64_t otg_o_rows = 0, otg_i_rows = 0, otg_g_rows = 0;
 	double otg_max_v[8]{}, otg_max_a[8]{};
+	bool otg_goals_dirty = true;  // a goal field was written (or the state restored) since the last k_otg_advance
+	int* otg_slow = nullptr;      // device: [2] ping-pong counters + [stride] list of the robots on the general path
+	int otg_parity = 0;
 };
 
 struct Loc {
@@ -66,7 +69,7 @@ struct Ops {
 	virtual int materialise(Batch& b) = 0;
 	virtual void otg_rows(Batch& b, int t, int64_t& o, int64_t& i, int64_t& g) = 0;
 	virtual int otg_reinit(Batch& b, int t, int mode) = 0;  // k_otg_reinit modes (osc_otg.cuh)
-	virtual int otg_tick(Batch& b, int t) = 0;              // goal filter + update() + desired rows of task t  // after a fused tick: run the per-call model / task-model kernels (no state advance)
+	virtual int otg_tick(Batch& b, int t) = 0;              // goal filter + update() + desired rows of task t (all tasks: t < 0)  // after a fused tick: run the per-call model / task-model kernels (no state advance)
 };
 
 Ops* make_ops(int precision, int n);  // nullptr when that (precision, dof) pair was not compiled in

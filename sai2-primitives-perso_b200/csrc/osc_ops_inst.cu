@@ -194,6 +194,7 @@ template <class T, int N> struct OpsImpl : Ops {
 	}
 	int otg_reinit(Batch& b, int t, int mode) override {
 		TaskH& th = b.tasks[t];
+		th.otg_goals_dirty = true;
 		const dim3 g((unsigned)((b.B + 127) / 128));
 		if (th.type == OSC_TASK_MOTION_FORCE)
 			k_otg_reinit<T, 6, true><<<g, 128, 0, b.stream>>>(otg_job(b, th), (const T*)th.P, b.B, b.stride, mode, (int)th.otg_g_rows);
@@ -202,12 +203,51 @@ template <class T, int N> struct OpsImpl : Ops {
 															   (int)th.otg_g_rows);
 		return done(b, "k_otg_reinit");
 	}
+	// goal filter + update() + desired rows of task t (t >= 0) or of every task whose OTG is on (t < 0): two launches
 	int otg_tick(Batch& b, int t) override {
-		TaskH& th = b.tasks[t];
-		const dim3 g((unsigned)((b.B + 127) / 128));
-		if (th.type == OSC_TASK_MOTION_FORCE) k_otg_tick<T, 6, true><<<g, 128, 0, b.stream>>>(otg_job(b, th), b.B, b.stride);
-		else k_otg_tick<T, N, false><<<g, 128, 0, b.stream>>>(otg_job(b, th), b.B, b.stride);
-		return done(b, "k_otg_tick");
+		OtgJobs js{};
+		int cnt = 0;
+		for (int i = 0; i < (int)b.tasks.size(); ++i) {
+			TaskH& th = b.tasks[i];
+			if (!th.otg_on || (t >= 0 && i != t)) continue;
+			if (!th.otg_slow) {
+				cudaError_t e = cudaMalloc((void**)&th.otg_slow, (size_t)(b.stride + 2) * sizeof(int));
+				if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc(otg slow list)");
+				e = cudaMemsetAsync(th.otg_slow, 0, 2 * sizeof(int), b.stream);
+				if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(otg slow counters)");
+				th.otg_parity = 0;
+			}
+			OtgJob& j = js.j[cnt];
+			j = otg_job(b, th);
+			j.check_goals = th.otg_goals_dirty ? 1 : 0;
+			j.slow_count = th.otg_slow + th.otg_parity;
+			j.slow_next = th.otg_slow + (th.otg_parity ^ 1);
+			j.slow_list = th.otg_slow + 2;
+			js.cart[cnt] = th.type == OSC_TASK_MOTION_FORCE;
+			th.otg_parity ^= 1;
+			th.otg_goals_dirty = false;
+			++cnt;
+		}
+		if (!cnt) return OSC_OK;
+		const dim3 g((unsigned)((b.B + 127) / 128), cnt);
+		k_otg_advance<T, N><<<g, 128, 0, b.stream>>>(js, b.B, b.stride);
+		if (int rc = done(b, "k_otg_advance")) return rc;
+		cudaLaunchConfig_t cfg = {};
+		// a goal write may send every robot to the general path (MPC: new goals each tick): full grid then, else a small one
+		bool any_goal_write = false;
+		for (int i = 0; i < cnt; ++i) any_goal_write |= js.j[i].check_goals != 0;
+		cfg.gridDim = dim3((unsigned)(any_goal_write ? (b.B + 127) / 128 : std::min<int64_t>((b.B + 127) / 128, 148 * 2)), cnt);
+		cfg.blockDim = dim3(128);
+		cfg.stream = b.stream;
+		cudaLaunchAttribute at[1];
+		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+		at[0].val.programmaticStreamSerializationAllowed = 1;
+		static const bool pdl = !getenv("OSC_NO_PDL");
+		cfg.attrs = at;
+		cfg.numAttrs = pdl ? 1 : 0;
+		cudaError_t e = cudaLaunchKernelEx(&cfg, k_otg_slow<T, N>, js, b.stride);
+		if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_otg_slow)");
+		return done(b, "k_otg_slow");
 	}
 
 	bool locate(Batch& b, int task, int field, Loc& l) override;

@@ -36,10 +36,14 @@ template <int D> struct OtgL {
 						 TRAJ = 8 * D,  // 11 per DoF: brake t, brake a, p start, v start, t0, t1, t2, t6, a0, a2, a6
 						 TIME = 19 * D, DUR = TIME + 1,
 						 REF = DUR + 1, GORI = REF + 9, GANG = GORI + 9,  // cartesian only: _reference_frame, _goal_*_in_base_frame
-						 O_SIZE = GANG + 3;
+						 // current segment of every DoF, 6 per DoF (row e of DoF d at SEG + e * D + d): time offset (brake duration
+						 // once past it), segment start / end in that clock, p, v at the start, acceleration.  end < 0 = stale.
+						 SEG = GANG + 3, O_SIZE = SEG + 6 * D;
 	static constexpr int FLAGS = 0, RESULT = 1, ERRORS = 2, I_SIZE = 3;
 };
-enum : int { OTG_REACHED = 1, OTG_INIT = 2, OTG_DIRTY = 4, OTG_IN_SYNCED = 8 };
+// OUT_LIVE: the OUT rows are stale, the current output is the stored trajectory evaluated at TIME (the steady-state
+// advance does not store what it can re-derive)
+enum : int { OTG_REACHED = 1, OTG_INIT = 2, OTG_DIRTY = 4, OTG_IN_SYNCED = 8, OTG_OUT_LIVE = 16 };
 enum : int { OTG_WORKING = 0, OTG_FINISHED = 1, OTG_ERR_INPUT = -100, OTG_ERR_DURATION = -101, OTG_ERR_STEP1 = -110, OTG_ERR_SYNC = -111 };
 
 struct OtgJob {
@@ -52,6 +56,10 @@ struct OtgJob {
 	int k;            // joints: task dof
 	double dt;
 	double max_v[8], max_a[8];
+	int check_goals;  // 0: no goal field was written since the last tick (host knowledge): the goal filter is skipped
+	int* slow_count;  // robots that need the general path this tick (compacted list, filled by k_otg_advance)
+	int* slow_next;   // the counter of the next tick (zeroed by k_otg_slow)
+	int* slow_list;
 };
 
 // ---- one DoF profile, compact ----
@@ -359,6 +367,25 @@ __device__ inline void otg_eval(const OtgProf& p, double tm, double duration, do
 	na = ba + t * 0.0;
 }
 
+// The segment of a profile that contains time tm (< duration), in the form the advance kernel caches: the same branches
+// and the same subtraction order as otg_eval, so that evaluating the cached segment reproduces otg_eval bit for bit.
+struct OtgSeg { double off, ts, te, p, v, a; };
+__device__ inline OtgSeg otg_segment(const OtgProf& p, double tm) {
+	const double v1 = p.v0 + p.t0 * p.a0, p1 = p.p0 + p.t0 * (p.v0 + p.t0 * p.a0 / 2);
+	const double p2 = p1 + p.t1 * (v1 + p.t1 * 0.0 / 2);
+	const double v3 = v1 + p.t2 * p.a2, p3 = p2 + p.t2 * (v1 + p.t2 * p.a2 / 2);
+	const double v7 = v3 + p.t6 * p.a6, p7 = p3 + p.t6 * (v3 + p.t6 * p.a6 / 2);
+	const double s0 = p.t0, s1 = s0 + p.t1, s2 = s1 + p.t2, s6 = s2 + p.t6;
+	if (p.brT > 0 && tm < p.brT) return OtgSeg{0.0, 0.0, p.brT, p.pS, p.vS, p.brA};
+	const double off = p.brT > 0 ? p.brT : 0.0;
+	const double td = p.brT > 0 ? tm - p.brT : tm;
+	if (td >= s6) return OtgSeg{off, s6, CUDART_INF, p7, v7, 0.0};
+	if (td < s0) return OtgSeg{off, 0.0, s0, p.p0, p.v0, p.a0};
+	if (td < s1) return OtgSeg{off, s0, s1, p1, v1, 0.0};
+	if (td < s2) return OtgSeg{off, s1, s2, p2, v1, p.a2};
+	return OtgSeg{off, s2, s6, p3, v3, p.a6};
+}
+
 // Eigen DenseBase::isApprox: |a-b|^2 <= prec^2 min(|a|^2, |b|^2)
 template <int K> __device__ inline bool otg_approx(const double* a, const double* b, int k, double prec) {
 	double d2 = 0, a2 = 0, b2 = 0;
@@ -445,13 +472,40 @@ __device__ inline bool otg_valid_rotation(const double* R) {  // OTG_6dof_cartes
 	return !(fabs(det - 1) > 1e-3);
 }
 
-// ---- the per-tick kernel -------------------------------------------------------------------------------------------
+// stored profile of DoF d (11 doubles) -> registers; p0, v0 re-derived from the brake segment like brake.hpp:65-75
+template <int D> __device__ inline void otg_load_prof(const Row<double>& O, int d, OtgProf& p) {
+	const int o = OtgL<D>::TRAJ + 11 * d;
+	p.brT = O(o); p.brA = O(o + 1); p.pS = O(o + 2); p.vS = O(o + 3); p.t0 = O(o + 4); p.t1 = O(o + 5); p.t2 = O(o + 6);
+	p.t6 = O(o + 7); p.a0 = O(o + 8); p.a2 = O(o + 9); p.a6 = O(o + 10);
+	if (p.brT > 0.0) {
+		p.p0 = p.pS + p.brT * (p.vS + p.brT * (p.brA / 2 + p.brT * 0.0 / 6));
+		p.v0 = p.vS + p.brT * (p.brA + p.brT * 0.0 / 2);
+	} else { p.p0 = p.pS; p.v0 = p.vS; }
+}
+// _output.new_* of a robot: the OUT rows, or the stored trajectory at TIME when the advance kernel skipped the stores
+template <int D> __device__ inline void otg_current_output(const Row<double>& O, int flags, int k, double* out_p, double* out_v, double* out_a) {
+	using L = OtgL<D>;
+	if (flags & OTG_OUT_LIVE) {
+		const double tm = O(L::TIME), dur = O(L::DUR);
+		for (int d = 0; d < k; ++d) {
+			OtgProf p;
+			otg_load_prof<D>(O, d, p);
+			otg_eval(p, tm, dur, out_p[d], out_v[d], out_a[d]);
+		}
+	} else {
+		for (int d = 0; d < k; ++d) { out_p[d] = O(L::OUT_P + d); out_v[d] = O(L::OUT_V + d); out_a[d] = O(L::OUT_A + d); }
+	}
+}
+
+// ---- the per-tick kernels ------------------------------------------------------------------------------------------
+// k_otg_advance: every robot.  Goal filter as a pure comparison (only when the host saw a goal write), then the state
+// advance along the stored trajectory: registers only, no local memory.  Robots that need anything else this tick (goal
+// change, pending recalculation, trajectory finishing, invalid goal) are appended to a compacted list.
+// k_otg_slow: grid-stride over that list with the general per-robot routine below (otg_general).
 // D = robot dof (joint task, k <= D task dofs) or 6 (cartesian).  GOFF_* = offsets of the goal rows in the G / P arenas.
 template <class T, int D, bool CART>
-__global__ void __launch_bounds__(128) k_otg_tick(const __grid_constant__ OtgJob job, int64_t B, int64_t stride) {
+__device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r) {
 	using L = OtgL<D>;
-	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (r >= B) return;
 	const Row<double> O{job.O, stride, r};
 	const Row<int32_t> OI{job.OI, stride, r};
 	const Row<T> G{(T*)job.G, stride, r}, P{(T*)job.P, stride, r};
@@ -465,8 +519,8 @@ __global__ void __launch_bounds__(128) k_otg_tick(const __grid_constant__ OtgJob
 	bool have_out = false, out_dirty = false;
 	auto load_out = [&]() {
 		if (have_out) return;
-		OSC_UNROLL for (int i = 0; i < D; ++i)
-			if (i < k) { out_p[i] = O(L::OUT_P + i); out_v[i] = O(L::OUT_V + i); out_a[i] = O(L::OUT_A + i); }
+		otg_current_output<D>(O, flags, k, out_p, out_v, out_a);
+		if (flags & OTG_OUT_LIVE) { flags &= ~OTG_OUT_LIVE; out_dirty = true; }
 		have_out = true;
 	};
 	double ref[9], gori[9], gang[3];
@@ -597,22 +651,14 @@ __global__ void __launch_bounds__(128) k_otg_tick(const __grid_constant__ OtgJob
 				const int o = L::TRAJ + 11 * d;
 				O(o) = p.brT; O(o + 1) = p.brA; O(o + 2) = p.pS; O(o + 3) = p.vS; O(o + 4) = p.t0; O(o + 5) = p.t1; O(o + 6) = p.t2;
 				O(o + 7) = p.t6; O(o + 8) = p.a0; O(o + 9) = p.a2; O(o + 10) = p.a6;
+				O(L::SEG + 2 * D + d) = -1.0;  // cached segment stale
 			}
 		O(L::DUR) = duration;
 		time = 0.0;
 		flags = (flags | OTG_INIT) & ~OTG_DIRTY;
 	} else {
-		OSC_UNROLL for (int d = 0; d < D; ++d)
-			if (d < k) {
-				OtgProf& p = prof[d];
-				const int o = L::TRAJ + 11 * d;
-				p.brT = O(o); p.brA = O(o + 1); p.pS = O(o + 2); p.vS = O(o + 3); p.t0 = O(o + 4); p.t1 = O(o + 5); p.t2 = O(o + 6);
-				p.t6 = O(o + 7); p.a0 = O(o + 8); p.a2 = O(o + 9); p.a6 = O(o + 10);
-				if (p.brT > 0.0) {
-					p.p0 = p.pS + p.brT * (p.vS + p.brT * (p.brA / 2 + p.brT * 0.0 / 6));
-					p.v0 = p.vS + p.brT * (p.brA + p.brT * 0.0 / 2);
-				} else { p.p0 = p.pS; p.v0 = p.vS; }
-			}
+		if (flags & OTG_IN_SYNCED) load_out();  // before the clock moves: a Finished tick needs the previous output as _input
+		for (int d = 0; d < k; ++d) otg_load_prof<D>(O, d, prof[d]);
 		duration = O(L::DUR);
 		time = O(L::TIME);
 	}
@@ -682,6 +728,140 @@ __global__ void __launch_bounds__(128) k_otg_tick(const __grid_constant__ OtgJob
 	store_desired();
 }
 
+// every OTG of the hierarchy in ONE launch: blockIdx.y selects the task
+struct OtgJobs {
+	OtgJob j[OSC_MAX_TASKS];
+	int cart[OSC_MAX_TASKS];
+};
+
+// N = robot dof.  Launched with programmatic stream serialisation behind k_otg_advance: its launch latency hides under the
+// advance kernel; the list is complete and visible once griddepcontrol.wait returns (a no-op under a plain launch).
+template <class T, int N>
+__global__ void __launch_bounds__(128) k_otg_slow(const __grid_constant__ OtgJobs js, int64_t stride) {
+	asm volatile("griddepcontrol.wait;" ::: "memory");
+	const OtgJob& job = js.j[blockIdx.y];
+	const int n = *job.slow_count;
+	if (blockIdx.x == 0 && threadIdx.x == 0) *job.slow_next = 0;  // re-arm the other counter (ping-pong, like k_tick_tail)
+	if (js.cart[blockIdx.y]) {
+		for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) otg_general<T, 6, true>(job, stride, job.slow_list[i]);
+	} else {
+		for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) otg_general<T, N, false>(job, stride, job.slow_list[i]);
+	}
+}
+
+template <class T, int D, bool CART>
+__device__ __forceinline__ void otg_advance_robot(const OtgJob& job, int64_t B, int64_t stride) {
+	using L = OtgL<D>;
+	const int64_t r0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const bool live = r0 < B && !(!CART && job.rank && job.rank[r0 < B ? r0 : 0] == 0);
+	const int64_t r = r0 < B ? r0 : B - 1;  // out-of-range lanes stay in the warp for the ballot below
+	const Row<double> O{job.O, stride, r};
+	const Row<int32_t> OI{job.OI, stride, r};
+	const Row<T> G{(T*)job.G, stride, r}, P{(T*)job.P, stride, r};
+	const int k = CART ? 6 : job.k;
+	const int flags = OI(L::FLAGS);
+	bool slow = false;
+	if (job.check_goals) {  // the comparisons of setGoal*And*Velocity without their side effects
+		if constexpr (!CART) {
+			double d2p = 0, g2p = 0, t2p = 0, d2v = 0, g2v = 0, t2v = 0;
+			OSC_UNROLL for (int i = 0; i < D; ++i)
+				if (i < k) {
+					const double gp = (double)G.ro(i), gv = (double)G.ro(D + i), tp = O(L::TGT_P + i), tv = O(L::TGT_V + i);
+					d2p += (gp - tp) * (gp - tp); g2p += gp * gp; t2p += tp * tp;
+					d2v += (gv - tv) * (gv - tv); g2v += gv * gv; t2v += tv * tv;
+				}
+			slow = !(d2p <= 1e-24 * fmin(g2p, t2p) && d2v <= 1e-24 * fmin(g2v, t2v));
+		} else {
+			using ML = MftL<7>;
+			double gp[3], gv[3], gw[3], gR[9], tp[3], tv[3], gori[9], gang[3];
+			OSC_UNROLL for (int i = 0; i < 3; ++i) {
+				gp[i] = (double)G.ro(ML::GOAL_POS + i); gv[i] = (double)G.ro(ML::GOAL_LINVEL + i); gw[i] = (double)G.ro(ML::GOAL_ANGVEL + i);
+				tp[i] = O(L::TGT_P + i); tv[i] = O(L::TGT_V + i); gang[i] = O(L::GANG + i);
+			}
+			OSC_UNROLL for (int i = 0; i < 9; ++i) { gR[i] = (double)G.ro(ML::GOAL_ORI + i); gori[i] = O(L::GORI + i); }
+			slow = !(otg_approx<3>(gp, tp, 3, 1e-3) && otg_approx<3>(gv, tv, 3, 1e-3)) || !otg_valid_rotation(gR) ||
+				   !(otg_approx<9>(gori, gR, 9, 1e-3) && otg_approx<3>(gang, gw, 3, 1e-3));
+		}
+	}
+	bool idle = false;
+	if (!slow) {
+		idle = (flags & OTG_REACHED) != 0;  // OTG_joints.cpp:116-118
+		slow = !idle && ((flags & OTG_DIRTY) || !(flags & OTG_INIT));
+	}
+	// one batch of independent loads (clock, duration, the cached segment of every DoF) BEFORE any store: a load per DoF
+	// iteration behind the previous iteration's possibly-aliasing store paid a DRAM round trip each (ncu r1p: 24 us -> see
+	// profiles/README.md)
+	double time = 0, duration = 0;
+	double s_off[D], s_ts[D], s_te[D], s_p[D], s_v[D], s_a[D];
+	double ref[CART ? 9 : 1];
+	if (!slow && !idle) {
+		time = O(L::TIME) + job.dt;  // ruckig.hpp:207
+		duration = O(L::DUR);
+		if constexpr (CART) {
+			OSC_UNROLL for (int i = 0; i < 9; ++i) ref[i] = O(L::REF + i);
+		}
+		OSC_UNROLL for (int d = 0; d < D; ++d)
+			if (d < k) {
+				s_off[d] = O(L::SEG + d); s_ts[d] = O(L::SEG + D + d); s_te[d] = O(L::SEG + 2 * D + d); s_p[d] = O(L::SEG + 3 * D + d);
+				s_v[d] = O(L::SEG + 4 * D + d); s_a[d] = O(L::SEG + 5 * D + d);
+			}
+		slow = time > duration;      // Result::Finished this tick: wrapper logic in the general routine
+	}
+	slow = slow && live;
+	{  // warp-aggregated append: one atomic per warp, consecutive robots stay consecutive in the list (coalesced general path)
+		const unsigned m = __ballot_sync(0xffffffffu, slow);
+		if (m) {
+			const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+			int base = 0;
+			if (lane == leader) base = atomicAdd(job.slow_count, __popc(m));
+			base = __shfl_sync(0xffffffffu, base, leader);
+			if (slow) job.slow_list[base + __popc(m & ((1u << lane) - 1u))] = (int)r;
+		}
+	}
+	if (slow || idle || !live) return;
+	double np[D], nv[D], na[D];
+	OSC_UNROLL for (int d = 0; d < D; ++d)
+		if (d < k) {
+			OtgSeg sg{s_off[d], s_ts[d], s_te[d], s_p[d], s_v[d], s_a[d]};
+			double td = sg.off > 0 ? time - sg.off : time;
+			if (!(td < sg.te) || td < sg.ts) {  // crossed into the next segment (or stale): rebuild from the stored profile
+				OtgProf p;
+				otg_load_prof<D>(O, d, p);
+				sg = otg_segment(p, time);
+				O(L::SEG + d) = sg.off; O(L::SEG + D + d) = sg.ts; O(L::SEG + 2 * D + d) = sg.te; O(L::SEG + 3 * D + d) = sg.p;
+				O(L::SEG + 4 * D + d) = sg.v; O(L::SEG + 5 * D + d) = sg.a;
+				td = sg.off > 0 ? time - sg.off : time;
+			}
+			const double t = td - sg.ts;
+			np[d] = sg.p + t * (sg.v + t * (sg.a / 2 + t * 0.0 / 6));  // utils.hpp:43-49
+			nv[d] = sg.v + t * (sg.a + t * 0.0 / 2);
+			na[d] = sg.a + t * 0.0;
+		}
+	O(L::TIME) = time;
+	if ((flags & (OTG_IN_SYNCED | OTG_OUT_LIVE)) != (OTG_IN_SYNCED | OTG_OUT_LIVE)) OI(L::FLAGS) = flags | OTG_IN_SYNCED | OTG_OUT_LIVE;
+	if constexpr (!CART) {
+		OSC_UNROLL for (int i = 0; i < D; ++i)
+			if (i < k) { P(i) = (T)np[i]; P(D + i) = (T)nv[i]; P(2 * D + i) = (T)na[i]; }
+	} else {
+		using ML = MftL<7>;
+		double Rn[9];
+		const double rv[3] = {np[3], np[4], np[5]};
+		otg_next_orientation(ref, rv, Rn);
+		OSC_UNROLL for (int i = 0; i < 3; ++i) {
+			P(ML::GOAL_POS + i) = (T)np[i]; P(ML::GOAL_LINVEL + i) = (T)nv[i]; P(ML::GOAL_LINACC + i) = (T)na[i];
+			P(ML::GOAL_ANGVEL + i) = (T)(ref[3 * i] * nv[3] + ref[3 * i + 1] * nv[4] + ref[3 * i + 2] * nv[5]);
+			P(ML::GOAL_ANGACC + i) = (T)(ref[3 * i] * na[3] + ref[3 * i + 1] * na[4] + ref[3 * i + 2] * na[5]);
+		}
+		OSC_UNROLL for (int i = 0; i < 9; ++i) P(ML::GOAL_ORI + i) = (T)Rn[i];
+	}
+}
+template <class T, int N>
+__global__ void __launch_bounds__(128, 4) k_otg_advance(const __grid_constant__ OtgJobs js, int64_t B, int64_t stride) {
+	asm volatile("griddepcontrol.launch_dependents;");  // lets the launch of k_otg_slow proceed under this kernel
+	if (js.cart[blockIdx.y]) otg_advance_robot<T, 6, true>(js.j[blockIdx.y], B, stride);
+	else otg_advance_robot<T, N, false>(js.j[blockIdx.y], B, stride);
+}
+
 // ---- cold path: reInitialize / enable / disable ---------------------------------------------------------------------
 // mode bit 1: reInitialize (all), 2: reInitializeLinear, 4: reInitializeAngular (OTG_6dof_cartesian.cpp:46-84, OTG_joints.cpp:28-41);
 // 64: the caller also reset the task's goals to the current state (reInitializeTask, parametrize*Spaces): mirror that in G;
@@ -724,11 +904,13 @@ __global__ void __launch_bounds__(128) k_otg_reinit(const __grid_constant__ OtgJ
 		for (int i = 0; i < k; ++i) { O(L::OUT_P + i) = p0[i]; O(L::OUT_V + i) = 0.0; O(L::OUT_A + i) = 0.0; }
 		if (mode & 64)
 			for (int i = 0; i < k; ++i) { G(i) = (T)p0[i]; G(D + i) = T(0); G(2 * D + i) = T(0); }
-		flags |= OTG_IN_SYNCED | OTG_DIRTY;
+		flags = (flags & ~OTG_OUT_LIVE) | OTG_IN_SYNCED | OTG_DIRTY;
 	} else {
 		using ML = MftL<7>;
 		double tp[6], tv[6], ref[9], gori[9], gang[3], out_p[6], out_v[6], out_a[6];
-		for (int i = 0; i < 6; ++i) { tp[i] = O(L::TGT_P + i); tv[i] = O(L::TGT_V + i); out_p[i] = O(L::OUT_P + i); out_v[i] = O(L::OUT_V + i); out_a[i] = O(L::OUT_A + i); }
+		for (int i = 0; i < 6; ++i) { tp[i] = O(L::TGT_P + i); tv[i] = O(L::TGT_V + i); }
+		otg_current_output<6>(O, flags, 6, out_p, out_v, out_a);
+		flags &= ~OTG_OUT_LIVE;
 		for (int i = 0; i < 9; ++i) { ref[i] = O(L::REF + i); gori[i] = O(L::GORI + i); }
 		for (int i = 0; i < 3; ++i) gang[i] = O(L::GANG + i);
 		double in_p[6], in_v[6], in_a[6];

@@ -42,11 +42,18 @@ int main(int argc, char** argv) {
 		// end-effector link = fixed link on the last body at (0, 0, 0.15) (panda_arm.urdf:179-183); control point (0, 0, 0.07)
 		const Link ee(n - 1, Affine3::Translation(0, 0, 0.15));
 		auto motion_force_task = std::make_shared<MotionForceTask>(robot, ee, Affine3::Translation(0, 0, 0.07), "cartesian_task");
-		motion_force_task->disableInternalOtg();
+		// mode 3 keeps the reference defaults (both internal OTGs on, MotionForceTask.h:67 / JointTask.h:38); the other modes run
+		// OTG-off like examples/04...cpp:115
+		if (!motion_force_task->getInternalOtgEnabled()) return 7;
+		if (mode != 3) motion_force_task->disableInternalOtg();
 		motion_force_task->setPosControlGains(120.0, 22.0);
 		motion_force_task->setOriControlGains(PIDGains(210.0, 29.0, 0.0));
 		auto joint_task = std::make_shared<JointTask>(robot, "joint_task");
 		joint_task->setGains(55.0, 15.0);
+		if (mode != 3) joint_task->disableInternalOtg();
+		bool unsupported = false;
+		try { joint_task->enableInternalOtgJerkLimited(1.0, 1.0, 1.0); } catch (const std::exception&) { unsupported = true; }
+		if (!unsupported) return 8;
 		std::vector<std::shared_ptr<TemplateTask>> task_list = {motion_force_task, joint_task};
 		auto robot_controller = std::make_unique<RobotController>(robot, task_list);
 		if (robot_controller->getTaskNames().size() != 2 || robot_controller->getJointTaskByName("joint_task") != joint_task) return 4;
@@ -63,7 +70,7 @@ int main(int argc, char** argv) {
 		joint_task->setGoalPosition(hostAOS(gq.data()));
 		std::vector<double> tau(B * n), x(B * 3);
 		for (int t = 0; t < ticks; ++t) {
-			if (mode == 1) {
+			if (mode == 1 || mode == 3) {
 				robot_controller->tick(Out(tau.data()));
 			} else if (mode == 0) {
 				robot->updateModel();

@@ -50,12 +50,12 @@ def test_facade_compiles_and_refuses_cpu(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
 def test_facade_matches_oracle(tmp_path, oracle_built, mode):
     orc = oracle_built
     exe = _build()
     chain = load_chain("panda")
-    B, ticks = 256, 3
+    B, ticks = 256, (3 if mode != 3 else 60)
     w = _inputs(tmp_path, chain, B, 40 + mode)
     r = subprocess.run([exe, str(tmp_path / "chain.bin"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), str(B), str(ticks), str(mode)],
                        capture_output=True, text=True)
@@ -74,6 +74,9 @@ def test_facade_matches_oracle(tmp_path, oracle_built, mode):
     for a in range(7):
         jp.kp[a], jp.kv[a] = 55.0, 15.0
     o.set_joint_task_params(t1, jp)
+    if mode == 3:  # the reference defaults: both internal OTGs on (MotionForceTask.h:67-72, JointTask.h:38-41)
+        o.enable_internal_otg(t0, [0.3, np.pi / 3], [2.0, 2 * np.pi])
+        o.enable_internal_otg(t1, np.pi / 3, 2 * np.pi)
     o.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); o.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
     o.set(abi.F_GOAL_LINEAR_VELOCITY, np.array([0.01, -0.02, 0.03]), t0); o.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
     for _ in range(ticks):
