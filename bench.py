@@ -30,6 +30,9 @@ ALG_BYTES_PER_TICK = 416.0
 # desired (p, v, a) written, plus the trajectory clock; the cartesian OTG also writes the 9 entries of the desired orientation
 # joints (n = 7): (4*7 + 1 + 3*7) * 8 = 400 B; cartesian: (4*6 + 1 + 24) * 8 = 392 B
 OTG_BYTES_PER_TICK = 792.0
+# rollout step, n = 7: FK 504 + CRBA 1,680 + recursive Newton-Euler ~ 150 n = 1,050
+# + Cholesky factor n^3/3 and two triangular solves 2 n^2 (FMA = 2) = 327 + integrator 4 n = 28
+ROLLOUT_FLOP_PER_STEP = 3589.0
 
 
 def load_chain(name="panda"):
@@ -335,6 +338,26 @@ def run_b200(args, rank, world, local_rank):
                    json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0),
                "robots_at_goal_after": float(reached), "limits": "reference defaults (MotionForceTask.h:68-71, JointTask.h:40-41)"}
         batch.disable_internal_otg(t0); batch.disable_internal_otg(t1)
+    # ---- device-side rollout: [tick ; forward dynamics + symplectic Euler] with q, dq never leaving the GPU
+    rollout = None
+    if not args.no_otg and fused:
+        snap = batch.snapshot()
+        batch.enable_gravity_compensation(True)
+        for _ in range(args.warmup):
+            batch.tick(True, fetch=False); batch.rollout_step(1e-3, 1, 0.0)
+        ts, ts_step = [], []
+        for _ in range(min(args.steps, 20)):
+            flush.zero_()
+            s, m, e = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            s.record(); batch.tick(True, fetch=False); m.record(); batch.rollout_step(1e-3, 1, 0.0); e.record(); torch.cuda.synchronize()
+            ts.append(s.elapsed_time(e)); ts_step.append(m.elapsed_time(e))
+        finite = bool(np.isfinite(np.asarray(batch.get(abi.F_Q))).all())
+        rollout = {"ms_per_tick_and_step": float(np.mean(ts)), "value": B / (float(np.mean(ts)) * 1e-3), "unit": "robot-(tick+sim step)s/s",
+                   "k_rollout_step_ms": float(np.mean(ts_step)), "sim_dt": 1e-3, "substeps": 1, "state_finite_after": finite,
+                   "alg_flop_per_robot_step": ROLLOUT_FLOP_PER_STEP,
+                   "note": "k_rollout_step = FK + CRBA + recursive Newton-Euler + Cholesky solve + integrator per robot; q, dq, tau stay in HBM"}
+        batch.enable_gravity_compensation(False)
+        batch.restore(snap)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -385,6 +408,9 @@ def run_b200(args, rank, world, local_rank):
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_hbm": roof_hbm}
     if otg:
         line["otg_on"] = otg
+    if rollout:
+        rollout["fp64_frac"] = ROLLOUT_FLOP_PER_STEP * B / (rollout["k_rollout_step_ms"] * 1e-3) / 1e12 / fp64_peak
+        line["rollout"] = rollout
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(chain)
     print(json.dumps(line))

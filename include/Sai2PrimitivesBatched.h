@@ -86,6 +86,10 @@ public:
 	// Sai2Model::updateModel / updateKinematics (examples/05-using_robot_controller/05-using_robot_controller.cpp:143-145)
 	void updateModel() { check(osc_update_model(_h)); }
 	void updateKinematics() { check(osc_update_kinematics(_h)); }
+	// the simulation side of examples/05...cpp:219-233 on the device (contact-free): sim->setJointTorques(tau); sim->integrate();
+	// robot->setQ(...); robot->setDq(...) with tau = the controller's last torques
+	void integrate(double dt, int substeps = 1, double joint_damping = 0.0) { check(osc_rollout_step(_h, dt, substeps, joint_damping)); }
+	void coriolisPlusGravity(const Out& o) { get(-1, OSC_F_NONLINEAR_EFFECTS, o); }  // of the state the last integrate() started from
 	void M(const Out& o) { get(-1, OSC_F_M, o); }
 	void MInv(const Out& o) { get(-1, OSC_F_MINV, o); }
 	void jointGravityVector(const Out& o) { get(-1, OSC_F_GRAVITY, o); }
@@ -475,6 +479,10 @@ public:
 	// robot->updateModel(); updateControllerTaskModels(); computeControlTorques() in one (fused) launch
 	void tick(const Out& tau) { check(osc_tick(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem)); }
 	void tick() { check(osc_tick(_robot->handle(), 1, nullptr, 0, 0)); }
+	// `ticks` control cycles with the device-side dynamics in between (MPC rollout): no host synchronisation inside
+	void rollout(int ticks, double sim_dt, int substeps = 1, double joint_damping = 0.0) {
+		check(osc_rollout(_robot->handle(), 1, ticks, sim_dt, substeps, joint_damping, nullptr, 0, 0));
+	}
 	void getControlTorques(const Out& tau) { _robot->get(-1, OSC_F_TAU, tau); }
 	void enableGravityCompensation(bool enable) { check(osc_enable_gravity_compensation(_robot->handle(), enable)); }  // RobotController.h:31-33
 	void reinitializeTasks() { check(osc_reinitialize_tasks(_robot->handle(), -1)); }

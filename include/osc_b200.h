@@ -163,6 +163,7 @@ enum {
 	OSC_F_N_TOTAL = 5,      /* n*n out     N_prec after the last task, RobotController.cpp:58 */
 	OSC_F_STATUS = 6,       /* 1 (int32) out */
 	OSC_F_GRAVITY = 7,      /* n   out     jointGravityVector() (valid when gravity compensation is on) */
+	OSC_F_NONLINEAR_EFFECTS = 8, /* n out  b(q,dq) + g(q) = Sai2Model::coriolisPlusGravity at the state osc_rollout_step started from */
 	/* any task */
 	OSC_F_TASK_TORQUES = 20,   /* n   out  this task's computeTorques result */
 	OSC_F_N_TASK = 21,         /* n*n out  getTaskNullspace() */
@@ -324,6 +325,18 @@ int64_t osc_launch_count(const osc_batch_t* batch);
 
 /* RobotController::reinitializeTasks / TemplateTask::reInitializeTask; task = -1 for all */
 int osc_reinitialize_tasks(osc_batch_t* batch, int task);
+
+/* ---- device-side rollout (the caller of the tick in MPC rollouts / parallel environments) ----
+ * Stands in for the simulation side of the reference's examples: sim->setJointTorques(tau); sim->integrate();
+ * robot->setQ(sim->getJointPositions()); robot->setDq(sim->getJointVelocities())
+ * (examples/05-using_robot_controller/05-using_robot_controller.cpp:219-233; Sai2Simulation is un-vendored).  Contact-free
+ * forward dynamics qdd = M^-1 (tau - b(q,dq) - g(q) - joint_damping * dq) with tau = the batch's OSC_F_TAU held for
+ * `substeps` symplectic-Euler steps of `dt` (dq += qdd dt; q += dq dt); q and dq are updated in place on the device.
+ * Gravity is the chain's gravity vector (zero it to simulate a gravity-compensated robot). */
+int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_damping);
+/* `ticks` x (osc_tick(stacked) ; osc_rollout_step(sim_dt, substeps, joint_damping)) queued without any host
+ * synchronisation; tau_out (may be NULL) receives the torques of the last tick. */
+int osc_rollout(osc_batch_t* batch, int stacked, int ticks, double sim_dt, int substeps, double joint_damping, void* tau_out, int layout, int mem);
 
 /* ---- measurement helper: sustained FP64 FMA throughput of `device` in TFLOP/s (DFMA microbenchmark, 2 flop per FMA),
  * the denominator of the FP64 roofline bench.py reports (MEASURED_PEAKS.json has no FP64 entry). ---- */

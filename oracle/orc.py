@@ -58,6 +58,10 @@ def lib():
         L.orc_tick.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.orc_reinitialize_tasks.argtypes = [C.c_void_p, C.c_int]
         L.orc_hardware_threads.restype = C.c_int
+        L.orc_rollout_step.restype = C.c_int
+        L.orc_rollout_step.argtypes = [C.c_void_p, C.c_double, C.c_int, C.c_double, C.c_int]
+        L.orc_nonlinear_effects.restype = C.c_int
+        L.orc_nonlinear_effects.argtypes = [C.c_void_p, C.c_void_p]
         # internal OTG (otg_oracle.hpp)
         L.orc_otg_use_reference.restype = C.c_int
         L.orc_otg_use_reference.argtypes = [C.c_char_p]
@@ -269,6 +273,15 @@ class OracleBatch:
 
     def reinitialize_tasks(self, task=-1):
         self.L.orc_reinitialize_tasks(self.h, task)
+
+    def rollout_step(self, dt, substeps=1, joint_damping=0.0):
+        self.L.orc_rollout_step(self.h, dt, substeps, joint_damping, self.nthreads)
+
+    def nonlinear_effects(self):
+        """b(q, dq) + g(q) at the current q, dq (call update_kinematics / update_model first)"""
+        out = np.empty((self.B, self.n), dtype=np.float64)
+        self.L.orc_nonlinear_effects(self.h, out.ctypes.data)
+        return out
 
     def enable_internal_otg(self, task, max_velocity, max_acceleration):
         """JointTask: scalars or length-k vectors.  MotionForceTask: (lin, ang) pairs."""

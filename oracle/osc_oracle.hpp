@@ -524,6 +524,68 @@ struct Model {
 		m.N = Mat::Identity(n) - m.Jbar * J;
 		return m;
 	}
+	// Sai2Model::coriolisPlusGravity: h = b(q, dq) + g(q) by the recursive Newton-Euler algorithm in LINK coordinates (the
+	// structure of RBDL's InverseDynamics with qdd = 0: velocities / accelerations base -> tip in each body's own frame,
+	// forces tip -> base).  Row f-2 of SURVEY.md 8(f); restatement only (sai2-model / RBDL are un-vendored).
+	void nonlinearEffects(double* h) const {
+		M3 E[8]; V3 r[8];
+		V3 w[8], wd[8], a[8], F[8], Nn[8];
+		const V3 gb = M3(ch.world_rot).T() * V3(ch.gravity);
+		V3 wp, wdp, ap = -1.0 * gb;  // base: at rest, accelerating against gravity
+		for (int i = 0; i < n; ++i) {
+			jointTransform(i, E[i], r[i]);
+			const V3 ax(ch.joint_axis[i]);
+			const M3 Et = E[i].T();
+			// acceleration of origin i as a point of the parent, in parent coordinates, then in frame i
+			V3 ao = ap + wdp.cross(r[i]) + wp.cross(wp.cross(r[i]));
+			const V3 wpi = Et * wp;
+			if (ch.joint_type[i] == OSC_JOINT_REVOLUTE) {
+				w[i] = wpi + dq[i] * ax;
+				wd[i] = Et * wdp + wpi.cross(dq[i] * ax);
+				a[i] = Et * ao;
+			} else {
+				w[i] = wpi;
+				wd[i] = Et * wdp;
+				a[i] = Et * ao + 2.0 * wpi.cross(dq[i] * ax);
+			}
+			const V3 c(ch.com[i]);
+			const M3 I(ch.inertia[i]);
+			const V3 ac = a[i] + wd[i].cross(c) + w[i].cross(w[i].cross(c));
+			F[i] = ch.mass[i] * ac;
+			Nn[i] = I * wd[i] + w[i].cross(I * w[i]) + c.cross(F[i]);  // moment about origin i
+			wp = w[i]; wdp = wd[i]; ap = a[i];
+		}
+		V3 f, nn;  // wrench of the subtree, frame i, about origin i
+		for (int i = n - 1; i >= 0; --i) {
+			if (i < n - 1) {
+				const V3 fc = E[i + 1] * f;
+				nn = E[i + 1] * nn + r[i + 1].cross(fc);
+				f = fc;
+			}
+			f = f + F[i];
+			nn = nn + Nn[i];
+			const V3 ax(ch.joint_axis[i]);
+			h[i] = (ch.joint_type[i] == OSC_JOINT_REVOLUTE) ? ax.dot(nn) : ax.dot(f);
+		}
+	}
+	// the simulation side of examples/05...cpp:219-233 without contact: qdd = M^-1 (tau - h - d dq), symplectic Euler
+	void rolloutStep(const double* tau, double dt, int substeps, double damping, double* h_out) {
+		for (int s = 0; s < substeps; ++s) {
+			updateModel();
+			double h[8];
+			nonlinearEffects(h);
+			if (s == 0 && h_out) for (int i = 0; i < n; ++i) h_out[i] = h[i];
+			double qdd[8];
+			for (int i = 0; i < n; ++i) {
+				qdd[i] = 0;
+				for (int j = 0; j < n; ++j) qdd[i] += Minv(i, j) * (tau[j] - h[j] - damping * dq[j]);
+			}
+			for (int i = 0; i < n; ++i) {
+				dq[i] += qdd[i] * dt;
+				q[i] += dq[i] * dt;
+			}
+		}
+	}
 	// Sai2Model::jointGravityVector (RobotController.cpp:71)
 	void jointGravityVector(double* g) const {
 		const V3 gw = M3(ch.world_rot).T() * V3(ch.gravity);
@@ -1242,6 +1304,7 @@ struct Robot {
 	bool gravity_comp = false;
 	Mat N_total, tau;
 	double gravity[8];
+	double nle[8] = {0};  // b + g of the last rollout step
 	explicit Robot(const osc_chain_desc& c) : model(c) {
 		tau = Mat::Zero(c.n, 1); N_total = Mat::Identity(c.n);
 		for (double& g : gravity) g = 0;

@@ -117,6 +117,7 @@ static int field_io(orc_batch* b, Robot& r, int task, int field, double* o, cons
 			case OSC_F_MINV: if (o) putMat(o, r.model.Minv, n, n); return n * n;
 			case OSC_F_N_TOTAL: if (o) putMat(o, r.N_total, n, n); return n * n;
 			case OSC_F_GRAVITY: if (o) for (int i = 0; i < n; ++i) o[i] = r.gravity[i]; return n;
+			case OSC_F_NONLINEAR_EFFECTS: if (o) for (int i = 0; i < n; ++i) o[i] = r.nle[i]; return n;
 			case OSC_F_STATUS: if (o) o[0] = 0; return 1;
 		}
 		return -1;
@@ -254,6 +255,14 @@ int orc_tick(orc_batch* b, int stacked, int nthreads) {
 		r.updateControllerTaskModels();
 		r.computeControlTorques(stacked != 0);
 	});
+	return 0;
+}
+int orc_rollout_step(orc_batch* b, double dt, int substeps, double damping, int nthreads) {
+	parallel_for(b, nthreads, [=](Robot& r) { r.model.rolloutStep(r.tau.a, dt, substeps, damping, r.nle); });
+	return 0;
+}
+int orc_nonlinear_effects(orc_batch* b, double* out) {
+	for (int64_t i = 0; i < b->B; ++i) b->robots[i]->model.nonlinearEffects(out + i * b->n);
 	return 0;
 }
 int orc_reinitialize_tasks(orc_batch* b, int task) {

@@ -92,6 +92,21 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	if (int rc = osc_update_task_models(batch)) return rc;
 	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
 }
+int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_damping) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (!(dt > 0) || substeps < 1 || substeps > 1000 || joint_damping < 0) return invalid("rollout step: dt > 0, 1 <= substeps <= 1000, damping >= 0");
+	if (int rc = use_device(*b)) return rc;
+	return b->ops->rollout_step(*b, dt, substeps, joint_damping);
+}
+int osc_rollout(osc_batch_t* batch, int stacked, int ticks, double sim_dt, int substeps, double joint_damping, void* tau_out, int layout, int mem) {
+	if (ticks < 1) return invalid("rollout: ticks >= 1");
+	for (int t = 0; t < ticks; ++t) {
+		if (int rc = osc_tick(batch, stacked, t == ticks - 1 ? tau_out : nullptr, layout, mem)) return rc;
+		if (int rc = osc_rollout_step(batch, sim_dt, substeps, joint_damping)) return rc;
+	}
+	return OSC_OK;
+}
 int osc_batch_set_tick_outputs(osc_batch_t* batch, int outputs) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");

@@ -67,6 +67,7 @@ struct Ops {
 	virtual bool fused_supported(Batch& b) = 0;
 	virtual int tick_fused(Batch& b, int stacked) = 0;
 	virtual int materialise(Batch& b) = 0;
+	virtual int rollout_step(Batch& b, double dt, int substeps, double damping) = 0;  // osc_rollout.cuh
 	virtual void otg_rows(Batch& b, int t, int64_t& o, int64_t& i, int64_t& g) = 0;
 	virtual int otg_reinit(Batch& b, int t, int mode) = 0;  // k_otg_reinit modes (osc_otg.cuh)
 	virtual int otg_tick(Batch& b, int t) = 0;              // goal filter + update() + desired rows of task t (all tasks: t < 0)  // after a fused tick: run the per-call model / task-model kernels (no state advance)

@@ -15,7 +15,7 @@ template <int N> struct RobotL {
 	static constexpr int Q = 0, DQ = N, P_SIZE = 2 * N;
 	// S
 	static constexpr int TAU = 0, KR = TAU + N, KO = KR + 9 * N, M = KO + 3 * N, MINV = M + N * N, NTOT = MINV + N * N,
-						 GRAV = NTOT + N * N, S_SIZE = GRAV + N;
+						 GRAV = NTOT + N * N, NLE = GRAV + N /* b(q,dq) + g(q), written by k_rollout_step */, S_SIZE = NLE + N;
 	// I
 	static constexpr int STATUS = 0, I_SIZE = 1;
 };

@@ -16,6 +16,7 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 			case OSC_F_M: return set(1, R::M, N * N, false);
 			case OSC_F_MINV: return set(1, R::MINV, N * N, false);
 			case OSC_F_GRAVITY: return set(1, R::GRAV, N, false);
+			case OSC_F_NONLINEAR_EFFECTS: return set(1, R::NLE, N, false);
 			case OSC_F_STATUS: return set(2, R::STATUS, 1, true, true);
 			case OSC_F_N_TOTAL: {
 				if (b.tasks.empty()) return false;

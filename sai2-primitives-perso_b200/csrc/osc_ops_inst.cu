@@ -7,6 +7,7 @@
 #include "osc_aux_kernels.cuh"
 #include "osc_fused2.cuh"
 #include "osc_otg.cuh"
+#include "osc_rollout.cuh"
 #include "osc_host.h"
 
 #ifndef OSC_T
@@ -175,6 +176,11 @@ template <class T, int N> struct OpsImpl : Ops {
 		TaskH& th = b.tasks[t];
 		k_mft_sensed<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride);
 		return done(b, "k_mft_sensed");
+	}
+
+	int rollout_step(Batch& b, double dt, int substeps, double damping) override {
+		k_rollout_step<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride, (T)dt, substeps, (T)damping, 1);
+		return done(b, "k_rollout_step");
 	}
 
 	// ---- internal OTG (osc_otg.cuh) ----

@@ -83,6 +83,8 @@ def lib():
         "osc_task_enable_internal_otg_jerk_limited": (i, [vp, i, vp, i]),
         "osc_task_disable_internal_otg": (i, [vp, i]),
         "osc_task_internal_otg_enabled": (i, [vp, i]),
+        "osc_rollout_step": (i, [vp, C.c_double, i, C.c_double]),
+        "osc_rollout": (i, [vp, i, i, C.c_double, i, C.c_double, vp, i, i]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -102,7 +104,8 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
             "osc_tick", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",
-            "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled"]
+            "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled",
+            "osc_rollout_step", "osc_rollout"]
 
 
 def measure_fp64_peak(device=0):
@@ -266,6 +269,15 @@ class Batch:
 
     def internal_otg_enabled(self, task):
         return bool(self.L.osc_task_internal_otg_enabled(self.h, task))
+
+    def rollout_step(self, dt, substeps=1, joint_damping=0.0):
+        """sim->integrate() stand-in: forward dynamics under the current OSC_F_TAU + symplectic Euler, on the device"""
+        self._chk(self.L.osc_rollout_step(self.h, dt, substeps, joint_damping))
+
+    def rollout(self, ticks, sim_dt, substeps=1, joint_damping=0.0, stacked=True):
+        tau = np.empty((self.B, self.n), dtype=self.dtype)
+        self._chk(self.L.osc_rollout(self.h, int(stacked), ticks, sim_dt, substeps, joint_damping, tau.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
+        return tau
 
     def synchronize(self):
         self._chk(self.L.osc_synchronize(self.h))
