@@ -258,6 +258,10 @@ int osc_task_enable_internal_otg_acceleration_limited(osc_batch_t* batch, int ta
 		if (int rc = alloc_rows(*b, (void**)&t.otgO, t.otg_o_rows, 8)) return rc;
 		if (int rc = alloc_rows(*b, (void**)&t.otgI, t.otg_i_rows, 4)) return rc;
 		if (int rc = alloc_rows(*b, &t.otgG, t.otg_g_rows, b->esz)) return rc;
+		// ping-pong counters + compacted list of the robots on the general path: allocated here so that no tick ever allocates
+		OSC_CUDA(cudaMalloc((void**)&t.otg_slow, (size_t)(b->stride + 2) * sizeof(int)));
+		OSC_CUDA(cudaMemsetAsync(t.otg_slow, 0, 2 * sizeof(int), b->stream));
+		t.otg_parity = 0;
 		fresh = true;
 	}
 	const bool limits_changed = memcmp(t.otg_max_v, mv, sizeof mv) != 0 || memcmp(t.otg_max_a, ma, sizeof ma) != 0;

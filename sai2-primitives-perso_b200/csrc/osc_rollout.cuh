@@ -97,14 +97,17 @@ __global__ void __launch_bounds__(OSC_THREADS) k_rollout_step(const __grid_const
 	for (int s = 0; s < substeps; ++s) {
 		Kin<T, N> kin;
 		forward_kinematics<T, N>(ch, q, kin);
-		T M[N][N], h[N];
+		T x[N];
+		{  // the Newton-Euler pass first: its per-body wrenches are dead before the mass matrix is born
+			T h[N];
+			nonlinear_effects<T, N>(ch, kin, dq, h);
+			if (export_h && s == 0) st_vec<T, N>(S, RobotL<N>::NLE, h);
+			OSC_UNROLL for (int i = 0; i < N; ++i) x[i] = tau[i] - h[i] - damping * dq[i];
+		}
+		T M[N][N];
 		mass_matrix<T, N>(ch, kin, M);
-		nonlinear_effects<T, N>(ch, kin, dq, h);
-		if (export_h && s == 0) st_vec<T, N>(S, RobotL<N>::NLE, h);
 		Chol<T, N> L;
 		if (!chol_factor<T, N>(M, L)) status |= 16;  // OSC_STATUS_NOT_POSITIVE_DEFINITE
-		T x[N];
-		OSC_UNROLL for (int i = 0; i < N; ++i) x[i] = tau[i] - h[i] - damping * dq[i];
 		chol_fwd<T, N>(L, x);
 		chol_bwd<T, N>(L, x);
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
