@@ -169,7 +169,8 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
-			const bool simple = fused2_simple(b) && !getenv("OSC_FUSED_NOSIMPLE");
+			static const bool nosimple = getenv("OSC_FUSED_NOSIMPLE") != nullptr, debug_occ = getenv("OSC_DEBUG_OCC") != nullptr;
+			const bool simple = fused2_simple(b) && !nosimple;
 			if (simple && N == 7) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
 			// block shape: 224 threads with phase barriers once the batch fills two such blocks per SM (r1l: 44.7 us against
 			// 45.7 us for 64-thread blocks at 65,536 robots), 64-thread blocks below that so that small batches still spread
@@ -178,9 +179,14 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			const int bt = bt_env ? bt_env : (b.B >= 224 * 148 ? 224 : 64);
 			auto go = [&](auto kern, int threads) -> int {
 				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(T);
-				cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-				if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused2)");
-				if (getenv("OSC_DEBUG_OCC")) {
+				static bool configured[64] = {};  // per kernel (one instantiation of this lambda each) and per device: set once, not per tick
+				const int dv = b.device >= 0 && b.device < 64 ? b.device : 0;
+				if (!configured[dv] || b.device >= 64) {
+					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused2)");
+					configured[dv] = true;
+				}
+				if (debug_occ) {
 					int nb = 0;
 					cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, threads, smem);
 					fprintf(stderr, "k_tick_fused2<%d>: %d threads/block, %d blocks/SM, %d stash slots\n", N, threads, nb, F2<N>::SLOTS);

@@ -90,8 +90,19 @@ __device__ inline bool otg_check(OtgProf& p, double aUp, double aDown, double vM
 	return fabs(p7 - p.pf) < 1e-8 && fabs(v7 - p.vf) < 1e-8 && v2 <= vUpp && v3 <= vUpp && v2 >= vLow && v3 >= vLow;
 }
 
+// what step 1 decides for a DoF: the boundary / brake part of a candidate is the caller's `base`, so a block keeps only this
+// (64 B instead of a 128 B profile: the blocks of all DoF live in local memory, which is what bounds k_otg_slow)
+struct OtgTimes {
+	double t0, t1, t2, t6, a0, a2, a6;
+	int up;
+	__device__ double tsum() const { return ((t0 + t1) + t2) + t6; }
+};
+__device__ inline OtgTimes otg_times(const OtgProf& p) { return OtgTimes{p.t0, p.t1, p.t2, p.t6, p.a0, p.a2, p.a6, p.up}; }
+__device__ inline void otg_apply(OtgProf& p, const OtgTimes& t) {
+	p.t0 = t.t0; p.t1 = t.t1; p.t2 = t.t2; p.t6 = t.t6; p.a0 = t.a0; p.a2 = t.a2; p.a6 = t.a6; p.up = t.up;
+}
 struct OtgBlock {  // ruckig/include/ruckig/block.hpp: fastest profile + at most one blocked interval in second order
-	OtgProf pmin, pa;
+	OtgTimes pmin, pa;
 	double tmin, aL, aR;
 	bool hasA;
 	__device__ bool blocked(double t) const { return (t < tmin) || (hasA && aL < t && t < aR); }
@@ -102,7 +113,7 @@ struct OtgBlock {  // ruckig/include/ruckig/block.hpp: fastest profile + at most
 static __device__ __noinline__ bool otg_step1(const OtgProf& base, double vMax_, double aMax_, OtgBlock& blk) {
 	const double vMin_ = -vMax_, aMin_ = -aMax_;
 	const double v0 = base.v0, vf = base.vf, pd = base.pf - base.p0;
-	OtgProf cand[4];
+	OtgTimes cand[4];
 	int n = 0;
 	auto try_none = [&](double vMax, double vMin, double aMax, double aMin, bool first_only) {  // :25-58
 		double h1 = (aMax * vf * vf - aMin * v0 * v0 - 2 * aMax * aMin * pd) / (aMax - aMin);
@@ -114,7 +125,7 @@ static __device__ __noinline__ bool otg_step1(const OtgProf& base, double vMax_,
 			c.t0 = s == 0 ? -(v0 + h1) / aMax : (-v0 + h1) / aMax;
 			c.t2 = s == 0 ? (vf + h1) / aMin : (vf - h1) / aMin;
 			if (otg_check(c, aMax, aMin, vMax, vMin)) {
-				cand[n++] = c;
+				cand[n++] = otg_times(c);
 				if (first_only) return;
 			}
 		}
@@ -126,7 +137,7 @@ static __device__ __noinline__ bool otg_step1(const OtgProf& base, double vMax_,
 		c.t1 = (aMin * v0 * v0 - aMax * vf * vf) / (2 * aMax * aMin * vMax) + vMax * (aMax - aMin) / (2 * aMax * aMin) + pd / vMax;
 		c.t2 = (vf - vMax) / aMin;
 		c.t6 = 0;
-		if (otg_check(c, aMax, aMin, vMax, vMin)) cand[n++] = c;
+		if (otg_check(c, aMax, aMin, vMax, vMin)) cand[n++] = otg_times(c);
 	};
 	if (fabs(vf) < 2.220446049250313e-16) {  // no blocked interval when vf == 0: first hit wins (:111-124)
 		const bool fw = pd >= 0;
@@ -144,9 +155,9 @@ static __device__ __noinline__ bool otg_step1(const OtgProf& base, double vMax_,
 	// block.hpp:58-131
 	const double eps = 2.220446049250313e-16;
 	blk.hasA = false;
-	auto set_min = [&](const OtgProf& p) { blk.pmin = p; blk.tmin = p.total(); };
-	auto set_a = [&](const OtgProf& l, const OtgProf& r) {  // Interval(profile_left, profile_right), :30-43
-		const double ld = l.total(), rd = r.total();
+	auto set_min = [&](const OtgTimes& p) { blk.pmin = p; blk.tmin = p.tsum() + base.brT; };  // Profile total = times + brake
+	auto set_a = [&](const OtgTimes& l, const OtgTimes& r) {  // Interval(profile_left, profile_right), :30-43
+		const double ld = l.tsum() + base.brT, rd = r.tsum() + base.brT;
 		blk.hasA = true;
 		if (ld < rd) { blk.aL = ld; blk.aR = rd; blk.pa = r; }
 		else { blk.aL = rd; blk.aR = ld; blk.pa = l; }
@@ -256,7 +267,7 @@ __device__ __noinline__ int otg_calculate(int n, const double* cp, const double*
 	}
 	if (n == 1) {  // :340-345
 		duration = blk[0].tmin;
-		prof[0] = blk[0].pmin;
+		otg_apply(prof[0], blk[0].pmin);
 		return OTG_WORKING;
 	}
 	// synchronize, :121-205: candidates t_min[d], a.right[d] in ascending order (ties by index), from the (n-1)-th on
@@ -285,14 +296,14 @@ __device__ __noinline__ int otg_calculate(int n, const double* cp, const double*
 			if (blocked || bv < 0.0 || isinf(bv)) continue;
 			duration = bv;
 			limiting = bi % n;
-			prof[limiting] = bi < n ? blk[limiting].pmin : blk[limiting].pa;
+			otg_apply(prof[limiting], bi < n ? blk[limiting].pmin : blk[limiting].pa);
 			found = true;
 		}
 		if (!found) return OTG_ERR_SYNC;
 	}
 	if (duration > 7.6e3) return OTG_ERR_DURATION;  // :388-392
 	if (duration == 0.0) {                          // :394-400
-		for (int d = 0; d < n; ++d) prof[d] = blk[d].pmin;
+		for (int d = 0; d < n; ++d) otg_apply(prof[d], blk[d].pmin);
 		return OTG_WORKING;
 	}
 	{  // phase synchronisation, :46-119 and :406-473
@@ -335,8 +346,8 @@ __device__ __noinline__ int otg_calculate(int n, const double* cp, const double*
 		if (d == limiting) continue;
 		OtgProf& p = prof[d];
 		const double tprof = duration - p.brT;
-		if (fabs(tprof - blk[d].tmin) < 2 * eps) { p = blk[d].pmin; continue; }
-		if (blk[d].hasA && fabs(tprof - blk[d].aR) < 2 * eps) { p = blk[d].pa; continue; }
+		if (fabs(tprof - blk[d].tmin) < 2 * eps) { otg_apply(p, blk[d].pmin); continue; }
+		if (blk[d].hasA && fabs(tprof - blk[d].aR) < 2 * eps) { otg_apply(p, blk[d].pa); continue; }
 		if (!otg_step2(p, tprof, mv[d], ma[d])) return OTG_ERR_SYNC;
 	}
 	return OTG_WORKING;
