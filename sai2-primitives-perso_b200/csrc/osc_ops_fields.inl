@@ -210,7 +210,10 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 #undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
-		{
+		// OSC_DIAG_NO_TAIL: diagnosis only (what the tail launch costs a tick whose fallback list is empty); fallback robots get
+		// no torques in such a run, so nothing measured with it is a result
+		static const bool no_tail = getenv("OSC_DIAG_NO_TAIL") != nullptr;
+		if (!no_tail) {
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(tail_blocks);
 			cfg.blockDim = dim3(OSC_THREADS);
