@@ -179,6 +179,25 @@ template <class T, int N> struct OpsImpl : Ops {
 	}
 
 	int rollout_step(Batch& b, double dt, int substeps, double damping) override {
+		bool revolute = true;
+		for (int i = 0; i < N; ++i) revolute = revolute && !ch.prismatic[i];
+		static const int ver = [] { const char* e = getenv("OSC_ROLLOUT_V"); return e ? atoi(e) : 2; }();
+		if (revolute && ver == 2) {  // body-frame kernel with a shared-memory stash (osc_rollout.cuh); block shape as the fused tick
+			auto go = [&](auto kern, int threads) -> int {
+				const size_t smem = (size_t)R2<N>::SLOTS * threads * sizeof(T);
+				static bool configured[64] = {};
+				const int dv = b.device >= 0 && b.device < 64 ? b.device : 0;
+				if (!configured[dv] || b.device >= 64) {
+					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_rollout_step2)");
+					configured[dv] = true;
+				}
+				kern<<<dim3((unsigned)((b.B + threads - 1) / threads)), threads, smem, b.stream>>>(ch, rob(b), b.B, b.stride, (T)dt, substeps, (T)damping, 1);
+				return OSC_OK;
+			};
+			if (int rc = b.B >= 224 * 148 ? go(k_rollout_step2<T, N, 224>, 224) : go(k_rollout_step2<T, N, 64>, 64)) return rc;
+			return done(b, "k_rollout_step2");
+		}
 		k_rollout_step<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride, (T)dt, substeps, (T)damping, 1);
 		return done(b, "k_rollout_step");
 	}

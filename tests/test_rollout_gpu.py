@@ -63,3 +63,19 @@ def test_closed_loop_rollout(oracle_built):
     p.gpu.set(abi.F_Q, w["q"]); p.gpu.set(abi.F_DQ, np.zeros_like(w["dq"]))
     p.gpu.rollout(ticks, 1e-3, 1, 0.0, True)
     assert np.array_equal(p.gpu.get(abi.F_Q), q_loop)
+
+
+def test_step_large_batch_block_shape(oracle_built):
+    """batches of 224 * 148 robots and more run k_rollout_step2 with 224-thread blocks (two per SM): same parity bar"""
+    chain = load_chain("panda")
+    n, B = chain["n"], 224 * 148 + 37
+    rng = np.random.default_rng(21)
+    p = Pair(chain, B)
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-1, 1, (B, n))
+    tau = rng.uniform(-5, 5, (B, n))
+    p.set(abi.F_Q, q); p.set(abi.F_DQ, dq); p.set(abi.F_TAU, tau)
+    p.both("rollout_step", 1e-3, 3, 0.1)
+    assert rel_err(p.gpu.get(abi.F_NONLINEAR_EFFECTS), p.ref.get(abi.F_NONLINEAR_EFFECTS))[0] <= FP64_TOL
+    assert rel_err(p.gpu.get(abi.F_DQ), p.ref.get(abi.F_DQ))[0] <= FP64_TOL
+    assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP64_TOL
