@@ -2,6 +2,8 @@
 // The C ABI (osc_capi.cu) is precision/dof agnostic; everything that launches a templated kernel goes through Ops,
 // implemented once per (T, N) in osc_ops_inst.cu (compiled once per instantiation so the builds run in parallel).
 #pragma once
+#include <mutex>
+#include <unordered_map>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -108,6 +110,21 @@ struct Batch {
 
 void set_error(const std::string& msg);
 int cuda_fail(cudaError_t e, const char* what);
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is needed once per (kernel, device), not per launch.  Keyed by the kernel's
+// address: kernels that differ only in a template argument have the same function type, so a static flag inside a generic
+// lambda would be shared between them.
+inline bool first_launch_on_device(const void* kernel, int device) {
+	static std::mutex mu;
+	static std::unordered_map<const void*, uint64_t> seen;
+	std::lock_guard<std::mutex> lock(mu);
+	uint64_t& mask = seen[kernel];
+	if (device < 0 || device >= 64) return true;
+	const uint64_t bit = 1ull << device;
+	if (mask & bit) return false;
+	mask |= bit;
+	return true;
+}
+
 #define OSC_CUDA(x)                                      \
 	do {                                                 \
 		cudaError_t e_ = (x);                            \

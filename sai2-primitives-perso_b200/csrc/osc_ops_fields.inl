@@ -179,12 +179,9 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			const int bt = bt_env ? bt_env : (b.B >= 224 * 148 ? 224 : 64);
 			auto go = [&](auto kern, int threads) -> int {
 				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(T);
-				static bool configured[64] = {};  // per kernel (one instantiation of this lambda each) and per device: set once, not per tick
-				const int dv = b.device >= 0 && b.device < 64 ? b.device : 0;
-				if (!configured[dv] || b.device >= 64) {
+				if (first_launch_on_device((const void*)kern, b.device)) {  // once per kernel and device, not per tick
 					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused2)");
-					configured[dv] = true;
 				}
 				if (debug_occ) {
 					int nb = 0;

@@ -185,12 +185,9 @@ template <class T, int N> struct OpsImpl : Ops {
 		if (revolute && ver == 2) {  // body-frame kernel with a shared-memory stash (osc_rollout.cuh); block shape as the fused tick
 			auto go = [&](auto kern, int threads) -> int {
 				const size_t smem = (size_t)R2<N>::SLOTS * threads * sizeof(T);
-				static bool configured[64] = {};
-				const int dv = b.device >= 0 && b.device < 64 ? b.device : 0;
-				if (!configured[dv] || b.device >= 64) {
+				if (first_launch_on_device((const void*)kern, b.device)) {
 					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_rollout_step2)");
-					configured[dv] = true;
 				}
 				kern<<<dim3((unsigned)((b.B + threads - 1) / threads)), threads, smem, b.stream>>>(ch, rob(b), b.B, b.stride, (T)dt, substeps, (T)damping, 1);
 				return OSC_OK;

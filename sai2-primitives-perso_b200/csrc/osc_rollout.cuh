@@ -142,6 +142,11 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 	extern __shared__ __align__(16) unsigned char osc_stash_raw[];
 	T* const sm = reinterpret_cast<T*>(osc_stash_raw);
 #define ST(slot) sm[(slot) * BT + threadIdx.x]
+// phase boundary: the compiler fence keeps nvcc, the block barrier keeps ptxas from interleaving the phases (register pressure);
+// the barrier also keeps the warps of a block in the same stretch of code (instruction cache), as in k_tick_fused2
+#define OSC_R2_PHASE() \
+	OSC_FENCE();       \
+	__syncthreads()
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	const Row<T> P{rob.P, stride, r}, S{rob.S, stride, r};
@@ -160,13 +165,13 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 			ST(F::SC + 2 * i) = s;
 			ST(F::SC + 2 * i + 1) = c;
 		}
-		OSC_FENCE();
+		OSC_R2_PHASE();
 		T h[N];
 		{  // Newton-Euler, outward: body i in its own frame; x_parent = xyz_i + E_i x_i with E_i = rot_i Rz(q_i)
 			T w[3] = {T(0), T(0), T(0)}, al[3] = {T(0), T(0), T(0)}, ac[3] = {ab[0], ab[1], ab[2]};
 			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				const T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
-				T E[3][3];
+				T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
+								T E[3][3];
 				OSC_UNROLL for (int a = 0; a < 3; ++a) {
 					E[a][0] = ch.rot[i][a][0] * c + ch.rot[i][a][1] * s;
 					E[a][1] = ch.rot[i][a][1] * c - ch.rot[i][a][0] * s;
@@ -200,16 +205,17 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 					ST(F::FN + 6 * i + a) = ch.mass[i] * ac[a] + ah[a] + wwh[a];
 					ST(F::FN + 6 * i + 3 + a) = Ia[a] + wIw[a] + ha[a];
 				}
+				OSC_FENCE();  // one body at a time: left alone, ptxas builds every E_i up front and spills
 			}
-			OSC_FENCE();
+			OSC_R2_PHASE();
 			// inward: wrench of bodies >= i about origin i; the joint torque is its moment about z_i
 			T Fc[3] = {T(0), T(0), T(0)}, Nc[3] = {T(0), T(0), T(0)};
 			OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
 				OSC_UNROLL for (int a = 0; a < 3; ++a) { Fc[a] += ST(F::FN + 6 * i + a); Nc[a] += ST(F::FN + 6 * i + 3 + a); }
 				h[i] = Nc[2];
 				if (i > 0) {
-					const T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
-					T E[3][3];
+					T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
+										T E[3][3];
 					OSC_UNROLL for (int a = 0; a < 3; ++a) {
 						E[a][0] = ch.rot[i][a][0] * c + ch.rot[i][a][1] * s;
 						E[a][1] = ch.rot[i][a][1] * c - ch.rot[i][a][0] * s;
@@ -221,6 +227,7 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 					cross3(ch.xyz[i], Fp, rF);
 					OSC_UNROLL for (int a = 0; a < 3; ++a) { Fc[a] = Fp[a]; Nc[a] = Np[a] + rF[a]; }
 				}
+				OSC_FENCE();
 			}
 		}
 		if (export_h && step == 0) st_vec<T, N>(S, RobotL<N>::NLE, h);
@@ -232,7 +239,7 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 		}
 		// q, dq wait in the 14 slots the lower triangle of M leaves free while the factorisation needs the registers
 		OSC_UNROLL for (int i = 0; i < N; ++i) { ST(F::QP + i) = q[i]; ST(F::QP + N + i) = dq[i]; }
-		OSC_FENCE();
+		OSC_R2_PHASE();
 		{  // mass matrix: the composite-rigid-body recursion in body frames of k_tick_fused2 (P2), lower triangle into the FN slots
 			T cm = T(0), h0 = T(0), h1 = T(0), h2 = T(0), Ixx = T(0), Ixy = T(0), Ixz = T(0), Iyy = T(0), Iyz = T(0), Izz = T(0);
 			OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
@@ -243,8 +250,8 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 				const int row = F::FN + i * (i + 1) / 2;
 				ST(row + i) = l2;
 				OSC_UNROLL for (int j = i; j >= 1; --j) {  // carried down the chain: M[i][j-1] = z . l in frame j-1
-					const T s = ST(F::SC + 2 * j), c = ST(F::SC + 2 * j + 1);
-					const T a0 = c * p0 - s * p1, a1 = s * p0 + c * p1, b0 = c * l0 - s * l1, b1 = s * l0 + c * l1;
+					T s = ST(F::SC + 2 * j), c = ST(F::SC + 2 * j + 1);
+										const T a0 = c * p0 - s * p1, a1 = s * p0 + c * p1, b0 = c * l0 - s * l1, b1 = s * l0 + c * l1;
 					p0 = ch.rot[j][0][0] * a0 + ch.rot[j][0][1] * a1 + ch.rot[j][0][2] * p2;
 					p1 = ch.rot[j][1][0] * a0 + ch.rot[j][1][1] * a1 + ch.rot[j][1][2] * p2;
 					p2 = ch.rot[j][2][0] * a0 + ch.rot[j][2][1] * a1 + ch.rot[j][2][2] * p2;
@@ -257,8 +264,8 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 					ST(row + j - 1) = l2;
 				}
 				if (i > 0) {  // the composite in the parent frame
-					const T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
-					T E[3][3];
+					T s = ST(F::SC + 2 * i), c = ST(F::SC + 2 * i + 1);
+										T E[3][3];
 					OSC_UNROLL for (int a = 0; a < 3; ++a) {
 						E[a][0] = ch.rot[i][a][0] * c + ch.rot[i][a][1] * s;
 						E[a][1] = ch.rot[i][a][1] * c - ch.rot[i][a][0] * s;
@@ -279,9 +286,10 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 					Iyz = EI[1][0] * E[2][0] + EI[1][1] * E[2][1] + EI[1][2] * E[2][2] - cm * r1 * r2 - r1 * g2 - g1 * r2;
 					h0 = g0 + cm * r0; h1 = g1 + cm * r1; h2 = g2 + cm * r2;
 				}
+				OSC_FENCE();
 			}
 		}
-		OSC_FENCE();
+		OSC_R2_PHASE();
 		{  // M = L L^T in registers; x <- M^-1 x
 			T Mx[N][N], li[N];
 			OSC_UNROLL for (int i = 0; i < N; ++i)
@@ -308,6 +316,7 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 	st_vec<T, N>(P, RobotL<N>::DQ, dq);
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 #undef ST
+#undef OSC_R2_PHASE
 }
 
 }  // namespace osc

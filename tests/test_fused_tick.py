@@ -177,3 +177,17 @@ def test_fused_fp32(oracle_built):
     err = np.abs(tg - tr).max(axis=1) / np.maximum(np.abs(tr).max(axis=1), 1e-2)
     assert np.median(err[well]) < FP32_TOL, np.median(err[well])
     assert err[well].max() < 50 * FP32_TOL, err[well].max()
+
+
+def test_small_then_large_batch_in_one_process(oracle_built):
+    """The fused tick switches to 224-thread blocks (100 KB of stash per block) once a batch fills the GPU; that kernel needs
+    its own shared-memory attribute even when the 64-thread one already ran in this process (regression: the per-kernel flag
+    was once shared between the two block shapes, and the large launch failed with "invalid argument")."""
+    chain = load_chain("panda")
+    for B, seed in ((512, 5), (224 * 148 + 11, 6), (512, 7)):
+        p, q, dq, rng = _two_task(chain, B, seed)
+        assert p.gpu.tick_is_fused()
+        tg, tr = p.both("tick", True)
+        assert _tau_err(tg, tr) <= FP64_TOL, B
+        p.both("rollout_step", 1e-3, 1, 0.0)
+        assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP64_TOL, B
