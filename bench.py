@@ -423,7 +423,7 @@ def run_b200(args, rank, world, local_rank):
         rollout = {"ms_per_tick_and_step": float(np.mean(ts)), "value": B / (float(np.mean(ts)) * 1e-3), "unit": "robot-(tick+sim step)s/s",
                    "k_rollout_step_ms": float(np.mean(ts_step)), "sim_dt": 1e-3, "substeps": 1, "state_finite_after": finite,
                    "alg_flop_per_robot_step": ROLLOUT_FLOP_PER_STEP,
-                   "note": "k_rollout_step = FK + CRBA + recursive Newton-Euler + Cholesky solve + integrator per robot; q, dq, tau stay in HBM"}
+                   "note": "k_rollout_step2 = sin/cos + link-frame recursive Newton-Euler + body-frame CRBA + Cholesky solve + integrator per robot; q, dq, tau stay in HBM"}
         batch.enable_gravity_compensation(False)
         batch.restore(snap)
     if rank != 0:
