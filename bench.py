@@ -66,13 +66,19 @@ class NearGpu:
 
     def __enter__(self):
         if self.cpus:
-            self.saved = os.sched_getaffinity(0)
-            os.sched_setaffinity(0, self.cpus)
+            try:
+                self.saved = os.sched_getaffinity(0)
+                os.sched_setaffinity(0, self.cpus)
+            except OSError:  # not permitted in this container: carry on unbound
+                self.saved, self.cpus = None, None
         return self
 
     def __exit__(self, *a):
         if self.saved:
-            os.sched_setaffinity(0, self.saved)
+            try:
+                os.sched_setaffinity(0, self.saved)
+            except OSError:
+                pass
         return False
 
 
