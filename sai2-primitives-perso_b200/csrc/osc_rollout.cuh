@@ -127,12 +127,13 @@ __global__ void __launch_bounds__(OSC_THREADS) k_rollout_step(const __grid_const
 //     then tip to base; the per-body force / moment about the body origin wait in a per-thread SHARED-memory stash;
 //   * the mass matrix from the body-frame composite-rigid-body recursion of k_tick_fused2 (phase P2 there), into the same slots;
 //   * Cholesky in registers, two triangular solves, symplectic Euler.
-// 128 registers, no local memory, 224-thread blocks x 2 per SM (56 stash slots per thread).
+// 128 registers, 224-thread blocks x 2 per SM (63 stash slots per thread).
 template <int N> struct R2 {
 	static constexpr int SC = 0;            // sin/cos (2N)
 	static constexpr int FN = 2 * N;        // per body f (3), n (3) in its own frame; later the lower triangle of M
-	static constexpr int QP = FN + N * (N + 1) / 2;  // q, dq parked behind M
-	static constexpr int SLOTS = QP + 2 * N > 8 * N ? QP + 2 * N : 8 * N;
+	static constexpr int DQP = FN + N * (N + 1) / 2;  // dq parked behind M while the factorisation needs the registers
+	static constexpr int QQ = 8 * N;                   // q, from the top of a substep to its integration (N slots of its own)
+	static constexpr int SLOTS = DQP + N > 9 * N ? DQP + N : 9 * N;  // n = 7: 63 slots, 2 x (224 x 63 x 8 B + 1 KB) = 223 KB of the SM's 228 KB
 };
 
 template <class T, int N, int BT>
@@ -158,7 +159,7 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 		ab[a] = -(ch.world_rot[0][a] * ch.gravity[0] + ch.world_rot[1][a] * ch.gravity[1] + ch.world_rot[2][a] * ch.gravity[2]);
 	int status = 0;
 	for (int step = 0; step < substeps; ++step) {
-		OSC_UNROLL for (int i = 0; i < N; ++i) ST(F::SC + 2 * i) = q[i];
+		OSC_UNROLL for (int i = 0; i < N; ++i) { ST(F::SC + 2 * i) = q[i]; ST(F::QQ + i) = q[i]; }
 		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
 			T s, c;
 			Num<T>::sincos_(ST(F::SC + 2 * i), &s, &c);
@@ -237,8 +238,8 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 			ld_vec<T, N>(S, RobotL<N>::TAU, tau);
 			OSC_UNROLL for (int i = 0; i < N; ++i) x[i] = tau[i] - h[i] - damping * dq[i];
 		}
-		// q, dq wait in the 14 slots the lower triangle of M leaves free while the factorisation needs the registers
-		OSC_UNROLL for (int i = 0; i < N; ++i) { ST(F::QP + i) = q[i]; ST(F::QP + N + i) = dq[i]; }
+		// dq waits in slots the lower triangle of M leaves free while the factorisation needs the registers
+		OSC_UNROLL for (int i = 0; i < N; ++i) ST(F::DQP + i) = dq[i];
 		OSC_R2_PHASE();
 		{  // mass matrix: the composite-rigid-body recursion in body frames of k_tick_fused2 (P2), lower triangle into the FN slots
 			T cm = T(0), h0 = T(0), h1 = T(0), h2 = T(0), Ixx = T(0), Ixy = T(0), Ixz = T(0), Iyy = T(0), Iyz = T(0), Izz = T(0);
@@ -308,8 +309,8 @@ __global__ void __launch_bounds__(BT, 512 / BT) k_rollout_step2(const __grid_con
 		}
 		OSC_FENCE();
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			dq[i] = Num<T>::fma_(x[i], dt, ST(F::QP + N + i));
-			q[i] = Num<T>::fma_(dq[i], dt, ST(F::QP + i));
+			dq[i] = Num<T>::fma_(x[i], dt, ST(F::DQP + i));
+			q[i] = Num<T>::fma_(dq[i], dt, ST(F::QQ + i));
 		}
 	}
 	st_vec<T, N>(P, RobotL<N>::Q, q);
