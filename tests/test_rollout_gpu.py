@@ -5,7 +5,7 @@ import pytest
 
 import osc_abi as abi
 import workloads
-from common import FP64_TOL, Pair, load_chain, random_q, rel_err
+from common import FP32_TOL, FP64_TOL, Pair, load_chain, random_q, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -79,3 +79,20 @@ def test_step_large_batch_block_shape(oracle_built):
     assert rel_err(p.gpu.get(abi.F_NONLINEAR_EFFECTS), p.ref.get(abi.F_NONLINEAR_EFFECTS))[0] <= FP64_TOL
     assert rel_err(p.gpu.get(abi.F_DQ), p.ref.get(abi.F_DQ))[0] <= FP64_TOL
     assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP64_TOL
+
+
+@pytest.mark.parametrize("name", ["panda", "panda_sliding_base"])
+def test_step_fp32(oracle_built, name):
+    """FP32 batch (both kernels: body-frame for the Panda, general for the sliding base) against the FP64 oracle, 1e-4"""
+    chain = load_chain(name)
+    n, B = chain["n"], 512
+    rng = np.random.default_rng(33)
+    p = Pair(chain, B, abi.PRECISION_F32)
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-1, 1, (B, n))
+    tau = rng.uniform(-5, 5, (B, n))
+    p.set(abi.F_Q, q); p.set(abi.F_DQ, dq); p.set(abi.F_TAU, tau)
+    p.both("rollout_step", 1e-3, 1, 0.2)
+    assert rel_err(p.gpu.get(abi.F_NONLINEAR_EFFECTS), p.ref.get(abi.F_NONLINEAR_EFFECTS))[0] <= FP32_TOL
+    assert rel_err(p.gpu.get(abi.F_DQ), p.ref.get(abi.F_DQ))[0] <= FP32_TOL
+    assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP32_TOL
