@@ -1,5 +1,7 @@
 """GPU parity of the device-side rollout step against the C++ oracle: b(q,dq) + g(q), one and many
 symplectic-Euler steps, and the closed loop controller + dynamics that an MPC rollout runs without leaving the device."""
+import copy
+
 import numpy as np
 import pytest
 
@@ -96,3 +98,35 @@ def test_step_fp32(oracle_built, name):
     assert rel_err(p.gpu.get(abi.F_NONLINEAR_EFFECTS), p.ref.get(abi.F_NONLINEAR_EFFECTS))[0] <= FP32_TOL
     assert rel_err(p.gpu.get(abi.F_DQ), p.ref.get(abi.F_DQ))[0] <= FP32_TOL
     assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP32_TOL
+
+
+@pytest.mark.parametrize("name", ["panda", "panda_sliding_base"])
+def test_step_tilted_base_and_full_inertias(oracle_built, name):
+    """a base that is rotated and offset in the world, gravity off the world axes and inertia tensors with products of inertia:
+    nothing the fixtures exercise, all of it enters b + g (the base acceleration that stands for gravity is expressed in base
+    coordinates; the body-frame inertias about the joint origins pick up the off-diagonal terms)"""
+    chain = copy.deepcopy(load_chain(name))
+    cz, sz, cy, sy, cx, sx = np.cos(0.4), np.sin(0.4), np.cos(0.7), np.sin(0.7), np.cos(-0.3), np.sin(-0.3)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]); Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    chain["world_rot"] = (Rz @ Ry @ Rx).tolist()
+    chain["world_xyz"] = [0.1, -0.2, 0.3]
+    chain["gravity"] = [1.0, -2.0, -9.0]
+    rng = np.random.default_rng(77)
+    for b in chain["bodies"]:
+        I = np.array(b["inertia"], float)
+        A = rng.uniform(-0.3, 0.3, (3, 3))
+        Q = np.linalg.qr(np.eye(3) + A)[0]
+        b["inertia"] = (Q @ I @ Q.T).tolist()  # same principal moments, rotated axes: symmetric positive definite, full
+    n, B = chain["n"], 256
+    p = Pair(chain, B)
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-1, 1, (B, n))
+    tau = rng.uniform(-5, 5, (B, n))
+    p.set(abi.F_Q, q); p.set(abi.F_DQ, dq); p.set(abi.F_TAU, tau)
+    p.both("rollout_step", 1e-3, 2, 0.1)
+    h_ref = p.ref.get(abi.F_NONLINEAR_EFFECTS)
+    assert np.abs(h_ref).max() > 1.0
+    assert rel_err(p.gpu.get(abi.F_NONLINEAR_EFFECTS), h_ref)[0] <= FP64_TOL
+    assert rel_err(p.gpu.get(abi.F_DQ), p.ref.get(abi.F_DQ))[0] <= FP64_TOL
+    assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP64_TOL
