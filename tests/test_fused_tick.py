@@ -1,6 +1,8 @@
 """GPU parity of the single-launch tick (csrc/osc_fused.cuh): k_tick_fused for the robots it can certify non-singular,
 k_tick_tail (API-faithful route) for the rest, against the C++ oracle, which follows the reference's route (two Jacobi
 SVDs per tick) line by line.  Tolerance: 1e-9 relative in FP64 (BASELINE north_star)."""
+import copy
+
 import numpy as np
 import pytest
 
@@ -191,3 +193,25 @@ def test_small_then_large_batch_in_one_process(oracle_built):
         assert _tau_err(tg, tr) <= FP64_TOL, B
         p.both("rollout_step", 1e-3, 1, 0.0)
         assert rel_err(p.gpu.get(abi.F_Q), p.ref.get(abi.F_Q))[0] <= FP64_TOL, B
+
+
+def test_tilted_base_full_inertias_gravity_compensation(oracle_built):
+    """Nothing in the fixtures rotates the base, tilts gravity or has products of inertia; the body-frame mass matrix of the fused
+    tick, the world-frame one of the per-call route and the gravity vector must all agree with the oracle when they do."""
+    chain = copy.deepcopy(load_chain("panda"))
+    cz, sz, cy, sy = np.cos(0.4), np.sin(0.4), np.cos(0.7), np.sin(0.7)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]); Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    chain["world_rot"] = (Rz @ Ry).tolist()
+    chain["world_xyz"] = [0.1, -0.2, 0.3]
+    chain["gravity"] = [1.0, -2.0, -9.0]
+    rng = np.random.default_rng(78)
+    for b in chain["bodies"]:
+        Q = np.linalg.qr(np.eye(3) + rng.uniform(-0.3, 0.3, (3, 3)))[0]
+        b["inertia"] = (Q @ np.array(b["inertia"], float) @ Q.T).tolist()
+    p, q, dq, rng = _two_task(chain, 1024, 79)
+    p.both("enable_gravity_compensation", True)
+    assert p.gpu.tick_is_fused()
+    tg, tr = p.both("tick", True)
+    assert _tau_err(tg, tr) <= FP64_TOL
+    assert np.abs(p.ref.get(abi.F_GRAVITY)).max() > 1.0
+    p.compare(FP64_TOL)  # every getter, through the per-call kernels (lazy materialisation)
