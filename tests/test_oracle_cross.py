@@ -5,6 +5,8 @@ PARITY UNPINNED: the reference has no tests / golden vectors for 
 (Eigen3 + sai2-model absent), so the two restatements -- written on different numerical routes (world-frame composite
 rigid body + Cholesky + one-sided Jacobi   vs   per-body kinetic-energy Hessians + LAPACK inv/svd) -- pin each other.
 """
+import copy
+
 import numpy as np
 import pytest
 
@@ -239,3 +241,48 @@ def test_controller_rules():
         npo.RobotController(m, [npo.JointTask(m, np.eye(7)[:1], name="a"), npo.JointTask(m, name="a")])
     with pytest.raises(ValueError):
         npo.RobotController(m, [])
+
+
+def test_tilted_base_full_inertias_gravity(oracle_built):
+    """the two restatements on a chain the fixtures do not offer: base rotated and offset in the world, gravity off the world
+    axes, inertia tensors with products of inertia, gravity compensation on (the GPU tests use the same chain:
+    tests/test_fused_tick.py::test_tilted_base_full_inertias_gravity_compensation, tests/test_rollout_gpu.py)"""
+    orc = oracle_built
+    chain = copy.deepcopy(load_chain("panda"))
+    cz, sz, cy, sy = np.cos(0.4), np.sin(0.4), np.cos(0.7), np.sin(0.7)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]); Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    chain["world_rot"] = (Rz @ Ry).tolist()
+    chain["world_xyz"] = [0.1, -0.2, 0.3]
+    chain["gravity"] = [1.0, -2.0, -9.0]
+    rng = np.random.default_rng(78)
+    for b in chain["bodies"]:
+        Q = np.linalg.qr(np.eye(3) + rng.uniform(-0.3, 0.3, (3, 3)))[0]
+        b["inertia"] = (Q @ np.array(b["inertia"], float) @ Q.T).tolist()
+    B = 12
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-0.5, 0.5, (B, 7))
+    o = orc.OracleBatch(chain, B, q0=q0_of(chain))
+    o.set(abi.F_Q, q); o.set(abi.F_DQ, dq); o.update_model()
+    t0 = o.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = o.add_joint_task(abi.joint_task_desc(7))
+    o.enable_gravity_compensation(True)
+    x0 = o.get(abi.F_CURRENT_POSITION, t0)
+    gp = rng.normal(0, 0.05, (B, 3)); gq = q + rng.normal(0, 0.1, (B, 7))
+    o.set(abi.F_GOAL_POSITION, x0 + gp, t0); o.set(abi.F_JT_GOAL_POSITION, gq, t1)
+    tau = o.tick(True)
+    g = o.get(abi.F_GRAVITY)
+    assert np.abs(g).max() > 1.0
+    for r in range(B):
+        rb = _two_task_np(chain, q[r], dq[r])
+        m, j = rb.tasks
+        assert _rel(m.x, x0[r]) < 1e-12
+        m.goal_pos = m.x + gp[r]; j.goal_pos = gq[r]
+        c = rb.controller()
+        c.gravity_comp = True
+        rb.model.updateModel()
+        c.updateControllerTaskModels()
+        assert _rel(tau[r], c.computeControlTorques()) < TOL, r
+        assert _rel(g[r], rb.model.jointGravityVector()) < TOL
+        assert _rel(o.get(abi.F_M)[r], rb.model.M()) < TOL
+        assert _rel(o.get(abi.F_JACOBIAN, t0)[r], m.J) < TOL
+        assert _rel(o.get(abi.F_LAMBDA_WORLD, t0)[r], m.handler.lambda_world()) < TOL

@@ -108,3 +108,44 @@ def test_holding_torque_and_energy(oracle_built):
     b.set(abi.F_TAU, np.zeros((B, n)))
     b.rollout_step(1e-3, 200, 2.0)
     assert (np.abs(b.get(abi.F_DQ)).max(axis=1) < np.abs(dq).max(axis=1)).all()
+
+
+def test_tilted_base_full_inertias(oracle_built):
+    """b from the derivatives of the mass matrix and g from the gravity vector, on a chain with a rotated base, off-axis gravity
+    and products of inertia (the chain of tests/test_rollout_gpu.py::test_step_tilted_base_and_full_inertias)"""
+    orc = oracle_built
+    chain = copy.deepcopy(load_chain("panda"))
+    cz, sz, cy, sy = np.cos(0.4), np.sin(0.4), np.cos(0.7), np.sin(0.7)
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]]); Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    chain["world_rot"] = (Rz @ Ry).tolist()
+    chain["world_xyz"] = [0.1, -0.2, 0.3]
+    chain["gravity"] = [1.0, -2.0, -9.0]
+    rng = np.random.default_rng(78)
+    for b in chain["bodies"]:
+        Q = np.linalg.qr(np.eye(3) + rng.uniform(-0.3, 0.3, (3, 3)))[0]
+        b["inertia"] = (Q @ np.array(b["inertia"], float) @ Q.T).tolist()
+    n, B = chain["n"], 8
+    q = random_q(chain, B, rng)
+    dq = rng.uniform(-1, 1, (B, n))
+    h = _batch(orc, chain, q, dq).nonlinear_effects()
+    o0 = _batch(orc, chain, q, np.zeros((B, n)))
+    g = o0.nonlinear_effects()
+    o0.add_joint_task(abi.joint_task_desc(n))
+    o0.enable_gravity_compensation(True)
+    o0.update_task_models()
+    o0.compute_torques(True)
+    g_ref = o0.get(abi.F_GRAVITY)
+    assert np.abs(g_ref).max() > 1.0
+    assert np.abs(g - g_ref).max() < 1e-11 * np.abs(g_ref).max()
+    eps = 1e-5
+    dM = np.zeros((n, B, n, n))
+    for k in range(n):
+        e = np.zeros(n); e[k] = eps
+        dM[k] = (_mass(orc, chain, q + e) - _mass(orc, chain, q - e)) / (2 * eps)
+    b = np.zeros((B, n))
+    for r in range(B):
+        Mdot = sum(dM[k][r] * dq[r, k] for k in range(n))
+        b[r] = Mdot @ dq[r] - 0.5 * np.array([dq[r] @ dM[i][r] @ dq[r] for i in range(n)])
+    scale = np.abs(h - g).max()
+    assert scale > 1e-2
+    assert np.abs((h - g) - b).max() < 2e-6 * max(scale, 1.0)
