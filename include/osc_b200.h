@@ -37,6 +37,7 @@ extern "C" {
 #define OSC_MAX_TASKS 4
 #define OSC_POPC_RING_CAPACITY 1024 /* bounded stand-in for the unbounded std::queue, POPCExplicitForceControl.h:44 (quirk Q9) */
 #define OSC_MAX_SINGULARITY_BUFFER 256 /* >= BUFFER_SIZE = 200, SingularityHandler.cpp:16 */
+#define OSC_NOALLOC_MAX_ROBOTS 262144 /* largest batch osc_tick_noalloc accepts (its static device scratch is 4 bytes per robot) */
 
 /* ---- status codes ---- */
 enum {
@@ -307,6 +308,22 @@ int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layo
 /* updateModel + updateControllerTaskModels + computeControlTorques in one call; uses the fused single-launch kernel
  * when the hierarchy is [MotionForceTask, full JointTask], otherwise the sequence above. */
 int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
+/* osc_tick for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same fused tick, same results as osc_tick, but the one scratch buffer the fused kernels use (the compacted list of the
+ * robots that leave the fast path for the API-faithful route, 2 counters + one int per robot) lives in a file-scope
+ * static __device__ array of the library instead of a cudaMalloc'ed one; the call performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  Limits and rules:
+ *   - at most OSC_NOALLOC_MAX_ROBOTS (262,144) robots per batch, else OSC_ERR_INVALID_ARGUMENT; every GPU that loads the
+ *     library holds the array (1 MiB + 256 B) until the process exits;
+ *   - only hierarchies the fused tick serves (osc_tick_is_fused() == 1), else OSC_ERR_UNSUPPORTED; a task whose internal
+ *     OTG is on must have gone through one osc_tick before (that is where the OTG's own list is allocated);
+ *   - tau_out_device is DEVICE memory on the batch's device (AOS [B][n] or SOA [n][B]) or NULL (read OSC_F_TAU later);
+ *   - the array is shared by every batch and every call on that GPU and keeps the last call's contents (the call clears
+ *     the two counters it needs at zero): calls that overlap on the GPU -- two batches on different streams, or two host
+ *     threads -- RACE on it.  Serialise them (same stream, or events).  osc_tick is unaffected and may overlap freely;
+ *   - osc_tick_fallback_count() keeps reporting the last osc_tick, not this call. */
+int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_device, int layout);
 /* 1 if osc_tick runs the fused kernel for the current hierarchy / parameters */
 int osc_tick_is_fused(const osc_batch_t* batch);
 /* What osc_tick leaves behind besides tau and the persistent controller state (integrators, observers, history):

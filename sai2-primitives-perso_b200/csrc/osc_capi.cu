@@ -113,3 +113,66 @@ int osc_enable_gravity_compensation(osc_batch_t* batch, int enable) {
 #include "osc_capi_tasks.inl"
 #include "osc_capi_fields.inl"
 #include "osc_capi_tick.inl"
+
+// ---- osc_tick_noalloc: the fused tick for callers that may not allocate (no counterpart in the reference).
+// The one piece of scratch memory the fused tick uses -- the compacted list of robots
+// that take the API-faithful route, [2] ping-pong counters + one int per robot, normally cudaMalloc'ed by the first
+// osc_tick of a batch -- lives in this file-scope device array instead.  Every GPU that loads the library holds its
+// (OSC_NOALLOC_MAX_ROBOTS + 64) * 4 bytes until exit.  The array's name below is a HOST-side stand-in, not a device
+// address: its device address is resolved once per device with cudaGetSymbolAddress, with that device current.
+namespace osc {
+static __device__ __align__(256) int g_noalloc_fallback[OSC_NOALLOC_MAX_ROBOTS + 64];
+
+static int noalloc_scratch(int device, int** out) {
+	static std::mutex mu;
+	static int* ptr[64] = {};
+	if (device < 0 || device >= 64) return invalid("osc_tick_noalloc: device index out of range");
+	std::lock_guard<std::mutex> lock(mu);
+	if (!ptr[device]) {
+		int cur = -1;
+		OSC_CUDA(cudaGetDevice(&cur));
+		if (cur != device) OSC_CUDA(cudaSetDevice(device));
+		void* p = nullptr;
+		OSC_CUDA(cudaGetSymbolAddress(&p, g_noalloc_fallback));
+		ptr[device] = (int*)p;
+	}
+	*out = ptr[device];
+	return OSC_OK;
+}
+}  // namespace osc
+
+extern "C" int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_device, int layout) {
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
+	if (b->stride > OSC_NOALLOC_MAX_ROBOTS) return invalid("osc_tick_noalloc: the batch has more than OSC_NOALLOC_MAX_ROBOTS (262144) robots; use osc_tick");
+	if (tau_out_device && layout != OSC_LAYOUT_AOS && layout != OSC_LAYOUT_SOA) return invalid("osc_tick_noalloc: tau_out layout must be AOS or SOA");
+	if (!b->ops->fused_supported(*b)) {
+		set_error("osc_tick_noalloc: only the fused tick ([6-DoF MotionForceTask, full JointTask], outputs LAZY or TAU) runs without allocating; use osc_tick");
+		return OSC_ERR_UNSUPPORTED;
+	}
+	for (const TaskH& t : b->tasks)
+		if (t.otg_on && !t.otg_slow) {
+			set_error("osc_tick_noalloc: the internal OTG of a task is on and has not ticked yet (its list is allocated by the first osc_tick)");
+			return OSC_ERR_UNSUPPORTED;
+		}
+	if (int rc = use_device(*b)) return rc;
+	int* scratch = nullptr;
+	if (int rc = noalloc_scratch(b->device, &scratch)) return rc;
+	// the array keeps the last call's contents: both counters must start at zero (the list itself is write-before-read)
+	OSC_CUDA(cudaMemsetAsync(scratch, 0, 2 * sizeof(int), b->stream));
+	int* const own_fb = b->fb;
+	const int own_parity = b->fb_parity, own_last = b->fb_last;
+	b->fb = scratch;
+	b->fb_parity = 0;
+	int rc = b->ops->otg_tick(*b, -1);
+	if (rc == OSC_OK) rc = b->ops->tick_fused(*b, stacked);
+	b->fb = own_fb;
+	b->fb_parity = own_parity;
+	b->fb_last = own_last;
+	if (rc != OSC_OK) return rc;
+	if (!tau_out_device) return OSC_OK;
+	Loc l;
+	b->ops->locate(*b, -1, OSC_F_TAU, l);
+	return export_rows(*b, row_ptr(*b, l), l.width, false, tau_out_device, layout, OSC_MEM_DEVICE);  // device destination: no staging
+}

@@ -9,6 +9,7 @@ MAX_DOF = 8
 MAX_TASKS = 4
 POPC_RING_CAPACITY = 1024
 MAX_SINGULARITY_BUFFER = 256
+NOALLOC_MAX_ROBOTS = 262144
 
 OK, ERR_INVALID_ARGUMENT, ERR_CUDA, ERR_NO_DEVICE, ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 PRECISION_F64, PRECISION_F32 = 64, 32

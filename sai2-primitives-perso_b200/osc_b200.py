@@ -70,6 +70,7 @@ def lib():
         "osc_task_compute_torques": (i, [vp, i, i]),
         "osc_compute_torques": (i, [vp, i, vp, i, i]),
         "osc_tick": (i, [vp, i, vp, i, i]),
+        "osc_tick_noalloc": (i, [vp, i, vp, i]),
         "osc_tick_is_fused": (i, [vp]),
         "osc_batch_set_tick_outputs": (i, [vp, i]),
         "osc_tick_fallback_count": (i64, [vp]),
@@ -102,7 +103,7 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_enable_gravity_compensation", "osc_field_size", "osc_set_field", "osc_get_field",
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
-            "osc_tick", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
+            "osc_tick", "osc_tick_noalloc", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",
             "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled",
             "osc_rollout_step", "osc_rollout"]
@@ -241,6 +242,10 @@ class Batch:
         out = np.empty((self.B, self.n), dtype=self.dtype)
         self._chk(self.L.osc_tick(self.h, int(stacked), out.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
         return out
+
+    def tick_noalloc(self, tau_device_ptr, stacked=True, layout=abi.LAYOUT_AOS):
+        """osc_tick_noalloc: fused tick with the library's static device scratch; tau lands in DEVICE memory (or nowhere)"""
+        self._chk(self.L.osc_tick_noalloc(self.h, int(stacked), C.c_void_p(tau_device_ptr) if tau_device_ptr else None, layout))
 
     def tick_is_fused(self):
         return bool(self.L.osc_tick_is_fused(self.h))

@@ -43,10 +43,11 @@ def test_constants_match_header():
     txt = _header_text()
     enums = dict((k, int(eval(v))) for k, v in re.findall(r"\b(OSC_[A-Z0-9_]+)\s*=\s*(-?\d+(?:\s*<<\s*\d+)?)", txt))
     defines = dict((k, int(v)) for k, v in re.findall(r"#define\s+(OSC_[A-Z0-9_]+)\s+(\d+)", txt))
+    assert defines["OSC_NOALLOC_MAX_ROBOTS"] == abi.NOALLOC_MAX_ROBOTS
     assert defines["OSC_MAX_DOF"] == abi.MAX_DOF and defines["OSC_POPC_RING_CAPACITY"] == abi.POPC_RING_CAPACITY
     checked = 0
     for name, val in vars(abi).items():
-        if not isinstance(val, int) or name.startswith("_") or name in ("MAX_DOF", "MAX_TASKS", "POPC_RING_CAPACITY", "MAX_SINGULARITY_BUFFER"):
+        if not isinstance(val, int) or name.startswith("_") or name in ("MAX_DOF", "MAX_TASKS", "POPC_RING_CAPACITY", "MAX_SINGULARITY_BUFFER", "NOALLOC_MAX_ROBOTS"):
             continue
         key = "OSC_" + name
         if key in enums:
