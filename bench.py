@@ -362,7 +362,7 @@ def run_b200(args, rank, world, local_rank):
     # ---- roofline of the dominant kernel (its own launches timed with CUDA events, L2 flushed)
     fused = batch.tick_is_fused()
     stages = {}
-    FUSED = "k_tick_fused2" if os.environ.get("OSC_FUSED_V", "2") == "2" else "k_tick_fused"
+    FUSED = "k_tick_fused2"
     if fused:
         stages[FUSED] = float(np.mean(step_ms))  # the step is this kernel + the (empty) k_tick_tail launch
     else:

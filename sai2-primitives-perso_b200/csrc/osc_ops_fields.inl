@@ -158,9 +158,17 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 		const dim3 g((unsigned)((b.B + OSC_FUSED_THREADS - 1) / OSC_FUSED_THREADS));
 		const MftC<T> tc = mftc(m);
 		const JtC<T, N> jc = jtc(b, j);
-		// OSC_FUSED_V=1 selects the first-generation kernel (osc_fused.cuh), OSC_FUSED_MINB its occupancy variant: experiment knobs
+		// Experiment knobs (kernel generation, occupancy / block-shape variants, no-PDL, no-tail diagnosis) exist only in
+		// builds made with -DOSC_EXPERIMENT (profiles/ runs); the product build has none of them and reads no environment.
+#ifdef OSC_EXPERIMENT
 		static const int ver = [] { const char* e = getenv("OSC_FUSED_V"); return e ? atoi(e) : 2; }();
-		static const int minb = [] { const char* e = getenv("OSC_FUSED_MINB"); return e ? atoi(e) : 8; }();
+		static const int bt_env = [] { const char* e = getenv("OSC_FUSED_BT"); return e ? atoi(e) : 0; }();
+		static const bool nosimple = getenv("OSC_FUSED_NOSIMPLE") != nullptr, debug_occ = getenv("OSC_DEBUG_OCC") != nullptr;
+		static const bool no_tail = getenv("OSC_DIAG_NO_TAIL") != nullptr, pdl = !getenv("OSC_NO_PDL");
+#else
+		constexpr int ver = 2, bt_env = 0;
+		constexpr bool nosimple = false, debug_occ = false, no_tail = false, pdl = true;
+#endif
 #define OSC_FUSED_ARGS ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list
 		int reuse_law = 0;
 		if (ver == 2 && fused2_supported(b)) {
@@ -169,13 +177,11 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
-			static const bool nosimple = getenv("OSC_FUSED_NOSIMPLE") != nullptr, debug_occ = getenv("OSC_DEBUG_OCC") != nullptr;
 			const bool simple = fused2_simple(b) && !nosimple;
 			if (simple && N == 7) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
 			// block shape: 224 threads with phase barriers once the batch fills two such blocks per SM (r1l: 44.7 us against
 			// 45.7 us for 64-thread blocks at 65,536 robots), 64-thread blocks below that so that small batches still spread
-			// over the SMs.  OSC_FUSED_BT = 64 | 65 (64 + barriers) | 224 | 448 overrides (experiment knob).
-			static const int bt_env = [] { const char* e = getenv("OSC_FUSED_BT"); return e ? atoi(e) : 0; }();
+			// over the SMs
 			const int bt = bt_env ? bt_env : (b.B >= 224 * 148 ? 224 : 64);
 			auto go = [&](auto kern, int threads) -> int {
 				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(T);
@@ -193,24 +199,21 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				return OSC_OK;
 			};
 			int rc = OSC_OK;
-			if (minb < 8) rc = simple ? go(k_tick_fused2<T, N, 168, true>, 64) : go(k_tick_fused2<T, N, 168, false>, 64);
+			if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true>, 224);
+#ifdef OSC_EXPERIMENT
 			else if (bt == 65) rc = simple ? go(k_tick_fused2<T, N, 128, true, 64, true>, 64) : go(k_tick_fused2<T, N, 128, false, 64, true>, 64);
-			else if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true>, 224);
 			else if (bt == 448) rc = simple ? go(k_tick_fused2<T, N, 128, true, 448, true>, 448) : go(k_tick_fused2<T, N, 128, false, 448, true>, 448);
+#endif
 			else rc = simple ? go(k_tick_fused2<T, N, 128, true>, 64) : go(k_tick_fused2<T, N, 128, false>, 64);
 			if (rc) return rc;
 		} else {
-			if (minb >= 8) k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else if (minb >= 6) k_tick_fused<T, N, 6><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
-			else k_tick_fused<T, N, 4><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
+			// first-generation kernel (osc_fused.cuh): control link not on the last body, or a prismatic joint in the chain
+			k_tick_fused<T, N, 8><<<g, OSC_FUSED_THREADS, 0, b.stream>>>(OSC_FUSED_ARGS);
 		}
 #undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
-		// OSC_DIAG_NO_TAIL: diagnosis only (what the tail launch costs a tick whose fallback list is empty); fallback robots get
-		// no torques in such a run, so nothing measured with it is a result
-		static const bool no_tail = getenv("OSC_DIAG_NO_TAIL") != nullptr;
-		if (!no_tail) {
+		if (!no_tail) {  // (no_tail: diagnosis builds only -- fallback robots get no torques in such a run)
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(tail_blocks);
 			cfg.blockDim = dim3(OSC_THREADS);
@@ -218,7 +221,6 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			cudaLaunchAttribute at[1];
 			at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 			at[0].val.programmaticStreamSerializationAllowed = 1;
-			static const bool pdl = !getenv("OSC_NO_PDL");
 			cfg.attrs = at;
 			cfg.numAttrs = pdl ? 1 : 0;
 			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<T, N>, ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,

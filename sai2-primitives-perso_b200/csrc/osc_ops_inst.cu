@@ -181,7 +181,11 @@ template <class T, int N> struct OpsImpl : Ops {
 	int rollout_step(Batch& b, double dt, int substeps, double damping) override {
 		bool revolute = true;
 		for (int i = 0; i < N; ++i) revolute = revolute && !ch.prismatic[i];
+#ifdef OSC_EXPERIMENT
 		static const int ver = [] { const char* e = getenv("OSC_ROLLOUT_V"); return e ? atoi(e) : 2; }();
+#else
+		constexpr int ver = 2;
+#endif
 		if (revolute && ver == 2) {  // body-frame kernel with a shared-memory stash (osc_rollout.cuh); block shape as the fused tick
 			auto go = [&](auto kern, int threads) -> int {
 				const size_t smem = (size_t)R2<N>::SLOTS * threads * sizeof(T);
@@ -264,7 +268,11 @@ template <class T, int N> struct OpsImpl : Ops {
 		cudaLaunchAttribute at[1];
 		at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
 		at[0].val.programmaticStreamSerializationAllowed = 1;
+#ifdef OSC_EXPERIMENT
 		static const bool pdl = !getenv("OSC_NO_PDL");
+#else
+		constexpr bool pdl = true;
+#endif
 		cfg.attrs = at;
 		cfg.numAttrs = pdl ? 1 : 0;
 		cudaError_t e = cudaLaunchKernelEx(&cfg, k_otg_slow<T, N>, js, b.stride);

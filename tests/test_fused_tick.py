@@ -215,3 +215,29 @@ def test_tilted_base_full_inertias_gravity_compensation(oracle_built):
     assert _tau_err(tg, tr) <= FP64_TOL
     assert np.abs(p.ref.get(abi.F_GRAVITY)).max() > 1.0
     p.compare(FP64_TOL)  # every getter, through the per-call kernels (lazy materialisation)
+
+
+@pytest.mark.parametrize("precision", [abi.PRECISION_F64, abi.PRECISION_F32])
+def test_first_generation_kernel_control_link_not_on_last_body(oracle_built, precision):
+    """k_tick_fused2 needs the control link on the last body; a MotionForceTask on `link6` (body 5 of 7) makes osc_tick take
+    the first-generation fused kernel (csrc/osc_fused.cuh k_tick_fused + k_tick_tail): the last joint does not move the
+    control point, so J has a zero column and the joint task's range is wider than in config 2."""
+    chain = load_chain("panda")
+    B = 1024
+    p, q, dq, rng = _two_task(chain, B, 37, precision, link="link6", p_c=(0.05, 0.0, 0.1), margin=0.3)
+    assert p.gpu.tick_is_fused()
+    for tick in range(3):
+        p.set(abi.F_Q, q + 0.01 * tick)
+        tg, tr = p.both("tick", True)
+        if precision == abi.PRECISION_F64:
+            assert _tau_err(tg, tr) <= FP64_TOL
+    if precision == abi.PRECISION_F64:
+        fb = p.gpu.tick_fallback_count()
+        blend = int((p.ref.get(abi.F_ALPHA, 0)[:, 0] < 1).sum())
+        assert blend <= fb < B
+        p.compare(FP64_TOL)
+    else:
+        sv = p.ref.get(abi.F_SINGULAR_VALUES, 0)
+        well = sv[:, 5] / sv[:, 0] > 0.09
+        err = np.abs(tg - tr).max(axis=1) / np.maximum(np.abs(tr).max(axis=1), 1e-2)
+        assert well.sum() > 30 and err[well].max() <= FP32_TOL, err[well].max()
