@@ -8,12 +8,12 @@ namespace osc {
 
 // MotionForceTask::initialSetup (handler part, SingularityHandler.cpp:53-63) + POPC reInitialize
 // (POPCExplicitForceControl.cpp:10-21)
-template <class T, int N>
-__global__ void k_mft_init(const __grid_constant__ ChainC<T, N> ch, Arena<T> tk, int64_t B, int64_t stride) {
+template <class T, int N, class S = T>
+__global__ void k_mft_init(const __grid_constant__ ChainC<T, N> ch, Arena<S> tk, int64_t B, int64_t stride) {
 	using L = MftL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> tP{tk.P, stride, r};
+	const Row<T, S> tP{tk.P, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		tP(L::Q_PRIOR + i) = T(0.5) * (ch.q_lower[i] + ch.q_upper[i]);
@@ -26,12 +26,12 @@ __global__ void k_mft_init(const __grid_constant__ ChainC<T, N> ch, Arena<T> tk,
 }
 
 // MotionForceTask::reInitializeTask (MotionForceTask.cpp:204-245)
-template <class T, int N>
-__global__ void k_mft_reinit(const __grid_constant__ MftC<T> tc, Arena<T> rob, Arena<T> tk, int64_t B, int64_t stride) {
+template <class T, int N, class S = T>
+__global__ void k_mft_reinit(const __grid_constant__ MftC<T> tc, Arena<S> rob, Arena<S> tk, int64_t B, int64_t stride) {
 	using L = MftL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	Kin<T, N> kin;
 	ld_kin<T, N>(rS, kin);
 	T x[3], R[3][3];
@@ -48,12 +48,12 @@ __global__ void k_mft_reinit(const __grid_constant__ MftC<T> tc, Arena<T> rob, A
 
 // side effects of parametrizeForceMotionSpaces / parametrizeMomentRotMotionSpaces (MotionForceTask.cpp:850-856, 882-888),
 // setClosedLoopForce/MomentControl (.cpp:973-986) and disablePassivity (POPCExplicitForceControl.cpp:25-28)
-template <class T, int N>
-__global__ void k_mft_reset(Arena<T> tk, int64_t B, int64_t stride, int flags) {
+template <class T, int N, class S = T>
+__global__ void k_mft_reset(Arena<S> tk, int64_t B, int64_t stride, int flags) {
 	using L = MftL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> tP{tk.P, stride, r};
+	const Row<T, S> tP{tk.P, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	if (flags & 1) {
 		for (int a = 0; a < 3; ++a) { tP(L::GOAL_POS + a) = tP(L::CUR_POS + a); tP(L::GOAL_LINVEL + a) = T(0); tP(L::GOAL_LINACC + a) = T(0); }
@@ -75,12 +75,12 @@ __global__ void k_mft_reset(Arena<T> tk, int64_t B, int64_t stride, int flags) {
 }
 
 // JointTask::reInitializeTask (JointTask.cpp:91-107)
-template <class T, int N>
-__global__ void k_jt_reinit(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk, int64_t B, int64_t stride, int init) {
+template <class T, int N, class S = T>
+__global__ void k_jt_reinit(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk, int64_t B, int64_t stride, int init) {
 	using L = JtL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> rP{rob.P, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	T q[N], cp[N];
 	ld_vec<T, N>(rP, RobotL<N>::Q, q);
 	mv<T, N, N>(jc.S, q, cp);
@@ -101,12 +101,12 @@ __global__ void k_jt_reinit(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, 
 }
 
 // MotionForceTask::updateSensedForceAndMoment (MotionForceTask.cpp:805-828); in6 = SoA [6][stride] sensor-frame wrench
-template <class T, int N>
-__global__ void k_mft_sensed(const __grid_constant__ MftC<T> tc, Arena<T> rob, Arena<T> tk, const T* in6, int64_t B, int64_t stride) {
+template <class T, int N, class S = T>
+__global__ void k_mft_sensed(const __grid_constant__ MftC<T> tc, Arena<S> rob, Arena<S> tk, const S* in6, int64_t B, int64_t stride) {
 	using L = MftL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> rS{rob.S, stride, r}, tP{tk.P, stride, r};
+	const Row<T, S> rS{rob.S, stride, r}, tP{tk.P, stride, r};
 	Kin<T, N> kin;
 	ld_kin<T, N>(rS, kin);
 	T x[3], R[3][3];
@@ -123,20 +123,20 @@ __global__ void k_mft_sensed(const __grid_constant__ MftC<T> tc, Arena<T> rob, A
 	st_vec<T, 3>(tP, L::SENSED_M, mw);
 }
 
-template <class T, int N>
-__global__ void k_add_gravity(Arena<T> rob, int64_t B, int64_t stride) {
+template <class T, int N, class S = T>
+__global__ void k_add_gravity(Arena<S> rob, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> rS{rob.S, stride, r};
+	const Row<T, S> rS{rob.S, stride, r};
 	for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += rS(RobotL<N>::GRAV + i);
 }
 
 // out[(i*C + j)] = sum_ab U[i][a] L[a][b] U[j][b] : the basis-independent export of a Lambda stored in a range basis
-template <class T, int R, int K>
-__global__ void k_pack_ulut(const T* S, int offU, int offL, T* out, int64_t B, int64_t stride, int out_dim) {
+template <class T, int R, int K, class St = T>
+__global__ void k_pack_ulut(const St* S, int offU, int offL, St* out, int64_t B, int64_t stride, int out_dim) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> s{const_cast<T*>(S), stride, r};
+	const Row<T, St> s{const_cast<St*>(S), stride, r};
 	T U[R][K], Lm[K][K], UL[R][K];
 	ld_mat<T, R, K>(s, offU, U);
 	ld_mat<T, K, K>(s, offL, Lm);
@@ -145,7 +145,7 @@ __global__ void k_pack_ulut(const T* S, int offU, int offL, T* out, int64_t B, i
 		for (int j = 0; j < out_dim; ++j) {
 			T v = T(0);
 			for (int k = 0; k < K; ++k) v += UL[i][k] * U[j][k];
-			out[(int64_t)(i * out_dim + j) * stride + r] = v;
+			out[(int64_t)(i * out_dim + j) * stride + r] = (St)v;
 		}
 }
 // singularity types unpack / counters

@@ -25,9 +25,9 @@ namespace osc {
 
 enum { OSC_EXPORT_VECTORS = 1 };
 
-template <class T, int N, int MINB>
+template <class T, int N, int MINB, class S = T>
 __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-																   const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
+																   const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk0, Arena<S> tk1,
 																   int64_t B, int64_t stride, int stacked, int gravity, int exports,
 																   int* __restrict__ fb_count, int* __restrict__ fb_list) {
 	static_assert(N == 6 || N == 7, "the fused tick covers n - 6 <= 1 (one-dimensional joint-task range)");
@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __
 	using JL = JtL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
 	const Row<int32_t> mI{tk0.I, stride, r};
 	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
 	int status = 0;
@@ -246,9 +246,9 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __
 
 // The robots k_tick_fused could not certify: the API-faithful route (every branch of SingularityHandler, full Jacobi
 // SVDs), one robot per thread over the compacted list.  Also re-arms the other fallback counter for the next tick.
-template <class T, int N>
+template <class T, int N, class S = T>
 __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-															const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1, int64_t stride,
+															const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk0, Arena<S> tk1, int64_t stride,
 															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law) {
 	// launched with programmatic stream serialisation behind the fused kernel: its launch latency overlaps the fused kernel's
 	// run; the fallback list is complete (and visible) once the wait returns.  A no-op under a plain launch.
@@ -258,12 +258,12 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 	for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
 		const int64_t r = fb_list[idx];
 		model_robot<T, N>(ch, rob, stride, r, 1, gravity);
-		mft_update_robot<T, N>(ch, tc, rob, tk0, nullptr, stride, r, 0);
+		mft_update_robot<T, N>(ch, tc, rob, tk0, (const S*)nullptr, stride, r, 0);
 		jt_update_robot<T, N>(jc, rob, tk1, tk0.S + (int64_t)MftL<N>::NTP * stride, stride, r);
 		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1, reuse_law & 1);
 		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2, reuse_law & 2);
 		if (gravity) {
-			const Row<T> rS{rob.S, stride, r};
+			const Row<T, S> rS{rob.S, stride, r};
 			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += rS(RobotL<N>::GRAV + i);
 		}
 	}
@@ -281,6 +281,10 @@ template <class T, int N> bool fused_tick_supported(Batch& b) {
 		m.mp.bie_threshold != j.jp.bie_threshold)
 		return false;
 	if (!(m.mp.s_max > 0) || !(m.mp.s_abs_tol > 0)) return false;
+	// The branch certificate of the fused kernels is an FP32 bound on G = J J^T (absolute error ~ 4e-7 lambda_max): its shift
+	// s_max^2 lambda_max must stay far above that noise, or a truly singular robot could be certified non-singular
+	// (ADVICE r1).  Below s_max = 1e-2 (default 6e-2, setSingularityHandlingBounds) the tick takes the API-faithful kernels.
+	if (m.mp.s_max < 1e-2) return false;
 	return true;
 }
 

@@ -48,8 +48,13 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	using ML = MftL<N>;
 	using JL = JtL<N>;
 	using F = F2<N>;
+	// Mixed precision of an FP32 batch: state in HBM, sin/cos, kinematics, the control law, the mass-matrix recursion and the
+	// branch certificate are FP32; the factorisation chain (Cholesky of M, Y = L^-1 J^T, Gram-Schmidt, the triangular sweeps
+	// of P10/P11) accumulates in FP64, because its rounding error is amplified by kappa(M) kappa(J)^2 (1e3-1e5 for the Panda)
+	// and would otherwise eat the 1e-4 FP32 tolerance of the north star.  A = T for an FP64 batch: nothing changes there.
+	using A = double;
 	extern __shared__ __align__(16) unsigned char osc_stash_raw[];
-	T* const sm = reinterpret_cast<T*>(osc_stash_raw);
+	A* const sm = reinterpret_cast<A*>(osc_stash_raw);
 #define SM(slot) sm[(slot) * BT + threadIdx.x]
 #define OSC_PHASE()                       \
 	OSC_FENCE();                          \
@@ -252,34 +257,34 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 
 	OSC_PHASE();
 	// ---- P3: M = L L^T in place in registers, then parked in the stash; bounded-inertia clamp pattern ----
-	T rho2 = T(1), beta = T(0);  // BIE: L_BIE = L except its last pivot; rho = L_nn / L_BIE,nn, beta = 1 - rho^2
+	A rho2 = A(1), beta = A(0);  // BIE: L_BIE = L except its last pivot; rho = L_nn / L_BIE,nn, beta = 1 - rho^2
 	{
-		T Mx[N][N], li[N];
+		A Mx[N][N], li[N];
 		OSC_UNROLL for (int i = 0; i < N; ++i)
 			OSC_UNROLL for (int j = 0; j <= i; ++j) Mx[i][j] = SM(F::MM + i * (i + 1) / 2 + j);
-		T delta = T(0);
+		A delta = A(0);
 		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
-			const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
+			const A thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
 			OSC_UNROLL for (int i = 0; i < N - 1; ++i) other = other || (Mx[i][i] < thr);
 			if (other) OSC_FALL_BACK()  // a clamp that is not confined to the last joint: API-faithful route
 			if (Mx[N - 1][N - 1] < thr) delta = thr - Mx[N - 1][N - 1];
 		}
-		if (!chol_inplace<T, N>(Mx, li)) status |= 16;
+		if (!chol_inplace<A, N>(Mx, li)) status |= 16;
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::LL + i * (i - 1) / 2 + j) = Mx[i][j];
 			SM(F::LI + i) = li[i];
 		}
-		if (delta > T(0)) {
-			const T d = Mx[N - 1][N - 1] * Mx[N - 1][N - 1];
+		if (delta > A(0)) {
+			const A d = Mx[N - 1][N - 1] * Mx[N - 1][N - 1];
 			rho2 = d / (d + delta);
-			beta = T(1) - rho2;
+			beta = A(1) - rho2;
 		}
 	}
 
 	OSC_PHASE();
 	// ---- P4: forward kinematics (revolute chain, control link on the last body) and the Jacobian at the compliant frame ----
-	T J[6][N];
+	A J[6][N];  // built in the batch type, held in the accumulation type: Y = L^-1 J^T overwrites it in place
 	{
 		T Rp[3][3], pp[3], Jz[N][3], Jo[N][3], x[3];
 		OSC_UNROLL for (int a = 0; a < 3; ++a) {
@@ -342,16 +347,16 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	OSC_PHASE();
 	// ---- P7: Y = L^-1 J^T in place (J[c][:] <- L^-1 J[c][:]), L streamed row by row from the stash ----
 	OSC_UNROLL for (int k = 0; k < N; ++k) {
-		T Lk[N];
+		A Lk[N];
 		OSC_UNROLL for (int m = 0; m < k; ++m) Lk[m] = SM(F::LL + k * (k - 1) / 2 + m);
-		const T li = SM(F::LI + k);
+		const A li = SM(F::LI + k);
 		OSC_UNROLL for (int c = 0; c < 6; ++c) {
-			T s = J[c][k];
-			OSC_UNROLL for (int m = 0; m < k; ++m) s = Num<T>::fma_(-Lk[m], J[c][m], s);
+			A s = J[c][k];
+			OSC_UNROLL for (int m = 0; m < k; ++m) s = Num<A>::fma_(-Lk[m], J[c][m], s);
 			J[c][k] = s * li;
 		}
 	}
-	T (&Y)[6][N] = J;
+	A (&Y)[6][N] = J;
 
 	OSC_PHASE();
 	// ---- P8: orthonormalise the rows of Y in place (modified Gram-Schmidt): Y = C W with W W^T = I and C lower triangular,
@@ -359,102 +364,102 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	// C goes to the stash (strictly lower part + 1/C_cc); W stays in the registers of Y. ----
 	// The SIMPLE kernel carries F* through the same row operations as an extra column: C^-1 [Y | F*] = [W | g] with
 	// g = C^-1 F* = C^T Lambda F*, which is all P10 needs of C -- so C is not stored at all there.
-	T g[6];
+	A g[6];
 	if constexpr (SIMPLE) {
 		OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::CC + c);
 	}
 	OSC_UNROLL for (int c = 0; c < 6; ++c) {
-		T nn = T(0);
-		OSC_UNROLL for (int i = 0; i < N; ++i) nn = Num<T>::fma_(Y[c][i], Y[c][i], nn);
-		if (!(nn > T(0))) status |= 16;
-		const T inv = Num<T>::rsqrt_(nn);
+		A nn = A(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) nn = Num<A>::fma_(Y[c][i], Y[c][i], nn);
+		if (!(nn > A(0))) status |= 16;
+		const A inv = Num<A>::rsqrt_(nn);
 		if constexpr (SIMPLE) g[c] *= inv;
 		else SM(F::cli(c)) = inv;
 		OSC_UNROLL for (int i = 0; i < N; ++i) Y[c][i] *= inv;
 		OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) {
-			T rr = T(0);
-			OSC_UNROLL for (int i = 0; i < N; ++i) rr = Num<T>::fma_(Y[c][i], Y[c2][i], rr);
-			if constexpr (SIMPLE) g[c2] = Num<T>::fma_(-rr, g[c], g[c2]);
+			A rr = A(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) rr = Num<A>::fma_(Y[c][i], Y[c2][i], rr);
+			if constexpr (SIMPLE) g[c2] = Num<A>::fma_(-rr, g[c], g[c2]);
 			else SM(F::CC + c2 * (c2 - 1) / 2 + c) = rr;
-			OSC_UNROLL for (int i = 0; i < N; ++i) Y[c2][i] = Num<T>::fma_(-rr, Y[c][i], Y[c2][i]);
+			OSC_UNROLL for (int i = 0; i < N; ++i) Y[c2][i] = Num<A>::fma_(-rr, Y[c][i], Y[c2][i]);
 		}
 	}
-	T (&W)[6][N] = Y;
+	A (&W)[6][N] = Y;
 
 	OSC_PHASE();
 	// ---- P9: u = unit vector orthogonal to the rows of W (n = 7): P = I - W^T W = u u^T, N_1 = (L^-T u)(L u)^T ----
-	T u[N];
-	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = T(0);
+	A u[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = A(0);
 	if constexpr (N == 7) {
-		T best = T(-1);
+		A best = A(-1);
 		int kb = 0;
 		OSC_UNROLL for (int k = 0; k < N; ++k) {  // residual of e_k: P_kk = 1 - |W[:,k]|^2
-			T s = T(1);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][k], W[c][k], s);
+			A s = A(1);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<A>::fma_(-W[c][k], W[c][k], s);
 			if (s > best) { best = s; kb = k; }
 		}
-		T a[6];
+		A a[6];
 		OSC_UNROLL for (int c = 0; c < 6; ++c) {
-			T s = T(0);
+			A s = A(0);
 			OSC_UNROLL for (int k = 0; k < N; ++k) s = (k == kb) ? W[c][k] : s;
 			a[c] = s;
 		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			T s = (i == kb) ? T(1) : T(0);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][i], a[c], s);
+			A s = (i == kb) ? A(1) : A(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<A>::fma_(-W[c][i], a[c], s);
 			u[i] = s;
 		}
 		// second projection ("twice is enough")
 		OSC_UNROLL for (int c = 0; c < 6; ++c) {
-			T s = T(0);
-			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<T>::fma_(W[c][i], u[i], s);
+			A s = A(0);
+			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<A>::fma_(W[c][i], u[i], s);
 			a[c] = s;
 		}
-		T nu = T(0);
+		A nu = A(0);
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			T s = u[i];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(-W[c][i], a[c], s);
+			A s = u[i];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<A>::fma_(-W[c][i], a[c], s);
 			u[i] = s;
-			nu = Num<T>::fma_(s, s, nu);
+			nu = Num<A>::fma_(s, s, nu);
 		}
-		const T inv = Num<T>::rsqrt_(nu);
+		const A inv = Num<A>::rsqrt_(nu);
 		OSC_UNROLL for (int i = 0; i < N; ++i) u[i] *= inv;
 	}
 
 	OSC_PHASE();
 	// ---- P10: tau_1 = J^T (Lambda_mod F* + F_f) = L h with h = W^T g,  g = C^T (Lambda_mod F* + F_f)
 	// (SingularityHandler.cpp:160-225, 307-309).  Lambda = A^-1 = C^-T C^-1, so C^T Lambda F* = C^-1 F*: one forward solve. ----
-	T h[N];
+	A h[N];
 	{
 		if constexpr (!SIMPLE) {
 			OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = SM(F::SC + c);
 			if (tc.decoupling != OSC_IMPEDANCE) {
 				OSC_UNROLL for (int i = 0; i < 6; ++i) {  // g <- C^-1 F*
-					T s = g[i];
-					OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<T>::fma_(-SM(F::CC + i * (i - 1) / 2 + m), g[m], s);
+					A s = g[i];
+					OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<A>::fma_(-SM(F::CC + i * (i - 1) / 2 + m), g[m], s);
 					g[i] = s * SM(F::cli(i));
 				}
 			}
 		}
-		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > T(0)) {
+		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && beta > A(0)) {
 			// A_BIE = A - beta y y^T with y = C w (w = last column of W):  C^T A_BIE^-1 F* = g + beta w (w . g) / (1 - beta |w|^2)
-			T ww = T(0), wg = T(0);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) { ww = Num<T>::fma_(W[c][N - 1], W[c][N - 1], ww); wg = Num<T>::fma_(W[c][N - 1], g[c], wg); }
-			const T coef = beta * wg / (T(1) - beta * ww);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = Num<T>::fma_(coef, W[c][N - 1], g[c]);
+			A ww = A(0), wg = A(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) { ww = Num<A>::fma_(W[c][N - 1], W[c][N - 1], ww); wg = Num<A>::fma_(W[c][N - 1], g[c], wg); }
+			const A coef = beta * wg / (A(1) - beta * ww);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) g[c] = Num<A>::fma_(coef, W[c][N - 1], g[c]);
 		}
 		if constexpr (!SIMPLE) {  // + C^T F_f (and C^T F* when Lambda_mod = I)
-			T f[6];
-			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = SM(F::SC + 6 + c) + (tc.decoupling == OSC_IMPEDANCE ? g[c] : T(0));
+			A f[6];
+			OSC_UNROLL for (int c = 0; c < 6; ++c) f[c] = SM(F::SC + 6 + c) + (tc.decoupling == OSC_IMPEDANCE ? g[c] : A(0));
 			OSC_UNROLL for (int c = 0; c < 6; ++c) {
-				T s = f[c] / SM(F::cli(c));
-				OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) s = Num<T>::fma_(SM(F::CC + c2 * (c2 - 1) / 2 + c), f[c2], s);
-				g[c] = (tc.decoupling == OSC_IMPEDANCE ? T(0) : g[c]) + s;
+				A s = f[c] / SM(F::cli(c));
+				OSC_UNROLL for (int c2 = c + 1; c2 < 6; ++c2) s = Num<A>::fma_(SM(F::CC + c2 * (c2 - 1) / 2 + c), f[c2], s);
+				g[c] = (tc.decoupling == OSC_IMPEDANCE ? A(0) : g[c]) + s;
 			}
 		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			T s = T(0);
-			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<T>::fma_(W[c][i], g[c], s);
+			A s = A(0);
+			OSC_UNROLL for (int c = 0; c < 6; ++c) s = Num<A>::fma_(W[c][i], g[c], s);
 			h[i] = s;
 		}
 	}
@@ -477,12 +482,12 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	// ---- P11: tau_1 = L h and w = L u (one sweep over L), parked in the dead C slots ----
 	constexpr int TAU1 = SIMPLE ? F::SC : F::CC, WW = TAU1 + N;  // dead slots: sin/cos (SIMPLE, F* lives in registers) or C
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
-		const T ld = T(1) / SM(F::LI + i);
-		T s1 = ld * h[i], sw = ld * u[i];
+		const A ld = A(1) / SM(F::LI + i);
+		A s1 = ld * h[i], sw = ld * u[i];
 		OSC_UNROLL for (int m = 0; m < i; ++m) {
-			const T l = SM(F::LL + i * (i - 1) / 2 + m);
-			s1 = Num<T>::fma_(l, h[m], s1);
-			sw = Num<T>::fma_(l, u[m], sw);
+			const A l = SM(F::LL + i * (i - 1) / 2 + m);
+			s1 = Num<A>::fma_(l, h[m], s1);
+			sw = Num<A>::fma_(l, u[m], sw);
 		}
 		if (ex) mS(ML::TASK_TAU + i) = s1;
 		if constexpr (N == 7) { SM(TAU1 + i) = s1; SM(WW + i) = sw; }
@@ -491,53 +496,53 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	if constexpr (N == 7) {
 		OSC_FENCE();
 		// v = L^-T u, M^-1 tau_1 = L^-T h: in place (u -> v, h -> mt), one backward sweep over L
-		const T u_last = u[N - 1];
+		const A u_last = u[N - 1];
 		OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
-			T sv = u[i], st = h[i];
+			A sv = u[i], st = h[i];
 			OSC_UNROLL for (int k = i + 1; k < N; ++k) {
-				const T l = SM(F::LL + k * (k - 1) / 2 + i);
-				sv = Num<T>::fma_(-l, u[k], sv);
-				st = Num<T>::fma_(-l, h[k], st);
+				const A l = SM(F::LL + k * (k - 1) / 2 + i);
+				sv = Num<A>::fma_(-l, u[k], sv);
+				st = Num<A>::fma_(-l, h[k], st);
 			}
-			const T li = SM(F::LI + i);
+			const A li = SM(F::LI + i);
 			u[i] = sv * li; h[i] = st * li;
 		}
-		T (&v)[N] = u;
+		A (&v)[N] = u;
 		// JointTask in the nullspace (JointTask.cpp:218-356): R = v / |v|, Lambda = 1 / |v|^2,
 		// tau_2 = w [Lambda (v.a - v.M^-1 tau_1) + Lambda_mod v.u_pd]
-		T nv2 = T(0), vc = T(0);
-		OSC_UNROLL for (int i = 0; i < N; ++i) { nv2 = Num<T>::fma_(v[i], v[i], nv2); vc = Num<T>::fma_(v[i], h[i], vc); }
-		const T lam = T(1) / nv2;
-		T lam_mod = lam;  // JointTask.cpp:253-267
-		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = T(1) / (nv2 * (T(1) - beta * u_last * u_last));  // |L_BIE^-1 L u|^2
-		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = T(1);
-		T va = T(0), vu = T(0);
+		A nv2 = A(0), vc = A(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) { nv2 = Num<A>::fma_(v[i], v[i], nv2); vc = Num<A>::fma_(v[i], h[i], vc); }
+		const A lam = A(1) / nv2;
+		A lam_mod = lam;  // JointTask.cpp:253-267
+		if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) lam_mod = A(1) / (nv2 * (A(1) - beta * u_last * u_last));  // |L_BIE^-1 L u|^2
+		else if (jc.decoupling == OSC_IMPEDANCE) lam_mod = A(1);
+		A va = A(0), vu = A(0);
 		if constexpr (SIMPLE) {  // u_pd and the goal acceleration were staged by P1
 			OSC_UNROLL for (int i = 0; i < N; ++i) {
-				va = Num<T>::fma_(v[i], SM(F::GAC + i), va);
-				vu = Num<T>::fma_(v[i], SM(F::UPD + i), vu);
+				va = Num<A>::fma_(v[i], SM(F::GAC + i), va);
+				vu = Num<A>::fma_(v[i], SM(F::UPD + i), vu);
 			}
 		} else {
 			T q[N], dq[N], upd[N], acc[N];
 			ld_vec<T, N>(rP, RobotL<N>::Q, q);
 			ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
 			jt_pd_law<T, N>(jc, jP, jS, q, dq, upd, acc, ex);
-			OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<T>::fma_(v[i], acc[i], va); vu = Num<T>::fma_(v[i], upd[i], vu); }
+			OSC_UNROLL for (int i = 0; i < N; ++i) { va = Num<A>::fma_(v[i], acc[i], va); vu = Num<A>::fma_(v[i], upd[i], vu); }
 			if (ex) {
 				st_vec<T, N>(jS, JL::CUR_POS, q);
 				st_vec<T, N>(jS, JL::CUR_VEL, dq);
 			}
 		}
-		const T sc = lam * (va - (stacked ? vc : T(0))) + lam_mod * vu;
+		const A sc = lam * (va - (stacked ? vc : A(0))) + lam_mod * vu;
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
-			const T t2 = SM(WW + i) * sc;
-			T t = SM(TAU1 + i) + t2;
+			const A t2 = SM(WW + i) * sc;
+			A t = SM(TAU1 + i) + t2;
 			if (gravity) t += rS(RobotL<N>::GRAV + i);  // written by k_gravity ahead of this kernel
 			rS(RobotL<N>::TAU + i) = t;
 			if (ex) jS(JL::TASK_TAU + i) = t2;
 		}
 	} else if (ex) {
-		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); jS(JL::TASK_TAU + i) = T(0); }
+		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); jS(JL::TASK_TAU + i) = A(0); }
 	}
 	if (ex) {
 		tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;

@@ -8,8 +8,8 @@ namespace osc {
 
 // The joint-space control law of JointTask::computeTorques (JointTask.cpp:319-346): integrates the error, returns the
 // PID (or velocity-saturated) command u and the feed-forward acceleration; rows >= k are zero.
-template <class T, int N, bool NOSAT = false>
-OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, const T (&cp)[N], const T (&cv)[N], T (&u)[N], T (&acc)[N],
+template <class T, int N, bool NOSAT = false, class S = T>
+OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T, S>& tP, const Row<T, S>& tS, const T (&cp)[N], const T (&cv)[N], T (&u)[N], T (&acc)[N],
 					   bool export_vectors, bool integrate = true) {
 	using L = JtL<N>;
 	T dv[N];
@@ -37,15 +37,15 @@ OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T>& tP, const Row<T>& tS, 
 	if (export_vectors) st_vec<T, N>(tS, L::DES_VEL, dv);
 }
 
-template <class T, int N>
-__device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<T>& rob, const Arena<T>& tk, const T* nprec_src, int64_t stride, int64_t r) {
+template <class T, int N, class S = T>
+__device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk, const S* nprec_src, int64_t stride, int64_t r) {
 	using L = JtL<N>;
-	const Row<T> rS{rob.S, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rS{rob.S, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 	T Np[N][N];
 	if (nprec_src) {
-		const Row<T> src{const_cast<T*>(nprec_src), stride, r};
+		const Row<T, S> src{const_cast<S*>(nprec_src), stride, r};
 		ld_mat<T, N, N>(src, 0, Np);
 	} else {
 		OSC_UNROLL for (int i = 0; i < N; ++i)
@@ -181,19 +181,19 @@ __device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<T>& rob, const 
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 }
 
-template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk,
-															const T* nprec_src, int64_t B, int64_t stride) {
+template <class T, int N, class S = T>
+__global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk,
+															const S* nprec_src, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	jt_update_robot<T, N>(jc, rob, tk, nprec_src, stride, r);
 }
 
-template <class T, int N>
-__device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r, int with_tau_prec,
+template <class T, int N, class S = T>
+__device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk, int64_t stride, int64_t r, int with_tau_prec,
 								 int accumulate, int integrated_already = 0) {
 	using L = JtL<N>;
-	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	T q[N], dq[N], cp[N], cv[N];
 	ld_vec<T, N>(rP, RobotL<N>::Q, q);
@@ -255,8 +255,8 @@ __device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<T>& rob, const
 	}
 }
 
-template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk, int64_t B,
+template <class T, int N, class S = T>
+__global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk, int64_t B,
 															 int64_t stride, int with_tau_prec, int accumulate) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;

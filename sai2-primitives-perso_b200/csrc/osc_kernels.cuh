@@ -32,7 +32,7 @@ template <class T> struct MftC {
 	int buffer_size;
 	T sensor_R[3][3], sensor_p[3];
 	int apply_compensation;
-	T* popc_ring;  // [OSC_POPC_RING_CAPACITY][stride] or nullptr until passivity is first enabled
+	void* popc_ring;  // [OSC_POPC_RING_CAPACITY][stride] in the batch STORAGE type, or nullptr until passivity is first enabled
 };
 
 template <class T, int N> struct JtC {
@@ -45,32 +45,55 @@ template <class T, int N> struct JtC {
 };
 
 // ---- SoA access ----
-template <class T> struct Row {
+// T = the type the kernel computes in, S = the type the rows are stored in (S = T for an FP64 batch and for the fused kernels).
+// The API-faithful kernels of an FP32 batch run with T = double over S = float rows: their task models (Lambda, Jbar and above
+// all N = I - Jbar J, a cancellation whose FP32 rounding noise eps |Jbar| |J| reaches O(1) near singular postures and is then
+// mistaken for range by the next task of the hierarchy) need FP64 arithmetic to hold the 1e-4 FP32 tolerance of the north star.
+template <class T, class S> struct Ref {  // element proxy of a converting row
+	S* p;
+	OSC_DEV operator T() const { return (T)*p; }
+	OSC_DEV const Ref& operator=(T v) const { *p = (S)v; return *this; }
+	OSC_DEV const Ref& operator=(const Ref& o) const { *p = *o.p; return *this; }
+	OSC_DEV const Ref& operator+=(T v) const { *p = (S)((T)*p + v); return *this; }
+	OSC_DEV const Ref& operator-=(T v) const { *p = (S)((T)*p - v); return *this; }
+};
+template <class T, class S = T> struct Row {
+	S* base;
+	int64_t stride, r;
+	OSC_DEV Ref<T, S> operator()(int e) const { return Ref<T, S>{base + (int64_t)e * stride + r}; }
+	OSC_DEV T ro(int e) const { return (T)__ldg(base + (int64_t)e * stride + r); }
+};
+template <class T> struct Row<T, T> {
 	T* base;
 	int64_t stride, r;
 	OSC_DEV T& operator()(int e) const { return base[(int64_t)e * stride + r]; }
 	// read-only load (ld.global.nc): ONLY for rows the running kernel never writes; lets the compiler hoist it over stores
 	OSC_DEV T ro(int e) const { return __ldg(base + (int64_t)e * stride + r); }
 };
-template <class T, int R, int C> OSC_DEV void ld_mat(const Row<T>& a, int off, T (&A)[R][C]) {
+template <class T, int R, int C, class S = T>
+OSC_DEV void ld_mat(const Row<T, S>& a, int off, T (&A)[R][C]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i)
 		OSC_UNROLL for (int j = 0; j < C; ++j) A[i][j] = a(off + i * C + j);
 }
-template <class T, int R, int C> OSC_DEV void st_mat(const Row<T>& a, int off, const T (&A)[R][C]) {
+template <class T, int R, int C, class S = T>
+OSC_DEV void st_mat(const Row<T, S>& a, int off, const T (&A)[R][C]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i)
 		OSC_UNROLL for (int j = 0; j < C; ++j) a(off + i * C + j) = A[i][j];
 }
-template <class T, int R> OSC_DEV void ld_vec(const Row<T>& a, int off, T (&v)[R]) {
+template <class T, int R, class S = T>
+OSC_DEV void ld_vec(const Row<T, S>& a, int off, T (&v)[R]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i) v[i] = a(off + i);
 }
-template <class T, int R> OSC_DEV void st_vec(const Row<T>& a, int off, const T (&v)[R]) {
+template <class T, int R, class S = T>
+OSC_DEV void st_vec(const Row<T, S>& a, int off, const T (&v)[R]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i) a(off + i) = v[i];
 }
-template <class T, int N> OSC_DEV void ld_kin(const Row<T>& S, Kin<T, N>& k) {
+template <class T, int N, class S = T>
+OSC_DEV void ld_kin(const Row<T, S>& Sr, Kin<T, N>& k) {
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			k.o[i][a] = S(RobotL<N>::KO + 3 * i + a);
-			OSC_UNROLL for (int b = 0; b < 3; ++b) k.R[i][a][b] = S(RobotL<N>::KR + 9 * i + 3 * a + b);
+			k.o[i][a] = Sr(RobotL<N>::KO + 3 * i + a);
+			OSC_UNROLL for (int b = 0; b < 3; ++b) k.R[i][a][b] = Sr(RobotL<N>::KR + 9 * i + 3 * a + b);
 		}
 	}
 }
@@ -80,35 +103,35 @@ template <class T, int N> OSC_DEV void ld_kin(const Row<T>& S, Kin<T, N>& k) {
 // ------------------------------------------------------------------------------------------------------------------
 // robot->updateModel()
 // ------------------------------------------------------------------------------------------------------------------
-template <class T, int N>
-__device__ void model_robot(const ChainC<T, N>& ch, const Arena<T>& rob, int64_t stride, int64_t r, int dynamics, int gravity) {
-	const Row<T> P{rob.P, stride, r}, S{rob.S, stride, r};
+template <class T, int N, class S = T>
+__device__ void model_robot(const ChainC<T, N>& ch, const Arena<S>& rob, int64_t stride, int64_t r, int dynamics, int gravity) {
+	const Row<T, S> P{rob.P, stride, r}, Sr{rob.S, stride, r};
 	T q[N];
 	ld_vec<T, N>(P, RobotL<N>::Q, q);
 	Kin<T, N> kin;
 	forward_kinematics<T, N>(ch, q, kin);
 	OSC_UNROLL for (int i = 0; i < N; ++i) {
 		OSC_UNROLL for (int a = 0; a < 3; ++a) {
-			S(RobotL<N>::KO + 3 * i + a) = kin.o[i][a];
-			OSC_UNROLL for (int b = 0; b < 3; ++b) S(RobotL<N>::KR + 9 * i + 3 * a + b) = kin.R[i][a][b];
+			Sr(RobotL<N>::KO + 3 * i + a) = kin.o[i][a];
+			OSC_UNROLL for (int b = 0; b < 3; ++b) Sr(RobotL<N>::KR + 9 * i + 3 * a + b) = kin.R[i][a][b];
 		}
 	}
 	if (dynamics) {
 		T M[N][N], Minv[N][N];
 		mass_matrix<T, N>(ch, kin, M);
 		const bool ok = spd_inverse<T, N>(M, Minv);
-		st_mat<T, N, N>(S, RobotL<N>::M, M);
-		st_mat<T, N, N>(S, RobotL<N>::MINV, Minv);
+		st_mat<T, N, N>(Sr, RobotL<N>::M, M);
+		st_mat<T, N, N>(Sr, RobotL<N>::MINV, Minv);
 		if (!ok) rob.I[(int64_t)RobotL<N>::STATUS * stride + r] |= 16;  // OSC_STATUS_NOT_POSITIVE_DEFINITE
 	}
 	if (gravity) {
 		T g[N];
 		gravity_vector<T, N>(ch, kin, g);
-		st_vec<T, N>(S, RobotL<N>::GRAV, g);
+		st_vec<T, N>(Sr, RobotL<N>::GRAV, g);
 	}
 }
-template <class T, int N>
-__global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<T> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
+template <class T, int N, class S = T>
+__global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<S> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	model_robot<T, N>(ch, rob, stride, r, dynamics, gravity);
@@ -116,7 +139,8 @@ __global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ C
 
 // bounded-inertia-estimate inverse: M with every diagonal entry raised to >= threshold, inverted
 // (SingularityHandler.cpp:176-182, JointTask.cpp:254-260)
-template <class T, int N> OSC_DEV void bie_inverse(const Row<T>& robS, T thr, T (&W)[N][N]) {
+template <class T, int N, class S = T>
+OSC_DEV void bie_inverse(const Row<T, S>& robS, T thr, T (&W)[N][N]) {
 	T Mb[N][N];
 	ld_mat<T, N, N>(robS, RobotL<N>::M, Mb);
 	OSC_UNROLL for (int i = 0; i < N; ++i)

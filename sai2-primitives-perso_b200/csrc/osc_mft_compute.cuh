@@ -43,8 +43,8 @@ template <class T> OSC_DEV void sigma_complement(const T (&Psel)[3][3], const T 
 
 // POPCExplicitForceControl::computePassivitySaturatedForce; the std::queue is a ring of OSC_POPC_RING_CAPACITY slots
 // in HBM (quirk Q9).  Returns R_c * vcl - kv_f * vr.
-template <class T, int N>
-OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>& tI, int64_t stride, int64_t r, const T (&fd)[3], const T (&fs)[3],
+template <class T, int N, class S = T>
+OSC_DEV void popc_force(const MftC<T>& tc, const Row<T, S>& tP, const Row<int32_t>& tI, int64_t stride, int64_t r, const T (&fd)[3], const T (&fs)[3],
 						const T (&vcl)[3], const T (&vr)[3], T (&out)[3], int& status) {
 	using L = MftL<N>;
 	const T kv = tc.kv_force;
@@ -59,15 +59,15 @@ OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>&
 	const T vc2 = dot3(vcl, vcl);
 	const T p = (dot3(fdiff, vcl) - dot3(Fcmd, vr)) * tc.dt;
 	PO += p;
-	T* ring = tc.popc_ring;
+	S* const ring = static_cast<S*>(tc.popc_ring);  // the window lives in the batch storage type
 	if (len == 1024) {  // overflow: drop the oldest sample (status bit), Q9
 		head = (head + 1) & 1023; --len; status |= 2;
 	}
-	ring[(int64_t)((head + len) & 1023) * stride + r] = p;
+	ring[(int64_t)((head + len) & 1023) * stride + r] = (S)p;
 	++len;
 	if (PO + Ec > T(0)) {  // _stored_energy_PO is identically 0 (.cpp:13)
 		while (len > 250) {
-			const T front = ring[(int64_t)head * stride + r];
+			const T front = (T)ring[(int64_t)head * stride + r];
 			if (PO + Ec > front) {
 				if (front > T(0)) PO -= front;
 				head = (head + 1) & 1023; --len;
@@ -99,9 +99,9 @@ OSC_DEV void popc_force(const MftC<T>& tc, const Row<T>& tP, const Row<int32_t>&
 
 // One 3-dof half of the motion law (MotionForceTask.cpp:411-437 linear / 441-468 angular): integrates Sigma e, returns
 // Sigma (a_des - kp e - kv (v - v_des) - ki int) or its velocity-saturated variant; vd is the desired velocity (in/out).
-template <class T>
+template <class T, class S = T>
 OSC_DEV void motion_half(const T (&Sg)[3][3], const T (&err)[3], bool err_is_projected, const T (&vel)[3], T (&vd)[3], const T (&acc)[3],
-						 const T (&kp)[3], const T (&kv)[3], const T (&ki)[3], bool use_sat, T sat, T dt, const Row<T>& tP, int off_int, T (&out)[3]) {
+						 const T (&kp)[3], const T (&kv)[3], const T (&ki)[3], bool use_sat, T sat, T dt, const Row<T, S>& tP, int off_int, T (&out)[3]) {
 	T se[3], ip[3], raw[3];
 	mv3(Sg, err, se);
 	OSC_UNROLL for (int a = 0; a < 3; ++a) { ip[a] = tP(off_int + a) + se[a] * dt; tP(off_int + a) = ip[a]; }
@@ -128,8 +128,8 @@ OSC_DEV void motion_half(const T (&Sg)[3][3], const T (&err)[3], bool err_is_pro
 // The control law: returns F* (unit mass force) and F_f (force feedback + feed-forward); updates integrators and caches.
 // The linear half (force space + position) is finished before the angular half starts, so that only one pair of
 // selection matrices is live at a time.  FULL = the task controls all six directions (P = I).
-template <class T, int N, bool FULL = false>
-OSC_DEV void mft_control_law_vw(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
+template <class T, int N, bool FULL = false, class S = T>
+OSC_DEV void mft_control_law_vw(const MftC<T>& tc, const Row<T, S>& tP, const Row<T, S>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
 								const T (&v)[3], const T (&w)[3], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status,
 								bool export_vectors = true) {
 	using L = MftL<N>;
@@ -242,8 +242,8 @@ OSC_DEV void mft_control_law_vw(const MftC<T>& tc, const Row<T>& tP, const Row<T
 // The law for the plain motion task: no force / moment space (dimension 0), open loop, no velocity saturation, all six
 // directions controlled.  Then Sigma_force = Sigma_moment = 0, Sigma_position = Sigma_orientation = I and F_f = 0
 // (MotionForceTask.cpp:306-309, 352-353, 381-382, 427-467): F* = a_des - kp e - kv (v - v_des) - ki int e.
-template <class T, int N>
-OSC_DEV void mft_control_law_motion_only(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const T (&v)[3], const T (&w)[3], const T (&x)[3],
+template <class T, int N, class S = T>
+OSC_DEV void mft_control_law_motion_only(const MftC<T>& tc, const Row<T, S>& tP, const Row<T, S>& tS, const T (&v)[3], const T (&w)[3], const T (&x)[3],
 										 const T (&R)[3][3], T (&Fstar)[6], bool export_vectors) {
 	using L = MftL<N>;
 	// every load first (goals are read-only rows of this kernel, the integrators are read-modify-write), then the arithmetic,
@@ -281,8 +281,8 @@ OSC_DEV void mft_control_law_motion_only(const MftC<T>& tc, const Row<T>& tP, co
 }
 
 // same, from the task Jacobian: v = J[0:3] dq, w = J[3:6] dq (MotionForceTask.cpp:293-298)
-template <class T, int N>
-OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T>& tP, const Row<T>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
+template <class T, int N, class S = T>
+OSC_DEV void mft_control_law(const MftC<T>& tc, const Row<T, S>& tP, const Row<T, S>& tS, const Row<int32_t>& tI, int64_t stride, int64_t r,
 							 const T (&J)[6][N], const T (&dq)[N], const T (&x)[3], const T (&R)[3][3], T (&Fstar)[6], T (&Ff)[6], int& status,
 							 bool export_vectors = true) {
 	T v[3], w[3];

@@ -6,8 +6,8 @@
 namespace osc {
 
 // J_x^T (L_x U_x^T F* + U_x^T F_f) for a stored (U, J, Lambda_modified) triple
-template <class T, int N, int K>
-OSC_DEV void range_torque(const Row<T>& tS, int offU, int offJ, int offL, const T (&Fstar)[6], const T (&Ff)[6], bool use_lambda, T (&tau)[N]) {
+template <class T, int N, int K, class S = T>
+OSC_DEV void range_torque(const Row<T, S>& tS, int offU, int offJ, int offL, const T (&Fstar)[6], const T (&Ff)[6], bool use_lambda, T (&tau)[N]) {
 	T U[6][K], Jx[K][N];
 	ld_mat<T, 6, K>(tS, offU, U);
 	ld_mat<T, K, N>(tS, offJ, Jx);
@@ -25,12 +25,12 @@ OSC_DEV void range_torque(const Row<T>& tS, int offU, int offJ, int offL, const 
 	mtv<T, K, N>(Jx, f, tau);
 }
 
-template <class T, int N>
-__device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<T>& rob, const Arena<T>& tk, int64_t stride, int64_t r,
+template <class T, int N, class S = T>
+__device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<S>& rob, const Arena<S>& tk, int64_t stride, int64_t r,
 								  int with_tau_prec, int accumulate, int reuse_law = 0) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 
@@ -155,9 +155,9 @@ __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, con
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 }
 
-template <class T, int N>
+template <class T, int N, class S = T>
 __global__ void __launch_bounds__(OSC_THREADS) k_mft_compute(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-															  Arena<T> rob, Arena<T> tk, int64_t B, int64_t stride, int with_tau_prec, int accumulate) {
+															  Arena<S> rob, Arena<S> tk, int64_t B, int64_t stride, int with_tau_prec, int accumulate) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	mft_compute_robot<T, N>(ch, tc, rob, tk, stride, r, with_tau_prec, accumulate);

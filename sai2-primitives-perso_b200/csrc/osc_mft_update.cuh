@@ -22,12 +22,12 @@ OSC_DEV void task_jacobian(const ChainC<T, N>& ch, const MftC<T>& tc, const Kin<
 
 // One robot.  `no_history` re-evaluates the task model without pushing a classification sample (lazy materialisation
 // of the getters after a fused tick: the history was already advanced by the tick itself).
-template <class T, int N>
-__device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<T>& rob, const Arena<T>& tk, const T* nprec_src,
+template <class T, int N, class S = T>
+__device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<S>& rob, const Arena<S>& tk, const S* nprec_src,
 								 int64_t stride, int64_t r, int no_history) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 
@@ -39,7 +39,7 @@ __device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, cons
 	task_jacobian<T, N>(ch, tc, kin, x, J);
 	T Np[N][N];
 	if (nprec_src) {
-		const Row<T> src{const_cast<T*>(nprec_src), stride, r};
+		const Row<T, S> src{const_cast<S*>(nprec_src), stride, r};
 		ld_mat<T, N, N>(src, 0, Np);
 	} else {
 		OSC_UNROLL for (int i = 0; i < N; ++i)
@@ -236,6 +236,14 @@ __device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, cons
 		tI(L::NTYPES) = ntypes; tI(L::TYPES) = types;
 		// history ring of bits (1 = type 1), capacity OSC_MAX_SINGULARITY_BUFFER = 256
 		int len = tI(L::HIST_LEN), head = tI(L::HIST_HEAD);
+		// the deque of the reference pushes, then pops the front once it is longer than buffer_size (.cpp:276-294).  With
+		// buffer_size == 256 the slot of the new bit IS the front's: pop first (the outgoing bit is read before it is overwritten)
+		if (len >= tc.buffer_size) {
+			const int32_t w = tk.I[(int64_t)(L::HIST + (head >> 5)) * stride + r];
+			if ((w >> (head & 31)) & 1) --c1; else --c2;
+			head = (head + 1) & 255;
+			--len;
+		}
 		{
 			const int pos = (head + len) & 255;
 			int32_t& w = tk.I[(int64_t)(L::HIST + (pos >> 5)) * stride + r];
@@ -243,20 +251,14 @@ __device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, cons
 			++len;
 			if (any1) ++c1; else ++c2;
 		}
-		if (len > tc.buffer_size) {
-			const int32_t w = tk.I[(int64_t)(L::HIST + (head >> 5)) * stride + r];
-			if ((w >> (head & 31)) & 1) --c1; else --c2;
-			head = (head + 1) & 255;
-			--len;
-		}
 		tI(L::HIST_LEN) = len; tI(L::HIST_HEAD) = head; tI(L::C1) = c1; tI(L::C2) = c2;
 	}
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 }
 
-template <class T, int N>
+template <class T, int N, class S = T>
 __global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
-															 Arena<T> rob, Arena<T> tk, const T* nprec_src, int64_t B, int64_t stride, int no_history) {
+															 Arena<S> rob, Arena<S> tk, const S* nprec_src, int64_t B, int64_t stride, int no_history) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	mft_update_robot<T, N>(ch, tc, rob, tk, nprec_src, stride, r, no_history);

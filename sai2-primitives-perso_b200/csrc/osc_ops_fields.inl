@@ -116,7 +116,7 @@ template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l
 	switch (l.special) {
 		case 1:
 		case 2:
-			k_pack_ulut<T, 6, K><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, MftL<N>::U_NS, l.special == 1 ? MftL<N>::L_NS : MftL<N>::L_NS_MOD,
+			k_pack_ulut<C, 6, K, T><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, MftL<N>::U_NS, l.special == 1 ? MftL<N>::L_NS : MftL<N>::L_NS_MOD,
 																		 (T*)tmp, b.B, b.stride, 6);
 			return done(b, "k_pack_ulut");
 		case 3:
@@ -132,7 +132,7 @@ template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l
 		}
 		case 6:
 		case 7:
-			k_pack_ulut<T, N, N><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, JtL<N>::RANGE, l.special == 6 ? JtL<N>::LAM : JtL<N>::LAM_MOD,
+			k_pack_ulut<C, N, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, JtL<N>::RANGE, l.special == 6 ? JtL<N>::LAM : JtL<N>::LAM_MOD,
 																		 (T*)tmp, b.B, b.stride, t.dof);
 			return done(b, "k_pack_ulut");
 	}
@@ -184,7 +184,7 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			// over the SMs
 			const int bt = bt_env ? bt_env : (b.B >= 224 * 148 ? 224 : 64);
 			auto go = [&](auto kern, int threads) -> int {
-				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(T);
+				const size_t smem = (size_t)F2<N>::SLOTS * threads * sizeof(double);  // the stash is FP64 for both batch precisions
 				if (first_launch_on_device((const void*)kern, b.device)) {  // once per kernel and device, not per tick
 					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
 					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused2)");
@@ -223,7 +223,7 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			at[0].val.programmaticStreamSerializationAllowed = 1;
 			cfg.attrs = at;
 			cfg.numAttrs = pdl ? 1 : 0;
-			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<T, N>, ch, tc, jc, rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
+			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<C, N, T>, chc, mftcc(m), jtcc(b, j), rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
 											   (const int*)cnt, nxt, (const int*)list, reuse_law);
 			if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_tick_tail)");
 		}

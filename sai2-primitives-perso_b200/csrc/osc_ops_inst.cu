@@ -23,8 +23,12 @@ namespace osc {
 
 namespace {
 
+// T = the batch precision = the STORAGE type of every row.  The fused kernels compute in T (mixed with FP64 accumulation in
+// their factorisation chain); the API-faithful kernels compute in C = double whatever the batch precision (osc_kernels.cuh, Row).
 template <class T, int N> struct OpsImpl : Ops {
+	using C = double;
 	ChainC<T, N> ch;
+	ChainC<C, N> chc;
 
 	static dim3 grid(const Batch& b) { return dim3((unsigned)((b.B + OSC_THREADS - 1) / OSC_THREADS)); }
 	static Arena<T> rob(Batch& b) { return Arena<T>{(T*)b.P, (T*)b.S, b.I}; }
@@ -42,106 +46,113 @@ template <class T, int N> struct OpsImpl : Ops {
 		else { p = JtL<N>::P_SIZE; s = JtL<N>::S_SIZE; i = JtL<N>::I_SIZE; }
 	}
 
-	int set_chain(Batch& b) override {
-		const osc_chain_desc& c = b.chain;
+	template <class X> static void fill_chain(const osc_chain_desc& c, ChainC<X, N>& ch) {
 		for (int i = 0; i < N; ++i) {
 			for (int a = 0; a < 3; ++a) {
-				ch.xyz[i][a] = (T)c.joint_xyz[i][a];
-				ch.com[i][a] = (T)c.com[i][a];
-				for (int k = 0; k < 3; ++k) ch.rot[i][a][k] = (T)c.joint_rot[i][3 * a + k];
+				ch.xyz[i][a] = (X)c.joint_xyz[i][a];
+				ch.com[i][a] = (X)c.com[i][a];
+				for (int k = 0; k < 3; ++k) ch.rot[i][a][k] = (X)c.joint_rot[i][3 * a + k];
 			}
 			ch.prismatic[i] = c.joint_type[i] == OSC_JOINT_PRISMATIC;
-			ch.mass[i] = (T)c.mass[i];
+			ch.mass[i] = (X)c.mass[i];
 			const double* I = c.inertia[i];
-			ch.inertia[i][0] = (T)I[0]; ch.inertia[i][1] = (T)I[1]; ch.inertia[i][2] = (T)I[2];
-			ch.inertia[i][3] = (T)I[4]; ch.inertia[i][4] = (T)I[5]; ch.inertia[i][5] = (T)I[8];
-			ch.q_lower[i] = (T)c.q_lower[i]; ch.q_upper[i] = (T)c.q_upper[i]; ch.effort[i] = (T)c.effort[i];
+			ch.inertia[i][0] = (X)I[0]; ch.inertia[i][1] = (X)I[1]; ch.inertia[i][2] = (X)I[2];
+			ch.inertia[i][3] = (X)I[4]; ch.inertia[i][4] = (X)I[5]; ch.inertia[i][5] = (X)I[8];
+			ch.q_lower[i] = (X)c.q_lower[i]; ch.q_upper[i] = (X)c.q_upper[i]; ch.effort[i] = (X)c.effort[i];
 			const double m = c.mass[i], *cm = c.com[i];
 			const double cc = cm[0] * cm[0] + cm[1] * cm[1] + cm[2] * cm[2];
 			int e = 0;
 			for (int a = 0; a < 3; ++a) {
-				ch.hb[i][a] = (T)(m * cm[a]);
-				for (int k = a; k < 3; ++k) ch.Ib[i][e++] = (T)(I[3 * a + k] + m * ((a == k ? cc : 0.0) - cm[a] * cm[k]));
+				ch.hb[i][a] = (X)(m * cm[a]);
+				for (int k = a; k < 3; ++k) ch.Ib[i][e++] = (X)(I[3 * a + k] + m * ((a == k ? cc : 0.0) - cm[a] * cm[k]));
 			}
 		}
 		for (int a = 0; a < 3; ++a) {
-			ch.world_xyz[a] = (T)c.world_xyz[a]; ch.gravity[a] = (T)c.gravity[a];
-			for (int k = 0; k < 3; ++k) ch.world_rot[a][k] = (T)c.world_rot[3 * a + k];
+			ch.world_xyz[a] = (X)c.world_xyz[a]; ch.gravity[a] = (X)c.gravity[a];
+			for (int k = 0; k < 3; ++k) ch.world_rot[a][k] = (X)c.world_rot[3 * a + k];
 		}
+	}
+	int set_chain(Batch& b) override {
+		fill_chain<T>(b.chain, ch);
+		fill_chain<C>(b.chain, chc);
 		return OSC_OK;
 	}
 
-	MftC<T> mftc(const TaskH& t) {
-		MftC<T> c{};
+	MftC<T> mftc(const TaskH& t) { return mftc_<T>(t); }
+	MftC<C> mftcc(const TaskH& t) { return mftc_<C>(t); }
+	JtC<T, N> jtc(const Batch& b, const TaskH& t) { return jtc_<T>(b, t); }
+	JtC<C, N> jtcc(const Batch& b, const TaskH& t) { return jtc_<C>(b, t); }
+	template <class X> static MftC<X> mftc_(const TaskH& t) {
+		MftC<X> c{};
 		const osc_mft_params& p = t.mp;
 		c.body = t.md.body; c.partial = t.md.partial; c.rank = t.dof; c.in_compliant_frame = t.md.parametrization_in_compliant_frame;
 		for (int a = 0; a < 3; ++a) {
-			c.p_c[a] = (T)t.frame_p[a];
-			for (int k = 0; k < 3; ++k) { c.R_c[a][k] = (T)t.frame_R[a][k]; c.Pt[a][k] = (T)t.P6[a][k]; c.Pr[a][k] = (T)t.P6[3 + a][3 + k]; }
-			c.kp_pos[a] = (T)p.kp_pos[a]; c.kv_pos[a] = (T)p.kv_pos[a]; c.ki_pos[a] = (T)p.ki_pos[a];
-			c.kp_ori[a] = (T)p.kp_ori[a]; c.kv_ori[a] = (T)p.kv_ori[a]; c.ki_ori[a] = (T)p.ki_ori[a];
-			c.force_axis[a] = (T)p.force_or_motion_axis[a]; c.moment_axis[a] = (T)p.moment_or_rotmotion_axis[a];
-			c.sensor_p[a] = (T)p.sensor_xyz[a];
-			for (int k = 0; k < 3; ++k) c.sensor_R[a][k] = (T)p.sensor_rot[3 * a + k];
+			c.p_c[a] = (X)t.frame_p[a];
+			for (int k = 0; k < 3; ++k) { c.R_c[a][k] = (X)t.frame_R[a][k]; c.Pt[a][k] = (X)t.P6[a][k]; c.Pr[a][k] = (X)t.P6[3 + a][3 + k]; }
+			c.kp_pos[a] = (X)p.kp_pos[a]; c.kv_pos[a] = (X)p.kv_pos[a]; c.ki_pos[a] = (X)p.ki_pos[a];
+			c.kp_ori[a] = (X)p.kp_ori[a]; c.kv_ori[a] = (X)p.kv_ori[a]; c.ki_ori[a] = (X)p.ki_ori[a];
+			c.force_axis[a] = (X)p.force_or_motion_axis[a]; c.moment_axis[a] = (X)p.moment_or_rotmotion_axis[a];
+			c.sensor_p[a] = (X)p.sensor_xyz[a];
+			for (int k = 0; k < 3; ++k) c.sensor_R[a][k] = (X)p.sensor_rot[3 * a + k];
 		}
-		c.dt = (T)t.md.loop_timestep;
-		c.kp_force = (T)p.kp_force; c.kv_force = (T)p.kv_force; c.ki_force = (T)p.ki_force;
-		c.kp_moment = (T)p.kp_moment; c.kv_moment = (T)p.kv_moment; c.ki_moment = (T)p.ki_moment;
-		c.kff_force = (T)p.kff_force; c.kff_moment = (T)p.kff_moment;
-		c.max_force_fb = (T)p.max_force_control_feedback_output; c.max_moment_fb = (T)p.max_moment_control_feedback_output;
+		c.dt = (X)t.md.loop_timestep;
+		c.kp_force = (X)p.kp_force; c.kv_force = (X)p.kv_force; c.ki_force = (X)p.ki_force;
+		c.kp_moment = (X)p.kp_moment; c.kv_moment = (X)p.kv_moment; c.ki_moment = (X)p.ki_moment;
+		c.kff_force = (X)p.kff_force; c.kff_moment = (X)p.kff_moment;
+		c.max_force_fb = (X)p.max_force_control_feedback_output; c.max_moment_fb = (X)p.max_moment_control_feedback_output;
 		c.force_dim = p.force_space_dimension; c.moment_dim = p.moment_space_dimension;
 		c.closed_loop_force = p.closed_loop_force_control; c.closed_loop_moment = p.closed_loop_moment_control;
 		c.passivity = p.passivity_enabled; c.use_vel_sat = p.use_velocity_saturation;
-		c.lin_sat = (T)p.linear_saturation_velocity; c.ang_sat = (T)p.angular_saturation_velocity;
-		c.decoupling = p.dynamic_decoupling_type; c.bie_threshold = (T)p.bie_threshold;
+		c.lin_sat = (X)p.linear_saturation_velocity; c.ang_sat = (X)p.angular_saturation_velocity;
+		c.decoupling = p.dynamic_decoupling_type; c.bie_threshold = (X)p.bie_threshold;
 		c.handling = p.singularity_handling_enabled; c.enforce_type_1 = p.enforce_type_1_strategy;
-		c.s_min = (T)p.s_min; c.s_max = (T)p.s_max; c.kp1 = (T)p.kp_type_1; c.kv1 = (T)p.kv_type_1; c.kv2 = (T)p.kv_type_2;
-		c.s_abs_tol = (T)p.s_abs_tol; c.type_1_tol = (T)p.type_1_tol; c.type_2_torque_ratio = (T)p.type_2_torque_ratio;
-		c.type_2_angle_threshold = (T)p.type_2_angle_threshold; c.perturb_step = (T)p.perturb_step_size;
+		c.s_min = (X)p.s_min; c.s_max = (X)p.s_max; c.kp1 = (X)p.kp_type_1; c.kv1 = (X)p.kv_type_1; c.kv2 = (X)p.kv_type_2;
+		c.s_abs_tol = (X)p.s_abs_tol; c.type_1_tol = (X)p.type_1_tol; c.type_2_torque_ratio = (X)p.type_2_torque_ratio;
+		c.type_2_angle_threshold = (X)p.type_2_angle_threshold; c.perturb_step = (X)p.perturb_step_size;
 		c.buffer_size = p.buffer_size;
 		c.apply_compensation = p.apply_disturbance_compensation;
-		c.popc_ring = (T*)t.popc_ring;
+		c.popc_ring = t.popc_ring;
 		return c;
 	}
-	JtC<T, N> jtc(const Batch& b, const TaskH& t) {
-		JtC<T, N> c{};
-		c.k = t.dof; c.full = t.jd.full; c.dt = (T)t.jd.loop_timestep;
+	template <class X> static JtC<X, N> jtc_(const Batch& b, const TaskH& t) {
+		JtC<X, N> c{};
+		c.k = t.dof; c.full = t.jd.full; c.dt = (X)t.jd.loop_timestep;
 		for (int i = 0; i < N; ++i)
 			for (int j = 0; j < N; ++j)
-				c.S[i][j] = t.jd.full ? (T)(i == j) : (i < t.dof ? (T)t.jd.selection[i * b.n + j] : (T)0);
+				c.S[i][j] = t.jd.full ? (X)(i == j) : (i < t.dof ? (X)t.jd.selection[i * b.n + j] : (X)0);
 		for (int i = 0; i < N; ++i) {
-			c.kp[i] = (T)t.jp.kp[i]; c.kv[i] = (T)t.jp.kv[i]; c.ki[i] = (T)t.jp.ki[i]; c.sat[i] = (T)t.jp.saturation_velocity[i];
+			c.kp[i] = (X)t.jp.kp[i]; c.kv[i] = (X)t.jp.kv[i]; c.ki[i] = (X)t.jp.ki[i]; c.sat[i] = (X)t.jp.saturation_velocity[i];
 		}
-		c.use_vel_sat = t.jp.use_velocity_saturation; c.decoupling = t.jp.dynamic_decoupling_type; c.bie_threshold = (T)t.jp.bie_threshold;
+		c.use_vel_sat = t.jp.use_velocity_saturation; c.decoupling = t.jp.dynamic_decoupling_type; c.bie_threshold = (X)t.jp.bie_threshold;
 		return c;
 	}
 
 	int model(Batch& b, int dynamics) override {
-		k_model<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride, dynamics, b.gravity ? 1 : 0);
+		k_model<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(chc, rob(b), b.B, b.stride, dynamics, b.gravity ? 1 : 0);
 		return done(b, "k_model");
 	}
 	int task_init(Batch& b, int t) override {
 		TaskH& th = b.tasks[t];
 		if (th.type == OSC_TASK_MOTION_FORCE) {
-			k_mft_init<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, tk(th), b.B, b.stride);
+			k_mft_init<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(chc, tk(th), b.B, b.stride);
 			if (int rc = done(b, "k_mft_init")) return rc;
-			k_mft_reinit<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftc(th), rob(b), tk(th), b.B, b.stride);
+			k_mft_reinit<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftcc(th), rob(b), tk(th), b.B, b.stride);
 			return done(b, "k_mft_reinit");
 		}
-		k_jt_reinit<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtc(b, th), rob(b), tk(th), b.B, b.stride, 1);
+		k_jt_reinit<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtcc(b, th), rob(b), tk(th), b.B, b.stride, 1);
 		return done(b, "k_jt_reinit");
 	}
 	int task_reinit(Batch& b, int t) override {
 		TaskH& th = b.tasks[t];
 		if (th.type == OSC_TASK_MOTION_FORCE) {
-			k_mft_reinit<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftc(th), rob(b), tk(th), b.B, b.stride);
+			k_mft_reinit<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftcc(th), rob(b), tk(th), b.B, b.stride);
 			return done(b, "k_mft_reinit");
 		}
-		k_jt_reinit<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtc(b, th), rob(b), tk(th), b.B, b.stride, 0);
+		k_jt_reinit<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtcc(b, th), rob(b), tk(th), b.B, b.stride, 0);
 		return done(b, "k_jt_reinit");
 	}
 	int mft_reset(Batch& b, int t, int flags) override {
-		k_mft_reset<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(tk(b.tasks[t]), b.B, b.stride, flags);
+		k_mft_reset<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(tk(b.tasks[t]), b.B, b.stride, flags);
 		return done(b, "k_mft_reset");
 	}
 	const T* nprec_ptr(Batch& b, int src) {
@@ -153,28 +164,28 @@ template <class T, int N> struct OpsImpl : Ops {
 	int task_update(Batch& b, int t, int src, int no_history) override {
 		TaskH& th = b.tasks[t];
 		if (th.type == OSC_TASK_MOTION_FORCE) {
-			k_mft_update<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, mftc(th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride, no_history);
+			k_mft_update<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(chc, mftcc(th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride, no_history);
 			return done(b, "k_mft_update");
 		}
-		k_jt_update<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtc(b, th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride);
+		k_jt_update<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtcc(b, th), rob(b), tk(th), nprec_ptr(b, src), b.B, b.stride);
 		return done(b, "k_jt_update");
 	}
 	int task_compute(Batch& b, int t, int with_tau_prec, int accumulate) override {
 		TaskH& th = b.tasks[t];
 		if (th.type == OSC_TASK_MOTION_FORCE) {
-			k_mft_compute<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, mftc(th), rob(b), tk(th), b.B, b.stride, with_tau_prec, accumulate);
+			k_mft_compute<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(chc, mftcc(th), rob(b), tk(th), b.B, b.stride, with_tau_prec, accumulate);
 			return done(b, "k_mft_compute");
 		}
-		k_jt_compute<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtc(b, th), rob(b), tk(th), b.B, b.stride, with_tau_prec, accumulate);
+		k_jt_compute<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(jtcc(b, th), rob(b), tk(th), b.B, b.stride, with_tau_prec, accumulate);
 		return done(b, "k_jt_compute");
 	}
 	int add_gravity(Batch& b) override {
-		k_add_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(rob(b), b.B, b.stride);
+		k_add_gravity<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(rob(b), b.B, b.stride);
 		return done(b, "k_add_gravity");
 	}
 	int update_sensed(Batch& b, int t, const void* tmp6) override {
 		TaskH& th = b.tasks[t];
-		k_mft_sensed<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride);
+		k_mft_sensed<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftcc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride);
 		return done(b, "k_mft_sensed");
 	}
 

@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 import osc_abi as abi
-from common import FP32_TOL, FP64_TOL, Pair, load_chain, random_q, rel_err
+from common import FP32_TOL, FP64_TOL, Pair, load_chain, random_q, rel_err, task_kappa
 
 pytestmark = pytest.mark.gpu
 
@@ -145,10 +145,15 @@ def test_fused_puma_six_dof(oracle_built, decoupling):
         assert blend <= fb <= blend + 512 // 20
     else:
         assert blend <= fb <= 512
-    # nullspace projectors of blend-branch robots: N = I - Jbar J cancels to O(eps |Jbar| |J|); |Jbar| reaches 1e7 for the
-    # near-singular PUMA draws, so their absolute accuracy is 1e-8, not 1e-9 (same for the oracle vs LAPACK)
-    nfields = {abi.F_N_TOTAL: 1e-6, abi.F_N_TASK: 1e-6, abi.F_N_TASK_AND_PREC: 1e-6, abi.F_N_PREC: 1e-6}
-    p.compare(FP64_TOL, loose=nfields)
+    # nullspace projectors: N = I - Jbar J is a cancellation (for this 6-DoF robot the exact N is 0 outside the blend: what the
+    # getter returns is rounding noise in EVERY implementation, the oracle included).  Measured oracle-vs-LAPACK
+    # (tools/scratch, r2): the noise is 0.2-0.6 eps kappa(M) outside the blend (kappa(M) ~ 5e4 for the PUMA's light wrist) and
+    # grows with the conditioning of the inverted projected inertias inside it.  Per-robot bound:
+    # max(1e-9, 64 eps kappa_task sqrt(kappa(M))), instead of the flat 1e-6 of round 1.
+    kM = np.linalg.cond(p.ref.get(abi.F_M).reshape(512, 6, 6))
+    nb = np.maximum(FP64_TOL, 64 * 2.2e-16 * task_kappa(p.ref, 0) * np.sqrt(kM))
+    assert np.median(nb) <= 1e-6
+    p.compare(FP64_TOL, loose={abi.F_N_TOTAL: nb, abi.F_N_TASK: nb, abi.F_N_TASK_AND_PREC: nb, abi.F_N_PREC: nb})
 
 
 def test_outputs_modes_agree(oracle_built):
@@ -177,8 +182,9 @@ def test_fused_fp32(oracle_built):
     well = sv[:, 5] / sv[:, 0] > 0.09
     assert well.sum() > 30
     err = np.abs(tg - tr).max(axis=1) / np.maximum(np.abs(tr).max(axis=1), 1e-2)
-    assert np.median(err[well]) < FP32_TOL, np.median(err[well])
-    assert err[well].max() < 50 * FP32_TOL, err[well].max()
+    assert err[well].max() <= FP32_TOL, err[well].max()                 # north star: 1e-4 in FP32, on the MAX
+    alpha = p.ref.get(abi.F_ALPHA, 0)[:, 0]
+    assert err[alpha == 1].max() <= FP32_TOL, err[alpha == 1].max()      # every robot outside the blend, certified or not
 
 
 def test_small_then_large_batch_in_one_process(oracle_built):

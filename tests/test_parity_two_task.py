@@ -61,4 +61,5 @@ def test_panda_two_task_fp32(oracle_built):
     well = (alpha == 1) & (sv[:, 5] / sv[:, 0] > 0.1)
     assert well.sum() > 20
     err = np.abs(tg - tr).max(axis=1) / np.maximum(np.abs(tr).max(axis=1), 1e-2)
-    assert err[well].max() < FP32_TOL * 50, err[well].max()
+    assert err[well].max() <= FP32_TOL, err[well].max()   # north star: 1e-4 in FP32, asserted on the max
+    assert err[alpha == 1].max() <= FP32_TOL, err[alpha == 1].max()

@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 import osc_abi as abi
-from common import FP32_TOL, FP64_TOL, Pair, load_chain, q0_of
+from common import FP32_TOL, FP64_TOL, Pair, load_chain, q0_of, task_kappa
 
 pytestmark = pytest.mark.gpu
 EPS = (5e-1, 1e-1, 1e-2, 1e-3, 1e-4)  # BASELINE config 4 names the last four; 0.5 is the control group outside the singular set
@@ -61,7 +61,7 @@ def _run(chain_name, q, precision, ticks, vel_sat, gains, rng_seed):
     x = p.ref.get(abi.F_CURRENT_POSITION, t0)
     p.set(abi.F_GOAL_POSITION, x + rng.normal(0, 0.05, (B, 3)), t0)
     amp = rng.normal(0, 0.02, (B, n))
-    errs, alphas = [], []
+    errs, alphas, kappas = [], [], []
     for tick in range(ticks):
         qt = q + amp * np.sin(2 * np.pi * 0.5 * tick * 0.001)  # sweeps in and out of the singular region
         dqt = amp * 2 * np.pi * 0.5 * np.cos(2 * np.pi * 0.5 * tick * 0.001)
@@ -69,26 +69,33 @@ def _run(chain_name, q, precision, ticks, vel_sat, gains, rng_seed):
         tg, tr = p.both("tick", t1 is not None)
         errs.append(_tau_err(tg, tr))
         alphas.append(p.ref.get(abi.F_ALPHA, t0)[:, 0].copy())
-    return p, t0, np.array(errs), np.array(alphas)
+        kappas.append(task_kappa(p.ref, t0))
+    return p, t0, np.array(errs), np.array(alphas), np.array(kappas)
 
 
 @pytest.mark.parametrize("case", ["panda", "puma"])
 def test_singular_fp64_parity_300_ticks(oracle_built, case):
     rng = np.random.default_rng(4)
     if case == "panda":
-        p, t0, errs, alphas = _run("panda", _panda_q(rng), abi.PRECISION_F64, 300, True, None, 41)
+        p, t0, errs, alphas, kappas = _run("panda", _panda_q(rng), abi.PRECISION_F64, 300, True, None, 41)
     else:
-        p, t0, errs, alphas = _run("puma560_synthetic", _puma_q(rng), abi.PRECISION_F64, 300, False, (50.0, 20.0, 20.0), 42)
-    assert (alphas < 1).any() and (alphas == 0).any() or (alphas < 1).any(), "the batch never entered the singular branch"
+        p, t0, errs, alphas, kappas = _run("puma560_synthetic", _puma_q(rng), abi.PRECISION_F64, 300, False, (50.0, 20.0, 20.0), 42)
+    assert ((alphas > 0) & (alphas < 1)).any(), "no robot-tick inside the blend band (0 < alpha < 1)"
+    assert (alphas == 0).any(), "no robot-tick with alpha = 0 (singular directions fully handed to the joint strategy)"
     # discrete state must agree exactly: branch (ns rank), singularity types and counters after the 300-tick history
     for fld in (abi.F_NS_RANK, abi.F_SINGULARITY_TYPES, abi.F_SINGULARITY_COUNTERS):
         assert np.array_equal(np.asarray(p.gpu.get(fld, t0), np.int64), np.asarray(np.rint(p.ref.get(fld, t0)), np.int64)), fld
-    # torques: 1e-9 in the non-singular branch; inside the blend the projected inertia J_s M^-1 J_s^T is inverted at
-    # condition numbers up to 1e7 and both implementations are only accurate to eps * cond (same bound as tests/test_golden.py)
+    # torques: 1e-9 wherever the conditioning allows it.  Inside the blend the handler inverts J_s M^-1 J_s^T at condition
+    # numbers up to 1e7 (SingularityHandler.cpp:117-120); the oracle and the product are then both accurate to c eps kappa
+    # and no better, so the bound is per robot-tick: max(1e-9, 64 eps kappa), kappa rebuilt with LAPACK from the oracle.
     clean = alphas == 1
-    if clean.any():
+    if clean.any():  # (every robot of the Panda set sits in the blend: its q4 is on the elbow-extended limit)
         assert errs[clean].max() <= FP64_TOL, errs[clean].max()
-    assert errs.max() <= 1e-6, errs.max()
+    bound = np.maximum(FP64_TOL, 64 * 2.2e-16 * kappas)
+    worst = (errs / bound).max()
+    assert worst <= 1.0, "torque error above max(1e-9, 64 eps kappa): ratio %.2f (err %.2e, kappa %.2e)" % (
+        worst, errs.ravel()[(errs / bound).argmax()], kappas.ravel()[(errs / bound).argmax()])
+    assert (errs[kappas < 1e5] <= FP64_TOL).all(), "1e-9 must hold up to kappa = 1e5"
     assert np.abs(p.gpu.get(abi.F_ALPHA, t0) - p.ref.get(abi.F_ALPHA, t0)).max() <= 1e-9
     assert np.abs(p.gpu.get(abi.F_Q_PRIOR, t0) - p.ref.get(abi.F_Q_PRIOR, t0)).max() <= 1e-12
 
@@ -97,9 +104,9 @@ def test_singular_fp64_parity_300_ticks(oracle_built, case):
 def test_singular_fp32_error_study(oracle_built, case, capsys):
     rng = np.random.default_rng(4)
     if case == "panda":
-        p, t0, errs, alphas = _run("panda", _panda_q(rng), abi.PRECISION_F32, 300, True, None, 41)
+        p, t0, errs, alphas, kappas = _run("panda", _panda_q(rng), abi.PRECISION_F32, 300, True, None, 41)
     else:
-        p, t0, errs, alphas = _run("puma560_synthetic", _puma_q(rng), abi.PRECISION_F32, 300, False, (50.0, 20.0, 20.0), 42)
+        p, t0, errs, alphas, kappas = _run("puma560_synthetic", _puma_q(rng), abi.PRECISION_F32, 300, False, (50.0, 20.0, 20.0), 42)
     rows = []
     for k, eps in enumerate(EPS):
         e = errs[:, k * PER:(k + 1) * PER].ravel()
@@ -112,6 +119,18 @@ def test_singular_fp32_error_study(oracle_built, case, capsys):
         for r in rows:
             print("  %-7g  %.2e  %.2e  %.2e  %.2e  %.2f" % r)
     assert np.isfinite(errs).all()
+    # north star: 1e-4 in FP32.  An FP32 batch stores q, dq, goals in FP32 (relative input rounding 6e-8) and computes its
+    # factorisation chain / task models in FP64 (csrc/osc_fused2.cuh, csrc/osc_kernels.cuh Row<T, S>), so what is left is the
+    # amplification of the INPUT rounding by the conditioning of the inverted projected inertias: asserted as
+    # max(1e-4, 64 eps_f32 kappa) per robot-tick, i.e. a flat 1e-4 for every robot-tick with kappa <= 26.
     clean = alphas == 1
-    if clean.any():  # away from the singular set FP32 holds the 1e-4 bound up to the conditioning of Lambda (kappa <~ 50 here)
-        assert np.percentile(errs[clean], 50) <= FP32_TOL * 50, np.percentile(errs[clean], 50)
+    if clean.any():
+        assert errs[clean].max() <= FP32_TOL, errs[clean].max()
+    bound = np.maximum(FP32_TOL, 64 * 6e-8 * kappas)
+    flips = (errs > bound).mean()
+    with capsys.disabled():
+        print("  max over all robot-ticks %.2e (outside the blend: %s); share above max(1e-4, 64 eps32 kappa): %.4f; share with kappa <= 26: %.2f" % (
+            errs.max(), "%.2e" % errs[clean].max() if clean.any() else "none", flips, (kappas <= 26).mean()))
+    # a robot-tick may still differ when the FP32-rounded q puts it on the other side of a discrete decision (type-1 vs type-2
+    # vote, joint-limit direction latch): rare by construction
+    assert flips <= 0.01, flips

@@ -1,0 +1,577 @@
+"""Code-independent pins for the control-law CONVENTIONS: tests/golden/pins_*.npz.
+
+The reference has no golden vectors and cannot be built here; the two oracles (oracle/osc_oracle.hpp,
+oracle/np_oracle.py) were written from the same reading of it.  This generator shares NO code and no algorithm with
+either of them (and none with the CUDA kernels):
+
+* the robot model comes from ANALYTICAL MECHANICS, not from recursions: M(q) is the Hessian of the kinetic energy
+  T = sum_b 1/2 m |d c_b/dt|^2 + 1/2 w_b^T (R_b I_b R_b^T) w_b in the joint velocities, J(q) is the derivative of the
+  forward kinematics map (position: dx/dq; orientation: vee(dR/dq R^T)).  For the planar 4R `rrrrbot` both are derived in
+  closed form with sympy (Lagrange); for any serial chain (the Panda) the derivatives are central differences evaluated in
+  50-digit mpmath arithmetic (step 1e-20: truncation and rounding errors below 1e-28);
+* every matrix inverse is a 50-digit mpmath LU solve; Lambda, Jbar, N, the bounded-inertia variants and the range basis of
+  the joint task follow the DEFINITIONS (Lambda = (J M^-1 J^T)^-1, Jbar = M^-1 J^T Lambda,
+  N = I - Jbar J), not an SVD route;
+* the control law is typed in from the reference text (MotionForceTask.cpp:278-509, JointTask.cpp:285-356,
+  RobotController.cpp:53-74, POPCExplicitForceControl.cpp:30-96), with hand-derived closed forms for the pieces that have
+  one: orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a (proved symbolically below), the selection projectors
+  a a^T / I - a a^T, the velocity-saturation clamp.
+
+Outputs are float64 roundings of 50-digit results.  tests/test_pins.py replays the inputs on the C++ oracle, the numpy
+oracle (CPU) and the CUDA path (GPU) and compares at 1e-9.  Run in the build container:  python tools/make_sympy_golden.py
+"""
+import json
+import os
+import sys
+from collections import deque
+
+import mpmath as mp
+import numpy as np
+import sympy as sp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "tests", "golden")
+mp.mp.dps = 50
+H = mp.mpf(10) ** -20
+
+
+def chain(name):
+    return json.load(open(os.path.join(ROOT, "fixtures", name + ".chain.json")))
+
+
+def M3(a):
+    return mp.matrix([[mp.mpf(float(x)) for x in row] for row in a])
+
+
+def V3(a):
+    return mp.matrix([mp.mpf(float(x)) for x in a])
+
+
+def rot(axis, ang):
+    """Rodrigues in mpmath"""
+    a = V3(axis); a = a / mp.norm(a)
+    K = mp.matrix([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+    return mp.eye(3) + mp.sin(ang) * K + (1 - mp.cos(ang)) * (K * K)
+
+
+def vee(S):
+    return mp.matrix([(S[2, 1] - S[1, 2]) / 2, (S[0, 2] - S[2, 0]) / 2, (S[1, 0] - S[0, 1]) / 2])
+
+
+class MpChain:
+    """forward kinematics of a serial chain in mpmath; everything else is derived from it by differentiation"""
+
+    def __init__(self, c):
+        self.c, self.n = c, c["n"]
+
+    def fk(self, q):
+        """world pose (R, p) of every body frame"""
+        R, p = M3(self.c["world_rot"]), V3(self.c["world_xyz"])
+        out = []
+        for i, j in enumerate(self.c["joints"]):
+            p = p + R * V3(j["xyz"])
+            R = R * M3(j["rot"])
+            if j["type"] == "prismatic":
+                p = p + R * V3(j["axis"]) * q[i]
+            else:
+                R = R * rot(j["axis"], q[i])
+            out.append((R, p))
+        return out
+
+    def dfk(self, q):
+        """d/dq_i of every body pose: central differences, step 1e-20 at 50 digits"""
+        d = []
+        for i in range(self.n):
+            qp, qm = list(q), list(q)
+            qp[i] = q[i] + H; qm[i] = q[i] - H
+            fp, fm = self.fk(qp), self.fk(qm)
+            d.append([((a[0] - b[0]) / (2 * H), (a[1] - b[1]) / (2 * H)) for a, b in zip(fp, fm)])
+        return d  # d[i][b] = (dR_b/dq_i, dp_b/dq_i)
+
+    def mass_matrix(self, q):
+        """Hessian of the kinetic energy in dq (Lagrange), body by body"""
+        n, f, d = self.n, self.fk(q), self.dfk(q)
+        M = mp.zeros(n, n)
+        for b, body in enumerate(self.c["bodies"]):
+            Rb = f[b][0]
+            m, com, I = mp.mpf(body["mass"]), V3(body["com"]), M3(body["inertia"])
+            Iw = Rb * I * Rb.T
+            dc = [d[i][b][1] + d[i][b][0] * com for i in range(n)]          # d c_b / d q_i
+            w = [vee(d[i][b][0] * Rb.T) for i in range(n)]                  # angular velocity per unit dq_i
+            for i in range(n):
+                for j in range(n):
+                    M[i, j] += m * (dc[i].T * dc[j])[0] + (w[i].T * Iw * w[j])[0]
+        return M
+
+    def point(self, q, link, p_in_link, R_in_link=None):
+        """world pose of the compliant frame and its 6 x n Jacobian (linear rows first) by differentiation"""
+        L = self.c["links"][link]
+        b = L["body"]
+        pl = V3(L["xyz"]) + M3(L["rot"]) * V3(p_in_link)
+        Rl = M3(L["rot"]) * (mp.eye(3) if R_in_link is None else M3(R_in_link))
+        f, d = self.fk(q), self.dfk(q)
+        x, R = f[b][1] + f[b][0] * pl, f[b][0] * Rl
+        J = mp.zeros(6, self.n)
+        for i in range(self.n):
+            dx = d[i][b][1] + d[i][b][0] * pl
+            w = vee(d[i][b][0] * f[b][0].T)
+            for a in range(3):
+                J[a, i], J[3 + a, i] = dx[a], w[a]
+        return x, R, J
+
+
+def inv(A):
+    return mp.inverse(A)  # LU with partial pivoting at 50 digits
+
+
+def osm(J, Minv):
+    """operationalSpaceMatrices by definition"""
+    Lam = inv(J * Minv * J.T)
+    Jbar = Minv * J.T * Lam
+    return Lam, Jbar, mp.eye(J.cols) - Jbar * J
+
+
+def bie(M, thr=mp.mpf("0.1")):
+    Mb = M.copy()
+    for i in range(M.rows):
+        if Mb[i, i] < thr:
+            Mb[i, i] = thr
+    return Mb
+
+
+def orientation_error(Rd, R):
+    """Sai2Model::orientationError: -1/2 sum_i R[:,i] x Rd[:,i]"""
+    e = mp.matrix([0, 0, 0])
+    for i in range(3):
+        a, b = R[:, i], Rd[:, i]
+        e += mp.matrix([a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]])
+    return -e / 2
+
+
+def f64(A):
+    if isinstance(A, mp.matrix):
+        return np.array([[float(A[i, j]) for j in range(A.cols)] for i in range(A.rows)]).squeeze()
+    return np.array(A, dtype=np.float64)
+
+
+def diag3(v):
+    return mp.diag([mp.mpf(float(x)) for x in np.broadcast_to(np.asarray(v, float), (3,))])
+
+
+def sigma(dim, axis, Rot, Psel):
+    """MotionForceTask::sigmaForce / sigmaMoment (.cpp:892-971) -- closed forms: 0, a a^T, I - a a^T, I (in the rotated frame)"""
+    if dim == 0:
+        return mp.zeros(3, 3)
+    if dim == 3:
+        return Psel * Psel.T
+    a = Rot * V3(axis)
+    aa = a * a.T
+    return Psel * (aa if dim == 1 else mp.eye(3) - aa) * Psel.T
+
+
+class MftSpec:
+    """plain data: the MotionForceTask parameters the law below reads (defaults MotionForceTask.h:40-75)"""
+
+    def __init__(self, **kw):
+        self.kp_pos, self.kv_pos, self.ki_pos = 100.0, 20.0, 0.0
+        self.kp_ori, self.kv_ori, self.ki_ori = 200.0, 28.3, 0.0
+        self.kp_f, self.kv_f, self.ki_f = 0.7, 10.0, 1.3
+        self.kp_m, self.kv_m, self.ki_m = 0.7, 10.0, 1.3
+        self.kff_f, self.kff_m, self.max_f, self.max_m = 0.95, 0.95, 20.0, 10.0
+        self.force_dim, self.force_axis, self.moment_dim, self.moment_axis = 0, (0, 0, 1), 0, (0, 0, 1)
+        self.closed_force, self.closed_moment, self.passivity = False, False, False
+        self.vel_sat, self.lin_sat, self.ang_sat = False, 0.3, float(mp.pi / 3)
+        self.in_compliant_frame = False
+        self.Pt, self.Pr = mp.eye(3), mp.eye(3)
+        self.dt = 0.001
+        self.__dict__.update(kw)
+
+
+class Popc:
+    """POPCExplicitForceControl.cpp:10-96 typed in from the reference text, mpmath arithmetic, collections.deque window"""
+
+    def __init__(self, dt):
+        self.dt, self.PO, self.Ecorr, self.Estored, self.win, self.counter, self.Rc, self.vsq = mp.mpf(dt), mp.mpf(0), mp.mpf(0), mp.mpf(0), deque(), 50, mp.mpf(1), mp.mpf(0)
+
+    def __call__(self, fd, fs, vcl, vr, kv, kff, enabled):
+        if not enabled:
+            return vcl - kv * vr
+        Fcmd = kff * fd + self.Rc * vcl - kv * vr
+        p = (((fs - fd).T * vcl)[0] - (Fcmd.T * vr)[0]) * self.dt
+        self.PO += p
+        self.win.append(p)
+        if self.PO + self.Estored + self.Ecorr > 0:
+            while len(self.win) > 250:
+                if self.PO + self.Ecorr + self.Estored > self.win[0]:
+                    if self.win[0] > 0:
+                        self.PO -= self.win[0]
+                    self.win.popleft()
+                else:
+                    break
+        if self.counter <= 0:
+            self.counter = 50
+            old = self.Rc
+            if self.PO + self.Estored + self.Ecorr < 0:
+                self.Rc = min(mp.mpf(1), max(mp.mpf(0), 1 + (self.PO + self.Estored + self.Ecorr) / (self.vsq * self.dt)))
+            else:
+                self.Rc = (1 + (mp.mpf("0.1") * 50 - 1) * self.Rc) / (mp.mpf("0.1") * 50)
+            self.Ecorr += (1 - old) * self.vsq * self.dt
+            self.vsq = mp.mpf(0)
+        self.counter -= 1
+        self.vsq += (vcl.T * vcl)[0]
+        return self.Rc * vcl - kv * vr
+
+
+def mft_law(s, st, x, R, v, w, goal, sensed_f=None, sensed_m=None):
+    """MotionForceTask.cpp:306-500: returns F* (6) and F_f = force/moment feedback + feed-forward (6); st = integrators + popc"""
+    Rot = R if s.in_compliant_frame else mp.eye(3)
+    Sf, Sm = sigma(s.force_dim, s.force_axis, Rot, s.Pt), sigma(s.moment_dim, s.moment_axis, Rot, s.Pr)
+    Sp, So = s.Pt * (mp.eye(3) - Sf) * s.Pt.T, s.Pr * (mp.eye(3) - Sm) * s.Pr.T
+    Fg, Mg = Rot * V3(goal.get("force", (0, 0, 0))), Rot * V3(goal.get("moment", (0, 0, 0)))
+    dt = mp.mpf(s.dt)
+    if s.closed_force:
+        st["int_f"] += Sf * (sensed_f - Fg) * dt
+        fb = Sf * (-mp.mpf(s.kp_f) * (sensed_f - Fg) - mp.mpf(s.ki_f) * st["int_f"])
+        if mp.norm(fb) > s.max_f:
+            fb = fb * (mp.mpf(s.max_f) / mp.norm(fb))
+        Ffb = st["popc"](Sf * Fg, Sf * sensed_f, Sf * fb, Sf * v, mp.mpf(s.kv_f), mp.mpf(s.kff_f), s.passivity)
+    else:
+        Ffb = Sf * (-mp.mpf(s.kv_f) * v)
+    if s.closed_moment:
+        st["int_m"] += Sm * (sensed_m - Mg) * dt
+        mb = Sm * (-mp.mpf(s.kp_m) * (sensed_m - Mg) - mp.mpf(s.ki_m) * st["int_m"])
+        if mp.norm(mb) > s.max_m:
+            mb = mb * (mp.mpf(s.max_m) / mp.norm(mb))
+        Mfb = Sm * (mb - mp.mpf(s.kv_m) * w)
+    else:
+        Mfb = Sm * (-mp.mpf(s.kv_m) * w)
+    xd, Rd = goal["pos"], goal["ori"]
+    vd, wd = V3(goal.get("linvel", (0, 0, 0))), V3(goal.get("angvel", (0, 0, 0)))
+    ad, ald = V3(goal.get("linacc", (0, 0, 0))), V3(goal.get("angacc", (0, 0, 0)))
+    kp, kv, ki = diag3(s.kp_pos), diag3(s.kv_pos), diag3(s.ki_pos)
+    st["int_p"] += Sp * (x - xd) * dt
+    if s.vel_sat:
+        vd = -kp * inv(kv) * Sp * (x - xd) - ki * inv(kv) * st["int_p"]
+        if mp.norm(vd) > s.lin_sat:
+            vd = vd * (mp.mpf(s.lin_sat) / mp.norm(vd))
+        Fp = Sp * (ad - kv * (v - vd))
+    else:
+        Fp = Sp * (ad - kp * (x - xd) - kv * (v - vd) - ki * st["int_p"])
+    eo = So * orientation_error(Rd, R)
+    st["int_o"] += eo * dt
+    kp, kv, ki = diag3(s.kp_ori), diag3(s.kv_ori), diag3(s.ki_ori)
+    if s.vel_sat:
+        wd = -kp * inv(kv) * eo - ki * inv(kv) * st["int_o"]
+        if mp.norm(wd) > s.ang_sat:
+            wd = wd * (mp.mpf(s.ang_sat) / mp.norm(wd))
+        Fo = So * (ald - kv * (w - wd))
+    else:
+        Fo = So * (ald - kp * eo - kv * (w - wd) - ki * st["int_o"])
+    ff_f, ff_m = Sf * Fg, Sm * Mg
+    if s.closed_force:  # quirk Q3: the moment half is scaled by the FORCE flag (.cpp:484-487)
+        ff_f, ff_m = ff_f * mp.mpf(s.kff_f), ff_m * mp.mpf(s.kff_m)
+    Fstar = mp.matrix(list(Fp) + list(Fo))
+    Ff = mp.matrix(list(Ffb + ff_f) + list(Mfb + ff_m))
+    return Fstar, Ff, vd, wd, eo
+
+
+def new_state(dt=0.001):
+    z = lambda: mp.matrix([0, 0, 0])
+    return dict(int_p=z(), int_o=z(), int_f=z(), int_m=z(), popc=Popc(dt), int_q=None)
+
+
+def two_task_tick(model, q, dq, spec, st, link, p_c, goal, jgoal, B6=None, stacked=True, sensed=None, jt=True,
+                  jkp=50.0, jkv=14.0, jki=0.0):
+    """[MotionForceTask (rank = cols of B6), full JointTask] through RobotController.cpp:53-74, non-singular branch
+    (asserted), bounded inertia estimates (default).  B6: 6 x m basis of the controlled directions (identity when full)."""
+    n = model.n
+    qm, dqm = [mp.mpf(float(x)) for x in q], mp.matrix([mp.mpf(float(x)) for x in dq])
+    M = model.mass_matrix(qm)
+    Minv, Mbinv = inv(M), inv(bie(M))
+    x, R, J6 = model.point(qm, link, p_c)
+    B6 = mp.eye(6) if B6 is None else B6
+    P = B6 * B6.T
+    J = P * J6                                   # .cpp:262: _jacobian = _partial_task_projection * JWorldFrame
+    tw = J * dqm                                 # .cpp:293-298 (projected velocities for a partial task)
+    v, w = tw[0:3, 0], tw[3:6, 0]
+    g = dict(goal)
+    g["pos"] = x + V3(goal["dpos"]) if "dpos" in goal else V3(goal["pos"])
+    g["ori"] = (goal["dR"](R) if "dR" in goal else (M3(goal["ori"]) if "ori" in goal else R))
+    sf = sm = None
+    if sensed is not None:
+        sf, sm = V3(sensed[0]), V3(sensed[1])
+    Fstar, Ff, vd, wd, eo = mft_law(spec, st, x, R, v, w, g, sf, sm)
+    Jr = B6.T * J                                # m x n: the task in its own range (any orthonormal basis gives the same tau)
+    S = mp.svd_r(Jr, compute_uv=False)
+    assert S[len(S) - 1] / S[0] > mp.mpf("0.07"), "pin robots must sit in the non-singular branch (s_max = 6e-2)"
+    Lam, Jbar, N1 = osm(Jr, Minv)
+    Lam_b = inv(Jr * Mbinv * Jr.T)
+    tau1 = Jr.T * (Lam_b * (B6.T * Fstar) + B6.T * Ff)      # SingularityHandler.cpp:307-309
+    out = dict(x=x, R=R, J=J, M=M, Minv=Minv, Fstar=Fstar, ori_err=eo, tau1=tau1, v=v, w=w,
+               lam_world=B6 * Lam * B6.T, lam_mod_world=B6 * Lam_b * B6.T, N1=N1)
+    if not jt:
+        out["tau"] = tau1
+        return out
+    # full JointTask in the nullspace (JointTask.cpp:218-356): Jp = N1, range basis = any unit vector of its column space
+    Jp = N1
+    k = max(range(n), key=lambda c: mp.norm(Jp[:, c]))
+    rank_gap = mp.svd_r(Jp, compute_uv=False)
+    r_dim = sum(1 for sv in rank_gap if sv / rank_gap[0] > mp.mpf("1e-3"))
+    # orthonormal basis of range(Jp) by Gram-Schmidt on its largest columns (definition of matrixRangeBasis, App. B)
+    cols = sorted(range(n), key=lambda c: -mp.norm(Jp[:, c]))
+    Rb = []
+    for c in cols:
+        vcol = Jp[:, c]
+        for b in Rb:
+            vcol = vcol - b * (b.T * vcol)[0]
+        if len(Rb) < r_dim and mp.norm(vcol) > mp.mpf("1e-6"):
+            Rb.append(vcol / mp.norm(vcol))
+    Rm = mp.matrix(n, r_dim)
+    for c, b in enumerate(Rb):
+        Rm[:, c] = b
+    J2 = Rm.T * Jp
+    Lam2, Jbar2, N2 = osm(J2, Minv)
+    Lam2_b = inv(J2 * Mbinv * J2.T)
+    qd, dqd, ddqd = (mp.matrix([mp.mpf(float(x)) for x in jgoal[key]]) for key in ("pos", "vel", "acc"))
+    qv = mp.matrix(qm)
+    if st["int_q"] is None:
+        st["int_q"] = mp.zeros(n, 1)
+    st["int_q"] += (qv - qd) * mp.mpf(spec.dt)
+    u = -mp.mpf(jkp) * (qv - qd) - mp.mpf(jkv) * (dqm - dqd) - mp.mpf(jki) * st["int_q"]
+    tau2 = Jp.T * Rm * (Lam2 * (Rm.T * ddqd) + Lam2_b * (Rm.T * u))
+    if stacked:
+        tau2 = tau2 - Jp.T * Rm * (Lam2 * (Rm.T * (Minv * tau1)))      # JointTask.cpp:285-292, tau_prec = running sum
+    out.update(tau2=tau2, tau=tau1 + tau2, N_total=N2 * N1, jt_rank=r_dim, jt_lam_world=Rm * Lam2 * Rm.T)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def prove_orientation_error():
+    """orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a for every R_d: symbolic proof with sympy"""
+    th, a1, a2, a3 = sp.symbols("theta a1 a2 a3", real=True)
+    a = sp.Matrix([a1, a2, a3])
+    K = sp.Matrix([[0, -a3, a2], [a3, 0, -a1], [-a2, a1, 0]])
+    E = sp.eye(3) + sp.sin(th) * K + (1 - sp.cos(th)) * K * K
+    # R_d = I without loss of generality: the sum over an orthonormal frame is basis independent (vee(E - E^T))
+    e = sp.zeros(3, 1)
+    for i in range(3):
+        e += E[:, i].cross(sp.eye(3)[:, i])
+    e = sp.simplify((-e / 2 - sp.sin(th) * a).subs(a3 ** 2, 1 - a1 ** 2 - a2 ** 2))
+    assert e == sp.zeros(3, 1), e
+
+
+def rrrr_closed_form():
+    """planar 4R by Lagrange in sympy: M(q) = Hessian of T, J = d(x, y, phi)/dq at the tip; returns mpmath callables"""
+    c = chain("rrrrbot")
+    q = sp.symbols("q1:5", real=True)
+    dq = sp.symbols("dq1:5", real=True)
+    l = [sp.Rational(float(j["xyz"][0])) for j in c["joints"]][1:] + [sp.Rational(1, 2)]   # link lengths 0.5 (tip at 0.5 in link4)
+    th = [sum(q[:i + 1]) for i in range(4)]
+    T = 0
+    org = sp.Matrix([0, 0])
+    for i, body in enumerate(c["bodies"]):
+        m, cx, Izz = sp.Rational(float(body["mass"])), sp.Rational(float(body["com"][0])), sp.Rational(float(body["inertia"][2][2]))
+        pc = org + cx * sp.Matrix([sp.cos(th[i]), sp.sin(th[i])])
+        vc = sum((pc.diff(q[k]) * dq[k] for k in range(4)), sp.zeros(2, 1))
+        om = sum(dq[:i + 1])
+        T += m * (vc.T * vc)[0] / 2 + Izz * om ** 2 / 2
+        org = org + l[i] * sp.Matrix([sp.cos(th[i]), sp.sin(th[i])])
+    Msym = sp.hessian(T, dq)
+    tip = sp.Matrix([org[0], org[1], th[3]])
+    Jsym = tip.jacobian(q)
+    Mf = sp.lambdify(q, Msym, "mpmath")
+    Jf = sp.lambdify(q, Jsym, "mpmath")
+    tipf = sp.lambdify(q, tip, "mpmath")
+    return Mf, Jf, tipf
+
+
+def case_rrrr(rng):
+    """examples/11-planar_robot_controller: partial MotionForceTask (X, Y translation + Z rotation, .cpp:105-115) at
+    link4 + (0.5, 0, 0), full JointTask, RobotController.  The general differentiation model must reproduce the sympy
+    closed forms to 1e-25 before anything is written."""
+    c = chain("rrrrbot")
+    model = MpChain(c)
+    Mf, Jf, tipf = rrrr_closed_form()
+    B = 6
+    q = []
+    while len(q) < B:       # rejection: keep the task away from the blend band (sigma_min / sigma_max > 0.12; s_max = 0.06)
+        qc = rng.uniform(-2.0, 2.0, 4)
+        Jn = f64(Jf(*[mp.mpf(float(v)) for v in qc]))
+        sv = np.linalg.svd(Jn, compute_uv=False)
+        if sv[-1] / sv[0] > 0.12:
+            q.append(qc)
+    q = np.array(q)
+    dq = rng.uniform(-0.5, 0.5, (B, 4))
+    dpos = rng.normal(0, 0.05, (B, 3)); dpos[:, 2] = 0
+    dth = rng.normal(0, 0.2, B)
+    gv, gw = rng.normal(0, 0.05, (B, 3)), rng.normal(0, 0.05, (B, 3))
+    gq, gdq, gddq = q + rng.normal(0, 0.1, (B, 4)), rng.normal(0, 0.1, (B, 4)), rng.normal(0, 0.1, (B, 4))
+    B6 = mp.zeros(6, 3); B6[0, 0] = 1; B6[1, 1] = 1; B6[5, 2] = 1
+    spec = MftSpec(Pt=mp.diag([1, 1, 0]), Pr=mp.diag([0, 0, 1]))
+    rec = {k: [] for k in ("tau", "tau1", "tau2", "M", "J", "lam_world", "lam_mod_world", "N1", "N_total", "x", "R", "Fstar", "ori_err", "goal_ori", "tau_plain")}
+    for r in range(B):
+        qm = [mp.mpf(float(v)) for v in q[r]]
+        Mc, Jc, tipc = Mf(*qm), Jf(*qm), tipf(*qm)
+        Mg = model.mass_matrix(qm)
+        x, R, J6 = model.point(qm, "link4", (0.5, 0, 0))
+        assert mp.norm(Mc - Mg) < mp.mpf("1e-25"), "differentiation model vs sympy Lagrange (M)"
+        J3 = mp.matrix(3, 4)
+        for col in range(4):
+            J3[0, col], J3[1, col], J3[2, col] = J6[0, col], J6[1, col], J6[5, col]
+        assert mp.norm(J3 - Jc) < mp.mpf("1e-25"), "differentiation model vs sympy (J)"
+        assert abs(x[0] - tipc[0]) + abs(x[1] - tipc[1]) < mp.mpf("1e-30")
+        goal = dict(dpos=dpos[r], dR=lambda Rc, a=dth[r]: rot((0, 0, 1), a) * Rc, linvel=gv[r], angvel=gw[r])
+        jg = dict(pos=gq[r], vel=gdq[r], acc=gddq[r])
+        o = two_task_tick(model, q[r], dq[r], spec, new_state(), "link4", (0.5, 0, 0), goal, jg, B6=B6)
+        o2 = two_task_tick(model, q[r], dq[r], spec, new_state(), "link4", (0.5, 0, 0), goal, jg, B6=B6, stacked=False)
+        assert abs(o["ori_err"][2] + mp.sin(dth[r])) < mp.mpf("1e-30")            # closed form: R = Rot(z, -dth) R_goal
+        for k in rec:
+            if k == "goal_ori":
+                rec[k].append(f64(rot((0, 0, 1), dth[r]) * o["R"]).ravel())
+            elif k == "tau_plain":
+                rec[k].append(f64(o2["tau"]))
+            else:
+                rec[k].append(f64(o[k]).ravel())
+    return dict(q=q, dq=dq, dpos=dpos, gv=gv, gw=gw, gq=gq, gdq=gdq, gddq=gddq, **{k: np.array(v) for k, v in rec.items()})
+
+
+def well_conditioned_panda_q(model, rng, B):
+    c = model.c
+    lo = np.array([j["lower"] for j in c["joints"]]) + 0.3
+    hi = np.array([j["upper"] for j in c["joints"]]) - 0.3
+    out = []
+    while len(out) < B:
+        q = rng.uniform(lo, hi)
+        _, _, J = model.point([mp.mpf(float(v)) for v in q], "end-effector", (0, 0, 0.07))
+        s = np.linalg.svd(f64(J), compute_uv=False)
+        if s[5] / s[0] > 0.12:
+            out.append(q)
+    return np.array(out)
+
+
+def case_panda_two_task(rng):
+    """BASELINE config 2 shape: 6-DoF MotionForceTask at end-effector + (0, 0, 0.07), full JointTask, RobotController"""
+    model = MpChain(chain("panda"))
+    B = 4
+    q = well_conditioned_panda_q(model, rng, B)
+    dq = rng.uniform(-0.5, 0.5, (B, 7))
+    dpos, ax, ang = rng.normal(0, 0.05, (B, 3)), rng.normal(0, 1, (B, 3)), rng.normal(0, 0.2, B)
+    gv, gw, ga, gal = (rng.normal(0, 0.05, (B, 3)) for _ in range(4))
+    gq, gdq, gddq = q + rng.normal(0, 0.1, (B, 7)), rng.normal(0, 0.1, (B, 7)), rng.normal(0, 0.1, (B, 7))
+    keys = ("tau", "tau1", "tau2", "M", "Minv", "J", "lam_world", "lam_mod_world", "N1", "N_total", "x", "R", "Fstar", "ori_err", "v", "w", "jt_lam_world")
+    rec = {k: [] for k in keys + ("goal_ori", "tau_plain")}
+    for r in range(B):
+        goal = dict(dpos=dpos[r], dR=lambda Rc, a=ax[r], t=ang[r]: rot(a, -t) * Rc, linvel=gv[r], angvel=gw[r], linacc=ga[r], angacc=gal[r])
+        jg = dict(pos=gq[r], vel=gdq[r], acc=gddq[r])
+        o = two_task_tick(model, q[r], dq[r], MftSpec(), new_state(), "end-effector", (0, 0, 0.07), goal, jg)
+        o2 = two_task_tick(model, q[r], dq[r], MftSpec(), new_state(), "end-effector", (0, 0, 0.07), goal, jg, stacked=False)
+        a = V3(ax[r]) / mp.norm(V3(ax[r]))
+        # R = Rot(a, ang) R_goal -> sin(ang) a, up to the orthonormality of the fixture's float64 joint rotations (1e-16)
+        assert mp.norm(o["ori_err"] - mp.sin(ang[r]) * a) < mp.mpf("1e-14")
+        assert o["jt_rank"] == 1
+        for k in keys:
+            rec[k].append(f64(o[k]).ravel())
+        rec["goal_ori"].append(f64(rot(ax[r], -ang[r]) * o["R"]).ravel())
+        rec["tau_plain"].append(f64(o2["tau"]))
+    return dict(q=q, dq=dq, dpos=dpos, gv=gv, gw=gw, ga=ga, gal=gal, gq=gq, gdq=gdq, gddq=gddq, **{k: np.array(v) for k, v in rec.items()})
+
+
+LAW_CASES = [  # (name, MftSpec overrides, goal force, goal moment)
+    ("force1_z_world", dict(force_dim=1, force_axis=(0, 0, 1)), (0, 0, -5.0), (0, 0, 0)),
+    ("force2_x_compliant", dict(force_dim=2, force_axis=(1, 0, 0), in_compliant_frame=True), (1.0, -2.0, 3.0), (0, 0, 0)),
+    ("force3_moment1", dict(force_dim=3, moment_dim=1, moment_axis=(0, 1, 0)), (1.0, 2.0, -3.0), (0.1, 0.2, -0.3)),
+    ("moment2_compliant", dict(moment_dim=2, moment_axis=(0.6, 0, 0.8), in_compliant_frame=True), (0, 0, 0), (0.3, -0.1, 0.2)),
+    ("moment3", dict(moment_dim=3), (0, 0, 0), (0.3, -0.1, 0.2)),
+    ("vel_sat_saturated", dict(vel_sat=True, lin_sat=0.01, ang_sat=0.01), (0, 0, 0), (0, 0, 0)),
+    ("vel_sat_unsaturated", dict(vel_sat=True, lin_sat=50.0, ang_sat=50.0), (0, 0, 0), (0, 0, 0)),
+    ("anisotropic_gains_ki", dict(kp_pos=(100.0, 50.0, 150.0), kv_pos=(20.0, 10.0, 30.0), ki_pos=(3.0, 4.0, 5.0), kp_ori=(200.0, 100.0, 50.0),
+                                  kv_ori=(28.3, 20.0, 10.0), ki_ori=(1.0, 2.0, 3.0)), (0, 0, 0), (0, 0, 0)),
+    ("closed_loop_force_moment", dict(force_dim=1, force_axis=(0, 0, 1), moment_dim=1, moment_axis=(1, 0, 0), closed_force=True, closed_moment=True),
+     (0, 0, -5.0), (0.2, 0, 0)),
+    ("closed_loop_saturating_feedback", dict(force_dim=3, closed_force=True, max_f=2.0), (0, 0, -5.0), (0, 0, 0)),
+]
+
+
+def case_panda_law(rng):
+    """known answers of the control law on one Panda posture per case: Sigma projectors (dims 0-3, world / compliant frame),
+    velocity saturation (clamped and not), anisotropic gains with integrators (two ticks), closed-loop force/moment feedback
+    with its saturation, feed-forward scaling (Q3).  Single MotionForceTask (no joint task): tau = J^T (Lambda_mod F* + F_f)."""
+    model = MpChain(chain("panda"))
+    q = well_conditioned_panda_q(model, rng, len(LAW_CASES))
+    dq = rng.uniform(-0.5, 0.5, (len(LAW_CASES), 7))
+    out = dict(q=q, dq=dq, names=np.array([c[0] for c in LAW_CASES]))
+    dpos, ax, ang = rng.normal(0, 0.05, (len(LAW_CASES), 3)), rng.normal(0, 1, (len(LAW_CASES), 3)), rng.normal(0, 0.2, len(LAW_CASES))
+    sf, sm = rng.normal(0, 4, (len(LAW_CASES), 2, 3)), rng.normal(0, 0.5, (len(LAW_CASES), 2, 3))
+    rec = {k: [] for k in ("tau_t0", "tau_t1", "Fstar_t1", "goal_ori", "int_f", "int_p", "des_linvel", "des_angvel")}
+    for r, (name, kw, gf, gm) in enumerate(LAW_CASES):
+        spec, st = MftSpec(**kw), new_state()
+        res = []
+        Rg = None
+        for tick in range(2):   # two ticks so that the integrators matter; q advances by dq * dt (kinematic playback)
+            qt = q[r] + dq[r] * 0.001 * tick
+            if Rg is None:
+                _, R0, _ = model.point([mp.mpf(float(v)) for v in qt], "end-effector", (0, 0, 0.07))
+                x0 = model.point([mp.mpf(float(v)) for v in qt], "end-effector", (0, 0, 0.07))[0]
+                Rg, xg = rot(ax[r], -ang[r]) * R0, x0 + V3(dpos[r])
+            goal = dict(pos=f64(xg), ori=f64(Rg), force=gf, moment=gm)
+            # the goal pose is what the product receives: float64 roundings, so use the same roundings here
+            o = two_task_tick(model, qt, dq[r], spec, st, "end-effector", (0, 0, 0.07), goal, None, jt=False, sensed=(sf[r, tick], sm[r, tick]))
+            res.append(o)
+        _, _, vd, wd, _ = mft_law(spec, new_state(), res[1]["x"], res[1]["R"], res[1]["v"], res[1]["w"], dict(pos=V3(f64(xg)), ori=M3(f64(Rg)), force=gf, moment=gm),
+                                  V3(sf[r, 1]), V3(sm[r, 1])) if spec.vel_sat else (0, 0, V3((0, 0, 0)), V3((0, 0, 0)), 0)
+        rec["tau_t0"].append(f64(res[0]["tau"])); rec["tau_t1"].append(f64(res[1]["tau"])); rec["Fstar_t1"].append(f64(res[1]["Fstar"]))
+        rec["goal_ori"].append(f64(Rg).ravel()); rec["int_f"].append(f64(st["int_f"])); rec["int_p"].append(f64(st["int_p"]))
+        rec["des_linvel"].append(f64(vd)); rec["des_angvel"].append(f64(wd))
+        out.setdefault("goal_pos", []).append(f64(xg))
+    out.update(sensed_f=sf, sensed_m=sm, goal_force=np.array([c[2] for c in LAW_CASES], float), goal_moment=np.array([c[3] for c in LAW_CASES], float),
+               goal_pos=np.array(out["goal_pos"]), **{k: np.array(v) for k, v in rec.items()})
+    return out
+
+
+def case_popc_window(rng):
+    """one passivity window and more: closed-loop force control on z with the passivity observer/controller on
+    (examples/07 style), 420 ticks at a FIXED posture (the model is evaluated once, the law 420 times): the observer window
+    (250) slides, the 50-tick controller period fires 8 times, R_c drops below 1 and recovers."""
+    model = MpChain(chain("panda"))
+    q = well_conditioned_panda_q(model, rng, 1)[0]
+    dq = rng.uniform(-0.3, 0.3, 7)
+    T = 420
+    spec = MftSpec(force_dim=1, force_axis=(0, 0, 1), closed_force=True, passivity=True)
+    qm, dqm = [mp.mpf(float(x)) for x in q], mp.matrix([mp.mpf(float(x)) for x in dq])
+    M = model.mass_matrix(qm)
+    Mbinv = inv(bie(M))
+    x, R, J = model.point(qm, "end-effector", (0, 0, 0.07))
+    tw = J * dqm
+    v, w = tw[0:3, 0], tw[3:6, 0]
+    Lam_b = inv(J * Mbinv * J.T)
+    t = np.arange(T)
+    fz = -5.0 * (1 + 0.6 * np.sin(2 * np.pi * 3 * t * 0.001)) + rng.normal(0, 0.3, T)
+    fz[120:200] *= 5.0          # a burst of active behaviour: the observer goes negative, R_c is reduced
+    f = np.zeros((T, 3)); f[:, 2] = fz; f[:, :2] = rng.normal(0, 1.0, (T, 2))   # off-axis components must be projected out
+    st = new_state()
+    goal = dict(pos=x, ori=R, force=(0, 0, -5.0))
+    taus, rcs, pos_, ints = [], [], [], []
+    for k in range(T):
+        Fstar, Ff, _, _, _ = mft_law(spec, st, x, R, v, w, goal, V3(f[k]), V3((0, 0, 0)))
+        taus.append(f64(J.T * (Lam_b * Fstar + Ff)))
+        rcs.append(float(st["popc"].Rc)); pos_.append(float(st["popc"].PO)); ints.append(f64(st["int_f"]))
+    assert min(rcs) < 0.999 and len(st["popc"].win) <= 420
+    return dict(q=q, dq=dq, sensed_f=f, tau=np.array(taus), rc=np.array(rcs), po=np.array(pos_), int_f=np.array(ints),
+                window_len=np.array([len(st["popc"].win)]))
+
+
+def main():
+    prove_orientation_error()
+    print("orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a: proved")
+    os.makedirs(OUT, exist_ok=True)
+    for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
+                           ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104)):
+        if len(sys.argv) > 1 and name not in sys.argv[1:]:
+            continue
+        d = fn(np.random.default_rng(seed))
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **d)
+        print(name, {k: np.asarray(v).shape for k, v in d.items()})
+
+
+if __name__ == "__main__":
+    main()
