@@ -1,0 +1,235 @@
+"""Replay of the code-independent pins (tests/golden/pins_*.npz, made by tools/make_sympy_golden.py: sympy closed forms for the
+planar 4R, 50-digit mpmath differentiation of the kinematic map / kinetic energy for the Panda, the control law typed in from
+the reference text, hand-derived known answers) on
+  * the C++ oracle            (CPU, -m "not gpu")
+  * the numpy / LAPACK oracle (CPU, two-task cases)
+  * the CUDA path through the C ABI (GPU, -m gpu), fused and API-faithful routes.
+FP64, 1e-9 relative.  What these pin that the oracle-vs-oracle checks could not: the sign and frame of
+orientationError, the Sigma projectors (dims 0-3, world / compliant frame), the velocity-saturation law, feed-forward
+scaling (Q3), the bounded-inertia variants, Lambda / Jbar / N by their definitions, the joint task's range basis, the
+stacking of RobotController, and one full passivity window of POPCExplicitForceControl."""
+import os
+
+import numpy as np
+import pytest
+
+import osc_abi as abi
+from common import FP64_TOL, ROOT, load_chain, q0_of, rel_err
+
+
+def G(name):
+    return dict(np.load(os.path.join(ROOT, "tests", "golden", name + ".npz")))
+
+
+def make_batch(kind, chain, B):
+    if kind == "oracle":
+        import orc
+        orc.build()
+        return orc.OracleBatch(chain, B, q0=q0_of(chain))
+    import osc_b200
+    return osc_b200.Batch(chain, B, q0=q0_of(chain))
+
+
+KINDS = ["oracle", pytest.param("cuda", marks=pytest.mark.gpu)]
+
+
+def close(a, b, what, tol=FP64_TOL, floor=None):
+    b = np.asarray(b, float)
+    e, where = rel_err(np.asarray(a, float).reshape(len(b), -1), b.reshape(len(b), -1), floor)
+    assert e <= tol, "%s: rel err %.3e at robot %d" % (what, e, where)
+
+
+def _two_task(kind, g, chain, link, p_c, stacked, per_call, **mft_kw):
+    B = len(g["q"])
+    b = make_batch(kind, chain, B)
+    b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, link, p_c, **mft_kw))
+    t1 = b.add_joint_task(abi.joint_task_desc(chain["n"]))
+    x0 = b.get(abi.F_CURRENT_POSITION, t0)
+    close(x0, g["x"], "FK position")
+    close(b.get(abi.F_CURRENT_ORIENTATION, t0), g["R"], "FK orientation", floor=1.0)
+    b.set(abi.F_GOAL_POSITION, g["x"] + g["dpos"], t0); b.set(abi.F_GOAL_ORIENTATION, g["goal_ori"], t0)
+    b.set(abi.F_GOAL_LINEAR_VELOCITY, g["gv"], t0); b.set(abi.F_GOAL_ANGULAR_VELOCITY, g["gw"], t0)
+    if "ga" in g:
+        b.set(abi.F_GOAL_LINEAR_ACCELERATION, g["ga"], t0); b.set(abi.F_GOAL_ANGULAR_ACCELERATION, g["gal"], t0)
+    b.set(abi.F_JT_GOAL_POSITION, g["gq"], t1); b.set(abi.F_JT_GOAL_VELOCITY, g["gdq"], t1); b.set(abi.F_JT_GOAL_ACCELERATION, g["gddq"], t1)
+    if per_call:
+        b.update_model(); b.update_task_models()
+        tau = b.compute_torques(stacked)
+    else:
+        tau = b.tick(stacked)
+    return b, t0, t1, tau
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+def test_pin_planar_4r_partial_task_sympy(kind, per_call):
+    """examples/11: partial MotionForceTask (X, Y, rot Z) + JointTask on the planar 4R against the sympy Lagrange closed forms"""
+    g = G("pins_rrrr_two_task")
+    chain = load_chain("rrrrbot")
+    kw = dict(dirs_translation=[(1, 0, 0), (0, 1, 0)], dirs_rotation=[(0, 0, 1)])
+    b, t0, t1, tau = _two_task(kind, g, chain, "link4", (0.5, 0, 0), True, per_call, **kw)
+    close(tau, g["tau"], "tau (stacked)")
+    close(b.get(abi.F_M), g["M"], "M")
+    close(b.get(abi.F_JACOBIAN, t0), g["J"], "J")
+    close(b.get(abi.F_LAMBDA_WORLD, t0), g["lam_world"], "Lambda")
+    close(b.get(abi.F_LAMBDA_MODIFIED_WORLD, t0), g["lam_mod_world"], "Lambda (bounded inertia)")
+    close(b.get(abi.F_N_TASK, t0), g["N1"], "N_1", floor=1.0)
+    close(b.get(abi.F_N_TOTAL), g["N_total"], "N_total", floor=1.0)
+    close(b.get(abi.F_TASK_TORQUES, t0), g["tau1"], "tau_1")
+    close(b.get(abi.F_TASK_TORQUES, t1), g["tau2"], "tau_2")
+    close(b.get(abi.F_UNIT_MASS_FORCE, t0), g["Fstar"], "F*")
+    close(b.get(abi.F_ORIENTATION_ERROR, t0), g["ori_err"], "orientation error", floor=1e-3)
+    b2, _, _, tau_plain = _two_task(kind, g, chain, "link4", (0.5, 0, 0), False, per_call, **kw)
+    close(tau_plain, g["tau_plain"], "tau (plain sum)")
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+def test_pin_panda_two_task_mpmath(kind, per_call):
+    """BASELINE config 2 shape against the 50-digit differentiation model (per_call = False is the fused tick on the GPU)"""
+    g = G("pins_panda_two_task")
+    chain = load_chain("panda")
+    b, t0, t1, tau = _two_task(kind, g, chain, "end-effector", (0, 0, 0.07), True, per_call)
+    close(tau, g["tau"], "tau (stacked)")
+    close(b.get(abi.F_TASK_TORQUES, t0), g["tau1"], "tau_1")
+    close(b.get(abi.F_TASK_TORQUES, t1), g["tau2"], "tau_2")
+    close(b.get(abi.F_UNIT_MASS_FORCE, t0), g["Fstar"], "F*")
+    close(b.get(abi.F_ORIENTATION_ERROR, t0), g["ori_err"], "orientation error = sin(theta) a", floor=1e-3)
+    close(b.get(abi.F_CURRENT_LINEAR_VELOCITY, t0), g["v"], "v = J dq")
+    close(b.get(abi.F_CURRENT_ANGULAR_VELOCITY, t0), g["w"], "w = J dq")
+    close(b.get(abi.F_M), g["M"], "M")
+    close(b.get(abi.F_MINV), g["Minv"], "M^-1")
+    close(b.get(abi.F_JACOBIAN, t0), g["J"], "J")
+    close(b.get(abi.F_LAMBDA_WORLD, t0), g["lam_world"], "Lambda")
+    close(b.get(abi.F_LAMBDA_MODIFIED_WORLD, t0), g["lam_mod_world"], "Lambda (bounded inertia)")
+    close(b.get(abi.F_N_TASK, t0), g["N1"], "N_1", floor=1.0)
+    close(b.get(abi.F_N_TOTAL), g["N_total"], "N_total", floor=1.0)
+    close(b.get(abi.F_JT_LAMBDA_WORLD, t1), g["jt_lam_world"], "joint task R Lambda R^T")
+    assert (np.asarray(b.get(abi.F_JT_RANGE_RANK, t1)).ravel() == 1).all() and (np.asarray(b.get(abi.F_ALPHA, t0)).ravel() == 1).all()
+    if kind == "cuda":
+        assert b.tick_is_fused() and (per_call or b.tick_fallback_count() == 0), "the pins must exercise the fused fast path"
+    _, _, _, tau_plain = _two_task(kind, g, chain, "end-effector", (0, 0, 0.07), False, per_call)
+    close(tau_plain, g["tau_plain"], "tau (plain sum)")
+
+
+def test_pin_two_task_numpy_oracle():
+    """the second (numpy / LAPACK) oracle against the same pins"""
+    import np_oracle as npo
+    for name, chain_name, link, p_c, kw in (("pins_rrrr_two_task", "rrrrbot", "link4", (0.5, 0, 0),
+                                             dict(dirs_t=[np.array([1.0, 0, 0]), np.array([0, 1.0, 0])], dirs_r=[np.array([0, 0, 1.0])])),
+                                            ("pins_panda_two_task", "panda", "end-effector", (0, 0, 0.07), {})):
+        g, chain = G(name), load_chain(chain_name)
+        for r in range(len(g["q"])):
+            m = npo.Model(chain); m.setQ(g["q"][r]); m.setDq(g["dq"][r]); m.updateModel()
+            t0 = npo.MotionForceTask(m, link, np.array(p_c, float), **kw); t1 = npo.JointTask(m)
+            t0.goal_pos = g["x"][r] + g["dpos"][r]; t0.goal_ori = g["goal_ori"][r].reshape(3, 3)
+            t0.goal_linvel = g["gv"][r]; t0.goal_angvel = g["gw"][r]
+            if "ga" in g:
+                t0.goal_linacc = g["ga"][r]; t0.goal_angacc = g["gal"][r]
+            t1.goal_pos = g["gq"][r]; t1.goal_vel = g["gdq"][r]; t1.goal_acc = g["gddq"][r]
+            ctl = npo.RobotController(m, [t0, t1])
+            ctl.updateControllerTaskModels()
+            tau = ctl.computeControlTorques()
+            close(tau[None], g["tau"][r][None], "%s robot %d tau" % (name, r))
+            close(m.M().ravel()[None], g["M"][r][None], "M")
+
+
+LAW = {  # name -> osc_mft_params overrides (tools/make_sympy_golden.py LAW_CASES)
+    "force1_z_world": dict(force_space_dimension=1, force_or_motion_axis=(0, 0, 1)),
+    "force2_x_compliant": dict(force_space_dimension=2, force_or_motion_axis=(1, 0, 0)),
+    "force3_moment1": dict(force_space_dimension=3, moment_space_dimension=1, moment_or_rotmotion_axis=(0, 1, 0)),
+    "moment2_compliant": dict(moment_space_dimension=2, moment_or_rotmotion_axis=(0.6, 0, 0.8)),
+    "moment3": dict(moment_space_dimension=3),
+    "vel_sat_saturated": dict(use_velocity_saturation=1, linear_saturation_velocity=0.01, angular_saturation_velocity=0.01),
+    "vel_sat_unsaturated": dict(use_velocity_saturation=1, linear_saturation_velocity=50.0, angular_saturation_velocity=50.0),
+    "anisotropic_gains_ki": dict(kp_pos=(100.0, 50.0, 150.0), kv_pos=(20.0, 10.0, 30.0), ki_pos=(3.0, 4.0, 5.0), kp_ori=(200.0, 100.0, 50.0),
+                                 kv_ori=(28.3, 20.0, 10.0), ki_ori=(1.0, 2.0, 3.0)),
+    "closed_loop_force_moment": dict(force_space_dimension=1, force_or_motion_axis=(0, 0, 1), moment_space_dimension=1, moment_or_rotmotion_axis=(1, 0, 0),
+                                     closed_loop_force_control=1, closed_loop_moment_control=1),
+    "closed_loop_saturating_feedback": dict(force_space_dimension=3, closed_loop_force_control=1, max_force_control_feedback_output=2.0),
+}
+COMPLIANT = {"force2_x_compliant", "moment2_compliant"}
+
+
+def _set_params(b, t0, kw):
+    p = b.mft_params(t0)
+    for k, v in kw.items():
+        cur = getattr(p, k)
+        if hasattr(cur, "__len__"):
+            for i, x in enumerate(v):
+                cur[i] = float(x)
+        else:
+            setattr(p, k, v)
+    b.set_mft_params(t0, p)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_pin_control_law_known_answers(kind):
+    """one Panda per case, a single MotionForceTask, two ticks (integrators): Sigma projectors, velocity saturation, gains,
+    closed-loop force / moment feedback and its saturation, feed-forward scaling"""
+    g = G("pins_panda_law")
+    chain = load_chain("panda")
+    for r, name in enumerate(g["names"]):
+        name = str(name)
+        b = make_batch(kind, chain, 1)
+        b.set(abi.F_Q, g["q"][r][None]); b.set(abi.F_DQ, g["dq"][r][None]); b.update_model()
+        t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07), in_compliant_frame=name in COMPLIANT))
+        _set_params(b, t0, LAW[name])   # parametrize* resets the goal pose to the current one: set the goals afterwards
+        b.set(abi.F_GOAL_POSITION, g["goal_pos"][r][None], t0); b.set(abi.F_GOAL_ORIENTATION, g["goal_ori"][r][None], t0)
+        b.set(abi.F_GOAL_FORCE, g["goal_force"][r][None], t0); b.set(abi.F_GOAL_MOMENT, g["goal_moment"][r][None], t0)
+        for tick in range(2):
+            b.set(abi.F_Q, (g["q"][r] + g["dq"][r] * 0.001 * tick)[None])
+            b.update_model(); b.update_task_models()
+            b.update_sensed_force_and_moment(t0, g["sensed_f"][r, tick][None], g["sensed_m"][r, tick][None])
+            tau = b.compute_torques(True)
+            close(tau, g["tau_t%d" % tick][r][None], "%s tick %d tau" % (name, tick))
+        close(b.get(abi.F_UNIT_MASS_FORCE, t0), g["Fstar_t1"][r][None], name + " F*")
+        close(b.get(abi.F_INTEGRATED_FORCE_ERROR, t0), g["int_f"][r][None], name + " integrated force error", floor=1e-6)
+        close(b.get(abi.F_INTEGRATED_POSITION_ERROR, t0), g["int_p"][r][None], name + " integrated position error", floor=1e-9)
+        if "vel_sat" in name:
+            close(b.get(abi.F_DESIRED_LINEAR_VELOCITY, t0), g["des_linvel"][r][None], name + " saturated desired velocity")
+            close(b.get(abi.F_DESIRED_ANGULAR_VELOCITY, t0), g["des_angvel"][r][None], name + " saturated desired angular velocity")
+            n = np.linalg.norm(g["des_linvel"][r])
+            assert (abs(n - 0.01) < 1e-12) if name == "vel_sat_saturated" else (n < 50.0)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("route", ["per_call", "tick"])
+def test_pin_popc_window(kind, route):
+    """520 ticks of closed-loop force control with the passivity observer / controller at a fixed posture: the 250-sample window
+    slides, the 50-tick controller period fires 10 times, R_c leaves 1 and recovers (POPCExplicitForceControl.cpp:30-96)"""
+    g = G("pins_popc_window")
+    chain = load_chain("panda")
+    b = make_batch(kind, chain, 1)
+    b.set(abi.F_Q, g["q"][None]); b.set(abi.F_DQ, g["dq"][None]); b.update_model()
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = b.add_joint_task(abi.joint_task_desc(7)) if route == "tick" else None   # the fused tick needs the two-task hierarchy
+    _set_params(b, t0, dict(force_space_dimension=1, force_or_motion_axis=(0, 0, 1), closed_loop_force_control=1, passivity_enabled=1))
+    b.set(abi.F_GOAL_FORCE, np.array([[0, 0, -5.0]]), t0)
+    if t1 is not None:
+        _set_jt_zero_gains(b, t1)
+    worst, rc_err, po_err = 0.0, 0.0, 0.0
+    for k in range(len(g["sensed_f"])):
+        if route == "per_call":
+            b.update_model(); b.update_task_models()
+            b.update_sensed_force_and_moment(t0, g["sensed_f"][k][None], np.zeros((1, 3)))
+            b.compute_torques(True)
+        else:
+            b.update_sensed_force_and_moment(t0, g["sensed_f"][k][None], np.zeros((1, 3)))
+            b.tick(True)
+        tau = np.asarray(b.get(abi.F_TASK_TORQUES, t0), float)
+        worst = max(worst, rel_err(tau, g["tau"][k][None])[0])
+        rc_err = max(rc_err, abs(float(b.get(abi.F_POPC_RC, t0)[0, 0]) - g["rc"][k]))
+        po_err = max(po_err, abs(float(b.get(abi.F_POPC_OBSERVER, t0)[0, 0]) - g["po"][k]) / max(1e-6, abs(g["po"][k])))
+    assert worst <= FP64_TOL, worst
+    assert rc_err <= 1e-9 and po_err <= 1e-9, (rc_err, po_err)
+    assert g["rc"].min() == 0 and 0 < g["rc"][199] < 1 and g["rc"][-1] > 0.5   # drops, bottoms out, recovers
+    close(b.get(abi.F_INTEGRATED_FORCE_ERROR, t0), g["int_f"][-1][None], "integrated force error")
+
+
+def _set_jt_zero_gains(b, t1):
+    p = b.joint_task_params(t1)
+    for i in range(7):
+        p.kp[i], p.kv[i], p.ki[i] = 0.0, 0.0, 0.0
+    b.set_joint_task_params(t1, p)
