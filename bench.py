@@ -164,17 +164,19 @@ def build_batch(osc_b200, abi, chain, B, device, seed, precision):
 
 
 class CpuRef:
-    """The reference algorithm (oracle port of the reference path, g++ -O2, robots statically partitioned over the host
-    threads, one robot instance per thread at a time, each with its own model copy) on a bounded sample of config 2."""
+    """The reference algorithm (oracle port of the reference path, robots statically partitioned over the host threads, one
+    robot instance per thread at a time, each with its own model copy) on a bounded sample of config 2.
+    variant: "" = g++ -O2 (the reference's Release default, CMakeLists.txt:13-26), "O3" = -O3 -march=native,
+    "heap" = malloc'ed matrix temporaries like Eigen's dynamic MatrixXd (oracle/Makefile)."""
 
-    def __init__(self, chain, nthreads, Bc=4096):
+    def __init__(self, chain, nthreads, Bc=4096, variant=""):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import orc
         import osc_abi as abi
         import workloads
-        self.Bc, self.nthreads = Bc, nthreads
+        self.Bc, self.nthreads, self.variant = Bc, nthreads, variant
         w = workloads.config2(chain, Bc, seed=2)
-        o = orc.OracleBatch(chain, Bc, q0=[j["q0"] for j in chain["joints"]], nthreads=nthreads)
+        o = orc.OracleBatch(chain, Bc, q0=[j["q0"] for j in chain["joints"]], nthreads=nthreads, variant=variant)
         t0 = o.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
         t1 = o.add_joint_task(abi.joint_task_desc(chain["n"]))
         o.set(abi.F_Q, w["q"]); o.set(abi.F_DQ, w["dq"]); o.update_model()
@@ -191,17 +193,42 @@ class CpuRef:
         return time.perf_counter() - t
 
     def sample(self, ticks):
-        return "%d robots x %d ticks of config 2 (seed 2), %d threads, g++ -O2" % (self.Bc, ticks, self.nthreads)
+        flags = {"": "g++ -O2", "O3": "g++ -O3 -march=native", "heap": "g++ -O2, heap-allocated matrix temporaries"}[self.variant]
+        return "%d robots x %d ticks of config 2 (seed 2), %d threads, %s" % (self.Bc, ticks, self.nthreads, flags)
 
 
-def cpu_baseline(chain, seconds=12.0):
+def cpu_baseline(chain, seconds=10.0):
+    """bounded CPU legs, rank 0 only: config 2 on all host threads (-O2 = the reported baseline; -O3 -march=native and the
+    heap-temporaries proxy beside it), BASELINE config 1 (ONE robot, 10,000 cycles of the 04-task_and_redundancy loop, per-cycle
+    latency), and the operation count of one config-2 tick that freezes the algorithmic FLOP figure of SURVEY.md 8(d)."""
     nthreads = os.cpu_count() or 1
-    ref = CpuRef(chain, nthreads)
-    one = ref.run(1)
-    one = ref.run(1)
-    ticks = int(max(2, min(5000, seconds / max(one, 1e-6))))
-    el = ref.run(ticks)
-    return {"value": ref.Bc * ticks / el, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": ref.sample(ticks)}
+    out = None
+    for variant, secs in (("", seconds), ("O3", 3.0), ("heap", 3.0)):
+        ref = CpuRef(chain, nthreads, variant=variant)
+        ref.run(1)
+        one = ref.run(1)
+        ticks = int(max(2, min(5000, secs / max(one, 1e-6))))
+        el = ref.run(ticks)
+        rec = {"value": ref.Bc * ticks / el, "unit": UNIT, "cores": nthreads, "kind": "port", "sample": ref.sample(ticks)}
+        if out is None:
+            out = rec
+            out["variants"] = {}
+        else:
+            out["variants"]["O3_march_native" if variant == "O3" else "heap_temporaries"] = {"value": rec["value"], "sample": rec["sample"]}
+    import orc
+    import osc_abi as abi
+    q0 = [j["q0"] for j in chain["joints"]]
+    one = orc.OracleBatch(chain, 1, q0=q0)
+    one.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07))); one.add_joint_task(abi.joint_task_desc(chain["n"]))
+    us = one.config1_run(10000)
+    out["config1_single_robot"] = {"p50_us_per_tick": float(np.median(us)), "p99_us_per_tick": float(np.percentile(us, 99)),
+                                   "ticks": 10000, "what": "BASELINE config 1: one Panda, the 04-task_and_redundancy control cycle "
+                                   "(setQ/setDq, updateModel, 2 x updateTaskModel, goal generator, 2 x computeTorques), one host thread, g++ -O2"}
+    cnt = CpuRef(chain, 1, Bc=64, variant="count")
+    flops = [cnt.o.count_tick_flops(True) for _ in range(2)][-1]
+    out["counted_flop_per_robot_tick"] = {"value": flops, "what": "adds + multiplies of one config-2 tick of the oracle (reference route, two Jacobi "
+                                          "SVDs), counted by its instrumented primitives (oracle/Makefile target count); SURVEY.md 8(d) estimated 3.55e4"}
+    return out
 
 
 def run_reference(args, rank, world):
@@ -305,6 +332,54 @@ def run_b200(args, rank, world, local_rank):
     total_ms = max_over_ranks(float(step_ms.sum()))
     value = world * B * args.steps / (total_ms * 1e-3)
 
+    # ---- parity of the benchmarked state: 512 robots of this very batch against the oracle (outside every timed region)
+    parity = None
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import orc
+        pick = np.sort(np.random.default_rng(7).choice(B, min(512, B), replace=False))
+        tau_gpu = np.asarray(batch.tick(True), dtype=np.float64)[pick]
+        o = orc.OracleBatch(chain, len(pick), q0=[j["q0"] for j in chain["joints"]], nthreads=os.cpu_count() or 1)
+        o0 = o.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07))); o1 = o.add_joint_task(abi.joint_task_desc(n))
+        o.set(abi.F_Q, w["q"][pick]); o.set(abi.F_DQ, w["dq"][pick]); o.update_model()
+        o.set(abi.F_GOAL_POSITION, w["goal_pos"][pick], o0); o.set(abi.F_GOAL_ORIENTATION, w["goal_ori"][pick], o0)
+        o.set(abi.F_GOAL_LINEAR_VELOCITY, w["goal_linvel"][pick], o0); o.set(abi.F_GOAL_ANGULAR_VELOCITY, w["goal_angvel"][pick], o0)
+        o.set(abi.F_JT_GOAL_POSITION, w["jt_goal"][pick], o1)
+        tau_ref = o.tick(True)
+        err = np.abs(tau_gpu - tau_ref).max(axis=1) / np.maximum(np.abs(tau_ref).max(axis=1), 1e-3 * np.abs(tau_ref).max())
+        tol = 1e-9 if args.precision == 64 else 1e-4
+        parity = {"robots": int(len(pick)), "max_rel_err": float(err.max()), "tolerance": tol, "ok": bool(err.max() <= tol),
+                  "what": "torques of %d random robots of the benchmarked batch after the timed ticks vs the CPU oracle" % len(pick)}
+        del o
+
+    # ---- the same tick captured in a CUDA graph (osc_tick_noalloc: no allocation under capture), replayed: launch-gap-free latency
+    graph_tick = None
+    if batch.tick_is_fused() and B <= abi.NOALLOC_MAX_ROBOTS:
+        cap = torch.cuda.Stream()
+        g = torch.cuda.CUDAGraph()
+        batch.set_stream(cap.cuda_stream)
+        with torch.cuda.stream(cap):
+            batch.tick_noalloc(None, True)  # warm (function attributes, module load) outside the capture
+            cap.synchronize()
+            g.capture_begin()
+            batch.tick_noalloc(None, True)
+            g.capture_end()
+            cap.synchronize()
+            for _ in range(args.warmup):
+                g.replay()
+            evg = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+            for s_, e_ in evg:
+                if not noflush:
+                    flush.zero_()
+                s_.record(cap); g.replay(); e_.record(cap)
+            cap.synchronize()
+        gms = np.array([s_.elapsed_time(e_) for s_, e_ in evg])
+        graph_tick = {"p50_us": float(np.median(gms) * 1e3), "mean_us": float(gms.mean() * 1e3),
+                      "what": "osc_tick_noalloc captured once in a CUDA graph and replayed (k_tick_fused2 + k_tick_tail, L2 flushed between replays)"}
+        batch.set_stream(torch.cuda.current_stream().cuda_stream)
+        del g
+    barrier()
+
     # ---- end to end through the C ABI with HOST buffers: H2D of this step's state + goals, tick, D2H of the torques
     # The DMA rate of a pinned buffer depends on where its pages landed (measured on this pool, same process, same minute:
     # 47 GB/s for one cudaHostAlloc, 11 GB/s for the next; the boxes are VMs that show one NUMA node, so there is nothing to
@@ -315,7 +390,7 @@ def run_b200(args, rank, world, local_rank):
     def pinned(a, candidates=4):
         src = torch.from_numpy(np.ascontiguousarray(a.T)).to(real)  # SoA [k][B]
         dev = torch.empty_like(src, device="cuda")
-        best, best_ms = None, None
+        best, best_ms, first = None, None, None
         for _ in range(candidates):
             t = src.pin_memory()
             keep.append(t)  # held until all buffers are chosen, so that a rejected block is not handed out again at once
@@ -325,39 +400,53 @@ def run_b200(args, rank, world, local_rank):
                 s_, e_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 s_.record(); dev.copy_(t, non_blocking=True); e_.record(); torch.cuda.synchronize()
                 ms.append(s_.elapsed_time(e_))
+            if first is None:
+                first = t
             if best is None or min(ms) < best_ms:
                 best, best_ms = t, min(ms)
             rates.append(src.numel() * src.element_size() / (min(ms) * 1e-3) / 1e9)
-        return best
+        return first, best
+    # every per-tick input of SURVEY.md 8(d): q, dq (14) + the six MotionForceTask goals (24) + the joint goal (7) = 45 scalars
+    zeros3 = np.zeros((B, 3))
+    fields = [(abi.F_Q, -1, w["q"]), (abi.F_DQ, -1, w["dq"]), (abi.F_GOAL_POSITION, t0, w["goal_pos"]), (abi.F_GOAL_ORIENTATION, t0, w["goal_ori"]),
+              (abi.F_GOAL_LINEAR_VELOCITY, t0, w["goal_linvel"]), (abi.F_GOAL_ANGULAR_VELOCITY, t0, w["goal_angvel"]),
+              (abi.F_GOAL_LINEAR_ACCELERATION, t0, zeros3), (abi.F_GOAL_ANGULAR_ACCELERATION, t0, zeros3), (abi.F_JT_GOAL_POSITION, t1, w["jt_goal"])]
     near = NearGpu(local_rank)
     with near:
-        h_in = [(abi.F_Q, -1, pinned(w["q"])), (abi.F_DQ, -1, pinned(w["dq"])), (abi.F_GOAL_POSITION, t0, pinned(w["goal_pos"])),
-                (abi.F_GOAL_ORIENTATION, t0, pinned(w["goal_ori"])), (abi.F_JT_GOAL_POSITION, t1, pinned(w["jt_goal"]))]
-        h_tau = pinned(np.zeros((B, n)))
-    keep.clear()
-    host_buffers = "pinned; each the fastest of 4 candidates by a timed H2D copy (candidates ran %.0f-%.0f GB/s)" % (min(rates), max(rates))
-    if near.cpus:
-        host_buffers += "; allocated on the GPU's NUMA node (%d local CPUs)" % len(near.cpus)
-    h2d = sum(t.numel() * t.element_size() for _, _, t in h_in)
-    d2h = h_tau.numel() * h_tau.element_size()
+        bufs = [(f, task, pinned(a)) for f, task, a in fields]
+        tau_bufs = pinned(np.zeros((B, n)))
+    h2d = sum(t[0].numel() * t[0].element_size() for _, _, t in bufs)
+    d2h = tau_bufs[0].numel() * tau_bufs[0].element_size()
     L, h = batch.L, batch.h
 
-    def e2e_step():
-        for f, task, t in h_in:
-            L.osc_set_field(h, task, f, t.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)
-        rc = L.osc_tick(h, 1, h_tau.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)  # returns after the torques landed
-        assert rc == 0
-    for _ in range(args.warmup):
-        e2e_step()
-    barrier()
-    t_e2e = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t_e2e)
-    barrier()
+    def e2e_run(which):
+        h_in = [(f, task, t[which]) for f, task, t in bufs]
+        h_tau = tau_bufs[which]
+
+        def e2e_step():
+            for f, task, t in h_in:
+                L.osc_set_field(h, task, f, t.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)
+            rc = L.osc_tick(h, 1, h_tau.data_ptr(), abi.LAYOUT_SOA, abi.MEM_HOST)  # returns after the torques landed
+            assert rc == 0
+        for _ in range(args.warmup):
+            e2e_step()
+        barrier()
+        t_e2e = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        torch.cuda.synchronize()
+        el = max_over_ranks(time.perf_counter() - t_e2e)
+        barrier()
+        return el
+    e2e_first_s = e2e_run(0)   # the buffers as cudaHostAlloc first handed them out: the typical case
+    e2e_s = e2e_run(1)         # each buffer the fastest of 4 candidates: what an application that keeps its I/O buffers can reach
+    keep.clear()
+    host_buffers = "pinned; value = each buffer the fastest of 4 candidates by a timed H2D copy (candidates ran %.0f-%.0f GB/s); first_allocation = the first candidate of each" % (min(rates), max(rates))
+    if near.cpus:
+        host_buffers += "; allocated on the GPU's NUMA node (%d local CPUs)" % len(near.cpus)
     clocks = sampler.stop() if rank == 0 else None
     e2e_value = world * B * args.steps / e2e_s
+    e2e_first_value = world * B * args.steps / e2e_first_s
 
     # ---- roofline of the dominant kernel (its own launches timed with CUDA events, L2 flushed)
     fused = batch.tick_is_fused()
@@ -447,27 +536,28 @@ def run_b200(args, rank, world, local_rank):
     # algorithmic FLOP of each kernel per robot (whole tick = 3.6e4)
     alg = {"k_tick_fused": ALG_FLOP_PER_TICK, "k_tick_fused2": ALG_FLOP_PER_TICK, "k_model": 504 + 84 + 1680 + 686, "k_mft_update": 10800 + 504 + 1314 + 1092 + 2000,
            "k_jt_update": 15100 + 240, "k_mft_compute": 300 + 162 + 84 + 504, "k_jt_compute": 364}
-    traffic, executed = None, None
+    traffic, executed, capture = None, None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):  # per-launch figures of the committed `ncu --set full` capture of the same kernel (profiles/README.md)
         rec = json.load(open(tpath)).get(top) or {}
-        traffic, executed = rec.get("dram_bytes_per_launch"), rec.get("executed_fp64_flop_per_robot")
+        traffic, executed, capture = rec.get("dram_bytes_per_launch"), rec.get("executed_fp64_flop_per_robot"), rec.get("capture")
         if traffic is not None and rec.get("robots") and rec["robots"] != B:
             traffic = traffic * B / rec["robots"]
     t_top = stages[top] * 1e-3
-    roof = {"bound": "fp64", "kernel": top, "achieved": alg[top] * B / t_top / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-            "frac": alg[top] * B / t_top / 1e12 / fp64_peak, "traffic": traffic,
+    work = executed if executed else alg[top]  # FLOP the kernel really executes per robot (ncu SASS count); algorithmic if no capture
+    roof = {"bound": "fp64", "kernel": top, "achieved": work * B / t_top / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": work * B / t_top / 1e12 / fp64_peak, "traffic": traffic,
             "peak_source": "DFMA microbenchmark in this run (osc_measure_fp64_peak); nominal 148 SM x 64 DFMA/clk x 2 x 1.965 GHz = 37.2; "
                            "MEASURED_PEAKS.json has no FP64 entry",
-            "alg_flop_per_robot": alg[top],
-            "note": "achieved uses the frozen ALGORITHMIC count of SURVEY.md 8(d) (the reference's route, two Jacobi SVDs included), so frac "
-                    "can exceed 1 once the kernel avoids that work; executed_* is what the kernel really issues (FP64 add/mul/fma "
-                    "thread instructions of the committed ncu capture)",
+            "flop_per_robot": work,
+            "flop_source": ("FP64 add/mul/fma thread instructions of the committed ncu capture %s (profiles/traffic.json)" % capture) if executed
+                           else "algorithmic count of SURVEY.md 8(d) (no ncu capture of this kernel committed)",
+            "alg_flop_per_robot_reference_route": alg[top],
+            "alg_frac_reference_route": alg[top] * B / t_top / 1e12 / fp64_peak,
+            "note": "frac = EXECUTED FP64 work / measured DFMA peak over the bench step.  alg_frac_reference_route uses the frozen algorithmic "
+                    "count of SURVEY.md 8(d) (the reference's route with two Jacobi SVDs, 3.6e4 FLOP; the oracle's counter measures "
+                    "3.4e4) and exceeds 1 because the fused kernel does not execute that work (closed forms + a certificate instead of the SVDs)",
             "stage_ms": stages}
-    if executed:
-        roof["executed_flop_per_robot"] = executed
-        roof["executed_achieved"] = executed * B / t_top / 1e12
-        roof["executed_frac"] = roof["executed_achieved"] / fp64_peak
     roof_hbm = {"bound": "hbm", "achieved": ALG_BYTES_PER_TICK * B / (float(np.mean(step_ms)) * 1e-3) / 1e9, "peak": hbm_peak,
                 "unit": "GB/s", "peak_source": hbm_src}
     roof_hbm["frac"] = roof_hbm["achieved"] / hbm_peak
@@ -478,9 +568,13 @@ def run_b200(args, rank, world, local_rank):
                        "stacked": True, "tick_outputs": args.tick_outputs, "l2": "NOT FLUSHED (diagnostic run)" if noflush else "256 MB buffer written between timed steps (L2 flush)", "fused_tick": fused},
             "p50_tick_us": float(np.median(step_ms) * 1e3), "p99_tick_us": float(np.percentile(step_ms, 99) * 1e3),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "path": "osc_set_field x5 + osc_tick with pinned HOST SoA buffers (C ABI)",
+                    "path": "osc_set_field x9 (q, dq, six MotionForceTask goals, joint goal: all 45 input scalars of SURVEY.md 8d) + osc_tick "
+                            "with pinned HOST SoA buffers (C ABI), strictly serial on one stream",
                     "ms_per_step": e2e_s / args.steps * 1e3,
+                    "first_allocation": {"value": e2e_first_value, "ms_per_step": e2e_first_s / args.steps * 1e3},
+                    "pcie_gb_per_s": (h2d + d2h) / (e2e_s / args.steps) / 1e9,
                     "host_buffers": host_buffers},
+            "parity_sample": parity, "graph_tick": graph_tick,
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_hbm": roof_hbm}
     if otg:
         line["otg_on"] = otg

@@ -11,17 +11,19 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(os.path.dirname(_HERE), "sai2-primitives-perso_b200"))
 import osc_abi as abi  # noqa: E402
 
-_LIB = None
+_LIBS = {}
+VARIANTS = ("", "O3", "heap", "count")  # g++ -O2 (default) | -O3 -march=native | -DORACLE_HEAP_TEMPORARIES | -DORACLE_COUNT_FLOPS
 
 
 def build():
     subprocess.check_call(["make", "-s", "-C", _HERE])
 
 
-def lib():
-    global _LIB
-    if _LIB is None:
-        path = os.path.join(_HERE, "_build", "liboscoracle.so")
+def lib(variant=""):
+    """variant: "" = g++ -O2 (the checker and the default CPU baseline), "O3" = -O3 -march=native, "heap" = malloc'ed matrix
+    temporaries like Eigen's dynamic MatrixXd, "count" = operation-counting build (oracle/Makefile)"""
+    if variant not in _LIBS:
+        path = os.path.join(_HERE, "_build", "liboscoracle%s.so" % ("_" + variant if variant else ""))
         if not os.path.exists(path):
             build()
         L = C.CDLL(path)
@@ -83,8 +85,12 @@ def lib():
         L.orc_otgj_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.orc_otgc_step.restype = C.c_int
         L.orc_otgc_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
-        _LIB = L
-    return _LIB
+        L.orc_count_tick_flops.restype = C.c_longlong
+        L.orc_count_tick_flops.argtypes = [C.c_void_p, C.c_int]
+        L.orc_config1_run.restype = C.c_int
+        L.orc_config1_run.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _LIBS[variant] = L
+    return _LIBS[variant]
 
 
 REF_RUCKIG = os.path.join(_HERE, "_ref", "libruckig_ref.so")
@@ -174,8 +180,8 @@ class OtgCartesian:
 class OracleBatch:
     """B independent reference-style robots on the CPU.  Mirrors the method names of osc_b200.Batch."""
 
-    def __init__(self, chain: dict, n_robots: int, q0=None, nthreads: int = 1):
-        self.L = lib()
+    def __init__(self, chain: dict, n_robots: int, q0=None, nthreads: int = 1, variant: str = ""):
+        self.L = lib(variant)
         self.chain = chain
         self.n = chain["n"]
         self.B = int(n_robots)
@@ -291,3 +297,13 @@ class OracleBatch:
 
     def disable_internal_otg(self, task):
         self.L.orc_task_disable_internal_otg(self.h, task)
+
+    def count_tick_flops(self, stacked=True):
+        """FLOP of one tick of robot 0, counted by the primitives of the oracle (variant "count" only; -1 otherwise)"""
+        return int(self.L.orc_count_tick_flops(self.h, int(stacked)))
+
+    def config1_run(self, ticks):
+        """BASELINE config 1 (04-task_and_redundancy loop, robot 0): per-cycle wall time in microseconds"""
+        out = np.zeros(ticks)
+        self._chk(self.L.orc_config1_run(self.h, ticks, out.ctypes.data))
+        return out

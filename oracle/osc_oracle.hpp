@@ -11,6 +11,7 @@
 #pragma once
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <limits>
@@ -23,14 +24,45 @@
 
 namespace orc {
 
+// ---- operation counter ("freeze the algorithmic FLOP count by instrumenting the CPU oracle") ----
+// -DORACLE_COUNT_FLOPS: every matrix / vector primitive below adds its floating-point adds and multiplies (FMA = 2,
+// divisions and square roots = 1, transcendental calls not counted) to a thread-local counter; orc_count_tick_flops()
+// reads it around one tick.  Counting is at the granularity of the primitives (a product counts 2 r k c whatever the zeros).
+#ifdef ORACLE_COUNT_FLOPS
+inline long long& flop_counter() { static thread_local long long c = 0; return c; }
+#define ORC_OPS(n) (orc::flop_counter() += (long long)(n))
+#else
+#define ORC_OPS(n) ((void)0)
+#endif
+
+// -DORACLE_HEAP_TEMPORARIES: every matrix temporary owns a malloc'ed buffer, like the dynamic-size Eigen::MatrixXd
+// temporaries of the reference (one allocation per expression result): a closer proxy of the reference's CPU cost than the
+// default fixed-capacity storage (SURVEY.md 8d "Timing the reference CPU path beside it").
+#ifdef ORACLE_HEAP_TEMPORARIES
+struct MatBuf {
+	double* p;
+	MatBuf() : p((double*)std::malloc(64 * sizeof(double))) {}
+	MatBuf(const MatBuf& o) : p((double*)std::malloc(64 * sizeof(double))) { std::memcpy(p, o.p, 64 * sizeof(double)); }
+	MatBuf& operator=(const MatBuf& o) { if (this != &o) std::memcpy(p, o.p, 64 * sizeof(double)); return *this; }
+	~MatBuf() { std::free(p); }
+	double& operator[](int i) { return p[i]; }
+	double operator[](int i) const { return p[i]; }
+};
+#endif
+
 // ------------------------------------------------------------------------------------------------------------------
-// Tiny dense matrix with run-time shape (stands in for Eigen::MatrixXd on <= 8x8 data; no heap).
+// Tiny dense matrix with run-time shape (stands in for Eigen::MatrixXd on <= 8x8 data; no heap unless
+// ORACLE_HEAP_TEMPORARIES).
 // ------------------------------------------------------------------------------------------------------------------
 struct Mat {
 	int r = 0, c = 0;
+#ifdef ORACLE_HEAP_TEMPORARIES
+	MatBuf a;
+#else
 	double a[64];
+#endif
 	Mat() {}
-	Mat(int r_, int c_) : r(r_), c(c_) { std::fill(a, a + r * c, 0.0); }
+	Mat(int r_, int c_) : r(r_), c(c_) { for (int i = 0; i < r * c; ++i) a[i] = 0.0; }
 	double& operator()(int i, int j) { return a[i * c + j]; }
 	double operator()(int i, int j) const { return a[i * c + j]; }
 	static Mat Zero(int r, int c) { return Mat(r, c); }
@@ -46,6 +78,7 @@ struct Mat {
 		return t;
 	}
 	double norm() const {
+		ORC_OPS(2 * r * c + 1);
 		double s = 0;
 		for (int i = 0; i < r * c; ++i) s += a[i] * a[i];
 		return std::sqrt(s);
@@ -64,6 +97,7 @@ struct Mat {
 	}
 };
 inline Mat operator*(const Mat& A, const Mat& B) {
+	ORC_OPS(2LL * A.r * A.c * B.c);
 	Mat C(A.r, B.c);
 	for (int i = 0; i < A.r; ++i)
 		for (int k = 0; k < A.c; ++k) {
@@ -73,16 +107,19 @@ inline Mat operator*(const Mat& A, const Mat& B) {
 	return C;
 }
 inline Mat operator*(double s, const Mat& A) {
+	ORC_OPS(A.r * A.c);
 	Mat C = A;
 	for (int i = 0; i < A.r * A.c; ++i) C.a[i] *= s;
 	return C;
 }
 inline Mat operator+(const Mat& A, const Mat& B) {
+	ORC_OPS(A.r * A.c);
 	Mat C = A;
 	for (int i = 0; i < A.r * A.c; ++i) C.a[i] += B.a[i];
 	return C;
 }
 inline Mat operator-(const Mat& A, const Mat& B) {
+	ORC_OPS(A.r * A.c);
 	Mat C = A;
 	for (int i = 0; i < A.r * A.c; ++i) C.a[i] -= B.a[i];
 	return C;
@@ -100,16 +137,16 @@ struct V3 {
 	explicit V3(const double* p) : x(p[0]), y(p[1]), z(p[2]) {}
 	double operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
 	double& operator[](int i) { return i == 0 ? x : (i == 1 ? y : z); }
-	double norm() const { return std::sqrt(x * x + y * y + z * z); }
-	double dot(const V3& o) const { return x * o.x + y * o.y + z * o.z; }
-	V3 cross(const V3& o) const { return V3(y * o.z - z * o.y, z * o.x - x * o.z, x * o.y - y * o.x); }
+	double norm() const { ORC_OPS(6); return std::sqrt(x * x + y * y + z * z); }
+	double dot(const V3& o) const { ORC_OPS(5); return x * o.x + y * o.y + z * o.z; }
+	V3 cross(const V3& o) const { ORC_OPS(9); return V3(y * o.z - z * o.y, z * o.x - x * o.z, x * o.y - y * o.x); }
 };
-inline V3 operator+(const V3& a, const V3& b) { return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
-inline V3 operator-(const V3& a, const V3& b) { return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline V3 operator+(const V3& a, const V3& b) { ORC_OPS(3); return V3(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline V3 operator-(const V3& a, const V3& b) { ORC_OPS(3); return V3(a.x - b.x, a.y - b.y, a.z - b.z); }
 inline V3 operator-(const V3& a) { return V3(-a.x, -a.y, -a.z); }
-inline V3 operator*(double s, const V3& a) { return V3(s * a.x, s * a.y, s * a.z); }
-inline V3 operator*(const V3& a, double s) { return V3(s * a.x, s * a.y, s * a.z); }
-inline V3 cwise(const V3& a, const V3& b) { return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline V3 operator*(double s, const V3& a) { ORC_OPS(3); return V3(s * a.x, s * a.y, s * a.z); }
+inline V3 operator*(const V3& a, double s) { ORC_OPS(3); return V3(s * a.x, s * a.y, s * a.z); }
+inline V3 cwise(const V3& a, const V3& b) { ORC_OPS(3); return V3(a.x * b.x, a.y * b.y, a.z * b.z); }
 
 struct M3 {
 	double m[3][3];
@@ -128,6 +165,7 @@ struct M3 {
 		return r;
 	}
 	static M3 Outer(const V3& a, const V3& b) {
+		ORC_OPS(9);
 		M3 r;
 		for (int i = 0; i < 3; ++i)
 			for (int j = 0; j < 3; ++j) r.m[i][j] = a[i] * b[j];
@@ -142,6 +180,7 @@ struct M3 {
 	V3 col(int j) const { return V3(m[0][j], m[1][j], m[2][j]); }
 };
 inline M3 operator*(const M3& A, const M3& B) {
+	ORC_OPS(45);
 	M3 C;
 	for (int i = 0; i < 3; ++i)
 		for (int j = 0; j < 3; ++j)
@@ -149,22 +188,26 @@ inline M3 operator*(const M3& A, const M3& B) {
 	return C;
 }
 inline V3 operator*(const M3& A, const V3& v) {
+	ORC_OPS(15);
 	return V3(A.m[0][0] * v.x + A.m[0][1] * v.y + A.m[0][2] * v.z, A.m[1][0] * v.x + A.m[1][1] * v.y + A.m[1][2] * v.z,
 			  A.m[2][0] * v.x + A.m[2][1] * v.y + A.m[2][2] * v.z);
 }
 inline M3 operator+(const M3& A, const M3& B) {
+	ORC_OPS(9);
 	M3 C;
 	for (int i = 0; i < 3; ++i)
 		for (int j = 0; j < 3; ++j) C.m[i][j] = A.m[i][j] + B.m[i][j];
 	return C;
 }
 inline M3 operator-(const M3& A, const M3& B) {
+	ORC_OPS(9);
 	M3 C;
 	for (int i = 0; i < 3; ++i)
 		for (int j = 0; j < 3; ++j) C.m[i][j] = A.m[i][j] - B.m[i][j];
 	return C;
 }
 inline M3 operator*(double s, const M3& A) {
+	ORC_OPS(9);
 	M3 C;
 	for (int i = 0; i < 3; ++i)
 		for (int j = 0; j < 3; ++j) C.m[i][j] = s * A.m[i][j];
@@ -177,6 +220,7 @@ inline M3 operator*(double s, const M3& A) {
 // A.llt().solve(Identity): Lambda in Sai2Model::operationalSpaceMatrices
 inline Mat llt_solve_identity(const Mat& A) {
 	const int n = A.r;
+	ORC_OPS(n * n * n / 3 + 2LL * n * n * n);
 	Mat L(n, n);
 	for (int j = 0; j < n; ++j) {
 		double d = A(j, j);
@@ -210,6 +254,7 @@ inline Mat llt_solve_identity(const Mat& A) {
 // (used at SingularityHandler.cpp:120,182,190,201,212; JointTask.cpp:260-265)
 inline Mat lu_inverse(const Mat& A) {
 	const int n = A.r;
+	ORC_OPS(2LL * n * n * n / 3 + 2LL * n * n * n);
 	Mat LU = A;
 	int piv[8];
 	for (int i = 0; i < n; ++i) piv[i] = i;
@@ -267,6 +312,7 @@ inline Svd jacobi_svd(const Mat& A) {
 		bool rotated = false;
 		for (int p = 0; p < n - 1; ++p)
 			for (int q = p + 1; q < n; ++q) {
+				ORC_OPS(6 * m);
 				double al = 0, be = 0, ga = 0;
 				for (int i = 0; i < m; ++i) {
 					al += W(i, p) * W(i, p);
@@ -275,6 +321,7 @@ inline Svd jacobi_svd(const Mat& A) {
 				}
 				if (ga == 0.0 || al <= negl || be <= negl || std::fabs(ga) <= 1e-15 * std::sqrt(al * be)) continue;
 				rotated = true;
+				ORC_OPS(14 + 6 * m + 6 * n);
 				double zeta = (be - al) / (2.0 * ga);
 				double t = (zeta >= 0 ? 1.0 : -1.0) / (std::fabs(zeta) + std::sqrt(1.0 + zeta * zeta));
 				double cs = 1.0 / std::sqrt(1.0 + t * t), sn = cs * t;

@@ -3,6 +3,7 @@
 // much simpler calling convention: all per-robot buffers are host double arrays in AOS layout [B][k].
 // "One thread per robot instance": the batch is statically partitioned over `nthreads` std::threads and every robot
 // owns its model copy and task objects.
+#include <chrono>
 #include <string>
 #include <thread>
 
@@ -258,7 +259,7 @@ int orc_tick(orc_batch* b, int stacked, int nthreads) {
 	return 0;
 }
 int orc_rollout_step(orc_batch* b, double dt, int substeps, double damping, int nthreads) {
-	parallel_for(b, nthreads, [=](Robot& r) { r.model.rolloutStep(r.tau.a, dt, substeps, damping, r.nle); });
+	parallel_for(b, nthreads, [=](Robot& r) { r.model.rolloutStep(&r.tau.a[0], dt, substeps, damping, r.nle); });
 	return 0;
 }
 int orc_nonlinear_effects(orc_batch* b, double* out) {
@@ -358,6 +359,78 @@ int orc_otgc_step(void* h, const double* gp, const double* gR, const double* gv,
 	o->getNextAngularAcceleration(out + 21);
 	flags[0] = o->goal_reached ? 1 : 0;
 	return o->result_value;
+}
+
+// FLOP of one control tick of robot 0 (updateModel + updateControllerTaskModels + computeControlTorques), counted by the
+// primitives of osc_oracle.hpp; -1 unless this library was built with -DORACLE_COUNT_FLOPS (make count).
+long long orc_count_tick_flops(orc_batch* b, int stacked) {
+#ifdef ORACLE_COUNT_FLOPS
+	Robot& r = *b->robots[0];
+	const long long before = flop_counter();
+	r.model.updateModel();
+	r.updateControllerTaskModels();
+	r.computeControlTorques(stacked != 0);
+	return flop_counter() - before;
+#else
+	(void)b; (void)stacked;
+	return -1;
+#endif
+}
+
+// BASELINE config 1 on the CPU: ONE robot (robot 0 of the batch, hierarchy [MotionForceTask, JointTask] already added), `ticks`
+// cycles of the control loop of examples/04-task_and_redundancy/04-task_and_redundancy.cpp:133-206 -- setQ/setDq (kinematic
+// playback q0 + amp sin(w_j t): no simulator here), updateModel, the two updateTaskModel calls, the goal generator of
+// :155-185 (orientation +-pi/8 about Y at 0.2 Hz, circle r = 0.05 m at 0.33 Hz in y-z), the two computeTorques calls, the
+// joint goal step at cycle 5000 (:196-201) -- with every cycle timed by steady_clock into out_us[ticks].
+int orc_config1_run(orc_batch* b, int ticks, double* out_us) {
+	Robot& r = *b->robots[0];
+	if (r.tasks.size() != 2 || r.tasks[0]->type != OSC_TASK_MOTION_FORCE) { g_err = "config 1 needs [MotionForceTask, JointTask]"; return -1; }
+	auto* m = static_cast<MotionForceTask*>(r.tasks[0]);
+	auto* j = static_cast<JointTask*>(r.tasks[1]);
+	const int n = b->n;
+	double q0[8];
+	for (int i = 0; i < n; ++i) q0[i] = r.model.q[i];
+	r.model.updateModel();
+	m->reInitializeTask(); j->reInitializeTask();
+	const V3 x0 = m->x;
+	const M3 R0 = m->R;
+	const double wj[8] = {0.11, 0.13, 0.17, 0.19, 0.23, 0.29, 0.31, 0.37}, amp[8] = {0.3, 0.15, 0.3, 0.09, 0.3, 0.15, 0.3, 0.1};
+	const double two_pi = 6.283185307179586;
+	for (int tick = 0; tick < ticks; ++tick) {
+		const double t = tick * 0.001;
+		const auto t_start = std::chrono::steady_clock::now();
+		for (int i = 0; i < n; ++i) {
+			r.model.q[i] = q0[i] + amp[i] * std::sin(two_pi * wj[i] * t);
+			r.model.dq[i] = amp[i] * two_pi * wj[i] * std::cos(two_pi * wj[i] * t);
+		}
+		r.model.updateModel();
+		Mat N_prec = Mat::Identity(n);
+		m->updateTaskModel(N_prec);
+		N_prec = m->getTaskAndPreviousNullspace();
+		j->updateTaskModel(N_prec);
+		const double w_o = two_pi * 0.2, a_o = 3.141592653589793 / 8;
+		const double ang = a_o * std::sin(w_o * t), angv = a_o * w_o * std::cos(w_o * t), anga = -a_o * w_o * w_o * std::sin(w_o * t);
+		M3 Ry = M3::Identity();
+		Ry.m[0][0] = std::cos(ang); Ry.m[0][2] = std::sin(ang); Ry.m[2][0] = -std::sin(ang); Ry.m[2][2] = std::cos(ang);
+		m->goal_ori = Ry.T() * R0;
+		m->goal_angvel = V3(0, angv, 0);
+		m->goal_angacc = V3(0, anga, 0);
+		const double rad = 0.05, w_c = two_pi * 0.33;
+		m->goal_pos = x0 + rad * V3(0, std::sin(w_c * t), 1 - std::cos(w_c * t));
+		m->goal_linvel = (rad * w_c) * V3(0, std::cos(w_c * t), std::sin(w_c * t));
+		m->goal_linacc = (rad * w_c * w_c) * V3(0, -std::sin(w_c * t), std::cos(w_c * t));
+		Mat tau = m->computeTorques();
+		Mat tj = j->computeTorques();
+		if (tick >= 5000) tau = tau + tj;
+		if (tick == 5000) {
+			j->reInitializeTask();
+			for (int i = 0; i < n; ++i) j->goal_pos[i] = q0[i];
+			j->goal_pos[0] += 1.5;
+		}
+		r.tau = tau;
+		out_us[tick] = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_start).count();
+	}
+	return 0;
 }
 
 int orc_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
