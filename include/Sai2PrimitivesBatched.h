@@ -70,6 +70,12 @@ public:
 	RobotBatch(const osc_chain_desc& chain, int64_t n_robots, int precision = OSC_PRECISION_F64, int device = 0, const double* q0 = nullptr) {
 		check(osc_batch_create(&chain, n_robots, precision, device, q0, &_h));
 	}
+	// the same batch sharded over several GPUs of one box (osc_batch_create_multi): every call of this facade fans out over the
+	// devices, one host thread and one stream per device inside the library; buffers are HOST buffers spanning all robots
+	RobotBatch(const osc_chain_desc& chain, int64_t n_robots, const std::vector<int>& devices, int precision = OSC_PRECISION_F64, const double* q0 = nullptr) {
+		check(osc_batch_create_multi(&chain, n_robots, precision, devices.data(), (int)devices.size(), q0, &_h));
+	}
+	int shardCount() const { return osc_batch_shard_count(_h); }
 	~RobotBatch() { osc_batch_destroy(_h); }
 	RobotBatch(const RobotBatch&) = delete;
 	RobotBatch& operator=(const RobotBatch&) = delete;

@@ -236,6 +236,20 @@ int osc_version(void);
 int osc_device_count(void);
 /* Sai2Model(urdf) + B copies of the robot on `device`; q is initialised to q0 (may be NULL = zeros), dq to zero. */
 int osc_batch_create(const osc_chain_desc* chain, int64_t n_robots, int precision, int device, const double* q0, osc_batch_t** out);
+/* The same batch sharded over several GPUs of one box (independent robots, contiguous shards
+ * [k B / G, (k + 1) B / G), one host thread + one stream per device, no inter-GPU traffic, no collective).  The handle is an
+ * ordinary osc_batch_t: EVERY entry point of this header accepts it and fans out over the shards from one thread per device;
+ * per-robot HOST buffers span all n_robots (AOS [B][k], SOA [k][B] or UNIFORM [k]) and each shard reads / writes its own
+ * slice; a call that writes a host buffer returns when every shard's slice has landed.  Device buffers belong to one device:
+ * a multi-device batch rejects OSC_MEM_DEVICE (OSC_ERR_UNSUPPORTED) -- use osc_batch_shard() for per-device calls and streams.
+ * The reference drives one robot from one thread (src/RobotController.h:24-42); this is its batch-of-robots-on-8-GPUs form.
+ * device_ids may repeat a device (two shards on one GPU: used by the single-GPU tests). */
+int osc_batch_create_multi(const osc_chain_desc* chain, int64_t n_robots, int precision, const int* device_ids, int n_devices, const double* q0,
+                           osc_batch_t** out);
+/* number of shards (1 for a single-device batch) and shard k itself: an ordinary single-device batch handle owned by the parent
+ * (never destroy it), with its device, first robot and robot count; NULL if k is out of range */
+int osc_batch_shard_count(const osc_batch_t* batch);
+osc_batch_t* osc_batch_shard(osc_batch_t* batch, int k, int* device, int64_t* first_robot, int64_t* n_robots);
 void osc_batch_destroy(osc_batch_t* batch);
 int osc_batch_set_stream(osc_batch_t* batch, void* cuda_stream);
 int osc_synchronize(osc_batch_t* batch);

@@ -7,6 +7,7 @@
 #include <new>
 
 #include "osc_capi_util.h"
+#include "osc_capi_multi.h"
 
 using namespace osc;
 
@@ -65,10 +66,17 @@ int osc_batch_create(const osc_chain_desc* chain, int64_t n_robots, int precisio
 void osc_batch_destroy(osc_batch_t* batch) {
 	Batch* b = (Batch*)batch;
 	if (!b) return;
+	if (is_multi(b)) {
+		delete b->pool;  // joins the shard threads
+		for (Batch* s : b->shards) osc_batch_destroy((osc_batch_t*)s);
+		delete b;
+		return;
+	}
 	cudaSetDevice(b->device);
 	cudaStreamSynchronize(b->stream);
 	for (TaskH& t : b->tasks) { cudaFree(t.P); cudaFree(t.S); cudaFree(t.I); cudaFree(t.popc_ring); cudaFree(t.otgO); cudaFree(t.otgI); cudaFree(t.otgG); cudaFree(t.otg_slow); }
 	cudaFree(b->P); cudaFree(b->S); cudaFree(b->I); cudaFree(b->stage); cudaFree(b->stage2); cudaFree(b->fb);
+	if (b->owned_stream) cudaStreamDestroy(b->owned_stream);
 	delete b->ops;
 	delete b;
 }
@@ -76,12 +84,14 @@ void osc_batch_destroy(osc_batch_t* batch) {
 int osc_batch_set_stream(osc_batch_t* batch, void* s) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
+	if (is_multi(b)) return invalid("a multi-device batch has one stream per device: set it on osc_batch_shard(batch, k)");
 	b->stream = (cudaStream_t)s;
 	return OSC_OK;
 }
 int osc_synchronize(osc_batch_t* batch) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
+	if (is_multi(b)) return multi_fan(b, [](osc_batch_t* s, int) { return osc_synchronize(s); });
 	if (int rc = use_device(*b)) return rc;
 	OSC_CUDA(cudaStreamSynchronize(b->stream));
 	return OSC_OK;
@@ -89,14 +99,26 @@ int osc_synchronize(osc_batch_t* batch) {
 int64_t osc_batch_size(const osc_batch_t* b) { return b ? ((const Batch*)b)->B : 0; }
 int osc_batch_dof(const osc_batch_t* b) { return b ? ((const Batch*)b)->n : 0; }
 int osc_batch_precision(const osc_batch_t* b) { return b ? ((const Batch*)b)->precision : 0; }
-int64_t osc_launch_count(const osc_batch_t* b) { return b ? ((const Batch*)b)->launches : 0; }
-int osc_batch_task_count(const osc_batch_t* b) { return b ? (int)((const Batch*)b)->tasks.size() : 0; }
+int64_t osc_launch_count(const osc_batch_t* b) {
+	if (is_multi(b)) {
+		int64_t n = 0;
+		for (const Batch* s : ((const Batch*)b)->shards) n += s->launches;
+		return n;
+	}
+	return b ? ((const Batch*)b)->launches : 0;
+}
+int osc_batch_task_count(const osc_batch_t* b) {
+	if (is_multi(b)) b = (const osc_batch_t*)shard0(b);
+	return b ? (int)((const Batch*)b)->tasks.size() : 0;
+}
 int osc_batch_task_type(const osc_batch_t* batch, int task) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	const Batch* b = (const Batch*)batch;
 	if (!b || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
 	return b->tasks[task].type;
 }
 int osc_batch_task_dof(const osc_batch_t* batch, int task) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	const Batch* b = (const Batch*)batch;
 	if (!b || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
 	return b->tasks[task].dof;
@@ -104,8 +126,60 @@ int osc_batch_task_dof(const osc_batch_t* batch, int task) {
 int osc_enable_gravity_compensation(osc_batch_t* batch, int enable) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
+	if (is_multi(b)) return multi_fan(b, [=](osc_batch_t* s, int) { return osc_enable_gravity_compensation(s, enable); });
 	b->gravity = enable != 0;
 	return OSC_OK;
+}
+
+int osc_batch_create_multi(const osc_chain_desc* chain, int64_t n_robots, int precision, const int* device_ids, int n_devices, const double* q0,
+						   osc_batch_t** out) {
+	if (!chain || !out || !device_ids) return invalid("null argument in osc_batch_create_multi");
+	*out = nullptr;
+	if (n_devices < 1 || n_devices > 64) return invalid("n_devices must be between 1 and 64");
+	if (n_robots < n_devices) return invalid("fewer robots than devices");
+	Batch* p = new (std::nothrow) Batch();
+	if (!p) return invalid("out of host memory");
+	p->n = chain->n; p->B = n_robots; p->precision = precision; p->esz = precision == OSC_PRECISION_F64 ? 8 : 4;
+	p->chain_user = *chain; p->device = device_ids[0];
+	for (int k = 0; k < n_devices; ++k) {  // contiguous shards [k B / G, (k + 1) B / G)  
+		const int64_t lo = n_robots * k / n_devices, hi = n_robots * (k + 1) / n_devices;
+		osc_batch_t* s = nullptr;
+		const int rc = osc_batch_create(chain, hi - lo, precision, device_ids[k], q0, &s);
+		if (rc != OSC_OK) {
+			for (Batch* t : p->shards) osc_batch_destroy((osc_batch_t*)t);
+			delete p;
+			return rc;
+		}
+		// its own non-blocking stream, so that shards on one device (tests) and the default stream do not serialise each other
+		cudaStream_t st = nullptr;
+		if (cudaSetDevice(device_ids[k]) == cudaSuccess && cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess) {
+			cudaStreamSynchronize(((Batch*)s)->stream);
+			((Batch*)s)->stream = st;
+			((Batch*)s)->owned_stream = st;
+		}
+		p->shards.push_back((Batch*)s);
+		p->shard_first.push_back(lo);
+	}
+	p->pool = new MultiPool(n_devices);
+	*out = (osc_batch_t*)p;
+	return OSC_OK;
+}
+int osc_batch_shard_count(const osc_batch_t* batch) { return is_multi(batch) ? (int)((const Batch*)batch)->shards.size() : (batch ? 1 : 0); }
+osc_batch_t* osc_batch_shard(osc_batch_t* batch, int k, int* device, int64_t* first_robot, int64_t* n_robots) {
+	Batch* b = (Batch*)batch;
+	if (!b) return nullptr;
+	if (!is_multi(b)) {
+		if (k != 0) return nullptr;
+		if (device) *device = b->device;
+		if (first_robot) *first_robot = 0;
+		if (n_robots) *n_robots = b->B;
+		return batch;
+	}
+	if (k < 0 || k >= (int)b->shards.size()) return nullptr;
+	if (device) *device = b->shards[k]->device;
+	if (first_robot) *first_robot = b->shard_first[k];
+	if (n_robots) *n_robots = b->shards[k]->B;
+	return (osc_batch_t*)b->shards[k];
 }
 
 }  // extern "C"
@@ -144,6 +218,10 @@ static int noalloc_scratch(int device, int** out) {
 extern "C" int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_device, int layout) {
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
+	if (is_multi(b)) {
+		if (tau_out_device) return invalid("osc_tick_noalloc on a multi-device batch takes no output pointer (device memory belongs to one device): read OSC_F_TAU");
+		return multi_fan(b, [=](osc_batch_t* s, int) { return osc_tick_noalloc(s, stacked, nullptr, layout); });
+	}
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
 	if (b->stride > OSC_NOALLOC_MAX_ROBOTS) return invalid("osc_tick_noalloc: the batch has more than OSC_NOALLOC_MAX_ROBOTS (262144) robots; use osc_tick");
 	if (tau_out_device && layout != OSC_LAYOUT_AOS && layout != OSC_LAYOUT_SOA) return invalid("osc_tick_noalloc: tau_out layout must be AOS or SOA");

@@ -17,6 +17,7 @@ static bool lazily_materialised(int task, int field) {
 extern "C" {
 
 int osc_field_size(const osc_batch_t* batch, int task, int field) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	Loc l;
@@ -25,6 +26,19 @@ int osc_field_size(const osc_batch_t* batch, int task, int field) {
 }
 
 int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (!data) return invalid("null argument");
+		if (int rc = multi_host_only(mem)) return rc;
+		Loc l;
+		if (!shard0(p)->ops->locate(*shard0(p), task, field, l)) return invalid("unknown field for this task");
+		const size_t esz = l.is_int ? 4 : p->esz;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const int rc = osc_set_field(s, task, field, multi_slice(p, k, data, l.width, layout, esz), layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !data) return invalid("null argument");
 	Loc l;
@@ -36,6 +50,19 @@ int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int
 }
 
 int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (!out) return invalid("null argument");
+		if (int rc = multi_host_only(mem)) return rc;
+		Loc l;
+		if (!shard0(p)->ops->locate(*shard0(p), task, field, l)) return invalid("unknown field for this task");
+		const size_t esz = l.is_int ? 4 : p->esz;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const int rc = osc_get_field(s, task, field, multi_slice(p, k, out, l.width, layout, esz), layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !out) return invalid("null argument");
 	Loc l;
@@ -56,6 +83,18 @@ int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout
 }
 
 int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const void* force, const void* moment, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (!force || !moment) return invalid("null argument");
+		if (int rc = multi_host_only(mem)) return rc;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const void* f = multi_slice(p, k, force, 3, layout, p->esz);
+			const void* m = multi_slice(p, k, moment, 3, layout, p->esz);
+			const int rc = osc_mft_update_sensed_force_and_moment(s, task, f, m, layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !force || !moment) return invalid("null argument");
 	if (task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_MOTION_FORCE) return invalid("not a MotionForceTask");

@@ -95,6 +95,7 @@ void osc_joint_task_default_params(osc_joint_task_params* p, int k) {  // JointT
 }
 
 int osc_batch_add_motion_force_task(osc_batch_t* batch, const osc_mft_desc* d) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_batch_add_motion_force_task(s, d); });
 	Batch* b = (Batch*)batch;
 	if (!b || !d) return invalid("null argument");
 	if (d->body < 0 || d->body >= b->n) return invalid("control link body index out of range");
@@ -131,6 +132,7 @@ int osc_batch_add_motion_force_task(osc_batch_t* batch, const osc_mft_desc* d) {
 }
 
 int osc_batch_add_joint_task(osc_batch_t* batch, const osc_joint_task_desc* d) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_batch_add_joint_task(s, d); });
 	Batch* b = (Batch*)batch;
 	if (!b || !d) return invalid("null argument");
 	TaskH t;
@@ -173,6 +175,7 @@ int osc_batch_add_joint_task(osc_batch_t* batch, const osc_joint_task_desc* d) {
 }
 
 int osc_mft_get_params(const osc_batch_t* batch, int task, osc_mft_params* out) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	const Batch* b = (const Batch*)batch;
 	if (!b || !out || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_MOTION_FORCE) return invalid("not a MotionForceTask");
 	*out = b->tasks[task].mp;
@@ -180,6 +183,7 @@ int osc_mft_get_params(const osc_batch_t* batch, int task, osc_mft_params* out) 
 }
 
 int osc_mft_set_params(osc_batch_t* batch, int task, const osc_mft_params* np) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_mft_set_params(s, task, np); });
 	Batch* b = (Batch*)batch;
 	if (!b || !np || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_MOTION_FORCE) return invalid("not a MotionForceTask");
 	TaskH& t = b->tasks[task];
@@ -234,6 +238,7 @@ int osc_mft_set_params(osc_batch_t* batch, int task, const osc_mft_params* np) {
 }
 
 int osc_task_enable_internal_otg_acceleration_limited(osc_batch_t* batch, int task, const double* limits, int count) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_enable_internal_otg_acceleration_limited(s, task, limits, count); });
 	Batch* b = (Batch*)batch;
 	if (!b || !limits || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
 	TaskH& t = b->tasks[task];
@@ -282,6 +287,7 @@ int osc_task_enable_internal_otg_jerk_limited(osc_batch_t* batch, int task, cons
 	return OSC_ERR_UNSUPPORTED;
 }
 int osc_task_disable_internal_otg(osc_batch_t* batch, int task) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_disable_internal_otg(s, task); });
 	Batch* b = (Batch*)batch;
 	if (!b || task < 0 || task >= (int)b->tasks.size()) return invalid("task index out of range");
 	TaskH& t = b->tasks[task];
@@ -292,18 +298,21 @@ int osc_task_disable_internal_otg(osc_batch_t* batch, int task) {
 	return OSC_OK;
 }
 int osc_task_internal_otg_enabled(const osc_batch_t* batch, int task) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	const Batch* b = (const Batch*)batch;
 	if (!b || task < 0 || task >= (int)b->tasks.size()) return 0;
 	return b->tasks[task].otg_on ? 1 : 0;
 }
 
 int osc_joint_task_get_params(const osc_batch_t* batch, int task, osc_joint_task_params* out) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	const Batch* b = (const Batch*)batch;
 	if (!b || !out || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_JOINT) return invalid("not a JointTask");
 	*out = b->tasks[task].jp;
 	return OSC_OK;
 }
 int osc_joint_task_set_params(osc_batch_t* batch, int task, const osc_joint_task_params* p) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_joint_task_set_params(s, task, p); });
 	Batch* b = (Batch*)batch;
 	if (!b || !p || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_JOINT) return invalid("not a JointTask");
 	TaskH& t = b->tasks[task];

@@ -17,6 +17,7 @@ static int emit_tau(Batch& b, void* tau_out, int layout, int mem) {
 extern "C" {
 
 int osc_update_model(osc_batch_t* batch) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_model(s); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (int rc = use_device(*b)) return rc;
@@ -24,6 +25,7 @@ int osc_update_model(osc_batch_t* batch) {
 	return b->ops->model(*b, 1);
 }
 int osc_update_kinematics(osc_batch_t* batch) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_kinematics(s); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (int rc = use_device(*b)) return rc;
@@ -31,6 +33,7 @@ int osc_update_kinematics(osc_batch_t* batch) {
 	return b->ops->model(*b, 0);
 }
 int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_update_model(s, task, n_prec_task); });
 	Batch* b = (Batch*)batch;
 	if (int rc = check_task(b, task)) return rc;
 	if (n_prec_task >= (int)b->tasks.size() || n_prec_task == task)
@@ -39,7 +42,8 @@ int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
 	if (int rc = b->ops->materialise(*b)) return rc;
 	return b->ops->task_update(*b, task, n_prec_task < 0 ? -1 : n_prec_task);
 }
-int osc_update_task_models(osc_batch_t* batch) {  // RobotController.cpp:53-60
+int osc_update_task_models(osc_batch_t* batch) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_task_models(s); });  // RobotController.cpp:53-60
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
@@ -50,6 +54,7 @@ int osc_update_task_models(osc_batch_t* batch) {  // RobotController.cpp:53-60
 	return OSC_OK;
 }
 int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_compute_torques(s, task, with_tau_prec); });
 	Batch* b = (Batch*)batch;
 	if (int rc = check_task(b, task)) return rc;
 	if (int rc = use_device(*b)) return rc;
@@ -58,7 +63,17 @@ int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
 		if (int rc = b->ops->otg_tick(*b, task)) return rc;
 	return b->ops->task_compute(*b, task, with_tau_prec, 0);
 }
-int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {  // RobotController.cpp:62-74
+int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (tau_out)
+			if (int rc = multi_host_only(mem)) return rc;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const int rc = osc_compute_torques(s, stacked, multi_slice(p, k, tau_out, p->n, layout, p->esz), layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}  // RobotController.cpp:62-74
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
@@ -74,10 +89,21 @@ int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layo
 	return emit_tau(*b, tau_out, layout, mem);
 }
 int osc_tick_is_fused(const osc_batch_t* batch) {
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
 	Batch* b = (Batch*)batch;
 	return b && b->ops->fused_supported(*b) ? 1 : 0;
 }
 int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (tau_out)
+			if (int rc = multi_host_only(mem)) return rc;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const int rc = osc_tick(s, stacked, multi_slice(p, k, tau_out, p->n, layout, p->esz), layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (b->tasks.empty()) return invalid("RobotController must have at least one task");
@@ -93,6 +119,7 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
 }
 int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_damping) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_rollout_step(s, dt, substeps, joint_damping); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (!(dt > 0) || substeps < 1 || substeps > 1000 || joint_damping < 0) return invalid("rollout step: dt > 0, 1 <= substeps <= 1000, damping >= 0");
@@ -100,6 +127,16 @@ int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_d
 	return b->ops->rollout_step(*b, dt, substeps, joint_damping);
 }
 int osc_rollout(osc_batch_t* batch, int stacked, int ticks, double sim_dt, int substeps, double joint_damping, void* tau_out, int layout, int mem) {
+	if (is_multi(batch)) {
+		Batch* p = (Batch*)batch;
+		if (tau_out)
+			if (int rc = multi_host_only(mem)) return rc;
+		return multi_fan(p, [=](osc_batch_t* s, int k) {
+			const int rc = osc_rollout(s, stacked, ticks, sim_dt, substeps, joint_damping, multi_slice(p, k, tau_out, p->n, layout, p->esz), layout, mem);
+			((Batch*)s)->io_pitch = 0;
+			return rc;
+		});
+	}
 	if (ticks < 1) return invalid("rollout: ticks >= 1");
 	for (int t = 0; t < ticks; ++t) {
 		if (int rc = osc_tick(batch, stacked, t == ticks - 1 ? tau_out : nullptr, layout, mem)) return rc;
@@ -108,6 +145,7 @@ int osc_rollout(osc_batch_t* batch, int stacked, int ticks, double sim_dt, int s
 	return OSC_OK;
 }
 int osc_batch_set_tick_outputs(osc_batch_t* batch, int outputs) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_batch_set_tick_outputs(s, outputs); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (outputs != OSC_TICK_OUTPUTS_ALL && outputs != OSC_TICK_OUTPUTS_LAZY && outputs != OSC_TICK_OUTPUTS_TAU)
@@ -116,6 +154,15 @@ int osc_batch_set_tick_outputs(osc_batch_t* batch, int outputs) {
 	return OSC_OK;
 }
 int64_t osc_tick_fallback_count(osc_batch_t* batch) {
+	if (is_multi(batch)) {
+		int64_t n = 0;
+		for (Batch* s : ((Batch*)batch)->shards) {
+			const int64_t c = osc_tick_fallback_count((osc_batch_t*)s);
+			if (c < 0) return c;
+			n += c;
+		}
+		return n;
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !b->fb) return 0;
 	if (use_device(*b)) return -1;
@@ -126,6 +173,7 @@ int64_t osc_tick_fallback_count(osc_batch_t* batch) {
 }
 
 int osc_reinitialize_tasks(osc_batch_t* batch, int task) {
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_reinitialize_tasks(s, task); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (task >= (int)b->tasks.size()) return invalid("task index out of range");
@@ -167,11 +215,24 @@ static int64_t snapshot_walk(Batch& b, char* buf, int mem, int dir) {
 	return off;
 }
 int64_t osc_snapshot_bytes(const osc_batch_t* batch) {
+	if (is_multi(batch)) {
+		int64_t n = 0;
+		for (Batch* s : ((Batch*)batch)->shards) n += osc_snapshot_bytes((osc_batch_t*)s);
+		return n;
+	}
 	Batch* b = (Batch*)batch;
 	if (!b) return 0;
 	return snapshot_walk(*b, nullptr, OSC_MEM_DEVICE, 0);
 }
 int osc_snapshot(osc_batch_t* batch, void* dst, int mem) {
+	if (is_multi(batch)) {  // the shards' snapshots back to back, in shard order
+		Batch* p = (Batch*)batch;
+		if (!dst) return invalid("null argument");
+		if (int rc = multi_host_only(mem)) return rc;
+		std::vector<int64_t> off(p->shards.size(), 0);
+		for (size_t k = 1; k < off.size(); ++k) off[k] = off[k - 1] + osc_snapshot_bytes((osc_batch_t*)p->shards[k - 1]);
+		return multi_fan(p, [=, &off](osc_batch_t* s, int k) { return osc_snapshot(s, (char*)dst + off[k], mem); });
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !dst) return invalid("null argument");
 	if (int rc = use_device(*b)) return rc;
@@ -180,6 +241,14 @@ int osc_snapshot(osc_batch_t* batch, void* dst, int mem) {
 	return OSC_OK;
 }
 int osc_restore(osc_batch_t* batch, const void* src, int mem) {
+	if (is_multi(batch)) {  // the shards' snapshots back to back, in shard order
+		Batch* p = (Batch*)batch;
+		if (!src) return invalid("null argument");
+		if (int rc = multi_host_only(mem)) return rc;
+		std::vector<int64_t> off(p->shards.size(), 0);
+		for (size_t k = 1; k < off.size(); ++k) off[k] = off[k - 1] + osc_snapshot_bytes((osc_batch_t*)p->shards[k - 1]);
+		return multi_fan(p, [=, &off](osc_batch_t* s, int k) { return osc_restore(s, (const char*)src + off[k], mem); });
+	}
 	Batch* b = (Batch*)batch;
 	if (!b || !src) return invalid("null argument");
 	if (int rc = use_device(*b)) return rc;

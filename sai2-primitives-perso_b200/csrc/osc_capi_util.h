@@ -163,6 +163,10 @@ template <class E> int import_rows_t(Batch& b, E* rows, int w, const void* data,
 	}
 	if (layout == OSC_LAYOUT_SOA) {
 		const cudaMemcpyKind kind = mem == OSC_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+		if (b.io_pitch) {  // a shard's columns of its parent's [k][B_total] buffer
+			OSC_CUDA(cudaMemcpy2DAsync(rows, (size_t)b.stride * sizeof(E), data, (size_t)b.io_pitch * sizeof(E), (size_t)b.B * sizeof(E), w, kind, b.stream));
+			return OSC_OK;
+		}
 		if (b.stride == b.B) {  // rows are contiguous: one linear copy (the 2-D engine path is slower over PCIe)
 			OSC_CUDA(cudaMemcpyAsync(rows, data, (size_t)b.B * sizeof(E) * w, kind, b.stream));
 			return OSC_OK;
@@ -191,7 +195,10 @@ inline int import_rows(Batch& b, void* rows, int w, bool is_int, const void* dat
 
 template <class E> int export_rows_t(Batch& b, const E* rows, int w, void* out, int layout, int mem) {
 	const dim3 g((unsigned)((b.B + 255) / 256));
-	if (layout == OSC_LAYOUT_SOA && b.stride == b.B) {
+	if (layout == OSC_LAYOUT_SOA && b.io_pitch) {
+		OSC_CUDA(cudaMemcpy2DAsync(out, (size_t)b.io_pitch * sizeof(E), rows, (size_t)b.stride * sizeof(E), (size_t)b.B * sizeof(E), w,
+								   mem == OSC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, b.stream));
+	} else if (layout == OSC_LAYOUT_SOA && b.stride == b.B) {
 		OSC_CUDA(cudaMemcpyAsync(out, rows, (size_t)b.B * sizeof(E) * w, mem == OSC_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, b.stream));
 	} else if (layout == OSC_LAYOUT_SOA) {
 		OSC_CUDA(cudaMemcpy2DAsync(out, (size_t)b.B * sizeof(E), rows, (size_t)b.stride * sizeof(E), (size_t)b.B * sizeof(E), w,

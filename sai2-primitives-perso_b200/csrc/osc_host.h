@@ -106,6 +106,14 @@ struct Batch {
 	void* stage2 = nullptr; size_t stage2_bytes = 0;
 	void* ensure_stage(size_t bytes);
 	void* ensure_stage2(size_t bytes);
+	// ---- multi-device batch (osc_batch_create_multi): a parent owns one shard batch per device and a pool of one host
+	// thread per shard; every entry point fans out over the shards (osc_capi_multi.h).  A parent holds no device memory.
+	std::vector<Batch*> shards;
+	std::vector<int64_t> shard_first;  // first robot of shard k in the parent's numbering
+	struct MultiPool* pool = nullptr;
+	// SOA user buffers of a shard call made by its parent: rows are `io_pitch` elements apart (0 = this batch's own size)
+	int64_t io_pitch = 0;
+	cudaStream_t owned_stream = nullptr;  // created for a shard by osc_batch_create_multi, destroyed with it
 };
 
 void set_error(const std::string& msg);

@@ -41,6 +41,9 @@ def lib():
         "osc_version": (i, []),
         "osc_device_count": (i, []),
         "osc_batch_create": (i, [C.POINTER(abi.ChainDesc), i64, i, i, C.POINTER(C.c_double), C.POINTER(vp)]),
+        "osc_batch_create_multi": (i, [C.POINTER(abi.ChainDesc), i64, i, C.POINTER(C.c_int), i, C.POINTER(C.c_double), C.POINTER(vp)]),
+        "osc_batch_shard_count": (i, [vp]),
+        "osc_batch_shard": (vp, [vp, i, C.POINTER(C.c_int), C.POINTER(i64), C.POINTER(i64)]),
         "osc_batch_destroy": (None, [vp]),
         "osc_batch_set_stream": (i, [vp, vp]),
         "osc_synchronize": (i, [vp]),
@@ -95,7 +98,7 @@ def lib():
     return L
 
 
-EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_create", "osc_batch_destroy",
+EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_create", "osc_batch_create_multi", "osc_batch_shard_count", "osc_batch_shard", "osc_batch_destroy",
             "osc_batch_set_stream", "osc_synchronize", "osc_batch_size", "osc_batch_dof", "osc_batch_precision",
             "osc_batch_add_motion_force_task", "osc_batch_add_joint_task", "osc_batch_task_count", "osc_batch_task_type",
             "osc_batch_task_dof", "osc_mft_default_params", "osc_joint_task_default_params", "osc_mft_get_params",
@@ -121,7 +124,9 @@ def measure_fp64_peak(device=0):
 class Batch:
     """B robots on one GPU.  Method names follow the C ABI; host numpy arrays are AOS [B, k]."""
 
-    def __init__(self, chain: dict, n_robots: int, precision=abi.PRECISION_F64, device=0, q0=None):
+    def __init__(self, chain: dict, n_robots: int, precision=abi.PRECISION_F64, device=0, q0=None, devices=None):
+        """devices = a list of CUDA device indices: the batch is sharded over them (osc_batch_create_multi), one host thread and
+        one stream per device inside the library; every method below works unchanged on such a batch (HOST buffers only)."""
         self.L = lib()
         self.chain = chain
         self.n = chain["n"]
@@ -131,11 +136,24 @@ class Batch:
         self._cd = abi.chain_desc(chain)
         h = C.c_void_p()
         q0a = np.ascontiguousarray(q0, dtype=np.float64) if q0 is not None else None
-        rc = self.L.osc_batch_create(C.byref(self._cd), self.B, precision, device,
-                                     q0a.ctypes.data_as(C.POINTER(C.c_double)) if q0a is not None else None, C.byref(h))
+        q0p = q0a.ctypes.data_as(C.POINTER(C.c_double)) if q0a is not None else None
+        if devices is not None:
+            ids = (C.c_int * len(devices))(*[int(d) for d in devices])
+            rc = self.L.osc_batch_create_multi(C.byref(self._cd), self.B, precision, ids, len(devices), q0p, C.byref(h))
+        else:
+            rc = self.L.osc_batch_create(C.byref(self._cd), self.B, precision, device, q0p, C.byref(h))
         self.h = None
         self._chk(rc)
         self.h = h
+
+    def shards(self):
+        """[(device, first_robot, n_robots)] of a (multi-device) batch"""
+        out = []
+        for k in range(self.L.osc_batch_shard_count(self.h)):
+            d, f, n = C.c_int(), C.c_int64(), C.c_int64()
+            self.L.osc_batch_shard(self.h, k, C.byref(d), C.byref(f), C.byref(n))
+            out.append((d.value, f.value, n.value))
+        return out
 
     def close(self):
         if getattr(self, "h", None):

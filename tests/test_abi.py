@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     import osc_b200
     L = osc_b200.lib()
     declared = _declared_functions()
-    assert len(declared) >= 40
+    assert len(declared) >= 50
     nm = subprocess.run(["nm", "-D", "--defined-only", LIB], capture_output=True, text=True, check=True).stdout
     exported = set(re.findall(r"\bT (osc_[a-z0-9_]+)", nm))
     missing = [f for f in declared if f not in exported]
