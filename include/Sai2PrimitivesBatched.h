@@ -217,7 +217,28 @@ public:
 	void getDesiredOrientation(const Out& o) { _robot->get(_index, OSC_F_DESIRED_ORIENTATION, o); }
 	void getDesiredLinearVelocity(const Out& o) { _robot->get(_index, OSC_F_DESIRED_LINEAR_VELOCITY, o); }
 	void getDesiredAngularVelocity(const Out& o) { _robot->get(_index, OSC_F_DESIRED_ANGULAR_VELOCITY, o); }
-	void getOrientationError(const Out& o) { _robot->get(_index, OSC_F_ORIENTATION_ERROR, o); }
+	// Vector3d getPositionError() / getOrientationError() const (MotionForceTask.h:268-269, .cpp:540-546)
+	void getPositionError(const Out& o) { _robot->get(_index, OSC_F_POSITION_ERROR, o); }
+	void getOrientationError(const Out& o) { _robot->get(_index, OSC_F_SELECTED_ORIENTATION_ERROR, o); }
+	// Matrix3d sigmaForce / sigmaPosition / sigmaMoment / sigmaOrientation() const (MotionForceTask.h:611-614): [B][9] row-major
+	void sigmaForce(const Out& o) { _robot->get(_index, OSC_F_SIGMA_FORCE, o); }
+	void sigmaPosition(const Out& o) { _robot->get(_index, OSC_F_SIGMA_POSITION, o); }
+	void sigmaMoment(const Out& o) { _robot->get(_index, OSC_F_SIGMA_MOMENT, o); }
+	void sigmaOrientation(const Out& o) { _robot->get(_index, OSC_F_SIGMA_ORIENTATION, o); }
+	// Matrix3d posSelectionProjector() / oriSelectionProjector() const (MotionForceTask.h:653-659): uniform over the batch
+	std::array<double, 9> posSelectionProjector() const { std::array<double, 9> a; check(osc_mft_selection_projectors(_robot->handle(), _index, a.data(), nullptr)); return a; }
+	std::array<double, 9> oriSelectionProjector() const { std::array<double, 9> a; check(osc_mft_selection_projectors(_robot->handle(), _index, nullptr, a.data())); return a; }
+	// getGoalForce() / getGoalMoment() (MotionForceTask.cpp:755-769: rotated into the world frame when parametrised in the compliant frame)
+	void getGoalForce(const Out& o) { _robot->get(_index, OSC_F_GOAL_FORCE_WORLD, o); }
+	void getGoalMoment(const Out& o) { _robot->get(_index, OSC_F_GOAL_MOMENT_WORLD, o); }
+	// bool goalPositionReached(tolerance) / goalOrientationReached(tolerance) (MotionForceTask.h:508,521) for every robot:
+	// returns how many robots reached; flags (int32 [B], host) may be null
+	int64_t goalPositionReached(double tolerance, int32_t* flags = nullptr) {
+		int64_t n = 0; check(osc_task_goal_reached(_robot->handle(), _index, 0, tolerance, flags, OSC_MEM_HOST, &n)); return n;
+	}
+	int64_t goalOrientationReached(double tolerance, int32_t* flags = nullptr) {
+		int64_t n = 0; check(osc_task_goal_reached(_robot->handle(), _index, 1, tolerance, flags, OSC_MEM_HOST, &n)); return n;
+	}
 	void getUnitMassForce(const Out& o) { _robot->get(_index, OSC_F_UNIT_MASS_FORCE, o); }
 	void getSensedForceControlWorldFrame(const Out& o) { _robot->get(_index, OSC_F_SENSED_FORCE_WORLD, o); }
 	void getSensedMomentControlWorldFrame(const Out& o) { _robot->get(_index, OSC_F_SENSED_MOMENT_WORLD, o); }
@@ -417,6 +438,16 @@ public:
 		if ((int)kp.size() != _k || (int)kv.size() != _k || (!ki.empty() && (int)ki.size() != _k))
 			throw std::invalid_argument("size of gain vectors inconsistent with number of task dofs in JointTask::setGains\n");
 		edit([&](osc_joint_task_params& p) { for (int i = 0; i < _k; ++i) { p.kp[i] = kp[i]; p.kv[i] = kv[i]; p.ki[i] = ki.empty() ? 0 : ki[i]; } });
+	}
+	// setGainsUnsafe (JointTask.h:256, .cpp:136-156): no sign check; vectors of size 1 (isotropic) or task dof
+	void setGainsUnsafe(const std::vector<double>& kp, const std::vector<double>& kv, const std::vector<double>& ki) {
+		if (kp.size() != kv.size() || kp.size() != ki.size())
+			throw std::invalid_argument("size of gain vectors inconsistent with number of task dofs in JointTask::setGains\n");
+		check(osc_joint_task_set_gains_unsafe(_robot->handle(), _index, kp.data(), kv.data(), ki.data(), (int)kp.size()));
+	}
+	// bool goalPositionReached(tol = 1e-2) (JointTask.h:389) for every robot: how many reached; flags (int32 [B], host) may be null
+	int64_t goalPositionReached(double tolerance = 1e-2, int32_t* flags = nullptr) {
+		int64_t n = 0; check(osc_task_goal_reached(_robot->handle(), _index, 0, tolerance, flags, OSC_MEM_HOST, &n)); return n;
 	}
 	void enableVelocitySaturation(double saturation_velocity = 3.14159265358979323846 / 3) {
 		edit([&](osc_joint_task_params& p) { p.use_velocity_saturation = 1; for (int i = 0; i < _k; ++i) p.saturation_velocity[i] = saturation_velocity; });

@@ -222,6 +222,20 @@ enum {
 	OSC_F_JT_DESIRED_VELOCITY = 89,  /* k out */
 	OSC_F_JT_DESIRED_POSITION = 90,  /* k out */
 	OSC_F_JT_DESIRED_ACCELERATION = 91, /* k out */
+	/* MotionForceTask getters that are functions of the task state (evaluated on demand at the state of the last
+	 * computeTorques): MotionForceTask.h:611-614 / .cpp:892-971, .h:268-269 / .cpp:540-546, .cpp:755-769, .cpp:548-578 */
+	OSC_F_SIGMA_FORCE = 110,              /* 9 out sigmaForce() */
+	OSC_F_SIGMA_POSITION = 111,           /* 9 out sigmaPosition() */
+	OSC_F_SIGMA_MOMENT = 112,             /* 9 out sigmaMoment() */
+	OSC_F_SIGMA_ORIENTATION = 113,        /* 9 out sigmaOrientation() */
+	OSC_F_POSITION_ERROR = 114,           /* 3 out getPositionError() = sigmaPosition (goal - current) */
+	OSC_F_SELECTED_ORIENTATION_ERROR = 115, /* 3 out getOrientationError() = sigmaOrientation * _orientation_error */
+	OSC_F_GOAL_FORCE_WORLD = 116,         /* 3 out getGoalForce() (rotated when parametrised in the compliant frame) */
+	OSC_F_GOAL_MOMENT_WORLD = 117,        /* 3 out getGoalMoment() */
+	OSC_F_POSITION_ERROR_NORM = 118,      /* 1 out the norm goalPositionReached(tol) compares with tol */
+	OSC_F_ORIENTATION_ERROR_NORM = 119,   /* 1 out the norm goalOrientationReached(tol) compares with tol */
+	/* JointTask */
+	OSC_F_JT_POSITION_ERROR_NORM = 120,   /* 1 out the norm JointTask::goalPositionReached(tol) compares with tol (JointTask.cpp:437-446) */
 	/* internal OTG of a task (either type), valid once it has been enabled */
 	OSC_F_OTG_FLAGS = 100,  /* 1 (int32) out: bit 0 = isGoalReached() (OTG_joints.h, OTG_6dof_cartesian.h) */
 	OSC_F_OTG_RESULT = 101, /* 1 (int32) out: ruckig::Result of the last update (0 working, 1 finished, < 0 error) */
@@ -291,6 +305,18 @@ int osc_task_enable_internal_otg_jerk_limited(osc_batch_t* batch, int task, cons
 int osc_task_disable_internal_otg(osc_batch_t* batch, int task);
 /* getInternalOtgEnabled() */
 int osc_task_internal_otg_enabled(const osc_batch_t* batch, int task);
+
+/* JointTask::setGainsUnsafe, src/tasks/JointTask.h:256 / JointTask.cpp:136-156: setGains without the sign check.  count = 1
+ * (isotropic) or the task dof, else OSC_ERR_INVALID_ARGUMENT with the reference's message. */
+int osc_joint_task_set_gains_unsafe(osc_batch_t* batch, int task, const double* kp, const double* kv, const double* ki, int count);
+/* MotionForceTask::posSelectionProjector / oriSelectionProjector, src/tasks/MotionForceTask.h:653-659: the 3 x 3 diagonal blocks
+ * of _partial_task_projection (row-major; uniform over the batch) */
+int osc_mft_selection_projectors(const osc_batch_t* batch, int task, double pos_projector[9], double ori_projector[9]);
+/* goalPositionReached(tolerance) / goalOrientationReached(tolerance) (src/tasks/MotionForceTask.h:508,521, .cpp:548-578;
+ * src/tasks/JointTask.h:389, JointTask.cpp:437-446) for every robot: a device-side threshold of the error norm into one int32
+ * flag per robot (flags_out: [B], host or device, may be NULL) and the number of robots that reached (n_reached, may be NULL).
+ * what: 0 = position (MotionForceTask or JointTask), 1 = orientation (MotionForceTask). */
+int osc_task_goal_reached(osc_batch_t* batch, int task, int what, double tolerance, int32_t* flags_out, int mem, int64_t* n_reached);
 
 /* RobotController::enableGravityCompensation, src/RobotController.h:31-33 */
 int osc_enable_gravity_compensation(osc_batch_t* batch, int enable);

@@ -149,6 +149,69 @@ __global__ void k_pack_ulut(const St* S, int offU, int offL, St* out, int64_t B,
 		}
 }
 // singularity types unpack / counters
+// Getters of MotionForceTask that are functions of the task state rather than stored members (MotionForceTask.h:268-269,
+// 611-614; .cpp:540-578, 755-769, 892-971): the four Sigma selection matrices, getPositionError / getOrientationError, the goal
+// force / moment in the world frame, and the two error norms goalPositionReached / goalOrientationReached compare with their
+// tolerance.  The compliant-frame rotation is _current_orientation of the last computeTorques (or reInitializeTask).
+//   what: 0-3 sigmaForce / sigmaPosition / sigmaMoment / sigmaOrientation (9)   4 position error (3)   5 orientation error (3)
+//         6 goal force (3)   7 goal moment (3)   8 position error norm (1)   9 orientation error norm (1)
+template <class T, int N, class St = T>
+__global__ void k_pack_mft_getters(const __grid_constant__ MftC<T> tc, const St* P, const St* Sc, St* out, int64_t B, int64_t stride, int what) {
+	using L = MftL<N>;
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T, St> tP{const_cast<St*>(P), stride, r}, tS{const_cast<St*>(Sc), stride, r}, o{out, stride, r};
+	T R[3][3], rot[3][3];
+	ld_mat<T, 3, 3>(tP, L::CUR_ORI, R);
+	OSC_UNROLL for (int i = 0; i < 3; ++i)
+		OSC_UNROLL for (int j = 0; j < 3; ++j) rot[i][j] = tc.in_compliant_frame ? R[i][j] : (i == j ? T(1) : T(0));
+	T Sf[3][3], Sm[3][3], Sp[3][3], So[3][3];
+	sigma_matrix<T>(tc.force_dim, tc.Pt, rot, tc.force_axis, Sf);
+	sigma_matrix<T>(tc.moment_dim, tc.Pr, rot, tc.moment_axis, Sm);
+	sigma_complement<T>(tc.Pt, Sf, Sp);
+	sigma_complement<T>(tc.Pr, Sm, So);
+	if (what < 4) {
+		const T (&M)[3][3] = what == 0 ? Sf : (what == 1 ? Sp : (what == 2 ? Sm : So));
+		OSC_UNROLL for (int i = 0; i < 3; ++i)
+			OSC_UNROLL for (int j = 0; j < 3; ++j) o(3 * i + j) = M[i][j];
+		return;
+	}
+	T v[3], res[3];
+	if (what == 4 || what == 8) {  // sigmaPosition() * (_goal_position - _current_position), .cpp:540-542, 548-553
+		OSC_UNROLL for (int a = 0; a < 3; ++a) v[a] = (T)tP(L::GOAL_POS + a) - (T)tP(L::CUR_POS + a);
+		mv3(Sp, v, res);
+	} else if (what == 5 || what == 9) {  // sigmaOrientation() * _orientation_error, .cpp:544-546, 565-569
+		ld_vec<T, 3>(tS, L::ORI_ERR, v);
+		mv3(So, v, res);
+	} else {  // getGoalForce / getGoalMoment, .cpp:755-769
+		ld_vec<T, 3>(tP, what == 6 ? L::GOAL_FORCE : L::GOAL_MOMENT, v);
+		mv3(rot, v, res);
+	}
+	if (what >= 8) {
+		const T q = dot3(v, res);
+		o(0) = Num<T>::sqrt_(q > T(0) ? q : T(0));
+	} else {
+		OSC_UNROLL for (int a = 0; a < 3; ++a) o(a) = res[a];
+	}
+}
+// JointTask::goalPositionReached (JointTask.cpp:437-446): | R R^T (q_task - q_goal) | with R = _current_task_range
+template <class T, int N, class St = T>
+__global__ void k_pack_jt_error_norm(const St* P, const St* Sc, const int32_t* I, St* out, int64_t B, int64_t stride, int k) {
+	using L = JtL<N>;
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T, St> tP{const_cast<St*>(P), stride, r}, tS{const_cast<St*>(Sc), stride, r};
+	const int rank = I[(int64_t)L::RANK * stride + r];
+	T e[N];
+	OSC_UNROLL for (int i = 0; i < N; ++i) e[i] = i < k ? (T)tS(L::CUR_POS + i) - (T)tP(L::GOAL_POS + i) : T(0);
+	T s2 = T(0);
+	for (int c = 0; c < rank; ++c) {  // range basis stored k x rank, row-major N x N padded
+		T d = T(0);
+		OSC_UNROLL for (int i = 0; i < N; ++i) d = Num<T>::fma_((T)tS(L::RANGE + i * N + c), e[i], d);
+		s2 = Num<T>::fma_(d, d, s2);
+	}
+	out[r] = (St)Num<T>::sqrt_(s2);
+}
 template <int N>
 __global__ void k_pack_types(const int32_t* I, int32_t* out, int64_t B, int64_t stride, int what) {
 	using L = MftL<N>;

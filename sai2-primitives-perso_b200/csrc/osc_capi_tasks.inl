@@ -325,4 +325,30 @@ int osc_joint_task_set_params(osc_batch_t* batch, int task, const osc_joint_task
 	return OSC_OK;
 }
 
+
+int osc_joint_task_set_gains_unsafe(osc_batch_t* batch, int task, const double* kp, const double* kv, const double* ki, int count) {  // JointTask.cpp:136-156
+	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_joint_task_set_gains_unsafe(s, task, kp, kv, ki, count); });
+	Batch* b = (Batch*)batch;
+	if (!b || !kp || !kv || !ki || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_JOINT) return invalid("not a JointTask");
+	TaskH& t = b->tasks[task];
+	if (count != 1 && count != t.dof) return invalid("size of gain vectors inconsistent with number of task dofs in JointTask::setGains\n");
+	for (int i = 0; i < t.dof; ++i) {
+		const int s = count == 1 ? 0 : i;
+		t.jp.kp[i] = kp[s]; t.jp.kv[i] = kv[s]; t.jp.ki[i] = ki[s];
+	}
+	return OSC_OK;
+}
+int osc_mft_selection_projectors(const osc_batch_t* batch, int task, double pos_projector[9], double ori_projector[9]) {  // MotionForceTask.h:653-659
+	if (is_multi(batch)) batch = (const osc_batch_t*)shard0(batch);
+	const Batch* b = (const Batch*)batch;
+	if (!b || task < 0 || task >= (int)b->tasks.size() || b->tasks[task].type != OSC_TASK_MOTION_FORCE) return invalid("not a MotionForceTask");
+	const TaskH& t = b->tasks[task];
+	for (int i = 0; i < 3; ++i)
+		for (int j = 0; j < 3; ++j) {
+			if (pos_projector) pos_projector[3 * i + j] = t.P6[i][j];
+			if (ori_projector) ori_projector[3 * i + j] = t.P6[3 + i][3 + j];
+		}
+	return OSC_OK;
+}
+
 }  // extern "C"

@@ -136,6 +136,15 @@ template <class E> __global__ void k_broadcast(const __grid_constant__ Uniform64
 	for (int e = 0; e < w; ++e) soa[(int64_t)e * stride + r] = v[e];
 }
 
+// per-robot flag value < tolerance (goalPositionReached / goalOrientationReached) + the number of robots that reached
+template <class St> __global__ void k_below_tolerance(const St* v, double tol, int32_t* flags, int* count, int64_t B) {
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	const bool ok = r < B && (double)v[r] < tol;
+	if (r < B) flags[r] = ok ? 1 : 0;
+	const unsigned m = __ballot_sync(0xffffffffu, ok);
+	if ((threadIdx.x & 31) == 0 && m) atomicAdd(count, __popc(m));
+}
+
 inline void* arena_base(Batch& b, const Loc& l) {
 	if (l.owner < 0) return l.arena == 0 ? b.P : (l.arena == 1 ? b.S : (void*)b.I);
 	TaskH& t = b.tasks[l.owner];

@@ -75,6 +75,12 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 			case OSC_F_DESIRED_ANGULAR_VELOCITY: return set(1, L::DES_ANGVEL, 3, false);
 			case OSC_F_DESIRED_LINEAR_ACCELERATION: return set(0, L::GOAL_LINACC, 3, false);
 			case OSC_F_DESIRED_ANGULAR_ACCELERATION: return set(0, L::GOAL_ANGACC, 3, false);
+			case OSC_F_SIGMA_FORCE: case OSC_F_SIGMA_POSITION: case OSC_F_SIGMA_MOMENT: case OSC_F_SIGMA_ORIENTATION:
+				l.special = 10 + (field - OSC_F_SIGMA_FORCE); return set(1, 0, 9, false);
+			case OSC_F_POSITION_ERROR: case OSC_F_SELECTED_ORIENTATION_ERROR: case OSC_F_GOAL_FORCE_WORLD: case OSC_F_GOAL_MOMENT_WORLD:
+				l.special = 10 + (field - OSC_F_SIGMA_FORCE); return set(1, 0, 3, false);
+			case OSC_F_POSITION_ERROR_NORM: case OSC_F_ORIENTATION_ERROR_NORM:
+				l.special = 10 + (field - OSC_F_SIGMA_FORCE); return set(1, 0, 1, false);
 			case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<6>::FLAGS, 1, false, true);
 			case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<6>::RESULT, 1, false, true);
 			case OSC_F_OTG_STATE: if (!t.otgO || sizeof(T) != 8) return false; return set(5, 0, OtgL<6>::O_SIZE, false);
@@ -102,6 +108,7 @@ template <class T, int N> bool OpsImpl<T, N>::locate(Batch& b, int task, int fie
 		// _desired_position / _desired_acceleration: the rows the control law reads (= the goal rows while the OTG is off)
 		case OSC_F_JT_DESIRED_POSITION: return set(0, L::GOAL_POS, k, false);
 		case OSC_F_JT_DESIRED_ACCELERATION: return set(0, L::GOAL_ACC, k, false);
+		case OSC_F_JT_POSITION_ERROR_NORM: l.special = 20; return set(1, 0, 1, false);
 		case OSC_F_OTG_FLAGS: if (!t.otgI) return false; return set(4, OtgL<N>::FLAGS, 1, false, true);
 		case OSC_F_OTG_RESULT: if (!t.otgI) return false; return set(4, OtgL<N>::RESULT, 1, false, true);
 		case OSC_F_OTG_STATE: if (!t.otgO || sizeof(T) != 8) return false; return set(5, 0, OtgL<N>::O_SIZE, false);
@@ -135,6 +142,14 @@ template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l
 			k_pack_ulut<C, N, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.S, JtL<N>::RANGE, l.special == 6 ? JtL<N>::LAM : JtL<N>::LAM_MOD,
 																		 (T*)tmp, b.B, b.stride, t.dof);
 			return done(b, "k_pack_ulut");
+	}
+	if (l.special >= 10 && l.special <= 19) {
+		k_pack_mft_getters<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftcc(t), (const T*)t.P, (const T*)t.S, (T*)tmp, b.B, b.stride, l.special - 10);
+		return done(b, "k_pack_mft_getters");
+	}
+	if (l.special == 20) {
+		k_pack_jt_error_norm<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>((const T*)t.P, (const T*)t.S, t.I, (T*)tmp, b.B, b.stride, t.dof);
+		return done(b, "k_pack_jt_error_norm");
 	}
 	set_error("internal: unknown packed field");
 	return OSC_ERR_INVALID_ARGUMENT;

@@ -34,6 +34,9 @@ STATUS_OTG_ERROR = 1 << 7
 # field ids (enum in osc_b200.h)
 F_Q, F_DQ, F_TAU, F_M, F_MINV, F_N_TOTAL, F_STATUS, F_GRAVITY = 0, 1, 2, 3, 4, 5, 6, 7
 F_NONLINEAR_EFFECTS = 8
+F_SIGMA_FORCE, F_SIGMA_POSITION, F_SIGMA_MOMENT, F_SIGMA_ORIENTATION = 110, 111, 112, 113
+F_POSITION_ERROR, F_SELECTED_ORIENTATION_ERROR, F_GOAL_FORCE_WORLD, F_GOAL_MOMENT_WORLD = 114, 115, 116, 117
+F_POSITION_ERROR_NORM, F_ORIENTATION_ERROR_NORM, F_JT_POSITION_ERROR_NORM = 118, 119, 120
 F_TASK_TORQUES, F_N_TASK, F_N_PREC, F_N_TASK_AND_PREC = 20, 21, 22, 23
 F_GOAL_POSITION, F_GOAL_ORIENTATION, F_GOAL_LINEAR_VELOCITY, F_GOAL_ANGULAR_VELOCITY = 40, 41, 42, 43
 F_GOAL_LINEAR_ACCELERATION, F_GOAL_ANGULAR_ACCELERATION, F_GOAL_FORCE, F_GOAL_MOMENT = 44, 45, 46, 47

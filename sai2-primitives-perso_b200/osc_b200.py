@@ -62,6 +62,9 @@ def lib():
         "osc_joint_task_get_params": (i, [vp, i, C.POINTER(abi.JointTaskParams)]),
         "osc_joint_task_set_params": (i, [vp, i, C.POINTER(abi.JointTaskParams)]),
         "osc_enable_gravity_compensation": (i, [vp, i]),
+        "osc_joint_task_set_gains_unsafe": (i, [vp, i, vp, vp, vp, i]),
+        "osc_mft_selection_projectors": (i, [vp, i, vp, vp]),
+        "osc_task_goal_reached": (i, [vp, i, i, C.c_double, vp, i, C.POINTER(i64)]),
         "osc_field_size": (i, [vp, i, i]),
         "osc_set_field": (i, [vp, i, i, vp, i, i]),
         "osc_get_field": (i, [vp, i, i, vp, i, i]),
@@ -103,7 +106,7 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_batch_add_motion_force_task", "osc_batch_add_joint_task", "osc_batch_task_count", "osc_batch_task_type",
             "osc_batch_task_dof", "osc_mft_default_params", "osc_joint_task_default_params", "osc_mft_get_params",
             "osc_mft_set_params", "osc_joint_task_get_params", "osc_joint_task_set_params",
-            "osc_enable_gravity_compensation", "osc_field_size", "osc_set_field", "osc_get_field",
+            "osc_enable_gravity_compensation", "osc_joint_task_set_gains_unsafe", "osc_mft_selection_projectors", "osc_task_goal_reached", "osc_field_size", "osc_set_field", "osc_get_field",
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
             "osc_tick", "osc_tick_noalloc", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
@@ -194,6 +197,24 @@ class Batch:
 
     def set_joint_task_params(self, task, p):
         return self._chk(self.L.osc_joint_task_set_params(self.h, task, C.byref(p)))
+
+    def set_gains_unsafe(self, task, kp, kv, ki):
+        """JointTask::setGainsUnsafe: no sign check; scalars or length-k vectors"""
+        a = [np.ascontiguousarray(np.atleast_1d(x), dtype=np.float64) for x in (kp, kv, ki)]
+        self._chk(self.L.osc_joint_task_set_gains_unsafe(self.h, task, a[0].ctypes.data, a[1].ctypes.data, a[2].ctypes.data, len(a[0])))
+
+    def selection_projectors(self, task):
+        """posSelectionProjector(), oriSelectionProjector()"""
+        p, o = np.zeros(9), np.zeros(9)
+        self._chk(self.L.osc_mft_selection_projectors(self.h, task, p.ctypes.data, o.ctypes.data))
+        return p.reshape(3, 3), o.reshape(3, 3)
+
+    def goal_reached(self, task, tolerance, what=0):
+        """goalPositionReached (what = 0) / goalOrientationReached (what = 1): per-robot flags [B] and their count"""
+        flags = np.zeros(self.B, dtype=np.int32)
+        n = C.c_int64()
+        self._chk(self.L.osc_task_goal_reached(self.h, task, what, float(tolerance), flags.ctypes.data, abi.MEM_HOST, C.byref(n)))
+        return flags, n.value
 
     def enable_gravity_compensation(self, e=True):
         self._chk(self.L.osc_enable_gravity_compensation(self.h, int(e)))
