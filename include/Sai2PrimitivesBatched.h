@@ -64,6 +64,28 @@ struct Out {
 	Out(void* p, int layout_ = OSC_LAYOUT_AOS, int mem_ = OSC_MEM_HOST) : ptr(p), layout(layout_), mem(mem_) {}
 };
 
+// ---- Sai2Model(urdf_file) + the world file: the chain constants, the initial posture and the named links, read by the library's
+// own URDF reader (osc_urdf_load): examples/04-task_and_redundancy/04-task_and_redundancy.cpp:67 ----
+class UrdfModel {
+public:
+	explicit UrdfModel(const std::string& urdf_path, const std::string& world_path = "", const std::string& robot_name = "") {
+		check(osc_urdf_load(urdf_path.c_str(), world_path.empty() ? nullptr : world_path.c_str(), robot_name.empty() ? nullptr : robot_name.c_str(), &_u));
+		check(osc_urdf_chain(_u, &_chain, _q0));
+	}
+	~UrdfModel() { osc_urdf_free(_u); }
+	UrdfModel(const UrdfModel&) = delete;
+	UrdfModel& operator=(const UrdfModel&) = delete;
+	const osc_chain_desc& chain() const { return _chain; }
+	const double* q0() const { return _q0; }
+	int dof() const { return _chain.n; }
+	osc_urdf_t* handle() const { return _u; }
+
+private:
+	osc_urdf_t* _u = nullptr;
+	osc_chain_desc _chain;
+	double _q0[OSC_MAX_DOF];
+};
+
 // ---- the robot batch: stands in for std::shared_ptr<Sai2Model::Sai2Model> (one model per robot instance) ----
 class RobotBatch {
 public:
@@ -74,6 +96,13 @@ public:
 	// devices, one host thread and one stream per device inside the library; buffers are HOST buffers spanning all robots
 	RobotBatch(const osc_chain_desc& chain, int64_t n_robots, const std::vector<int>& devices, int precision = OSC_PRECISION_F64, const double* q0 = nullptr) {
 		check(osc_batch_create_multi(&chain, n_robots, precision, devices.data(), (int)devices.size(), q0, &_h));
+	}
+	// robots loaded from a URDF (+ world file): q is initialised to the URDF's calibration posture
+	RobotBatch(const UrdfModel& model, int64_t n_robots, int precision = OSC_PRECISION_F64, int device = 0) {
+		check(osc_batch_create(&model.chain(), n_robots, precision, device, model.q0(), &_h));
+	}
+	RobotBatch(const UrdfModel& model, int64_t n_robots, const std::vector<int>& devices, int precision = OSC_PRECISION_F64) {
+		check(osc_batch_create_multi(&model.chain(), n_robots, precision, devices.data(), (int)devices.size(), model.q0(), &_h));
 	}
 	int shardCount() const { return osc_batch_shard_count(_h); }
 	~RobotBatch() { osc_batch_destroy(_h); }
@@ -138,6 +167,8 @@ struct Link {
 	Affine3 in_body;
 	Link() {}
 	Link(int body_, const Affine3& in_body_ = Affine3()) : body(body_), in_body(in_body_) {}
+	// the `link_name` of the reference API, resolved by the URDF reader (fixed links are frames of their movable parent)
+	Link(const UrdfModel& model, const std::string& link_name) { check(osc_urdf_link(model.handle(), link_name.c_str(), &body, in_body.xyz, in_body.rot)); }
 };
 
 // ---- src/tasks/TemplateTask.h:25-123 ----

@@ -91,6 +91,25 @@ typedef struct osc_chain_desc {
 	double gravity[3];
 } osc_chain_desc;
 
+/* ---- URDF (+ world file) -> osc_chain_desc on the host: stands in for Sai2Model::Sai2Model(urdf_file) as the reference uses it
+ * (examples/04-task_and_redundancy/04-task_and_redundancy.cpp:67) and for the world file (examples/04-.../world.urdf:3 gravity
+ * attribute, :5-7 <robot> with its optional <origin> = T_world_robot).  Root link welded to the world, fixed joints merged into
+ * their movable parent (every link stays addressable by name), initial posture from <calibration falling="deg"> (rising, in
+ * metres, for a prismatic joint), limits / efforts from <limit>.  Serial chains of at most OSC_MAX_DOF joints.
+ * world_path may be NULL (identity pose, gravity (0, 0, -9.81)); robot_name selects the <robot name=...> of the world file
+ * (NULL = its first robot). ---- */
+typedef struct osc_urdf osc_urdf_t;
+int osc_urdf_load(const char* urdf_path, const char* world_path, const char* robot_name, osc_urdf_t** out);
+void osc_urdf_free(osc_urdf_t* urdf);
+/* the chain constants and (q0 may be NULL) the initial posture q0[n] */
+int osc_urdf_chain(const osc_urdf_t* urdf, struct osc_chain_desc* chain, double* q0);
+/* a named link (fixed links included): the movable body it is fixed in (-1 = welded to the world) and its pose in that body
+ * -- what osc_mft_desc.body / frame_* are built from (compose with the compliant frame given in the link) */
+int osc_urdf_link(const osc_urdf_t* urdf, const char* link_name, int* body, double xyz[3], double rot[9]);
+int osc_urdf_link_count(const osc_urdf_t* urdf);
+const char* osc_urdf_link_name(const osc_urdf_t* urdf, int i);
+const char* osc_urdf_joint_name(const osc_urdf_t* urdf, int i);
+
 /* MotionForceTask constructors, src/tasks/MotionForceTask.h:96-110, MotionForceTask.cpp:16-90 */
 typedef struct osc_mft_desc {
 	int32_t body;         /* movable body the control link is fixed in (the link's own offset is folded into frame_*) */

@@ -40,6 +40,13 @@ def lib():
         "osc_last_error": (C.c_char_p, []),
         "osc_version": (i, []),
         "osc_device_count": (i, []),
+        "osc_urdf_load": (i, [C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(vp)]),
+        "osc_urdf_free": (None, [vp]),
+        "osc_urdf_chain": (i, [vp, C.POINTER(abi.ChainDesc), C.POINTER(C.c_double)]),
+        "osc_urdf_link": (i, [vp, C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "osc_urdf_link_count": (i, [vp]),
+        "osc_urdf_link_name": (C.c_char_p, [vp, i]),
+        "osc_urdf_joint_name": (C.c_char_p, [vp, i]),
         "osc_batch_create": (i, [C.POINTER(abi.ChainDesc), i64, i, i, C.POINTER(C.c_double), C.POINTER(vp)]),
         "osc_batch_create_multi": (i, [C.POINTER(abi.ChainDesc), i64, i, C.POINTER(C.c_int), i, C.POINTER(C.c_double), C.POINTER(vp)]),
         "osc_batch_shard_count": (i, [vp]),
@@ -101,7 +108,8 @@ def lib():
     return L
 
 
-EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_create", "osc_batch_create_multi", "osc_batch_shard_count", "osc_batch_shard", "osc_batch_destroy",
+EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_urdf_load", "osc_urdf_free", "osc_urdf_chain", "osc_urdf_link", "osc_urdf_link_count",
+            "osc_urdf_link_name", "osc_urdf_joint_name", "osc_batch_create", "osc_batch_create_multi", "osc_batch_shard_count", "osc_batch_shard", "osc_batch_destroy",
             "osc_batch_set_stream", "osc_synchronize", "osc_batch_size", "osc_batch_dof", "osc_batch_precision",
             "osc_batch_add_motion_force_task", "osc_batch_add_joint_task", "osc_batch_task_count", "osc_batch_task_type",
             "osc_batch_task_dof", "osc_mft_default_params", "osc_joint_task_default_params", "osc_mft_get_params",
@@ -113,6 +121,35 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_batch_crea
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",
             "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled",
             "osc_rollout_step", "osc_rollout"]
+
+
+def load_urdf(urdf_path, world_path=None, robot_name=None):
+    """osc_urdf_load (the library's C++ URDF / world-file reader) -> the chain dict of fixtures/*.chain.json"""
+    L = lib()
+    h = C.c_void_p()
+    rc = L.osc_urdf_load(urdf_path.encode(), world_path.encode() if world_path else None, robot_name.encode() if robot_name else None, C.byref(h))
+    if rc < 0:
+        raise (OscInvalidArgument if rc == abi.ERR_INVALID_ARGUMENT else OscError)(rc, L.osc_last_error().decode())
+    try:
+        cd = abi.ChainDesc()
+        q0 = (C.c_double * abi.MAX_DOF)()
+        L.osc_urdf_chain(h, C.byref(cd), q0)
+        n = cd.n
+        m3 = lambda a: [[a[3 * r + c] for c in range(3)] for r in range(3)]
+        chain = dict(n=n, joints=[], bodies=[], links={}, world_xyz=list(cd.world_xyz), world_rot=m3(cd.world_rot), gravity=list(cd.gravity))
+        for k in range(n):
+            chain["joints"].append(dict(name=L.osc_urdf_joint_name(h, k).decode(), type="prismatic" if cd.joint_type[k] == abi.JOINT_PRISMATIC else "revolute",
+                                        axis=list(cd.joint_axis[k]), xyz=list(cd.joint_xyz[k]), rot=m3(cd.joint_rot[k]), lower=cd.q_lower[k],
+                                        upper=cd.q_upper[k], effort=cd.effort[k], q0=q0[k]))
+            chain["bodies"].append(dict(mass=cd.mass[k], com=list(cd.com[k]), inertia=m3(cd.inertia[k])))
+        for k in range(L.osc_urdf_link_count(h)):
+            name = L.osc_urdf_link_name(h, k)
+            body = C.c_int(); xyz = (C.c_double * 3)(); rot = (C.c_double * 9)()
+            L.osc_urdf_link(h, name, C.byref(body), xyz, rot)
+            chain["links"][name.decode()] = dict(body=body.value, xyz=list(xyz), rot=m3(rot))
+        return chain
+    finally:
+        L.osc_urdf_free(h)
 
 
 def measure_fp64_peak(device=0):

@@ -14,9 +14,10 @@ PKG = os.path.join(ROOT, "sai2-primitives-perso_b200")
 EXE = os.path.join(ROOT, "tests", "cpp", "_build", "facade_demo")
 
 
-def _build():
+def _build(name="facade_demo"):
+    EXE = os.path.join(ROOT, "tests", "cpp", "_build", name)
     os.makedirs(os.path.dirname(EXE), exist_ok=True)
-    src = os.path.join(ROOT, "tests", "cpp", "facade_demo.cpp")
+    src = os.path.join(ROOT, "tests", "cpp", name + ".cpp")
     if not os.path.exists(EXE) or os.path.getmtime(EXE) < max(os.path.getmtime(src), os.path.getmtime(os.path.join(ROOT, "include", "Sai2PrimitivesBatched.h"))):
         subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), src, "-o", EXE,
                                "-L", PKG, "-losc_b200", "-Wl,-rpath," + PKG])
@@ -83,3 +84,39 @@ def test_facade_matches_oracle(tmp_path, oracle_built, mode):
         ref = o.tick(mode != 2)
     assert rel_err(tau, ref)[0] <= FP64_TOL
     assert rel_err(x, o.get(abi.F_CURRENT_POSITION, t0))[0] <= FP64_TOL
+
+
+PUMA_URDF = os.path.join(ROOT, "fixtures", "puma560_synthetic.urdf")
+
+
+def _world(tmp_path):
+    w = tmp_path / "world.urdf"
+    w.write_text('<?xml version="1.0" ?>\n<world name="w" gravity="0.0 0.0 -3.5">\n <robot name="PUMA"><origin xyz="0.5 0 0.2" rpy="0 0 0.3" />'
+                 '<model dir="." path="puma560_synthetic.urdf" name="puma" /></robot>\n</world>\n')
+    return str(w)
+
+
+def test_facade_urdf_loader_on_cpu(tmp_path):
+    """a C++ user loads the URDF + world file through the facade with plain g++ (no GPU needed for that part)"""
+    import osc_b200
+    osc_b200.lib()
+    exe = _build("facade_urdf_multi")
+    r = subprocess.run([exe, PUMA_URDF, _world(tmp_path), "64", "2", str(tmp_path / "out.bin")], capture_output=True, text=True)
+    assert "dof 6 gravity 0.000 0.000 -3.500" in r.stdout and "end-effector body 5" in r.stdout, (r.stdout, r.stderr)
+    if osc_b200.lib().osc_device_count() == 0:
+        assert r.returncode == 10 and "no CUDA device" in r.stderr
+    else:
+        assert r.returncode == 0, r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shards", [2, 3])
+def test_facade_urdf_multi_device(tmp_path, shards):
+    """RobotBatch(UrdfModel, B, devices): the sharded batch gives the single batch's torques, bit for bit, through the facade"""
+    exe = _build("facade_urdf_multi")
+    B = 1000
+    r = subprocess.run([exe, PUMA_URDF, _world(tmp_path), str(B), str(shards), str(tmp_path / "out.bin")], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    out = np.fromfile(tmp_path / "out.bin", dtype=np.float64).reshape(2, B, 6)
+    assert np.isfinite(out).all() and np.abs(out[0]).max() > 0.1
+    assert np.array_equal(out[0], out[1])
