@@ -344,7 +344,10 @@ int osc_enable_gravity_compensation(osc_batch_t* batch, int enable);
 int osc_field_size(const osc_batch_t* batch, int task, int field); /* scalars per robot, < 0 on error */
 int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int layout, int mem);
 int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout, int mem);
-/* MotionForceTask::updateSensedForceAndMoment, src/tasks/MotionForceTask.cpp:805-828 (sensor-frame wrench in) */
+/* MotionForceTask::updateSensedForceAndMoment, src/tasks/MotionForceTask.cpp:805-828 (sensor-frame wrench in).  The compliant
+ * frame is the one of the last osc_update_model / osc_update_kinematics, like the reference; in a loop built around osc_tick
+ * (which runs updateModel itself) it is evaluated at the batch's current q, i.e. the reference's order of calls
+ * robot->setQ(); robot->updateModel(); task->updateSensedForceAndMoment(); ... computeTorques(). */
 int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const void* force, const void* moment, int layout, int mem);
 
 /* ---- the tick ---- */

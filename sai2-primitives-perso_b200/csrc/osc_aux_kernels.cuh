@@ -102,13 +102,23 @@ __global__ void k_jt_reinit(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, 
 
 // MotionForceTask::updateSensedForceAndMoment (MotionForceTask.cpp:805-828); in6 = SoA [6][stride] sensor-frame wrench
 template <class T, int N, class S = T>
-__global__ void k_mft_sensed(const __grid_constant__ MftC<T> tc, Arena<S> rob, Arena<S> tk, const S* in6, int64_t B, int64_t stride) {
+__global__ void k_mft_sensed(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc, Arena<S> rob, Arena<S> tk, const S* in6,
+							 int64_t B, int64_t stride, int kinematics_from_q) {
 	using L = MftL<N>;
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
-	const Row<T, S> rS{rob.S, stride, r}, tP{tk.P, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r};
 	Kin<T, N> kin;
-	ld_kin<T, N>(rS, kin);
+	if (kinematics_from_q) {
+		// after a fused tick the kinematics rows are older than q (the fused kernels keep them on chip): the compliant frame is
+		// evaluated here from the current q, which is what robot->updateModel() before updateSensedForceAndMoment gives the
+		// reference (examples/07-surface_surface_contact order of calls) -- without re-running the model and task-model kernels
+		T q[N];
+		ld_vec<T, N>(rP, RobotL<N>::Q, q);
+		forward_kinematics<T, N>(ch, q, kin);
+	} else {
+		ld_kin<T, N>(rS, kin);
+	}
 	T x[3], R[3][3];
 	frame_pose<T, N>(kin, tc.body, tc.p_c, tc.R_c, x, R);
 	T fs[3], ms[3], f[3], m[3], pxf[3], fw[3], mw[3];

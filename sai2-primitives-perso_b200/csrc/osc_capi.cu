@@ -75,7 +75,7 @@ void osc_batch_destroy(osc_batch_t* batch) {
 	cudaSetDevice(b->device);
 	cudaStreamSynchronize(b->stream);
 	for (TaskH& t : b->tasks) { cudaFree(t.P); cudaFree(t.S); cudaFree(t.I); cudaFree(t.popc_ring); cudaFree(t.otgO); cudaFree(t.otgI); cudaFree(t.otgG); cudaFree(t.otg_slow); }
-	cudaFree(b->P); cudaFree(b->S); cudaFree(b->I); cudaFree(b->stage); cudaFree(b->stage2); cudaFree(b->fb);
+	cudaFree(b->P); cudaFree(b->S); cudaFree(b->I); cudaFree(b->stage); cudaFree(b->stage2); cudaFree(b->fb); cudaFree(b->tail_scratch);
 	if (b->owned_stream) cudaStreamDestroy(b->owned_stream);
 	delete b->ops;
 	delete b;
@@ -243,8 +243,10 @@ extern "C" int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_d
 	const int own_parity = b->fb_parity, own_last = b->fb_last;
 	b->fb = scratch;
 	b->fb_parity = 0;
+	b->may_allocate = false;  // (k_tick_tail's compact scratch is used if an earlier osc_tick allocated it, else its robots work in place)
 	int rc = b->ops->otg_tick(*b, -1);
 	if (rc == OSC_OK) rc = b->ops->tick_fused(*b, stacked);
+	b->may_allocate = true;
 	b->fb = own_fb;
 	b->fb_parity = own_parity;
 	b->fb_last = own_last;

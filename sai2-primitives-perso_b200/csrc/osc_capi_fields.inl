@@ -103,7 +103,8 @@ int osc_mft_update_sensed_force_and_moment(osc_batch_t* batch, int task, const v
 	if (!tmp) return invalid("out of device memory (staging)");
 	if (int rc = import_rows(*b, tmp, 3, false, force, layout, mem)) return rc;
 	if (int rc = import_rows(*b, tmp + (size_t)3 * b->stride * b->esz, 3, false, moment, layout, mem)) return rc;
-	if (int rc = b->ops->materialise(*b)) return rc;  // the sensor-frame transform reads the kinematics of the last updateModel
+	// the sensor-frame transform reads the kinematics of the last updateModel; after a fused tick (stale rows) k_mft_sensed
+	// evaluates them from the current q itself, so a force-control loop around osc_tick stays at one extra small launch
 	return b->ops->update_sensed(*b, task, tmp);
 }
 

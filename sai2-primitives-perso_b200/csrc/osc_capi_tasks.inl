@@ -4,8 +4,9 @@ namespace osc {
 
 // projector onto the range of the 3 x k direction matrix, with Sai2Model::matrixRangeBasis' rank rule (tolerance 1e-3):
 // the B B^T blocks of MotionForceTask.cpp:82-87.  Returns the rank (0 when the list is empty / numerically zero).
-static int range_projector_3(const double dirs[3][3], int k, double P[3][3]) {
+static int range_projector_3(const double dirs[3][3], int k, double P[3][3], double Bout[3][3]) {
 	memset(P, 0, sizeof(double) * 9);
+	memset(Bout, 0, sizeof(double) * 9);
 	if (k == 0) return 0;
 	double C[3][3] = {{0}}, V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
 	double fro = 0;
@@ -39,10 +40,12 @@ static int range_projector_3(const double dirs[3][3], int k, double P[3][3]) {
 		if (s[i] / s[0] < 1e-3) --rank;
 		else break;
 	}
-	if (rank == 3) { P[0][0] = P[1][1] = P[2][2] = 1; return 3; }
+	if (rank == 3) { P[0][0] = P[1][1] = P[2][2] = 1; Bout[0][0] = Bout[1][1] = Bout[2][2] = 1; return 3; }
 	for (int c = 0; c < rank; ++c)
-		for (int i = 0; i < 3; ++i)
+		for (int i = 0; i < 3; ++i) {
+			Bout[i][c] = V[i][order[c]];
 			for (int j = 0; j < 3; ++j) P[i][j] += V[i][order[c]] * V[j][order[c]];
+		}
 	return rank;
 }
 
@@ -106,6 +109,8 @@ int osc_batch_add_motion_force_task(osc_batch_t* batch, const osc_mft_desc* d) {
 	memset(t.P6, 0, sizeof t.P6);
 	if (!d->partial) {  // MotionForceTask.cpp:28
 		for (int i = 0; i < 6; ++i) t.P6[i][i] = 1;
+		for (int i = 0; i < 3; ++i) t.Bt[i][i] = t.Br[i][i] = 1;
+		t.mt = t.mr = 3;
 		t.dof = 6;
 	} else {  // MotionForceTask.cpp:47-87, 146-160
 		if (d->n_dirs_translation < 0 || d->n_dirs_translation > 3 || d->n_dirs_rotation < 0 || d->n_dirs_rotation > 3)
@@ -113,8 +118,9 @@ int osc_batch_add_motion_force_task(osc_batch_t* batch, const osc_mft_desc* d) {
 		if (d->n_dirs_translation == 0 && d->n_dirs_rotation == 0)
 			return invalid("controlled_directions_translation and controlled_directions_rotation cannot both be empty in MotionForceTask::MotionForceTask\n");
 		double Pt[3][3], Pr[3][3];
-		const int rt = range_projector_3(d->dirs_translation, d->n_dirs_translation, Pt);
-		const int rr = range_projector_3(d->dirs_rotation, d->n_dirs_rotation, Pr);
+		const int rt = range_projector_3(d->dirs_translation, d->n_dirs_translation, Pt, t.Bt);
+		const int rr = range_projector_3(d->dirs_rotation, d->n_dirs_rotation, Pr, t.Br);
+		t.mt = rt; t.mr = rr;
 		for (int i = 0; i < 3; ++i)
 			for (int j = 0; j < 3; ++j) { t.P6[i][j] = Pt[i][j]; t.P6[3 + i][3 + j] = Pr[i][j]; }
 		t.dof = rt + rr;

@@ -249,22 +249,55 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __
 template <class T, int N, class S = T>
 __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk0, Arena<S> tk1, int64_t stride,
-															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law) {
+															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law,
+															S* scratch, int64_t scratch_stride, int exports) {
 	// launched with programmatic stream serialisation behind the fused kernel: its launch latency overlaps the fused kernel's
 	// run; the fallback list is complete (and visible) once the wait returns.  A no-op under a plain launch.
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	const int n = *fb_count;
 	if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count_next = 0;
-	for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+	using ML = MftL<N>;
+	using JL = JtL<N>;
+	const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	// The listed robots are scattered over the batch.  With a scratch arena (one slot per tail thread) every S row of the
+	// API-faithful chain below lives at [row][slot]: consecutive threads, consecutive addresses.  What the rest of the library reads
+	// at the robot's own rows -- tau, and in the LAZY output mode the vector getters -- is copied out at the end.
+	Arena<S> xr = rob, x0 = tk0, x1 = tk1;
+	if (scratch && slot < scratch_stride) {
+		xr.S = scratch; x0.S = scratch + (int64_t)RobotL<N>::S_SIZE * scratch_stride; x1.S = x0.S + (int64_t)ML::S_SIZE * scratch_stride;
+		xr.s_stride = x0.s_stride = x1.s_stride = scratch_stride;
+		xr.s_index = x0.s_index = x1.s_index = slot;
+	}
+	const bool redirected = xr.s_stride != 0;
+	for (int idx = (int)slot; idx < n; idx += gridDim.x * blockDim.x) {
 		const int64_t r = fb_list[idx];
-		model_robot<T, N>(ch, rob, stride, r, 1, gravity);
-		mft_update_robot<T, N>(ch, tc, rob, tk0, (const S*)nullptr, stride, r, 0);
-		jt_update_robot<T, N>(jc, rob, tk1, tk0.S + (int64_t)MftL<N>::NTP * stride, stride, r);
-		mft_compute_robot<T, N>(ch, tc, rob, tk0, stride, r, 0, 1, reuse_law & 1);
-		jt_compute_robot<T, N>(jc, rob, tk1, stride, r, stacked, 2, reuse_law & 2);
+		const Row<T, S> rS{rob.S, stride, r}, mS{tk0.S, stride, r}, jS{tk1.S, stride, r};                       // the robot's own rows
+		const Row<T, S> xS = srow<T>(xr, stride, r), xm = srow<T>(x0, stride, r), xj = srow<T>(x1, stride, r);   // where the chain works
+		if (redirected) {
+			if (reuse_law & 1) {  // F*, F_f handed over by the fused kernel
+				for (int i = 0; i < 6; ++i) { xm(ML::UMF + i) = (T)mS(ML::UMF + i); xm(ML::FFB + i) = (T)mS(ML::FFB + i); }
+			}
+			if (exports && reuse_law) {  // vector getters the fused kernel already wrote for this robot (the control laws it ran) ride along
+				for (int e = 0; e < ML::J; ++e) xm(e) = (T)mS(e);
+				for (int e = 0; e < JL::NT; ++e) xj(e) = (T)jS(e);
+			}
+			if (gravity) for (int i = 0; i < N; ++i) xS(RobotL<N>::GRAV + i) = (T)rS(RobotL<N>::GRAV + i);
+		}
+		model_robot<T, N>(ch, xr, stride, r, 1, gravity);
+		mft_update_robot<T, N>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
+		jt_update_robot<T, N>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
+		mft_compute_robot<T, N>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
+		jt_compute_robot<T, N>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
 		if (gravity) {
-			const Row<T, S> rS{rob.S, stride, r};
-			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) += rS(RobotL<N>::GRAV + i);
+			for (int i = 0; i < N; ++i) xS(RobotL<N>::TAU + i) += (T)xS(RobotL<N>::GRAV + i);
+		}
+		if (redirected) {
+			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) = (T)xS(RobotL<N>::TAU + i);
+			if (exports) {  // vector getters of the LAZY output mode: the leading rows of the two task arenas (osc_layout.cuh)
+				for (int e = 0; e < ML::J; ++e) mS(e) = (T)xm(e);
+				mS(ML::ALPHA) = (T)xm(ML::ALPHA);
+				for (int e = 0; e < JL::NT; ++e) jS(e) = (T)xj(e);
+			}
 		}
 	}
 }
@@ -276,7 +309,13 @@ template <class T, int N> bool fused_tick_supported(Batch& b) {
 	if (b.tasks.size() != 2) return false;
 	const TaskH &m = b.tasks[0], &j = b.tasks[1];
 	if (m.type != OSC_TASK_MOTION_FORCE || j.type != OSC_TASK_JOINT) return false;
-	if (m.md.partial || m.dof != 6 || !j.jd.full) return false;
+	if (!j.jd.full) return false;
+	if (m.md.partial) {  // partial task: k_tick_fused3, instantiated for the (n, task rank) pairs of OSC_FUSED3_SUPPORTED (osc_fused3.cuh)
+		if (!(N == 7 && (m.dof == 3 || m.dof == 2 || m.dof == 4 || m.dof == 5))) return false;
+		if (b.tasks[0].md.body != b.n - 1) return false;
+		for (int i = 0; i < b.n; ++i)
+			if (b.chain.joint_type[i] != OSC_JOINT_REVOLUTE) return false;
+	} else if (m.dof != 6) return false;
 	if (m.mp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES && j.jp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES &&
 		m.mp.bie_threshold != j.jp.bie_threshold)
 		return false;

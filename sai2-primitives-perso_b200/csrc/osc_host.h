@@ -22,6 +22,8 @@ struct TaskH {
 	osc_joint_task_params jp{};
 	int dof = 0;           // MotionForceTask: _pos_range + _ori_range; JointTask: k
 	double P6[6][6]{};     // _partial_task_projection
+	double Bt[3][3]{}, Br[3][3]{};  // orthonormal bases of its two diagonal blocks (columns), ranks mt, mr
+	int mt = 0, mr = 0;
 	double frame_p[3]{}, frame_R[3][3]{};  // compliant frame in the CANONICAL body frame
 	void *P = nullptr, *S = nullptr;
 	int32_t* I = nullptr;
@@ -100,6 +102,9 @@ struct Batch {
 	int* fb = nullptr;         // device: [2] fallback counters (ping-pong) + [stride] robot list
 	int fb_parity = 0;
 	int fb_last = 0;           // which counter the last fused tick filled
+	void* tail_scratch = nullptr;      // compact S rows of k_tick_tail, one slot per tail thread (osc_fused.cuh)
+	int64_t tail_scratch_stride = 0;
+	bool may_allocate = true;          // false inside osc_tick_noalloc
 	void* chain_dev = nullptr;  // ChainC<T,N> host copy owned by ops
 	// staging
 	void* stage = nullptr; size_t stage_bytes = 0;

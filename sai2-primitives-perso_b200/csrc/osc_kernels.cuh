@@ -18,6 +18,8 @@ template <class T> struct MftC {
 	int body, partial, rank, in_compliant_frame;
 	T p_c[3], R_c[3][3];
 	T Pt[3][3], Pr[3][3];  // diagonal blocks of _partial_task_projection
+	T Bt[3][3], Br[3][3];  // orthonormal bases of the controlled directions (columns 0..mt-1 / 0..mr-1; Pt = Bt Bt^T, Pr = Br Br^T)
+	int mt, mr;            // _pos_range, _ori_range (MotionForceTask.cpp:146-152)
 	T dt;
 	T kp_pos[3], kv_pos[3], ki_pos[3], kp_ori[3], kv_ori[3], ki_ori[3];
 	T kp_force, kv_force, ki_force, kp_moment, kv_moment, ki_moment, kff_force, kff_moment, max_force_fb, max_moment_fb;
@@ -70,6 +72,10 @@ template <class T> struct Row<T, T> {
 	// read-only load (ld.global.nc): ONLY for rows the running kernel never writes; lets the compiler hoist it over stores
 	OSC_DEV T ro(int e) const { return __ldg(base + (int64_t)e * stride + r); }
 };
+// the S (scratch) row of an owner: the robot's own, or the compact slot of a k_tick_tail thread (Arena::s_stride / s_index)
+template <class T, class S> OSC_DEV Row<T, S> srow(const Arena<S>& a, int64_t stride, int64_t r) {
+	return Row<T, S>{a.S, a.s_stride ? a.s_stride : stride, a.s_index >= 0 ? a.s_index : r};
+}
 template <class T, int R, int C, class S = T>
 OSC_DEV void ld_mat(const Row<T, S>& a, int off, T (&A)[R][C]) {
 	OSC_UNROLL for (int i = 0; i < R; ++i)
@@ -105,7 +111,7 @@ OSC_DEV void ld_kin(const Row<T, S>& Sr, Kin<T, N>& k) {
 // ------------------------------------------------------------------------------------------------------------------
 template <class T, int N, class S = T>
 __device__ void model_robot(const ChainC<T, N>& ch, const Arena<S>& rob, int64_t stride, int64_t r, int dynamics, int gravity) {
-	const Row<T, S> P{rob.P, stride, r}, Sr{rob.S, stride, r};
+	const Row<T, S> P{rob.P, stride, r}, Sr = srow<T>(rob, stride, r);
 	T q[N];
 	ld_vec<T, N>(P, RobotL<N>::Q, q);
 	Kin<T, N> kin;

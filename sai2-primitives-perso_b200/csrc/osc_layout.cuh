@@ -57,6 +57,11 @@ template <class T> struct Arena {
 	T* P;
 	T* S;
 	int32_t* I;
+	// k_tick_tail only: its robots are scattered over the batch, so the S rows (the ~1,200 intermediates a robot stores and reloads
+	// between the API-faithful functions) are redirected to a compact scratch arena indexed by the tail THREAD (coalesced) instead of
+	// by the robot (one 32-byte sector per 8-byte access: r2d capture, 180 KB of DRAM traffic per robot).  0 / -1 = the robot's own rows.
+	int64_t s_stride = 0;
+	int64_t s_index = -1;
 };
 
 }  // namespace osc

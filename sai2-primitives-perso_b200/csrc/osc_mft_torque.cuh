@@ -30,7 +30,7 @@ __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, con
 								  int with_tau_prec, int accumulate, int reuse_law = 0) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, tP{tk.P, stride, r}, tS{tk.S, stride, r};
+	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T>(tk, stride, r);
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 

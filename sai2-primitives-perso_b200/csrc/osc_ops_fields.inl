@@ -186,7 +186,33 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 #endif
 #define OSC_FUSED_ARGS ch, tc, jc, rob(b), tk(m), tk(j), b.B, b.stride, stacked, b.gravity ? 1 : 0, exports, cnt, list
 		int reuse_law = 0;
-		if (ver == 2 && fused2_supported(b)) {
+		int M3 = 0;
+		if (fused3_supported(b, M3)) {
+			if constexpr (N == 7) {
+				reuse_law = 1;
+				if (b.gravity) {
+					k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
+					if (int rc = done(b, "k_gravity")) return rc;
+				}
+				auto go3 = [&](auto kern, int threads, int slots) -> int {
+					const size_t smem = (size_t)slots * threads * sizeof(double);
+					if (first_launch_on_device((const void*)kern, b.device)) {
+						cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+						if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_fused3)");
+					}
+					const dim3 gg((unsigned)((b.B + threads - 1) / threads));
+					kern<<<gg, threads, smem, b.stream>>>(OSC_FUSED_ARGS);
+					return OSC_OK;
+				};
+				const bool big = b.B >= 224 * 148;
+				int rc = OSC_ERR_UNSUPPORTED;
+#define OSC_F3_CASE(MM)                                                                                                                    \
+				if (M3 == MM) rc = big ? go3(k_tick_fused3<T, N, MM, 128, 224, true>, 224, F3<N, MM>::SLOTS) : go3(k_tick_fused3<T, N, MM, 128>, 64, F3<N, MM>::SLOTS);
+				OSC_F3_CASE(2) OSC_F3_CASE(3) OSC_F3_CASE(4) OSC_F3_CASE(5)
+#undef OSC_F3_CASE
+				if (rc) return rc;
+			}
+		} else if (ver == 2 && fused2_supported(b)) {
 			reuse_law = 1;
 			if (b.gravity) {
 				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
@@ -228,6 +254,12 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 #undef OSC_FUSED_ARGS
 		if (int rc = done(b, "k_tick_fused")) return rc;
 		const unsigned tail_blocks = (unsigned)std::min<int64_t>((b.B + OSC_THREADS - 1) / OSC_THREADS, 148 * 2);
+		if (!b.tail_scratch && b.may_allocate) {  // one compact slot of S rows per tail thread (see k_tick_tail)
+			const int64_t slots = ((int64_t)tail_blocks * OSC_THREADS + 31) / 32 * 32;
+			const size_t rows = (size_t)RobotL<N>::S_SIZE + MftL<N>::S_SIZE + JtL<N>::S_SIZE;
+			if (cudaMalloc(&b.tail_scratch, rows * slots * sizeof(T)) == cudaSuccess) b.tail_scratch_stride = slots;
+			else { cudaGetLastError(); b.tail_scratch = nullptr; }  // not fatal: the tail then works on the robots' own rows
+		}
 		if (!no_tail) {  // (no_tail: diagnosis builds only -- fallback robots get no torques in such a run)
 			cudaLaunchConfig_t cfg = {};
 			cfg.gridDim = dim3(tail_blocks);
@@ -239,7 +271,8 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			cfg.attrs = at;
 			cfg.numAttrs = pdl ? 1 : 0;
 			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<C, N, T>, chc, mftcc(m), jtcc(b, j), rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
-											   (const int*)cnt, nxt, (const int*)list, reuse_law);
+											   (const int*)cnt, nxt, (const int*)list, reuse_law,
+											   (T*)b.tail_scratch, b.tail_scratch_stride, exports);
 			if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_tick_tail)");
 		}
 		if (int rc = done(b, "k_tick_tail")) return rc;

@@ -5,7 +5,7 @@
 #include <algorithm>
 
 #include "osc_aux_kernels.cuh"
-#include "osc_fused2.cuh"
+#include "osc_fused3.cuh"
 #include "osc_otg.cuh"
 #include "osc_rollout.cuh"
 #include "osc_host.h"
@@ -88,13 +88,14 @@ template <class T, int N> struct OpsImpl : Ops {
 		c.body = t.md.body; c.partial = t.md.partial; c.rank = t.dof; c.in_compliant_frame = t.md.parametrization_in_compliant_frame;
 		for (int a = 0; a < 3; ++a) {
 			c.p_c[a] = (X)t.frame_p[a];
-			for (int k = 0; k < 3; ++k) { c.R_c[a][k] = (X)t.frame_R[a][k]; c.Pt[a][k] = (X)t.P6[a][k]; c.Pr[a][k] = (X)t.P6[3 + a][3 + k]; }
+			for (int k = 0; k < 3; ++k) { c.R_c[a][k] = (X)t.frame_R[a][k]; c.Pt[a][k] = (X)t.P6[a][k]; c.Pr[a][k] = (X)t.P6[3 + a][3 + k]; c.Bt[a][k] = (X)t.Bt[a][k]; c.Br[a][k] = (X)t.Br[a][k]; }
 			c.kp_pos[a] = (X)p.kp_pos[a]; c.kv_pos[a] = (X)p.kv_pos[a]; c.ki_pos[a] = (X)p.ki_pos[a];
 			c.kp_ori[a] = (X)p.kp_ori[a]; c.kv_ori[a] = (X)p.kv_ori[a]; c.ki_ori[a] = (X)p.ki_ori[a];
 			c.force_axis[a] = (X)p.force_or_motion_axis[a]; c.moment_axis[a] = (X)p.moment_or_rotmotion_axis[a];
 			c.sensor_p[a] = (X)p.sensor_xyz[a];
 			for (int k = 0; k < 3; ++k) c.sensor_R[a][k] = (X)p.sensor_rot[3 * a + k];
 		}
+		c.mt = t.mt; c.mr = t.mr;
 		c.dt = (X)t.md.loop_timestep;
 		c.kp_force = (X)p.kp_force; c.kv_force = (X)p.kv_force; c.ki_force = (X)p.ki_force;
 		c.kp_moment = (X)p.kp_moment; c.kv_moment = (X)p.kv_moment; c.ki_moment = (X)p.ki_moment;
@@ -185,7 +186,7 @@ template <class T, int N> struct OpsImpl : Ops {
 	}
 	int update_sensed(Batch& b, int t, const void* tmp6) override {
 		TaskH& th = b.tasks[t];
-		k_mft_sensed<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(mftcc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride);
+		k_mft_sensed<C, N, T><<<grid(b), OSC_THREADS, 0, b.stream>>>(chc, mftcc(th), rob(b), tk(th), (const T*)tmp6, b.B, b.stride, b.stale ? 1 : 0);
 		return done(b, "k_mft_sensed");
 	}
 

@@ -69,13 +69,21 @@ def config3(torch, chain, B=262144, ticks=100):
     fd = torch.from_numpy(np.ascontiguousarray(f.T)).cuda(); md = torch.zeros_like(fd)
     L, h = b.L, b.h
 
-    def step():
+    def step_per_call():
         L.osc_update_model(h); L.osc_update_task_models(h)
         L.osc_mft_update_sensed_force_and_moment(h, t0, fd.data_ptr(), md.data_ptr(), abi.LAYOUT_SOA, abi.MEM_DEVICE)
         L.osc_compute_torques(h, 1, None, abi.LAYOUT_SOA, abi.MEM_DEVICE)
-    ms = timed(torch, step, ticks)
-    return {"config": 3, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
-            "robot_ticks_per_s": B / (ms.mean() * 1e-3), "route": "per-call kernels (partial task + force axes + POPC)"}
+
+    def step_tick():   # the control cycle around osc_tick: sensed wrench in, fused tick (k_mft_sensed + k_tick_fused3 + k_tick_tail)
+        L.osc_mft_update_sensed_force_and_moment(h, t0, fd.data_ptr(), md.data_ptr(), abi.LAYOUT_SOA, abi.MEM_DEVICE)
+        L.osc_tick(h, 1, None, abi.LAYOUT_SOA, abi.MEM_DEVICE)
+    out = []
+    for name, fn in (("per-call kernels (API-faithful route)", step_per_call), ("osc_tick: k_mft_sensed + k_tick_fused3 + k_tick_tail", step_tick)):
+        ms = timed(torch, fn, ticks)
+        out.append({"config": 3, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+                    "robot_ticks_per_s": B / (ms.mean() * 1e-3), "route": name, "fused": bool(b.tick_is_fused()),
+                    "fallback_robots": int(b.tick_fallback_count())})
+    return out
 
 
 def config4(torch, name, B=65536, ticks=50):
@@ -108,7 +116,8 @@ def main():
         if B <= args.max_batch:
             print(json.dumps(config5(torch, panda, B)), flush=True)
             torch.cuda.empty_cache()
-    print(json.dumps(config3(torch, panda)), flush=True)
+    for rec in config3(torch, panda):
+        print(json.dumps(rec), flush=True)
     print(json.dumps(config4(torch, "panda")), flush=True)
     print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
 
