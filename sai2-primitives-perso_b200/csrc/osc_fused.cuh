@@ -272,31 +272,31 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 	for (int idx = (int)slot; idx < n; idx += gridDim.x * blockDim.x) {
 		const int64_t r = fb_list[idx];
 		const Row<T, S> rS{rob.S, stride, r}, mS{tk0.S, stride, r}, jS{tk1.S, stride, r};                       // the robot's own rows
-		const Row<T, S> xS = srow<T>(xr, stride, r), xm = srow<T>(x0, stride, r), xj = srow<T>(x1, stride, r);   // where the chain works
+		const Row<T, S> xS = srow<T, true>(xr, stride, r), xm = srow<T, true>(x0, stride, r), xj = srow<T, true>(x1, stride, r);   // where the chain works
 		if (redirected) {
 			if (reuse_law & 1) {  // F*, F_f handed over by the fused kernel
 				for (int i = 0; i < 6; ++i) { xm(ML::UMF + i) = (T)mS(ML::UMF + i); xm(ML::FFB + i) = (T)mS(ML::FFB + i); }
 			}
-			if (exports && reuse_law) {  // vector getters the fused kernel already wrote for this robot (the control laws it ran) ride along
-				for (int e = 0; e < ML::J; ++e) xm(e) = (T)mS(e);
-				for (int e = 0; e < JL::NT; ++e) xj(e) = (T)jS(e);
-			}
+
 			if (gravity) for (int i = 0; i < N; ++i) xS(RobotL<N>::GRAV + i) = (T)rS(RobotL<N>::GRAV + i);
 		}
-		model_robot<T, N>(ch, xr, stride, r, 1, gravity);
-		mft_update_robot<T, N>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
-		jt_update_robot<T, N>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
-		mft_compute_robot<T, N>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
-		jt_compute_robot<T, N>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
+		model_robot<T, N, S, true>(ch, xr, stride, r, 1, gravity);
+		mft_update_robot<T, N, S, true>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
+		jt_update_robot<T, N, S, true>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
+		mft_compute_robot<T, N, S, true>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
+		jt_compute_robot<T, N, S, true>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
 		if (gravity) {
 			for (int i = 0; i < N; ++i) xS(RobotL<N>::TAU + i) += (T)xS(RobotL<N>::GRAV + i);
 		}
 		if (redirected) {
 			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) = (T)xS(RobotL<N>::TAU + i);
-			if (exports) {  // vector getters of the LAZY output mode: the leading rows of the two task arenas (osc_layout.cuh)
-				for (int e = 0; e < ML::J; ++e) mS(e) = (T)xm(e);
+			if (exports) {  // vector getters of the LAZY output mode (leading rows of the task arenas, osc_layout.cuh): the task
+				// torques and alpha always; the rows of a control law only when this kernel ran that law (else the fused kernel
+				// already wrote them at the robot's own rows)
+				for (int e = 0; e < N; ++e) { mS(ML::TASK_TAU + e) = (T)xm(ML::TASK_TAU + e); jS(JL::TASK_TAU + e) = (T)xj(JL::TASK_TAU + e); }
 				mS(ML::ALPHA) = (T)xm(ML::ALPHA);
-				for (int e = 0; e < JL::NT; ++e) jS(e) = (T)xj(e);
+				if (!(reuse_law & 1)) for (int e = N; e < ML::J; ++e) mS(e) = (T)xm(e);
+				if (!(reuse_law & 2)) for (int e = N; e < JL::NT; ++e) jS(e) = (T)xj(e);
 			}
 		}
 	}

@@ -37,16 +37,16 @@ OSC_DEV void jt_pd_law(const JtC<T, N>& jc, const Row<T, S>& tP, const Row<T, S>
 	if (export_vectors) st_vec<T, N>(tS, L::DES_VEL, dv);
 }
 
-template <class T, int N, class S = T>
+template <class T, int N, class S = T, bool REDIR = false>
 __device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk, const S* nprec_src, int64_t stride, int64_t r,
 								int64_t np_stride = 0, int64_t np_index = -1) {
 	using L = JtL<N>;
-	const Row<T, S> rS = srow<T>(rob, stride, r), tS = srow<T>(tk, stride, r);
+	const Row<T, S> rS = srow<T, REDIR>(rob, stride, r), tS = srow<T, REDIR>(tk, stride, r);
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 	T Np[N][N];
 	if (nprec_src) {
-		const Row<T, S> src{const_cast<S*>(nprec_src), np_stride ? np_stride : stride, np_index >= 0 ? np_index : r};
+		const Row<T, S> src{const_cast<S*>(nprec_src), (REDIR && np_stride) ? np_stride : stride, (REDIR && np_index >= 0) ? np_index : r};
 		ld_mat<T, N, N>(src, 0, Np);
 	} else {
 		OSC_UNROLL for (int i = 0; i < N; ++i)
@@ -190,11 +190,11 @@ __global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant
 	jt_update_robot<T, N>(jc, rob, tk, nprec_src, stride, r);
 }
 
-template <class T, int N, class S = T>
+template <class T, int N, class S = T, bool REDIR = false>
 __device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk, int64_t stride, int64_t r, int with_tau_prec,
 								 int accumulate, int integrated_already = 0) {
 	using L = JtL<N>;
-	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T>(tk, stride, r);
+	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T, REDIR>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T, REDIR>(tk, stride, r);
 	const Row<int32_t> tI{tk.I, stride, r};
 	T q[N], dq[N], cp[N], cv[N];
 	ld_vec<T, N>(rP, RobotL<N>::Q, q);

@@ -73,8 +73,10 @@ template <class T> struct Row<T, T> {
 	OSC_DEV T ro(int e) const { return __ldg(base + (int64_t)e * stride + r); }
 };
 // the S (scratch) row of an owner: the robot's own, or the compact slot of a k_tick_tail thread (Arena::s_stride / s_index)
-template <class T, class S> OSC_DEV Row<T, S> srow(const Arena<S>& a, int64_t stride, int64_t r) {
-	return Row<T, S>{a.S, a.s_stride ? a.s_stride : stride, a.s_index >= 0 ? a.s_index : r};
+// (REDIR is a compile-time property of the caller: only k_tick_tail's instantiations of the per-robot functions pay for the selects)
+template <class T, bool REDIR, class S> OSC_DEV Row<T, S> srow(const Arena<S>& a, int64_t stride, int64_t r) {
+	if constexpr (REDIR) return Row<T, S>{a.S, a.s_stride ? a.s_stride : stride, a.s_index >= 0 ? a.s_index : r};
+	else return Row<T, S>{a.S, stride, r};
 }
 template <class T, int R, int C, class S = T>
 OSC_DEV void ld_mat(const Row<T, S>& a, int off, T (&A)[R][C]) {
@@ -109,9 +111,9 @@ OSC_DEV void ld_kin(const Row<T, S>& Sr, Kin<T, N>& k) {
 // ------------------------------------------------------------------------------------------------------------------
 // robot->updateModel()
 // ------------------------------------------------------------------------------------------------------------------
-template <class T, int N, class S = T>
+template <class T, int N, class S = T, bool REDIR = false>
 __device__ void model_robot(const ChainC<T, N>& ch, const Arena<S>& rob, int64_t stride, int64_t r, int dynamics, int gravity) {
-	const Row<T, S> P{rob.P, stride, r}, Sr = srow<T>(rob, stride, r);
+	const Row<T, S> P{rob.P, stride, r}, Sr = srow<T, REDIR>(rob, stride, r);
 	T q[N];
 	ld_vec<T, N>(P, RobotL<N>::Q, q);
 	Kin<T, N> kin;

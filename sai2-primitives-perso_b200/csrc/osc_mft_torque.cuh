@@ -25,12 +25,12 @@ OSC_DEV void range_torque(const Row<T, S>& tS, int offU, int offJ, int offL, con
 	mtv<T, K, N>(Jx, f, tau);
 }
 
-template <class T, int N, class S = T>
+template <class T, int N, class S = T, bool REDIR = false>
 __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<S>& rob, const Arena<S>& tk, int64_t stride, int64_t r,
 								  int with_tau_prec, int accumulate, int reuse_law = 0) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T>(tk, stride, r);
+	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T, REDIR>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T, REDIR>(tk, stride, r);
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 

@@ -22,12 +22,12 @@ OSC_DEV void task_jacobian(const ChainC<T, N>& ch, const MftC<T>& tc, const Kin<
 
 // One robot.  `no_history` re-evaluates the task model without pushing a classification sample (lazy materialisation
 // of the getters after a fused tick: the history was already advanced by the tick itself).
-template <class T, int N, class S = T>
+template <class T, int N, class S = T, bool REDIR = false>
 __device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const Arena<S>& rob, const Arena<S>& tk, const S* nprec_src,
 								 int64_t stride, int64_t r, int no_history) {
 	using L = MftL<N>;
 	constexpr int K = L::K;
-	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T>(tk, stride, r);
+	const Row<T, S> rP{rob.P, stride, r}, rS = srow<T, REDIR>(rob, stride, r), tP{tk.P, stride, r}, tS = srow<T, REDIR>(tk, stride, r);
 	const Row<int32_t> tI{tk.I, stride, r};
 	int status = 0;
 

@@ -267,9 +267,28 @@ template <class T, int N> struct OpsImpl : Ops {
 			++cnt;
 		}
 		if (!cnt) return OSC_OK;
-		const dim3 g((unsigned)((b.B + 127) / 128), cnt);
-		k_otg_advance<T, N><<<g, 128, 0, b.stream>>>(js, b.B, b.stride);
-		if (int rc = done(b, "k_otg_advance")) return rc;
+		bool goal_write = false;
+		for (int i = 0; i < cnt; ++i) goal_write |= js.j[i].check_goals != 0;
+#ifdef OSC_EXPERIMENT
+		// measured A/B (profiles/README.md, r2f): the bulk-copy staged advance ties the plain kernel (27.3 vs 26.9 us at 65,536 robots,
+		// 312 vs 301 us at 1,048,576), so the product build launches the plain kernel only
+		static const int tma_mode = getenv("OSC_OTG_TMA") ? atoi(getenv("OSC_OTG_TMA")) : 0;
+		if (!goal_write && b.B >= 4096 && tma_mode) {
+			const int tiles_x = (int)((b.B + 127) / 128), n_tiles = tiles_x * cnt;
+			const size_t smem = (size_t)OtgStage<N>::BYTES;
+			auto kern = k_otg_advance_tma<T, N>;
+			if (first_launch_on_device((const void*)kern, b.device)) {
+				cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+				if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_otg_advance_tma)");
+			}
+			const int blocks = std::min(n_tiles, 148 * 4);
+			kern<<<blocks, 128, smem, b.stream>>>(js, b.B, b.stride, tiles_x, n_tiles);
+		} else
+#endif
+		{
+			const dim3 g((unsigned)((b.B + 127) / 128), cnt);
+			k_otg_advance<T, N><<<g, 128, 0, b.stream>>>(js, b.B, b.stride);
+		}
 		cudaLaunchConfig_t cfg = {};
 		// a goal write may send every robot to the general path (MPC: new goals each tick): full grid then, else a small one
 		bool any_goal_write = false;

@@ -873,6 +873,161 @@ __global__ void __launch_bounds__(128, 4) k_otg_advance(const __grid_constant__ 
 	else otg_advance_robot<T, N, false>(js.j[blockIdx.y], B, stride);
 }
 
+// ---- k_otg_advance_tma (EXPERIMENT builds only): the steady-state advance with bulk-copy (TMA) staging ------------------------
+// A persistent kernel: each block loops over tiles of 128 robots x one task; ONE thread issues the rows of the tile as
+// cp.async.bulk copies (global -> shared, completion on an mbarrier: SASS UBLKCP / SYNCS.ARRIVE.TRANS64), the 128 threads
+// evaluate the tile out of shared memory; four blocks per SM (54 KB each).  Measured on B200 (r2f): it ties the plain kernel
+// above at 65,536 and at 1,048,576 robots, and a two-stage variant (half the resident threads) is 30 % slower.  The advance
+// moves ~1.3 KB of DRAM traffic per robot and tick (6-row cached segments, REF, DUR, flags on top of the 792 algorithmic bytes)
+// at ~0.6 of the copy bandwidth either way: how the loads are issued is not its bound.  Kept out of the product build.
+#ifdef OSC_EXPERIMENT
+template <int N> struct OtgStage {
+	static constexpr int DMAX = N > 6 ? N : 6;
+	static constexpr int ROWS = 2 + 6 * DMAX + 9;          // doubles rows of 128 robots
+	static constexpr int BYTES = ROWS * 128 * 8 + 128 * 4;  // + the int flags row
+};
+__device__ __forceinline__ uint32_t otg_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void otg_mbar_init(uint64_t* bar, int count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(otg_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void otg_mbar_expect(uint64_t* bar, uint32_t bytes) {
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(otg_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void otg_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(otg_smem_u32(dst)), "l"(src),
+				 "r"(bytes), "r"(otg_smem_u32(bar))
+				 : "memory");
+}
+__device__ __forceinline__ void otg_mbar_wait(uint64_t* bar, uint32_t parity) {
+	asm volatile(
+		"{\n"
+		".reg .pred p;\n"
+		"OTG_WAIT_%=:\n"
+		"mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+		"@p bra OTG_DONE_%=;\n"
+		"bra OTG_WAIT_%=;\n"
+		"OTG_DONE_%=:\n"
+		"}\n" ::"r"(otg_smem_u32(bar)),
+		"r"(parity)
+		: "memory");
+}
+
+// issue the rows of one tile (one thread): D = dof of the task's OTG
+template <int D, bool CART> __device__ __forceinline__ void otg_tile_issue(const OtgJob& job, int64_t stride, int64_t r0, double* buf, int32_t* fl, uint64_t* bar) {
+	using L = OtgL<D>;
+	const int64_t left = stride - r0;
+	const uint32_t cnt = (uint32_t)(left < 128 ? left : 128);  // stride is a multiple of 32 robots: every piece is a multiple of 256 B
+	constexpr int NR = 2 + 6 * D + (CART ? 9 : 0);
+	otg_mbar_expect(bar, NR * cnt * 8 + cnt * 4);
+	const double* O = job.O + r0;
+	otg_bulk_g2s(buf, O + (int64_t)L::TIME * stride, cnt * 8, bar);
+	otg_bulk_g2s(buf + 128, O + (int64_t)L::DUR * stride, cnt * 8, bar);
+	_Pragma("unroll 1") for (int e = 0; e < 6 * D; ++e) otg_bulk_g2s(buf + (2 + e) * 128, O + (int64_t)(L::SEG + e) * stride, cnt * 8, bar);
+	if constexpr (CART) {
+		_Pragma("unroll 1") for (int e = 0; e < 9; ++e) otg_bulk_g2s(buf + (2 + 6 * D + e) * 128, O + (int64_t)(L::REF + e) * stride, cnt * 8, bar);
+	}
+	otg_bulk_g2s(fl, job.OI + (int64_t)L::FLAGS * stride + r0, cnt * 4, bar);
+}
+
+// evaluate one staged tile: same arithmetic, same stores and the same slow-list protocol as otg_advance_robot (check_goals == 0)
+template <class T, int D, bool CART>
+__device__ __forceinline__ void otg_tile_eval(const OtgJob& job, int64_t B, int64_t stride, int64_t r0, const double* buf, const int32_t* fl) {
+	using L = OtgL<D>;
+	const int tid = threadIdx.x;
+	const int64_t rr = r0 + tid;
+	const int64_t r = rr < B ? rr : B - 1;
+	const bool live = rr < B && !(!CART && job.rank && job.rank[r] == 0);
+	const Row<double> O{job.O, stride, r};
+	const Row<int32_t> OI{job.OI, stride, r};
+	const Row<T> P{(T*)job.P, stride, r};
+	const int k = CART ? 6 : job.k;
+	const int flags = rr < B ? fl[tid] : (int)OTG_REACHED;
+	const bool idle = (flags & OTG_REACHED) != 0;
+	bool slow = !idle && ((flags & OTG_DIRTY) || !(flags & OTG_INIT));
+	double time = 0;
+	if (!slow && !idle) {
+		time = buf[tid] + job.dt;
+		slow = time > buf[128 + tid];
+	}
+	slow = slow && live;
+	{
+		const unsigned m = __ballot_sync(0xffffffffu, slow);
+		if (m) {
+			const int lane = tid & 31, leader = __ffs(m) - 1;
+			int base = 0;
+			if (lane == leader) base = atomicAdd(job.slow_count, __popc(m));
+			base = __shfl_sync(0xffffffffu, base, leader);
+			if (slow) job.slow_list[base + __popc(m & ((1u << lane) - 1u))] = (int)r;
+		}
+	}
+	if (slow || idle || !live) return;
+	double np[D], nv[D], na[D];
+	OSC_UNROLL for (int d = 0; d < D; ++d)
+		if (d < k) {
+			const double* sg_ = buf + (2 + d) * 128 + tid;
+			OtgSeg sg{sg_[0], sg_[D * 128], sg_[2 * D * 128], sg_[3 * D * 128], sg_[4 * D * 128], sg_[5 * D * 128]};
+			double td = sg.off > 0 ? time - sg.off : time;
+			if (!(td < sg.te) || td < sg.ts) {
+				OtgProf p;
+				otg_load_prof<D>(O, d, p);
+				sg = otg_segment(p, time);
+				O(L::SEG + d) = sg.off; O(L::SEG + D + d) = sg.ts; O(L::SEG + 2 * D + d) = sg.te; O(L::SEG + 3 * D + d) = sg.p;
+				O(L::SEG + 4 * D + d) = sg.v; O(L::SEG + 5 * D + d) = sg.a;
+				td = sg.off > 0 ? time - sg.off : time;
+			}
+			const double t = td - sg.ts;
+			np[d] = sg.p + t * (sg.v + t * (sg.a / 2 + t * 0.0 / 6));
+			nv[d] = sg.v + t * (sg.a + t * 0.0 / 2);
+			na[d] = sg.a + t * 0.0;
+		}
+	O(L::TIME) = time;
+	if ((flags & (OTG_IN_SYNCED | OTG_OUT_LIVE)) != (OTG_IN_SYNCED | OTG_OUT_LIVE)) OI(L::FLAGS) = flags | OTG_IN_SYNCED | OTG_OUT_LIVE;
+	if constexpr (!CART) {
+		OSC_UNROLL for (int i = 0; i < D; ++i)
+			if (i < k) { P(i) = (T)np[i]; P(D + i) = (T)nv[i]; P(2 * D + i) = (T)na[i]; }
+	} else {
+		using ML = MftL<7>;
+		double ref[9], Rn[9];
+		OSC_UNROLL for (int i = 0; i < 9; ++i) ref[i] = buf[(2 + 6 * D + i) * 128 + tid];
+		const double rv[3] = {np[3], np[4], np[5]};
+		otg_next_orientation(ref, rv, Rn);
+		OSC_UNROLL for (int i = 0; i < 3; ++i) {
+			P(ML::GOAL_POS + i) = (T)np[i]; P(ML::GOAL_LINVEL + i) = (T)nv[i]; P(ML::GOAL_LINACC + i) = (T)na[i];
+			P(ML::GOAL_ANGVEL + i) = (T)(ref[3 * i] * nv[3] + ref[3 * i + 1] * nv[4] + ref[3 * i + 2] * nv[5]);
+			P(ML::GOAL_ANGACC + i) = (T)(ref[3 * i] * na[3] + ref[3 * i + 1] * na[4] + ref[3 * i + 2] * na[5]);
+		}
+		OSC_UNROLL for (int i = 0; i < 9; ++i) P(ML::GOAL_ORI + i) = (T)Rn[i];
+	}
+}
+
+template <class T, int N>
+__global__ void __launch_bounds__(128, 4) k_otg_advance_tma(const __grid_constant__ OtgJobs js, int64_t B, int64_t stride, int tiles_x, int n_tiles) {
+	extern __shared__ __align__(128) unsigned char otg_stage_raw[];
+	__shared__ __align__(8) uint64_t bar;
+	asm volatile("griddepcontrol.launch_dependents;");
+	double* buf = reinterpret_cast<double*>(otg_stage_raw);
+	int32_t* fl = reinterpret_cast<int32_t*>(otg_stage_raw + (size_t)OtgStage<N>::ROWS * 128 * 8);
+	if (threadIdx.x == 0) {
+		otg_mbar_init(&bar, 1);
+		asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+	}
+	__syncthreads();
+	int it = 0;
+	for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+		const int y = tile / tiles_x;
+		const int64_t r0 = (int64_t)(tile - y * tiles_x) * 128;
+		if (threadIdx.x == 0) {  // one stage: the other three resident blocks of the SM cover this block's copy latency
+			if (js.cart[y]) otg_tile_issue<6, true>(js.j[y], stride, r0, buf, fl, &bar);
+			else otg_tile_issue<N, false>(js.j[y], stride, r0, buf, fl, &bar);
+		}
+		otg_mbar_wait(&bar, it & 1);
+		if (js.cart[y]) otg_tile_eval<T, 6, true>(js.j[y], B, stride, r0, buf, fl);
+		else otg_tile_eval<T, N, false>(js.j[y], B, stride, r0, buf, fl);
+		__syncthreads();  // every read of the stage is done before it is refilled
+	}
+}
+#endif  // OSC_EXPERIMENT
+
 // ---- cold path: reInitialize / enable / disable ---------------------------------------------------------------------
 // mode bit 1: reInitialize (all), 2: reInitializeLinear, 4: reInitializeAngular (OTG_6dof_cartesian.cpp:46-84, OTG_joints.cpp:28-41);
 // 64: the caller also reset the task's goals to the current state (reInitializeTask, parametrize*Spaces): mirror that in G;

@@ -220,3 +220,42 @@ def test_otg_fp32_batch(oracle_built):
     a = np.asarray(p.gpu.get(abi.F_OTG_FLAGS, t1))[:, 0] & 1
     b = np.rint(p.ref.get(abi.F_OTG_FLAGS, t1))[:, 0].astype(int)
     assert (a == b).mean() > 0.98  # float goals differ from the double goals of the oracle in the last bits
+
+
+def test_otg_large_batch_ragged_advance(oracle_built):
+    """A batch of several thousand robots whose size is not a multiple of the 128-robot block: a subset of the robots -- the first
+    blocks and the ragged last one -- is followed by the oracle every tick through two goal changes (ticks with a goal write run the
+    goal filter, the others the steady-state advance only; an OSC_EXPERIMENT build with OSC_OTG_TMA=1 runs the bulk-copy staged
+    advance on the latter, interleaved with the plain kernel on the same state)."""
+    import orc
+    import osc_b200
+    chain = load_chain("panda")
+    B, T = 4096 + 200 + 13, 150
+    w = workloads.config2(chain, 512, seed=31)
+    rep = (B + 511) // 512
+    tile = lambda a: np.tile(a, (rep, 1))[:B] + 0.0
+    pick = np.concatenate([np.arange(0, 160), np.arange(B - 96, B)])
+    batches = []
+    for kind in ("gpu", "ref"):
+        sel = slice(None) if kind == "gpu" else pick
+        b = osc_b200.Batch(chain, B, q0=q0_of(chain)) if kind == "gpu" else orc.OracleBatch(chain, len(pick), q0=q0_of(chain))
+        t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07))); t1 = b.add_joint_task(abi.joint_task_desc(7))
+        b.set(abi.F_Q, tile(w["q"])[sel]); b.set(abi.F_DQ, tile(w["dq"])[sel]); b.update_model(); b.reinitialize_tasks()
+        b.enable_internal_otg(t0, *MFT_LIM); b.enable_internal_otg(t1, *JT_LIM)
+        batches.append(b)
+    g, r = batches
+    rng = np.random.default_rng(8)
+    gp, jg = tile(w["goal_pos"]), tile(w["jt_goal"])
+    for tick in range(T):
+        if tick in (0, 70):
+            gp = gp + rng.uniform(-0.08, 0.08, (B, 3)); jg = jg + rng.uniform(-0.4, 0.4, (B, 7))
+            g.set(abi.F_GOAL_POSITION, gp, t0); g.set(abi.F_JT_GOAL_POSITION, jg, t1)
+            r.set(abi.F_GOAL_POSITION, gp[pick], t0); r.set(abi.F_JT_GOAL_POSITION, jg[pick], t1)
+        tg, tr = g.tick(True), r.tick(True)
+        assert rel_err(np.asarray(tg)[pick], tr)[0] <= FP64_TOL, tick
+        if tick % 10 == 9:
+            for f, task, floor in ((abi.F_DESIRED_POSITION, t0, 1e-3), (abi.F_DESIRED_ORIENTATION, t0, 1.0), (abi.F_JT_DESIRED_POSITION, t1, 1e-3),
+                                   (abi.F_JT_DESIRED_VELOCITY, t1, 1e-3), (abi.F_DESIRED_ANGULAR_VELOCITY, t0, 1e-3)):
+                assert rel_err(g.get(f, task)[pick], r.get(f, task), floor)[0] <= FP64_TOL, (tick, f)
+    reached = (np.asarray(g.get(abi.F_OTG_FLAGS, t1))[:, 0] & 1)
+    assert np.array_equal(reached[pick], np.rint(r.get(abi.F_OTG_FLAGS, t1))[:, 0].astype(np.int64) & 1)
