@@ -879,7 +879,7 @@ __global__ void __launch_bounds__(128, 4) k_otg_advance(const __grid_constant__ 
 // evaluate the tile out of shared memory; four blocks per SM (54 KB each).  Measured on B200 (r2f): it ties the plain kernel
 // above at 65,536 and at 1,048,576 robots, and a two-stage variant (half the resident threads) is 30 % slower.  The advance
 // moves ~1.3 KB of DRAM traffic per robot and tick (6-row cached segments, REF, DUR, flags on top of the 792 algorithmic bytes)
-// at ~0.6 of the copy bandwidth either way: how the loads are issued is not its bound.  Kept out of the product build.
+// at ~0.7 of the copy bandwidth either way: how the loads are issued is not its bound.  Kept out of the product build.
 #ifdef OSC_EXPERIMENT
 template <int N> struct OtgStage {
 	static constexpr int DMAX = N > 6 ? N : 6;

@@ -106,12 +106,85 @@ def config4(torch, name, B=65536, ticks=50):
             "route": "fused tick; robots in the blend branch go through k_tick_tail"}
 
 
+def config1(torch, chain, ticks=10000):
+    """BASELINE config 1: ONE Panda, the control cycle of examples/04-task_and_redundancy (…cpp:138-199) with the host in the loop
+    every tick: q, dq from host memory -> osc_tick -> tau back in host memory, wall-clock per tick (what a 1 kHz control thread
+    would see).  The goal moves on the circle of :163-172.  Not a throughput configuration: a single robot uses one thread of one SM."""
+    import time
+    from common import q0_of
+    b = osc_b200.Batch(chain, 1, q0=q0_of(chain))
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    t1 = b.add_joint_task(abi.joint_task_desc(chain["n"]))
+    q = np.array([q0_of(chain)], float); dq = np.zeros((1, chain["n"]))
+    b.set(abi.F_Q, q); b.set(abi.F_DQ, dq); b.update_model(); b.reinitialize_tasks()
+    x0 = np.asarray(b.get(abi.F_CURRENT_POSITION, t0)).copy()
+    lat = np.empty(ticks)
+    for k in range(ticks + 200):
+        t = 1e-3 * k
+        goal = x0 + 0.1 * np.array([[np.sin(np.pi * t), 1 - np.cos(np.pi * t), 0.0]])
+        b.set(abi.F_GOAL_POSITION, goal, t0)
+        a = time.perf_counter()
+        b.set(abi.F_Q, q); b.set(abi.F_DQ, dq)
+        tau = b.tick(True)          # returns the torques in host memory (synchronises)
+        e = time.perf_counter()
+        if k >= 200:
+            lat[k - 200] = (e - a) * 1e6
+        q = q + 1e-6 * np.asarray(tau)  # keep the inputs changing without leaving the neighbourhood
+    return {"config": 1, "robots": 1, "ticks": ticks, "p50_us": float(np.percentile(lat, 50)), "p99_us": float(np.percentile(lat, 99)),
+            "what": "host in the loop: 2 x osc_set_field(q, dq) + osc_tick returning tau to host memory, wall clock through the ctypes binding",
+            "fused": bool(b.tick_is_fused())}
+
+
+def config4_stages(torch, name="panda", B=65536, ticks=10):
+    """Where the per-call route spends its time when EVERY robot is in the singular blend branch (what k_tick_tail runs per robot)."""
+    import test_singular_gpu as S
+    from common import q0_of
+    chain = chain_of(name)
+    rng = np.random.default_rng(4)
+    base = S._panda_q(rng) if name == "panda" else S._puma_q(rng)
+    q = np.tile(base, ((B + len(base) - 1) // len(base), 1))[:B]
+    n = chain["n"]
+    b = osc_b200.Batch(chain, B, q0=q0_of(chain))
+    b.set_stream(torch.cuda.current_stream().cuda_stream)
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0)))
+    t1 = b.add_joint_task(abi.joint_task_desc(n)) if n > 6 else None
+    b.set(abi.F_Q, q); b.set(abi.F_DQ, np.zeros((B, n))); b.update_model(); b.reinitialize_tasks()
+    calls = [("k_model", lambda: b.update_model()), ("k_mft_update", lambda: b.task_update_model(t0, -1)),
+             ("k_mft_compute", lambda: b.task_compute_torques(t0, False))]
+    if t1 is not None:
+        calls += [("k_jt_update", lambda: b.task_update_model(t1, t0)), ("k_jt_compute", lambda: b.task_compute_torques(t1, True))]
+    out = {}
+    for nm, fn in calls:
+        out[nm] = float(np.median(timed(torch, fn, ticks, warm=2)) * 1e3)
+    return {"config": 4, "chain": name, "robots": B, "route": "per-call kernels, every robot in the blend branch", "stage_us": out}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-batch", type=int, default=3000000)
+    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5")
     args = ap.parse_args()
     import torch
     panda = chain_of("panda")
+    only = set(args.only.split(",")) if args.only else None
+    if only is not None:
+        if "1" in only:
+            print(json.dumps(config1(torch, panda)), flush=True)
+        if "5" in only:
+            for B in (10000, 30000, 100000, 300000, 1000000, 3000000, 10000000):
+                if B <= args.max_batch:
+                    print(json.dumps(config5(torch, panda, B)), flush=True)
+        if "3" in only:
+            for rec in config3(torch, panda):
+                print(json.dumps(rec), flush=True)
+        if "4" in only:
+            print(json.dumps(config4(torch, "panda")), flush=True)
+            print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
+        if "4s" in only:
+            print(json.dumps(config4_stages(torch, "panda")), flush=True)
+            print(json.dumps(config4_stages(torch, "puma560_synthetic")), flush=True)
+        return
+    print(json.dumps(config1(torch, panda)), flush=True)
     for B in (10000, 30000, 100000, 300000, 1000000, 3000000, 10000000):
         if B <= args.max_batch:
             print(json.dumps(config5(torch, panda, B)), flush=True)
