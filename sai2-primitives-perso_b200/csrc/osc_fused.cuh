@@ -244,20 +244,72 @@ __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 }
 
-// The robots k_tick_fused could not certify: the API-faithful route (every branch of SingularityHandler, full Jacobi
-// SVDs), one robot per thread over the compacted list.  Also re-arms the other fallback counter for the next tick.
-template <class T, int N, class S = T>
+// osc_blend.cuh: the singular-blend branch in closed form (tried first by k_tick_tail<.., MB > 0>)
+template <class T, int N, int M, class S>
+__device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk0,
+											const Arena<S>& tk1, const Row<T, S>& xm, int64_t stride, int64_t r, int stacked, int gravity, int reuse_law,
+											int exports, T* __restrict__ sm);
+
+// The API-faithful chain for one listed robot (every branch of SingularityHandler, full Jacobi SVDs): see k_tick_tail.
+template <class T, int N, class S>
+__device__ __forceinline__ void tail_chain_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk0,
+												  const Arena<S>& tk1, const Arena<S>& xr, const Arena<S>& x0, const Arena<S>& x1, int64_t stride, int64_t r,
+												  int stacked, int gravity, int reuse_law, int exports) {
+	using ML = MftL<N>;
+	using JL = JtL<N>;
+	const bool redirected = xr.s_stride != 0;
+	const Row<T, S> rS{rob.S, stride, r}, mS{tk0.S, stride, r}, jS{tk1.S, stride, r};                       // the robot's own rows
+	const Row<T, S> xS = srow<T, true>(xr, stride, r), xm = srow<T, true>(x0, stride, r), xj = srow<T, true>(x1, stride, r);   // where the chain works
+	if (redirected) {
+		if (reuse_law & 1) {  // F*, F_f handed over by the fused kernel
+			for (int i = 0; i < 6; ++i) { xm(ML::UMF + i) = (T)mS(ML::UMF + i); xm(ML::FFB + i) = (T)mS(ML::FFB + i); }
+		}
+		if (gravity) for (int i = 0; i < N; ++i) xS(RobotL<N>::GRAV + i) = (T)rS(RobotL<N>::GRAV + i);
+	}
+	model_robot<T, N, S, true>(ch, xr, stride, r, 1, gravity);
+	mft_update_robot<T, N, S, true>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
+	jt_update_robot<T, N, S, true>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
+	mft_compute_robot<T, N, S, true>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
+	jt_compute_robot<T, N, S, true>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
+	if (gravity) {
+		for (int i = 0; i < N; ++i) xS(RobotL<N>::TAU + i) += (T)xS(RobotL<N>::GRAV + i);
+	}
+	if (redirected) {
+		for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) = (T)xS(RobotL<N>::TAU + i);
+		if (exports) {  // vector getters of the LAZY output mode (leading rows of the task arenas, osc_layout.cuh): the task
+			// torques and alpha always; the rows of a control law only when this kernel ran that law (else the fused kernel
+			// already wrote them at the robot's own rows)
+			for (int e = 0; e < N; ++e) { mS(ML::TASK_TAU + e) = (T)xm(ML::TASK_TAU + e); jS(JL::TASK_TAU + e) = (T)xj(JL::TASK_TAU + e); }
+			mS(ML::ALPHA) = (T)xm(ML::ALPHA);
+			if (!(reuse_law & 1)) for (int e = N; e < ML::J; ++e) mS(e) = (T)xm(e);
+			if (!(reuse_law & 2)) for (int e = N; e < JL::NT; ++e) jS(e) = (T)xj(e);
+		}
+	}
+}
+// out of line for the kernels that try the closed-form blend first (MB > 0): the chain is their rare second resort, and one copy
+// of its 70 k instructions serves every MB
+template <class T, int N, class S>
+__device__ __noinline__ void tail_chain_robot_call(const ChainC<T, N>& ch, const MftC<T>& tc, const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk0,
+													const Arena<S>& tk1, const Arena<S>& xr, const Arena<S>& x0, const Arena<S>& x1, int64_t stride, int64_t r,
+													int stacked, int gravity, int reuse_law, int exports) {
+	tail_chain_robot<T, N, S>(ch, tc, jc, rob, tk0, tk1, xr, x0, x1, stride, r, stacked, gravity, reuse_law, exports);
+}
+
+// The robots the fused kernels could not certify as non-singular, one per thread over the compacted list.  MB > 0 (n = 7, task rank
+// MB): the closed-form singular-blend routine of osc_blend.cuh first; what it declines -- and everything when MB == 0 -- takes the
+// API-faithful chain.  Also re-arms the other fallback counter for the next tick.
+template <class T, int N, class S = T, int MB = 0>
 __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk0, Arena<S> tk1, int64_t stride,
 															int stacked, int gravity, const int* fb_count, int* fb_count_next, const int* fb_list, int reuse_law,
 															S* scratch, int64_t scratch_stride, int exports) {
+	extern __shared__ __align__(16) unsigned char osc_stash_raw[];
 	// launched with programmatic stream serialisation behind the fused kernel: its launch latency overlaps the fused kernel's
 	// run; the fallback list is complete (and visible) once the wait returns.  A no-op under a plain launch.
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	const int n = *fb_count;
 	if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count_next = 0;
 	using ML = MftL<N>;
-	using JL = JtL<N>;
 	const int64_t slot = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	// The listed robots are scattered over the batch.  With a scratch arena (one slot per tail thread) every S row of the
 	// API-faithful chain below lives at [row][slot]: consecutive threads, consecutive addresses.  What the rest of the library reads
@@ -268,36 +320,14 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 		xr.s_stride = x0.s_stride = x1.s_stride = scratch_stride;
 		xr.s_index = x0.s_index = x1.s_index = slot;
 	}
-	const bool redirected = xr.s_stride != 0;
 	for (int idx = (int)slot; idx < n; idx += gridDim.x * blockDim.x) {
 		const int64_t r = fb_list[idx];
-		const Row<T, S> rS{rob.S, stride, r}, mS{tk0.S, stride, r}, jS{tk1.S, stride, r};                       // the robot's own rows
-		const Row<T, S> xS = srow<T, true>(xr, stride, r), xm = srow<T, true>(x0, stride, r), xj = srow<T, true>(x1, stride, r);   // where the chain works
-		if (redirected) {
-			if (reuse_law & 1) {  // F*, F_f handed over by the fused kernel
-				for (int i = 0; i < 6; ++i) { xm(ML::UMF + i) = (T)mS(ML::UMF + i); xm(ML::FFB + i) = (T)mS(ML::FFB + i); }
-			}
-
-			if (gravity) for (int i = 0; i < N; ++i) xS(RobotL<N>::GRAV + i) = (T)rS(RobotL<N>::GRAV + i);
-		}
-		model_robot<T, N, S, true>(ch, xr, stride, r, 1, gravity);
-		mft_update_robot<T, N, S, true>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
-		jt_update_robot<T, N, S, true>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
-		mft_compute_robot<T, N, S, true>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
-		jt_compute_robot<T, N, S, true>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
-		if (gravity) {
-			for (int i = 0; i < N; ++i) xS(RobotL<N>::TAU + i) += (T)xS(RobotL<N>::GRAV + i);
-		}
-		if (redirected) {
-			for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) = (T)xS(RobotL<N>::TAU + i);
-			if (exports) {  // vector getters of the LAZY output mode (leading rows of the task arenas, osc_layout.cuh): the task
-				// torques and alpha always; the rows of a control law only when this kernel ran that law (else the fused kernel
-				// already wrote them at the robot's own rows)
-				for (int e = 0; e < N; ++e) { mS(ML::TASK_TAU + e) = (T)xm(ML::TASK_TAU + e); jS(JL::TASK_TAU + e) = (T)xj(JL::TASK_TAU + e); }
-				mS(ML::ALPHA) = (T)xm(ML::ALPHA);
-				if (!(reuse_law & 1)) for (int e = N; e < ML::J; ++e) mS(e) = (T)xm(e);
-				if (!(reuse_law & 2)) for (int e = N; e < JL::NT; ++e) jS(e) = (T)xj(e);
-			}
+		if constexpr (MB > 0) {
+			const Row<T, S> xm = srow<T, true>(x0, stride, r);
+			if (blend_robot<T, N, MB, S>(ch, tc, jc, rob, tk0, tk1, xm, stride, r, stacked, gravity, reuse_law, exports, reinterpret_cast<T*>(osc_stash_raw))) continue;
+			tail_chain_robot_call<T, N, S>(ch, tc, jc, rob, tk0, tk1, xr, x0, x1, stride, r, stacked, gravity, reuse_law, exports);
+		} else {
+			tail_chain_robot<T, N, S>(ch, tc, jc, rob, tk0, tk1, xr, x0, x1, stride, r, stacked, gravity, reuse_law, exports);
 		}
 	}
 }

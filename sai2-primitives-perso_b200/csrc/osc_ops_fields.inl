@@ -270,9 +270,35 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			at[0].val.programmaticStreamSerializationAllowed = 1;
 			cfg.attrs = at;
 			cfg.numAttrs = pdl ? 1 : 0;
-			cudaError_t e = cudaLaunchKernelEx(&cfg, k_tick_tail<C, N, T>, chc, mftcc(m), jtcc(b, j), rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
-											   (const int*)cnt, nxt, (const int*)list, reuse_law,
-											   (T*)b.tail_scratch, b.tail_scratch_stride, exports);
+			// closed-form blend routine ahead of the API-faithful chain (osc_blend.cuh): n = 7, task rank 3 (translation-only, config
+			// 3) or 6 (config 4), the fused kernel ran the control law, singularity handling on, no IMPEDANCE decoupling
+			int mb = 0;
+			if constexpr (N == 7) {
+				if ((reuse_law & 1) && m.mp.singularity_handling_enabled && m.mp.dynamic_decoupling_type != OSC_IMPEDANCE && (m.dof == 6 || m.dof == 3) &&
+					(m.dof < 6) == (m.md.partial != 0))
+					mb = m.dof;
+#ifdef OSC_EXPERIMENT
+				static const bool no_blend = getenv("OSC_NO_BLEND") != nullptr;
+				if (no_blend) mb = 0;
+#endif
+			}
+			cudaError_t e = cudaSuccess;
+			auto go_tail = [&](auto kern, size_t smem) {
+				if (smem > 48 * 1024 && first_launch_on_device((const void*)kern, b.device)) {
+					e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+					if (e != cudaSuccess) return;
+				}
+				cfg.dynamicSmemBytes = smem;
+				e = cudaLaunchKernelEx(&cfg, kern, chc, mftcc(m), jtcc(b, j), rob(b), tk(m), tk(j), b.stride, stacked, b.gravity ? 1 : 0,
+									   (const int*)cnt, nxt, (const int*)list, reuse_law, (T*)b.tail_scratch, b.tail_scratch_stride, exports);
+			};
+			if constexpr (N == 7) {
+				if (mb == 6) go_tail(k_tick_tail<C, N, T, 6>, (size_t)BL<N, 6>::SLOTS * OSC_THREADS * sizeof(C));
+				else if (mb == 3) go_tail(k_tick_tail<C, N, T, 3>, (size_t)BL<N, 3>::SLOTS * OSC_THREADS * sizeof(C));
+				else go_tail(k_tick_tail<C, N, T, 0>, 0);
+			} else {
+				go_tail(k_tick_tail<C, N, T, 0>, 0);
+			}
 			if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_tick_tail)");
 		}
 		if (int rc = done(b, "k_tick_tail")) return rc;
