@@ -109,7 +109,25 @@ public:
 	RobotBatch(const RobotBatch&) = delete;
 	RobotBatch& operator=(const RobotBatch&) = delete;
 
-	osc_batch_t* handle() const { return _h; }
+	// Every call made through handle() first applies a deferred control-cycle update (see setControlCycleFusion); rawHandle() does not.
+	osc_batch_t* handle() const { flushControlCycle(); return _h; }
+	osc_batch_t* rawHandle() const { return _h; }
+	// Control-cycle fusion (on by default).  The reference's cycle is three calls -- robot->updateModel();
+	// controller->updateControllerTaskModels(); controller->computeControlTorques() (examples/05...cpp:145-148,195).  With fusion on,
+	// the first two are DEFERRED and computeControlTorques() issues the single fused launch (osc_tick) for all three: same results,
+	// the rate of RobotController::tick() without touching the loop.  Goal setters and updateSensedForceAndMoment() keep the
+	// deferral; any other call in between (setQ/setDq, a getter, a parameter change, a per-task update) first applies the deferred
+	// updates with the API-faithful kernels, exactly where the reference would have run them, and that cycle then computes its
+	// torques per call.  Turn it off to force the API-faithful kernels everywhere.
+	void setControlCycleFusion(bool on) { flushControlCycle(); _fuse = on; }
+	bool controlCycleFusion() const { return _fuse; }
+	int64_t fusedControlCycles() const { return _fused_cycles; }  // how many computeControlTorques() calls took the fused launch
+	void flushControlCycle() const {
+		const int p = _pending;
+		_pending = 0;
+		if (p >= 1) check(osc_update_model(_h));
+		if (p == 2) check(osc_update_task_models(_h));
+	}
 	int dof() const { return osc_batch_dof(_h); }
 	int64_t size() const { return osc_batch_size(_h); }
 	int precision() const { return osc_batch_precision(_h); }
@@ -119,11 +137,15 @@ public:
 	void q(const Out& o) { get(-1, OSC_F_Q, o); }
 	void dq(const Out& o) { get(-1, OSC_F_DQ, o); }
 	// Sai2Model::updateModel / updateKinematics (examples/05-using_robot_controller/05-using_robot_controller.cpp:143-145)
-	void updateModel() { check(osc_update_model(_h)); }
-	void updateKinematics() { check(osc_update_kinematics(_h)); }
+	void updateModel() {
+		flushControlCycle();
+		if (_fuse) _pending = 1;
+		else check(osc_update_model(_h));
+	}
+	void updateKinematics() { flushControlCycle(); check(osc_update_kinematics(_h)); }
 	// the simulation side of examples/05...cpp:219-233 on the device (contact-free): sim->setJointTorques(tau); sim->integrate();
 	// robot->setQ(...); robot->setDq(...) with tau = the controller's last torques
-	void integrate(double dt, int substeps = 1, double joint_damping = 0.0) { check(osc_rollout_step(_h, dt, substeps, joint_damping)); }
+	void integrate(double dt, int substeps = 1, double joint_damping = 0.0) { flushControlCycle(); check(osc_rollout_step(_h, dt, substeps, joint_damping)); }
 	void coriolisPlusGravity(const Out& o) { get(-1, OSC_F_NONLINEAR_EFFECTS, o); }  // of the state the last integrate() started from
 	void M(const Out& o) { get(-1, OSC_F_M, o); }
 	void MInv(const Out& o) { get(-1, OSC_F_MINV, o); }
@@ -131,14 +153,24 @@ public:
 	void status(const Out& o) { get(-1, OSC_F_STATUS, o); }
 	void synchronize() { check(osc_synchronize(_h)); }
 	void setStream(void* cuda_stream) { check(osc_batch_set_stream(_h, cuda_stream)); }
-	void setTickOutputs(int outputs) { check(osc_batch_set_tick_outputs(_h, outputs)); }
+	void setTickOutputs(int outputs) { flushControlCycle(); check(osc_batch_set_tick_outputs(_h, outputs)); }
 
-	void set(int task, int field, const In& v) { check(osc_set_field(_h, task, field, v.ptr, v.layout, v.mem)); }
-	void get(int task, int field, const Out& o) { check(osc_get_field(_h, task, field, o.ptr, o.layout, o.mem)); }
+	void set(int task, int field, const In& v) {
+		if (task < 0) flushControlCycle();  // q, dq: the deferred updateModel() belongs to the state before this write
+		check(osc_set_field(_h, task, field, v.ptr, v.layout, v.mem));
+	}
+	void get(int task, int field, const Out& o) { flushControlCycle(); check(osc_get_field(_h, task, field, o.ptr, o.layout, o.mem)); }
 	int fieldSize(int task, int field) const { int n = osc_field_size(_h, task, field); check(n); return n; }
+
+	// (used by RobotController)
+	bool deferTaskModels() { if (_pending >= 1) { _pending = 2; return true; } return false; }
+	bool takeFullControlCycle() { if (_pending == 2) { _pending = 0; ++_fused_cycles; return true; } return false; }
 
 private:
 	osc_batch_t* _h = nullptr;
+	bool _fuse = true;
+	mutable int _pending = 0;  // 1: updateModel() deferred, 2: + updateControllerTaskModels()
+	int64_t _fused_cycles = 0;
 };
 
 // rigid transform (Eigen::Affine3d stand-in): p_parent = rot * p_child + xyz, rot row-major
@@ -342,7 +374,7 @@ public:
 	void updateSensedForceAndMoment(const In& sensed_force_sensor_frame, const In& sensed_moment_sensor_frame) {
 		if (sensed_force_sensor_frame.layout != sensed_moment_sensor_frame.layout || sensed_force_sensor_frame.mem != sensed_moment_sensor_frame.mem)
 			throw std::invalid_argument("force and moment must use the same layout and memory space in MotionForceTask::updateSensedForceAndMoment\n");
-		check(osc_mft_update_sensed_force_and_moment(_robot->handle(), _index, sensed_force_sensor_frame.ptr, sensed_moment_sensor_frame.ptr,
+		check(osc_mft_update_sensed_force_and_moment(_robot->rawHandle(), _index, sensed_force_sensor_frame.ptr, sensed_moment_sensor_frame.ptr,
 													 sensed_force_sensor_frame.layout, sensed_force_sensor_frame.mem));
 	}
 
@@ -540,10 +572,19 @@ public:
 		if ((int)tasks.size() != osc_batch_task_count(robot->handle()))
 			throw std::invalid_argument("every task constructed on the robot batch must be given to RobotController");
 	}
-	void updateControllerTaskModels() { check(osc_update_task_models(_robot->handle())); }  // RobotController.cpp:53-60
-	// VectorXd computeControlTorques()   RobotController.cpp:62-74
-	void computeControlTorques(const Out& tau) { check(osc_compute_torques(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem)); }
-	void computeControlTorques() { check(osc_compute_torques(_robot->handle(), 1, nullptr, 0, 0)); }
+	void updateControllerTaskModels() {  // RobotController.cpp:53-60
+		if (!_robot->deferTaskModels()) check(osc_update_task_models(_robot->handle()));
+	}
+	// VectorXd computeControlTorques()   RobotController.cpp:62-74.  After a deferred updateModel() + updateControllerTaskModels()
+	// (RobotBatch::setControlCycleFusion) the three calls are one fused launch.
+	void computeControlTorques(const Out& tau) {
+		if (_robot->takeFullControlCycle()) check(osc_tick(_robot->rawHandle(), 1, tau.ptr, tau.layout, tau.mem));
+		else check(osc_compute_torques(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem));
+	}
+	void computeControlTorques() {
+		if (_robot->takeFullControlCycle()) check(osc_tick(_robot->rawHandle(), 1, nullptr, 0, 0));
+		else check(osc_compute_torques(_robot->handle(), 1, nullptr, 0, 0));
+	}
 	// robot->updateModel(); updateControllerTaskModels(); computeControlTorques() in one (fused) launch
 	void tick(const Out& tau) { check(osc_tick(_robot->handle(), 1, tau.ptr, tau.layout, tau.mem)); }
 	void tick() { check(osc_tick(_robot->handle(), 1, nullptr, 0, 0)); }

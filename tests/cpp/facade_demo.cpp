@@ -3,8 +3,11 @@
 //   facade_demo <chain.bin> <in.bin> <out.bin> <B> <ticks> <mode>
 // chain.bin = raw osc_chain_desc; in.bin = q[B][n], dq[B][n], goal_pos[B][3], goal_ori[B][9], joint_goal[B][n] (double, AOS);
 // out.bin = tau of the last tick [B][n], then the motion task's current position [B][3].
-// mode 0: RobotController (stack B of SURVEY.md 3), per-call;  1: RobotController::tick (fused);  2: manual chaining of
-// examples/04-task_and_redundancy/04-task_and_redundancy.cpp:137-206 (stack C, plain sum of the task torques).
+// mode 0: RobotController (stack B of SURVEY.md 3), the reference's three calls per cycle -- with the facade's control-cycle fusion (on
+// by default) they become one fused launch, which the demo checks;  1: RobotController::tick (fused);  2: manual chaining of
+// examples/04-task_and_redundancy/04-task_and_redundancy.cpp:137-206 (stack C, plain sum of the task torques);  3: mode 1 with the
+// reference's default internal OTGs;  4: mode 0 with fusion off (API-faithful kernels);  5: mode 0 with a getter and a setQ between
+// the calls of a cycle (the deferred updates are applied where the reference runs them).
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
@@ -72,9 +75,13 @@ int main(int argc, char** argv) {
 		for (int t = 0; t < ticks; ++t) {
 			if (mode == 1 || mode == 3) {
 				robot_controller->tick(Out(tau.data()));
-			} else if (mode == 0) {
+			} else if (mode == 0 || mode == 4 || mode == 5) {
+				if (mode == 4) robot->setControlCycleFusion(false);
 				robot->updateModel();
+				if (mode == 5 && t == 1) motion_force_task->getCurrentPosition(Out(x.data()));  // a getter inside the cycle
 				robot_controller->updateControllerTaskModels();
+				if (mode == 5 && t == 2) robot->setQ(hostAOS(q.data()));  // same values: only the ordering is exercised
+				motion_force_task->setGoalPosition(hostAOS(gp.data()));     // goal setters keep the deferral
 				robot_controller->computeControlTorques(Out(tau.data()));
 			} else {
 				robot->updateModel();
@@ -86,6 +93,9 @@ int main(int argc, char** argv) {
 				for (size_t i = 0; i < tau.size(); ++i) tau[i] = t0[i] + t1[i];
 			}
 		}
+		if (mode == 0 && robot->fusedControlCycles() != ticks) return 12;
+		if (mode == 4 && robot->fusedControlCycles() != 0) return 13;
+		if (mode == 5 && robot->fusedControlCycles() != ticks - 2) return 14;
 		motion_force_task->getCurrentPosition(Out(x.data()));
 		FILE* fo = fopen(argv[3], "wb");
 		fwrite(tau.data(), sizeof(double), tau.size(), fo);

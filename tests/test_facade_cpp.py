@@ -51,12 +51,15 @@ def test_facade_compiles_and_refuses_cpu(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5])
 def test_facade_matches_oracle(tmp_path, oracle_built, mode):
+    """Modes of tests/cpp/facade_demo.cpp.  0: the reference's three calls per cycle, which the facade's control-cycle fusion turns
+    into one fused launch (the demo checks the count); 4: the same with fusion off; 5: the same with a getter / a setQ between the
+    calls of two of the cycles (those cycles run per call).  All must give the oracle's torques."""
     orc = oracle_built
     exe = _build()
     chain = load_chain("panda")
-    B, ticks = 256, (3 if mode != 3 else 60)
+    B, ticks = 256, (60 if mode == 3 else (5 if mode == 5 else 3))
     w = _inputs(tmp_path, chain, B, 40 + mode)
     r = subprocess.run([exe, str(tmp_path / "chain.bin"), str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), str(B), str(ticks), str(mode)],
                        capture_output=True, text=True)
