@@ -216,6 +216,7 @@ static int noalloc_scratch(int device, int** out) {
 }  // namespace osc
 
 extern "C" int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_device, int layout) {
+	OSC_RANGE("osc_tick_noalloc");
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
 	if (is_multi(b)) {

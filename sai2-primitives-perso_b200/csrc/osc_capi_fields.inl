@@ -26,6 +26,7 @@ int osc_field_size(const osc_batch_t* batch, int task, int field) {
 }
 
 int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int layout, int mem) {
+	OSC_RANGE("osc_set_field");
 	if (is_multi(batch)) {
 		Batch* p = (Batch*)batch;
 		if (!data) return invalid("null argument");
@@ -50,6 +51,7 @@ int osc_set_field(osc_batch_t* batch, int task, int field, const void* data, int
 }
 
 int osc_get_field(osc_batch_t* batch, int task, int field, void* out, int layout, int mem) {
+	OSC_RANGE("osc_get_field");
 	if (is_multi(batch)) {
 		Batch* p = (Batch*)batch;
 		if (!out) return invalid("null argument");

@@ -17,6 +17,7 @@ static int emit_tau(Batch& b, void* tau_out, int layout, int mem) {
 extern "C" {
 
 int osc_update_model(osc_batch_t* batch) {
+	OSC_RANGE("osc_update_model");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_model(s); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
@@ -25,6 +26,7 @@ int osc_update_model(osc_batch_t* batch) {
 	return b->ops->model(*b, 1);
 }
 int osc_update_kinematics(osc_batch_t* batch) {
+	OSC_RANGE("osc_update_kinematics");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_kinematics(s); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
@@ -33,6 +35,7 @@ int osc_update_kinematics(osc_batch_t* batch) {
 	return b->ops->model(*b, 0);
 }
 int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
+	OSC_RANGE("osc_task_update_model");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_update_model(s, task, n_prec_task); });
 	Batch* b = (Batch*)batch;
 	if (int rc = check_task(b, task)) return rc;
@@ -43,6 +46,7 @@ int osc_task_update_model(osc_batch_t* batch, int task, int n_prec_task) {
 	return b->ops->task_update(*b, task, n_prec_task < 0 ? -1 : n_prec_task);
 }
 int osc_update_task_models(osc_batch_t* batch) {
+	OSC_RANGE("osc_update_task_models");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_task_models(s); });  // RobotController.cpp:53-60
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
@@ -54,6 +58,7 @@ int osc_update_task_models(osc_batch_t* batch) {
 	return OSC_OK;
 }
 int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
+	OSC_RANGE("osc_task_compute_torques");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_task_compute_torques(s, task, with_tau_prec); });
 	Batch* b = (Batch*)batch;
 	if (int rc = check_task(b, task)) return rc;
@@ -64,6 +69,7 @@ int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec) {
 	return b->ops->task_compute(*b, task, with_tau_prec, 0);
 }
 int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {
+	OSC_RANGE("osc_compute_torques");
 	if (is_multi(batch)) {
 		Batch* p = (Batch*)batch;
 		if (tau_out)
@@ -94,6 +100,7 @@ int osc_tick_is_fused(const osc_batch_t* batch) {
 	return b && b->ops->fused_supported(*b) ? 1 : 0;
 }
 int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem) {
+	OSC_RANGE("osc_tick");
 	if (is_multi(batch)) {
 		Batch* p = (Batch*)batch;
 		if (tau_out)
@@ -119,6 +126,7 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
 }
 int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_damping) {
+	OSC_RANGE("osc_rollout_step");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_rollout_step(s, dt, substeps, joint_damping); });
 	Batch* b = (Batch*)batch;
 	if (!b) return invalid("null batch");
@@ -127,6 +135,7 @@ int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_d
 	return b->ops->rollout_step(*b, dt, substeps, joint_damping);
 }
 int osc_rollout(osc_batch_t* batch, int stacked, int ticks, double sim_dt, int substeps, double joint_damping, void* tau_out, int layout, int mem) {
+	OSC_RANGE("osc_rollout");
 	if (is_multi(batch)) {
 		Batch* p = (Batch*)batch;
 		if (tau_out)

@@ -1,5 +1,6 @@
 // osc_capi_util.h -- helpers of the C ABI translation unit (errors, allocation, chain canonicalisation, layout moves).
 #pragma once
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX v3: no link dependency, a no-op unless a profiler injects itself
 #include <math.h>
 #include <string.h>
 
@@ -9,6 +10,15 @@
 #include "osc_host.h"
 
 namespace osc {
+// NVTX range over one C-ABI call (nsys / ncu --nvtx show the control cycle by entry point: SURVEY.md 5 "tracing")
+struct NvtxRange {
+	explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+	~NvtxRange() { nvtxRangePop(); }
+	NvtxRange(const NvtxRange&) = delete;
+	NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define OSC_RANGE(name) ::osc::NvtxRange osc_nvtx_range_(name)
+
 
 inline std::string& last_error() {
 	static thread_local std::string e;

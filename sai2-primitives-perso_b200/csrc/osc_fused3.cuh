@@ -447,21 +447,29 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused3(const __
 			OSC_UNROLL for (int i = 0; i < N; ++i) mP(ML::Q_PRIOR + i) = q[i];
 		}
 	}
-	// V = L^-T Q column by column; z1 = V^T y1, z2 = V^T u_pd, H = V^T V
-	A V[R][N], z1[R], z2[R], H[R][R];
-	OSC_UNROLL for (int j = 0; j < R; ++j) {
-		OSC_UNROLL for (int i = 0; i < N; ++i) V[j][i] = SM(F::QQ + j * N + i);
+	// V = L^-T Q is never held: one column at a time, v_p = L^-T q_p gives z1[p] = v_p . y1 and z2[p] = v_p . u_pd, then
+	// w_p = L^-1 v_p gives the column H[:, p] = V^T v_p = Q^T w_p with Q read back from the stash (R x 7 doubles of registers less:
+	// the R = 4 instantiation of config 3 spilled 0.9 KB per thread and was bound by that traffic, r2e)
+	A z1[R], z2[R], H[R][R];
+	OSC_UNROLL for (int p = 0; p < R; ++p) {
+		A v[N];
+		OSC_UNROLL for (int i = 0; i < N; ++i) v[i] = SM(F::QQ + p * N + i);
 		OSC_UNROLL for (int i = N - 1; i >= 0; --i) {
-			A s = V[j][i];
-			OSC_UNROLL for (int k = i + 1; k < N; ++k) s = Num<A>::fma_(-SM(F::LL + k * (k - 1) / 2 + i), V[j][k], s);
-			V[j][i] = s * SM(F::LI + i);
+			A s = v[i];
+			OSC_UNROLL for (int k = i + 1; k < N; ++k) s = Num<A>::fma_(-SM(F::LL + k * (k - 1) / 2 + i), v[k], s);
+			v[i] = s * SM(F::LI + i);
 		}
 		A a = A(0), b = A(0);
-		OSC_UNROLL for (int i = 0; i < N; ++i) { a = Num<A>::fma_(V[j][i], y1[i], a); b = Num<A>::fma_(V[j][i], upd_[i], b); }
-		z1[j] = a; z2[j] = b;
-		OSC_UNROLL for (int p = 0; p <= j; ++p) {
+		OSC_UNROLL for (int i = 0; i < N; ++i) { a = Num<A>::fma_(v[i], y1[i], a); b = Num<A>::fma_(v[i], upd_[i], b); }
+		z1[p] = a; z2[p] = b;
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			A s = v[i];
+			OSC_UNROLL for (int m = 0; m < i; ++m) s = Num<A>::fma_(-SM(F::LL + i * (i - 1) / 2 + m), v[m], s);
+			v[i] = s * SM(F::LI + i);
+		}
+		OSC_UNROLL for (int j = p; j < R; ++j) {
 			A s = A(0);
-			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<A>::fma_(V[j][i], V[p][i], s);
+			OSC_UNROLL for (int i = 0; i < N; ++i) s = Num<A>::fma_(SM(F::QQ + j * N + i), v[i], s);
 			H[j][p] = s;
 		}
 	}

@@ -206,8 +206,11 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				};
 				const bool big = b.B >= 224 * 148;
 				int rc = OSC_ERR_UNSUPPORTED;
+				// block shape / register cap, measured on config 3 (262,144 robots, M = 3; r2i): 128 registers x 224 threads 0.53 ms per
+				// tick (0.4-1.4 KB of spills per thread, the kernel was bound by that local-memory traffic), 168 x 192 0.47 ms,
+				// 255 x 128 0.45 ms: unlike k_tick_fused2 this kernel wants the registers more than the resident warps
 #define OSC_F3_CASE(MM)                                                                                                                    \
-				if (M3 == MM) rc = big ? go3(k_tick_fused3<T, N, MM, 128, 224, true>, 224, F3<N, MM>::SLOTS) : go3(k_tick_fused3<T, N, MM, 128>, 64, F3<N, MM>::SLOTS);
+				if (M3 == MM) rc = big ? go3(k_tick_fused3<T, N, MM, 255, 128, true>, 128, F3<N, MM>::SLOTS) : go3(k_tick_fused3<T, N, MM, 128>, 64, F3<N, MM>::SLOTS);
 				OSC_F3_CASE(2) OSC_F3_CASE(3) OSC_F3_CASE(4) OSC_F3_CASE(5)
 #undef OSC_F3_CASE
 				if (rc) return rc;
