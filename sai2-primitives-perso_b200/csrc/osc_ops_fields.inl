@@ -273,11 +273,11 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			at[0].val.programmaticStreamSerializationAllowed = 1;
 			cfg.attrs = at;
 			cfg.numAttrs = pdl ? 1 : 0;
-			// closed-form blend routine ahead of the API-faithful chain (osc_blend.cuh): n = 7, task rank 3 (translation-only, config
-			// 3) or 6 (config 4), the fused kernel ran the control law, singularity handling on, no IMPEDANCE decoupling
+			// closed-form blend routine ahead of the API-faithful chain (osc_blend.cuh): n = 7, task rank 2..6 (3 = translation-only,
+			// config 3; 6 = config 4), the fused kernel ran the control law, singularity handling on, no IMPEDANCE decoupling
 			int mb = 0;
 			if constexpr (N == 7) {
-				if ((reuse_law & 1) && m.mp.singularity_handling_enabled && m.mp.dynamic_decoupling_type != OSC_IMPEDANCE && (m.dof == 6 || m.dof == 3) &&
+				if ((reuse_law & 1) && m.mp.singularity_handling_enabled && m.mp.dynamic_decoupling_type != OSC_IMPEDANCE && m.dof >= 2 && m.dof <= 6 &&
 					(m.dof < 6) == (m.md.partial != 0))
 					mb = m.dof;
 #ifdef OSC_EXPERIMENT
@@ -297,7 +297,10 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			};
 			if constexpr (N == 7) {
 				if (mb == 6) go_tail(k_tick_tail<C, N, T, 6>, (size_t)BL<N, 6>::SLOTS * OSC_THREADS * sizeof(C));
+				else if (mb == 5) go_tail(k_tick_tail<C, N, T, 5>, (size_t)BL<N, 5>::SLOTS * OSC_THREADS * sizeof(C));
+				else if (mb == 4) go_tail(k_tick_tail<C, N, T, 4>, (size_t)BL<N, 4>::SLOTS * OSC_THREADS * sizeof(C));
 				else if (mb == 3) go_tail(k_tick_tail<C, N, T, 3>, (size_t)BL<N, 3>::SLOTS * OSC_THREADS * sizeof(C));
+				else if (mb == 2) go_tail(k_tick_tail<C, N, T, 2>, (size_t)BL<N, 2>::SLOTS * OSC_THREADS * sizeof(C));
 				else go_tail(k_tick_tail<C, N, T, 0>, 0);
 			} else {
 				go_tail(k_tick_tail<C, N, T, 0>, 0);
