@@ -307,6 +307,17 @@ template <class T, int N> struct OpsImpl : Ops {
 #endif
 		cfg.attrs = at;
 		cfg.numAttrs = pdl ? 1 : 0;
+#ifdef OSC_EXPERIMENT
+		{  // occupancy experiment: dynamic shared memory the kernel does not use limits the resident blocks per SM
+			static const int smem = [] { const char* e = getenv("OSC_OTG_SLOW_SMEM"); return e ? atoi(e) : 0; }();
+			static const int cap = [] { const char* e = getenv("OSC_OTG_SLOW_GRID"); return e ? atoi(e) : 0; }();
+			if (smem > 0) {
+				if (first_launch_on_device((const void*)k_otg_slow<T, N>, b.device)) cudaFuncSetAttribute(k_otg_slow<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+				cfg.dynamicSmemBytes = smem;
+			}
+			if (cap > 0) cfg.gridDim.x = std::min<unsigned>(cfg.gridDim.x, (unsigned)cap);
+		}
+#endif
 		cudaError_t e = cudaLaunchKernelEx(&cfg, k_otg_slow<T, N>, js, b.stride);
 		if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_otg_slow)");
 		return done(b, "k_otg_slow");

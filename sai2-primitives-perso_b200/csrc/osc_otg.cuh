@@ -747,8 +747,15 @@ struct OtgJobs {
 
 // N = robot dof.  Launched with programmatic stream serialisation behind k_otg_advance: its launch latency hides under the
 // advance kernel; the list is complete and visible once griddepcontrol.wait returns (a no-op under a plain launch).
+// resident blocks per SM of k_otg_slow (register cap = 65536 / (128 * blocks)).  Measured on the all-robots-recalculate tick, 65,536
+// robots x 2 tasks (r2j): 2 blocks (255 registers) 0.412 ms, 4 blocks (128 registers, 2.2 KB of spills) 0.349 ms, 6 blocks (80
+// registers) 0.362 ms; fewer resident blocks than 2 (shared-memory limited) 0.59 ms.  The kernel is bound by the latency of one
+// thread walking 13 DoF profiles, not by its local-memory traffic: it wants resident warps.
+#ifndef OSC_OTG_SLOW_BLOCKS
+#define OSC_OTG_SLOW_BLOCKS 4
+#endif
 template <class T, int N>
-__global__ void __launch_bounds__(128) k_otg_slow(const __grid_constant__ OtgJobs js, int64_t stride) {
+__global__ void __launch_bounds__(128, OSC_OTG_SLOW_BLOCKS) k_otg_slow(const __grid_constant__ OtgJobs js, int64_t stride) {
 	asm volatile("griddepcontrol.wait;" ::: "memory");
 	const OtgJob& job = js.j[blockIdx.y];
 	const int n = *job.slow_count;
