@@ -183,7 +183,7 @@ __device__ void jt_update_robot(const JtC<T, N>& jc, const Arena<S>& rob, const 
 }
 
 template <class T, int N, class S = T>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk,
+__global__ void __launch_bounds__(OSC_THREADS, OSC_PERCALL_BLOCKS) k_jt_update(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk,
 															const S* nprec_src, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
@@ -257,7 +257,7 @@ __device__ void jt_compute_robot(const JtC<T, N>& jc, const Arena<S>& rob, const
 }
 
 template <class T, int N, class S = T>
-__global__ void __launch_bounds__(OSC_THREADS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk, int64_t B,
+__global__ void __launch_bounds__(OSC_THREADS, OSC_PERCALL_BLOCKS) k_jt_compute(const __grid_constant__ JtC<T, N> jc, Arena<S> rob, Arena<S> tk, int64_t B,
 															 int64_t stride, int with_tau_prec, int accumulate) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;

@@ -107,6 +107,11 @@ OSC_DEV void ld_kin(const Row<T, S>& Sr, Kin<T, N>& k) {
 }
 
 #define OSC_THREADS 128
+// resident blocks per SM of the API-faithful kernels: 2 (255 registers).  4 (128 registers) was measured slower (r2j: config 2 per-call
+// tick 0.66 -> 0.79 ms, config 3 2.89 -> 3.74 ms): these kernels already spill 1-11 KB at 255 registers
+#ifndef OSC_PERCALL_BLOCKS
+#define OSC_PERCALL_BLOCKS 2
+#endif
 
 // ------------------------------------------------------------------------------------------------------------------
 // robot->updateModel()
@@ -139,7 +144,7 @@ __device__ void model_robot(const ChainC<T, N>& ch, const Arena<S>& rob, int64_t
 	}
 }
 template <class T, int N, class S = T>
-__global__ void __launch_bounds__(OSC_THREADS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<S> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
+__global__ void __launch_bounds__(OSC_THREADS, OSC_PERCALL_BLOCKS) k_model(const __grid_constant__ ChainC<T, N> ch, Arena<S> rob, int64_t B, int64_t stride, int dynamics, int gravity) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	model_robot<T, N>(ch, rob, stride, r, dynamics, gravity);

@@ -156,7 +156,7 @@ __device__ void mft_compute_robot(const ChainC<T, N>& ch, const MftC<T>& tc, con
 }
 
 template <class T, int N, class S = T>
-__global__ void __launch_bounds__(OSC_THREADS) k_mft_compute(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+__global__ void __launch_bounds__(OSC_THREADS, OSC_PERCALL_BLOCKS) k_mft_compute(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															  Arena<S> rob, Arena<S> tk, int64_t B, int64_t stride, int with_tau_prec, int accumulate) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;

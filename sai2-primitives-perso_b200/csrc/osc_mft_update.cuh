@@ -257,7 +257,7 @@ __device__ void mft_update_robot(const ChainC<T, N>& ch, const MftC<T>& tc, cons
 }
 
 template <class T, int N, class S = T>
-__global__ void __launch_bounds__(OSC_THREADS) k_mft_update(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
+__global__ void __launch_bounds__(OSC_THREADS, OSC_PERCALL_BLOCKS) k_mft_update(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 															 Arena<S> rob, Arena<S> tk, const S* nprec_src, int64_t B, int64_t stride, int no_history) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;

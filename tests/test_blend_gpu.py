@@ -78,6 +78,31 @@ def test_blend_routine_flat_tolerance_and_discrete_state(oracle_built, decouplin
     p.compare(1e-6)   # every getter of the reference after the tick (lazy materialisation through the API-faithful kernels)
 
 
+def test_blend_routine_with_gravity_compensation_velocity_saturation_and_fp32(oracle_built):
+    """Gravity compensation (RobotController.h:31-33) is added by the routine itself; velocity saturation of both tasks (examples/18:
+    130-131) changes the control law the fused kernel hands over; an FP32 batch runs the same routine in double over float rows."""
+    p, t0, t1, q, rng = _panda_pair(31, use_velocity_saturation=1, linear_saturation_velocity=0.3, angular_saturation_velocity=0.5)
+    p.both("enable_gravity_compensation", True)
+    for tick in range(3):
+        p.set(abi.F_Q, q + 2e-4 * tick * rng.normal(0, 1, q.shape))
+        for stacked in (True, False):
+            _check_tick(p, t0, t1, stacked)
+    chain = load_chain("panda")
+    import osc_b200
+    f = osc_b200.Batch(chain, len(q), precision=abi.PRECISION_F32, q0=q0_of(chain))
+    f.set(abi.F_Q, q); f.set(abi.F_DQ, np.zeros_like(q)); f.update_model()
+    f0 = f.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07))); f1 = f.add_joint_task(abi.joint_task_desc(7))
+    p2, s0, s1, _, _ = _panda_pair(31)
+    p2.set(abi.F_DQ, np.zeros_like(q))
+    f.set(abi.F_GOAL_POSITION, p2.ref.get(abi.F_GOAL_POSITION, s0), f0); f.set(abi.F_GOAL_LINEAR_VELOCITY, p2.ref.get(abi.F_GOAL_LINEAR_VELOCITY, s0), f0)
+    f.set(abi.F_JT_GOAL_POSITION, p2.ref.get(abi.F_JT_GOAL_POSITION, s1), f1); f.set(abi.F_JT_GOAL_VELOCITY, p2.ref.get(abi.F_JT_GOAL_VELOCITY, s1), f1)
+    tr = p2.ref.tick(True)
+    tf = np.asarray(f.tick(True), float)
+    same_branch = np.asarray(f.get(abi.F_NS_RANK, f0))[:, 0] == p2.ref.get(abi.F_NS_RANK, s0)[:, 0]
+    assert same_branch.mean() > 0.9       # float inputs may put a robot on the other side of a band edge
+    assert _tau_err(tf[same_branch], tr[same_branch]).max() <= 1e-3   # q itself is rounded to float: kappa * 6e-8 inside the band
+
+
 @pytest.mark.parametrize("declined_by", ["impedance", "handling_off"])
 def test_configurations_the_routine_declines_take_the_chain(oracle_built, declined_by):
     kw = {"dynamic_decoupling_type": abi.IMPEDANCE} if declined_by == "impedance" else {"singularity_handling_enabled": 0}
