@@ -30,10 +30,9 @@ template <int N, int M> struct BL {
 	static constexpr int LL = HEAD;                                 // M lower triangle, then L strictly lower
 	static constexpr int LI = LL + N * (N - 1) / 2;                 // 1 / L_ii
 	static constexpr int XX = LL + N * (N + 1) / 2;                 // X = L^-1 V, column c at XX + c N + i
-	static constexpr int SLOTS = XX + N * M;
-};
-template <int N> struct BLMax {  // stash slots of the largest instantiation the tail kernel may carry
-	static constexpr int SLOTS = BL<N, 2>::SLOTS > BL<N, 6 < N ? 6 : N - 1>::SLOTS ? BL<N, 2>::SLOTS : BL<N, 6 < N ? 6 : N - 1>::SLOTS;
+	static constexpr int LM = XX + N * M;                           // n = 6 only: L_BIE = chol(M_BIE) for ANY clamp pattern (strictly lower, then 1 / diagonal)
+	static constexpr int LMI = LM + N * (N - 1) / 2;
+	static constexpr int SLOTS = LM + (N == 6 ? N * (N + 1) / 2 : 0);
 };
 
 // pose of the control frame at joint angles q; rolled over the joints (small code: it runs once per singular direction)
@@ -84,7 +83,7 @@ template <class T, int N, int M, class S>
 __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T>& tc, const JtC<T, N>& jc, const Arena<S>& rob, const Arena<S>& tk0,
 											const Arena<S>& tk1, const Row<T, S>& xm, int64_t stride, int64_t r, int stacked, int gravity, int reuse_law,
 											int exports, T* __restrict__ sm) {
-	static_assert(N == 7 && M >= 2 && M <= 6, "blend_robot: n = 7, task rank 2..6");
+	static_assert((N == 7 || N == 6) && M >= 2 && M <= 6 && M <= N, "blend_robot: n = 7 (task rank 2..6) or n = 6 (rank 6: no nullspace left)");
 	using ML = MftL<N>;
 	using JL = JtL<N>;
 	using F = BL<N, M>;
@@ -92,7 +91,8 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 #define SM(slot) sm[(slot) * OSC_THREADS + threadIdx.x]
 	// what this routine does not serve: a control law that was not run by the fused kernel, singularity handling off, IMPEDANCE
 	// decoupling of the motion task (its torque has no singular terms, .cpp:310-312), a rank that is not this instantiation's
-	if (!(reuse_law & 1) || !tc.handling || tc.decoupling == OSC_IMPEDANCE || tc.rank != M || !jc.full || (M < 6) != (tc.partial != 0)) return false;
+	const bool has_jt = !(exports & OSC_EXPORT_NO_JT);
+	if (!(reuse_law & 1) || !tc.handling || tc.decoupling == OSC_IMPEDANCE || tc.rank != M || (has_jt && !jc.full) || (M < 6) != (tc.partial != 0)) return false;
 	const Row<T, S> rP{rob.P, stride, r}, rS{rob.S, stride, r}, mP{tk0.P, stride, r}, mS{tk0.S, stride, r}, jP{tk1.P, stride, r}, jS{tk1.S, stride, r};
 	const Row<int32_t> mI{tk0.I, stride, r};
 	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
@@ -163,6 +163,20 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 		OSC_UNROLL for (int i = 0; i < N; ++i)
 			OSC_UNROLL for (int j = 0; j <= i; ++j) Mx[i][j] = SM(F::LL + i * (i + 1) / 2 + j);
 		T delta = T(0);
+		if constexpr (N == 6) {
+			// no nullspace below a full task on a 6-DoF arm, so the last-pivot shortcut (which exists for the joint task's sake) is not
+			// needed: keep L_BIE = chol(M_BIE) itself, whatever the clamp pattern (the PUMA clamps its three wrist joints)
+			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+				T Mb[N][N], lb[N];
+				OSC_UNROLL for (int i = 0; i < N; ++i)
+					OSC_UNROLL for (int j = 0; j <= i; ++j) Mb[i][j] = (i == j && Mx[i][i] < tc.bie_threshold) ? tc.bie_threshold : Mx[i][j];
+				if (!chol_inplace<T, N>(Mb, lb)) return false;
+				OSC_UNROLL for (int i = 0; i < N; ++i) {
+					OSC_UNROLL for (int j = 0; j < i; ++j) SM(F::LM + i * (i - 1) / 2 + j) = Mb[i][j];
+					SM(F::LMI + i) = lb[i];
+				}
+			}
+		} else
 		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
 			const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
@@ -348,15 +362,6 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 	T X[N][M];
 	OSC_UNROLL for (int c = 0; c < M; ++c)
 		OSC_UNROLL for (int i = 0; i < N; ++i) X[i][c] = SM(F::XX + c * N + i);
-	// G = X^T D^2 X = X^T X - beta x_n x_n^T (M x M): every projected inertia below is a block of it
-	T G[M][M];
-	OSC_UNROLL for (int i = 0; i < M; ++i)
-		OSC_UNROLL for (int j = 0; j <= i; ++j) {
-			T t = T(0);
-			OSC_UNROLL for (int k = 0; k < N; ++k) t = Num<T>::fma_(X[k][i], X[k][j], t);
-			t = Num<T>::fma_(-beta_m * X[N - 1][i], X[N - 1][j], t);
-			G[i][j] = t; G[j][i] = t;
-		}
 	T dq[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) dq[i] = rP(RobotL<N>::DQ + i);
 	auto Lmul = [&](const T (&h)[N], T (&y)[N]) {  // y = L h
@@ -366,6 +371,42 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 			y[i] = t;
 		}
 	};
+	const bool gen_bie = N == 6 && tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES;  // general clamp pattern: L_BIE in the stash
+	auto bie_map = [&](const T (&y)[N], T (&z)[N]) {  // z = L_BIE^-1 L y  (= D y for the last-pivot pattern)
+		T v[N];
+		Lmul(y, v);
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T t = v[i];
+			OSC_UNROLL for (int m = 0; m < i; ++m) t = Num<T>::fma_(-SM(F::LM + i * (i - 1) / 2 + m), z[m], t);
+			z[i] = t * SM(F::LMI + i);
+		}
+	};
+	// G = X^T (L_BIE^-1 L)^T (L_BIE^-1 L) X (M x M): every projected inertia below is a block of it.  Last-pivot pattern:
+	// L_BIE^-1 L = D = diag(1, .., 1, rho), G = X^T X - beta x_n x_n^T
+	T G[M][M];
+	if (gen_bie) {
+		T Z[N][M];
+		OSC_UNROLL for (int c = 0; c < M; ++c) {
+			T y[N], z[N];
+			OSC_UNROLL for (int i = 0; i < N; ++i) y[i] = X[i][c];
+			bie_map(y, z);
+			OSC_UNROLL for (int i = 0; i < N; ++i) Z[i][c] = z[i];
+		}
+		OSC_UNROLL for (int i = 0; i < M; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T t = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) t = Num<T>::fma_(Z[k][i], Z[k][j], t);
+				G[i][j] = t; G[j][i] = t;
+			}
+	} else {
+		OSC_UNROLL for (int i = 0; i < M; ++i)
+			OSC_UNROLL for (int j = 0; j <= i; ++j) {
+				T t = T(0);
+				OSC_UNROLL for (int k = 0; k < N; ++k) t = Num<T>::fma_(X[k][i], X[k][j], t);
+				t = Num<T>::fma_(-beta_m * X[N - 1][i], X[N - 1][j], t);
+				G[i][j] = t; G[j][i] = t;
+			}
+	}
 	auto range_coef = [&](unsigned mask, T (&h)[N]) {  // h = X_x (G_x^-1 (a_x / s_x) + s_x b_x): tau_x = L h
 		T Gc[M][M], Inv[M][M], rhs[M], coef[M];
 		OSC_UNROLL for (int i = 0; i < M; ++i)
@@ -468,13 +509,33 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 				OSC_UNROLL for (int p = 0; p <= c; ++p) t = (p >= ins) ? Num<T>::fma_(X[N - 1][p], Rm[p][c], t) : t;
 				yn[c] = t;
 			}
-			OSC_UNROLL for (int i = 0; i < M; ++i)
-				OSC_UNROLL for (int j = 0; j <= i; ++j) {
-					T t = T(0);
-					OSC_UNROLL for (int p = 0; p <= j; ++p) t = (p >= ins) ? Num<T>::fma_(Rm[p][i], Rm[p][j], t) : t;
-					t = Num<T>::fma_(-beta_m * yn[i], yn[j], t);
-					Gj[i][j] = t; Gj[j][i] = t;
+			if (gen_bie) {  // columns z_c = L_BIE^-1 L (W_s R_ss)[:, c]
+				T Z[N][M];
+				OSC_UNROLL for (int c = 0; c < M; ++c) {
+					T y[N], z[N];
+					OSC_UNROLL for (int i = 0; i < N; ++i) {
+						T t = T(0);
+						OSC_UNROLL for (int p = 0; p <= c; ++p) t = (p >= ins) ? Num<T>::fma_(X[i][p], Rm[p][c], t) : t;
+						y[i] = t;
+					}
+					bie_map(y, z);
+					OSC_UNROLL for (int i = 0; i < N; ++i) Z[i][c] = z[i];
 				}
+				OSC_UNROLL for (int i = 0; i < M; ++i)
+					OSC_UNROLL for (int j = 0; j <= i; ++j) {
+						T t = T(0);
+						OSC_UNROLL for (int k = 0; k < N; ++k) t = Num<T>::fma_(Z[k][i], Z[k][j], t);
+						Gj[i][j] = t; Gj[j][i] = t;
+					}
+			} else {
+				OSC_UNROLL for (int i = 0; i < M; ++i)
+					OSC_UNROLL for (int j = 0; j <= i; ++j) {
+						T t = T(0);
+						OSC_UNROLL for (int p = 0; p <= j; ++p) t = (p >= ins) ? Num<T>::fma_(Rm[p][i], Rm[p][j], t) : t;
+						t = Num<T>::fma_(-beta_m * yn[i], yn[j], t);
+						Gj[i][j] = t; Gj[j][i] = t;
+					}
+			}
 			if (!spd_inverse_masked<T, M>(Gj, mask_s, Ij)) status |= 16;
 			OSC_UNROLL for (int c = 0; c < M; ++c) {
 				T t = T(0);
@@ -515,6 +576,19 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 		}
 	}
 
+	if constexpr (R == 0) {
+		// n = 6 under a full task: no nullspace left -- a joint task below it has range rank 0 and contributes nothing (JointTask.cpp:234-239)
+		OSC_UNROLL for (int i = 0; i < N; ++i) {
+			T t = tau1[i];
+			if (gravity) t += (T)rS(RobotL<N>::GRAV + i);
+			rS(RobotL<N>::TAU + i) = t;
+			if (ex) {
+				mS(ML::TASK_TAU + i) = tau1[i];
+				if (has_jt) { jS(JL::TASK_TAU + i) = T(0); jS(JL::CUR_POS + i) = q[i]; jS(JL::CUR_VEL + i) = dq[i]; }
+			}
+		}
+		(void)jP; (void)stacked;
+	} else {
 	// ---- Q = orthonormal basis of the complement of range(W) (n x R): pivoted Gram-Schmidt on the unit vectors (k_tick_fused3 P9);
 	// sin/cos are dead, Q takes their slots ----
 	T k_last[R];
@@ -639,7 +713,8 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 		rS(RobotL<N>::TAU + i) = t;
 		if (ex) { mS(ML::TASK_TAU + i) = tau1[i]; jS(JL::TASK_TAU + i) = tau2[i]; }
 	}
-	tk1.I[(int64_t)JL::RANK * stride + r] = R;
+	}
+	if (has_jt) tk1.I[(int64_t)JL::RANK * stride + r] = R;
 	if (ex) mS(ML::ALPHA) = alpha;
 	if (status) atomicOr(&rob.I[(int64_t)RobotL<N>::STATUS * stride + r], status);
 	return true;

@@ -23,7 +23,7 @@ namespace osc {
 
 #define OSC_FUSED_THREADS 64
 
-enum { OSC_EXPORT_VECTORS = 1 };
+enum { OSC_EXPORT_VECTORS = 1, OSC_EXPORT_NO_JT = 2 };  // NO_JT: single-task hierarchy (6-DoF arm, one 6-DoF MotionForceTask): tk1 aliases tk0, never touched
 
 template <class T, int N, int MINB, class S = T>
 __global__ void __launch_bounds__(OSC_FUSED_THREADS, MINB) k_tick_fused(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
@@ -266,23 +266,25 @@ __device__ __forceinline__ void tail_chain_robot(const ChainC<T, N>& ch, const M
 		}
 		if (gravity) for (int i = 0; i < N; ++i) xS(RobotL<N>::GRAV + i) = (T)rS(RobotL<N>::GRAV + i);
 	}
+	const bool has_jt = !(exports & OSC_EXPORT_NO_JT);
 	model_robot<T, N, S, true>(ch, xr, stride, r, 1, gravity);
 	mft_update_robot<T, N, S, true>(ch, tc, xr, x0, (const S*)nullptr, stride, r, 0);
-	jt_update_robot<T, N, S, true>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
+	if (has_jt) jt_update_robot<T, N, S, true>(jc, xr, x1, x0.S + (int64_t)ML::NTP * (x0.s_stride ? x0.s_stride : stride), stride, r, x0.s_stride, x0.s_index);
 	mft_compute_robot<T, N, S, true>(ch, tc, xr, x0, stride, r, 0, 1, reuse_law & 1);
-	jt_compute_robot<T, N, S, true>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
+	if (has_jt) jt_compute_robot<T, N, S, true>(jc, xr, x1, stride, r, stacked, 2, reuse_law & 2);
 	if (gravity) {
 		for (int i = 0; i < N; ++i) xS(RobotL<N>::TAU + i) += (T)xS(RobotL<N>::GRAV + i);
 	}
 	if (redirected) {
 		for (int i = 0; i < N; ++i) rS(RobotL<N>::TAU + i) = (T)xS(RobotL<N>::TAU + i);
-		if (exports) {  // vector getters of the LAZY output mode (leading rows of the task arenas, osc_layout.cuh): the task
+		if (exports & OSC_EXPORT_VECTORS) {  // vector getters of the LAZY output mode (leading rows of the task arenas, osc_layout.cuh): the task
 			// torques and alpha always; the rows of a control law only when this kernel ran that law (else the fused kernel
 			// already wrote them at the robot's own rows)
-			for (int e = 0; e < N; ++e) { mS(ML::TASK_TAU + e) = (T)xm(ML::TASK_TAU + e); jS(JL::TASK_TAU + e) = (T)xj(JL::TASK_TAU + e); }
+			for (int e = 0; e < N; ++e) mS(ML::TASK_TAU + e) = (T)xm(ML::TASK_TAU + e);
+			if (has_jt) for (int e = 0; e < N; ++e) jS(JL::TASK_TAU + e) = (T)xj(JL::TASK_TAU + e);
 			mS(ML::ALPHA) = (T)xm(ML::ALPHA);
 			if (!(reuse_law & 1)) for (int e = N; e < ML::J; ++e) mS(e) = (T)xm(e);
-			if (!(reuse_law & 2)) for (int e = N; e < JL::NT; ++e) jS(e) = (T)xj(e);
+			if (has_jt && !(reuse_law & 2)) for (int e = N; e < JL::NT; ++e) jS(e) = (T)xj(e);
 		}
 	}
 }
@@ -336,19 +338,29 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 template <class T, int N> bool fused_tick_supported(Batch& b) {
 	if constexpr (N != 6 && N != 7) return false;
 	if (b.tick_outputs == OSC_TICK_OUTPUTS_ALL) return false;
-	if (b.tasks.size() != 2) return false;
-	const TaskH &m = b.tasks[0], &j = b.tasks[1];
-	if (m.type != OSC_TASK_MOTION_FORCE || j.type != OSC_TASK_JOINT) return false;
-	if (!j.jd.full) return false;
-	if (m.md.partial) {  // partial task: k_tick_fused3, instantiated for the (n, task rank) pairs of OSC_FUSED3_SUPPORTED (osc_fused3.cuh)
-		if (!(N == 7 && (m.dof == 3 || m.dof == 2 || m.dof == 4 || m.dof == 5))) return false;
-		if (b.tasks[0].md.body != b.n - 1) return false;
+	if (b.tasks.empty() || b.tasks[0].type != OSC_TASK_MOTION_FORCE) return false;
+	const TaskH& m = b.tasks[0];
+	if (b.tasks.size() == 1) {
+		// single-task hierarchy: a 6-DoF arm under one full MotionForceTask (examples/19 on the PUMA; BASELINE config 4), second-generation kernel only
+		if (!(N == 6 && !m.md.partial && m.dof == 6)) return false;
+		if (m.md.body != b.n - 1) return false;
 		for (int i = 0; i < b.n; ++i)
 			if (b.chain.joint_type[i] != OSC_JOINT_REVOLUTE) return false;
-	} else if (m.dof != 6) return false;
-	if (m.mp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES && j.jp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES &&
-		m.mp.bie_threshold != j.jp.bie_threshold)
-		return false;
+	} else {
+		if (b.tasks.size() != 2) return false;
+		const TaskH& j = b.tasks[1];
+		if (j.type != OSC_TASK_JOINT) return false;
+		if (!j.jd.full) return false;
+		if (m.md.partial) {  // partial task: k_tick_fused3, instantiated for the (n, task rank) pairs of OSC_FUSED3_SUPPORTED (osc_fused3.cuh)
+			if (!(N == 7 && (m.dof == 3 || m.dof == 2 || m.dof == 4 || m.dof == 5))) return false;
+			if (b.tasks[0].md.body != b.n - 1) return false;
+			for (int i = 0; i < b.n; ++i)
+				if (b.chain.joint_type[i] != OSC_JOINT_REVOLUTE) return false;
+		} else if (m.dof != 6) return false;
+		if (m.mp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES && j.jp.dynamic_decoupling_type == OSC_BOUNDED_INERTIA_ESTIMATES &&
+			m.mp.bie_threshold != j.jp.bie_threshold)
+			return false;
+	}
 	if (!(m.mp.s_max > 0) || !(m.mp.s_abs_tol > 0)) return false;
 	// The branch certificate of the fused kernels is an FP32 bound on G = J J^T (absolute error ~ 4e-7 lambda_max): its shift
 	// s_max^2 lambda_max must stay far above that noise, or a truly singular robot could be certified non-singular

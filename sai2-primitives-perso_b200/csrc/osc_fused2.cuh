@@ -263,6 +263,15 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 		OSC_UNROLL for (int i = 0; i < N; ++i)
 			OSC_UNROLL for (int j = 0; j <= i; ++j) Mx[i][j] = SM(F::MM + i * (i + 1) / 2 + j);
 		A delta = A(0);
+		if constexpr (N == 6) {
+			// n = 6 under a full task: no nullspace, tau = J^T (Lambda_mod F* + F_f) is the only result, and with L_BIE = chol(M_BIE)
+			// in place of L every step below yields exactly that (Y = L_BIE^-1 J^T = C W, tau = L_BIE W^T (C^-1 F* + C^T F_f)) for
+			// ANY clamp pattern (SingularityHandler.cpp:175-182) -- the PUMA clamps its three wrist joints
+			if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+				OSC_UNROLL for (int i = 0; i < N; ++i)
+					if (Mx[i][i] < (A)tc.bie_threshold) Mx[i][i] = (A)tc.bie_threshold;
+			}
+		} else
 		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
 			const A thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
@@ -541,11 +550,11 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 			rS(RobotL<N>::TAU + i) = t;
 			if (ex) jS(JL::TASK_TAU + i) = t2;
 		}
-	} else if (ex) {
+	} else if (ex && !(exports & OSC_EXPORT_NO_JT)) {
 		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); jS(JL::TASK_TAU + i) = A(0); }
 	}
 	if (ex) {
-		tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;
+		if (!(exports & OSC_EXPORT_NO_JT)) tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;
 		mS(ML::ALPHA) = T(1);
 		mI(ML::INS) = 6;
 	}
@@ -580,7 +589,7 @@ __global__ void __launch_bounds__(OSC_THREADS) k_gravity(const __grid_constant__
 inline bool fused2_simple(const Batch& b) {
 	const osc_mft_params& p = b.tasks[0].mp;
 	return p.dynamic_decoupling_type != OSC_IMPEDANCE && p.force_space_dimension == 0 && p.moment_space_dimension == 0 && !p.closed_loop_force_control && !p.closed_loop_moment_control &&
-		   !p.use_velocity_saturation && !b.tasks[1].jp.use_velocity_saturation;
+		   !p.use_velocity_saturation && !(b.tasks.size() > 1 && b.tasks[1].jp.use_velocity_saturation);
 }
 inline bool fused2_supported(Batch& b) {
 	if (b.tasks.empty() || b.tasks[0].md.body != b.n - 1) return false;

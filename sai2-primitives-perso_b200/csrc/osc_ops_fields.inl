@@ -165,11 +165,12 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(fallback counters)");
 			b.fb_parity = 0;
 		}
-		TaskH &m = b.tasks[0], &j = b.tasks[1];
+		const bool single = b.tasks.size() == 1;  // 6-DoF arm under one MotionForceTask: every joint-task argument below aliases the motion task and is never used
+		TaskH &m = b.tasks[0], &j = single ? b.tasks[0] : b.tasks[1];
 		int* cnt = b.fb + b.fb_parity;
 		int* nxt = b.fb + (b.fb_parity ^ 1);
 		int* list = b.fb + 2;
-		const int exports = b.tick_outputs == OSC_TICK_OUTPUTS_TAU ? 0 : OSC_EXPORT_VECTORS;
+		const int exports = (b.tick_outputs == OSC_TICK_OUTPUTS_TAU ? 0 : OSC_EXPORT_VECTORS) | (single ? OSC_EXPORT_NO_JT : 0);
 		const dim3 g((unsigned)((b.B + OSC_FUSED_THREADS - 1) / OSC_FUSED_THREADS));
 		const MftC<T> tc = mftc(m);
 		const JtC<T, N> jc = jtc(b, j);
@@ -301,6 +302,15 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				else if (mb == 4) go_tail(k_tick_tail<C, N, T, 4>, (size_t)BL<N, 4>::SLOTS * OSC_THREADS * sizeof(C));
 				else if (mb == 3) go_tail(k_tick_tail<C, N, T, 3>, (size_t)BL<N, 3>::SLOTS * OSC_THREADS * sizeof(C));
 				else if (mb == 2) go_tail(k_tick_tail<C, N, T, 2>, (size_t)BL<N, 2>::SLOTS * OSC_THREADS * sizeof(C));
+				else go_tail(k_tick_tail<C, N, T, 0>, 0);
+			} else if constexpr (N == 6) {
+				if ((reuse_law & 1) && m.mp.singularity_handling_enabled && m.mp.dynamic_decoupling_type != OSC_IMPEDANCE && m.dof == 6 && !m.md.partial)
+					mb = 6;
+#ifdef OSC_EXPERIMENT
+				static const bool no_blend6 = getenv("OSC_NO_BLEND") != nullptr;
+				if (no_blend6) mb = 0;
+#endif
+				if (mb == 6) go_tail(k_tick_tail<C, N, T, 6>, (size_t)BL<N, 6>::SLOTS * OSC_THREADS * sizeof(C));
 				else go_tail(k_tick_tail<C, N, T, 0>, 0);
 			} else {
 				go_tail(k_tick_tail<C, N, T, 0>, 0);

@@ -135,6 +135,28 @@ def config1(torch, chain, ticks=10000):
             "fused": bool(b.tick_is_fused())}
 
 
+def single_task(torch, name="puma560_synthetic", B=65536, ticks=50):
+    """A 6-DoF arm under one full MotionForceTask at random (mostly non-singular) postures: the single-task fused tick."""
+    from common import q0_of, random_q
+    chain = chain_of(name)
+    rng = np.random.default_rng(6)
+    q = random_q(chain, B, rng, 0.3)
+    n = chain["n"]
+    out = []
+    for outputs, tag in ((None, "fused tick (k_tick_fused2<6> + k_tick_tail)"), (abi.TICK_OUTPUTS_ALL, "per-call kernels (API-faithful route)")):
+        b = osc_b200.Batch(chain, B, q0=q0_of(chain))
+        b.set_stream(torch.cuda.current_stream().cuda_stream)
+        b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0)))
+        if outputs is not None:
+            b.set_tick_outputs(outputs)
+        b.set(abi.F_Q, q); b.set(abi.F_DQ, rng.uniform(-0.3, 0.3, (B, n))); b.update_model(); b.reinitialize_tasks()
+        ms = timed(torch, lambda: b.tick(False, fetch=False), ticks)
+        out.append({"config": "single 6-DoF task", "chain": name, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+                    "robot_ticks_per_s": B / (ms.mean() * 1e-3), "fallback_robots": int(b.tick_fallback_count()) if outputs is None else 0, "route": tag})
+        del b
+    return out
+
+
 def config4_stages(torch, name="panda", B=65536, ticks=10):
     """Where the per-call route spends its time when EVERY robot is in the singular blend branch (what k_tick_tail runs per robot)."""
     import test_singular_gpu as S
@@ -162,7 +184,7 @@ def config4_stages(torch, name="panda", B=65536, ticks=10):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-batch", type=int, default=3000000)
-    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5")
+    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5, st")
     args = ap.parse_args()
     import torch
     panda = chain_of("panda")
@@ -180,6 +202,9 @@ def main():
         if "4" in only:
             print(json.dumps(config4(torch, "panda")), flush=True)
             print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
+        if "st" in only:
+            for rec in single_task(torch):
+                print(json.dumps(rec), flush=True)
         if "4s" in only:
             print(json.dumps(config4_stages(torch, "panda")), flush=True)
             print(json.dumps(config4_stages(torch, "puma560_synthetic")), flush=True)
@@ -193,6 +218,8 @@ def main():
         print(json.dumps(rec), flush=True)
     print(json.dumps(config4(torch, "panda")), flush=True)
     print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
+    for rec in single_task(torch):
+        print(json.dumps(rec), flush=True)
 
 
 if __name__ == "__main__":
