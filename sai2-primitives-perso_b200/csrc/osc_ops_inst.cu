@@ -318,18 +318,7 @@ template <class T, int N> struct OpsImpl : Ops {
 			if (cap > 0) cfg.gridDim.x = std::min<unsigned>(cfg.gridDim.x, (unsigned)cap);
 		}
 #endif
-		cudaError_t e;
-#ifdef OSC_EXPERIMENT
-		// one lane per DoF for the Ruckig calculation (otg_calculate_coop, k_otg_slow_coop): same results (tests/test_otg_gpu.py pass on
-		// it), measured SLOWER on the all-robots-recalculate tick (r2l: 0.49 ms against 0.345 ms): a warp still walks 32 robots x 7 DoF
-		// in 8 rounds of one DoF-latency each -- the serial depth per warp is what it was -- and the owner threads keep their frames
-		static const bool coop = getenv("OSC_OTG_COOP") != nullptr;
-		if (coop) {
-			cfg.dynamicSmemBytes = (size_t)4 * OTG_COOP_DOUBLES_PER_WARP * sizeof(double);
-			e = cudaLaunchKernelEx(&cfg, k_otg_slow_coop<T, N>, js, b.stride);
-		} else
-#endif
-			e = cudaLaunchKernelEx(&cfg, k_otg_slow<T, N>, js, b.stride);
+		cudaError_t e = cudaLaunchKernelEx(&cfg, k_otg_slow<T, N>, js, b.stride);
 		if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(k_otg_slow)");
 		return done(b, "k_otg_slow");
 	}

@@ -514,183 +514,14 @@ template <int D> __device__ inline void otg_current_output(const Row<double>& O,
 // change, pending recalculation, trajectory finishing, invalid goal) are appended to a compacted list.
 // k_otg_slow: grid-stride over that list with the general per-robot routine below (otg_general).
 // D = robot dof (joint task, k <= D task dofs) or 6 (cartesian).  GOFF_* = offsets of the goal rows in the G / P arenas.
-// ---- otg_calculate, one LANE per degree of freedom ------------------------------------------------------------------------------
-// The thread-per-robot calculation above keeps the blocks and profiles of all D DoF in per-thread arrays (3-4 KB of local memory
-// per thread, more than the L2 holds for a GPU-full of threads: k_otg_slow waits on that memory).  Here the 32 threads of a warp
-// -- each the owner of one robot in otg_general -- publish their inputs in shared memory and then serve those robots four at a
-// time, eight lanes per robot, lane d holding the block and the profile of DoF d in REGISTERS; what TargetCalculator::calculate
-// does across DoF (calculator_target.hpp:121-205 synchronisation, :46-119 / :406-473 phase synchronisation, :476-520 time
-// synchronisation) becomes shuffles and ballots inside the 8-lane group.  Same arithmetic, same order of evaluation per DoF, same
-// decisions as otg_calculate (tests/test_otg_gpu.py replays the golden vectors through both).  The lanes store the profiles to the
-// robot's trajectory rows themselves; duration and result travel back to the owner thread through shared memory.
-constexpr int OTG_COOP_DOUBLES_PER_WARP = 32 * 5 * 8 + 32 * 2 + 32;  // inputs [robot][cp cv ca tp tv][dof] | duration, result | robot index
-template <int D>
-__device__ __noinline__ void otg_calculate_coop(bool need, int n, const double* cp, const double* cv, const double* ca, const double* tp, const double* tv,
-												   const OtgJob& job, int64_t stride, int64_t r, double* coop, int& result, double& duration) {
-	using L = OtgL<D>;
-	const double eps = 2.220446049250313e-16;
-	const int lane = threadIdx.x & 31;
-	double* sm = coop + (size_t)(threadIdx.x >> 5) * OTG_COOP_DOUBLES_PER_WARP;
-	double* in = sm;                       // [32][5][8]
-	double* out = sm + 32 * 5 * 8;         // [32][2]
-	long long* rix = reinterpret_cast<long long*>(sm + 32 * 5 * 8 + 32 * 2);
-	__syncwarp();
-	if (need) {
-		for (int d = 0; d < n; ++d) {
-			in[(lane * 5 + 0) * 8 + d] = cp[d]; in[(lane * 5 + 1) * 8 + d] = cv[d]; in[(lane * 5 + 2) * 8 + d] = ca[d];
-			in[(lane * 5 + 3) * 8 + d] = tp[d]; in[(lane * 5 + 4) * 8 + d] = tv[d];
-		}
-		rix[lane] = r;
-	}
-	const unsigned needmask = __ballot_sync(0xffffffffu, need);
-	__syncwarp();
-	const int grp = lane >> 3, d = lane & 7;
-	if (needmask && d < n) {
-		const unsigned gmask = ((1u << n) - 1u) << (grp * 8);
-		auto gshfl = [&](double v, int j) { return __shfl_sync(gmask, v, grp * 8 + j); };
-		auto gshfli = [&](int v, int j) { return __shfl_sync(gmask, v, grp * 8 + j); };
-		auto gany = [&](bool pr) { return (__ballot_sync(gmask, pr) & gmask) != 0u; };
-		auto gall = [&](bool pr) { return (__ballot_sync(gmask, pr) & gmask) == gmask; };
-		for (int g = 0; g < 8; ++g) {
-			const int rl = g * 4 + grp;
-			if (!((needmask >> rl) & 1u)) continue;  // uniform within the group
-			const double cpd = in[(rl * 5 + 0) * 8 + d], cvd = in[(rl * 5 + 1) * 8 + d], cad = in[(rl * 5 + 2) * 8 + d];
-			const double tpd = in[(rl * 5 + 3) * 8 + d], tvd = in[(rl * 5 + 4) * 8 + d];
-			const double mv = job.max_v[d], ma = job.max_a[d];
-			int res = OTG_WORKING;
-			double dur = 0.0;
-			OtgProf prof{};
-			prof.pS = cpd; prof.vS = cvd; prof.p0 = cpd; prof.v0 = cvd; prof.pf = tpd; prof.vf = tvd;
-			if (cvd > mv) {  // brake.cpp:82-102 (eps = 2.2e-14, brake.hpp:18), brake.hpp:65-75
-				prof.brA = -ma;
-				prof.brT = (mv - cvd) / -ma + 2.2e-14;
-			} else if (cvd < -mv) {
-				prof.brA = ma;
-				prof.brT = (-mv - cvd) / ma + 2.2e-14;
-			}
-			if (prof.brT > 0.0) {
-				prof.p0 = prof.pS + prof.brT * (prof.vS + prof.brT * (prof.brA / 2 + prof.brT * 0.0 / 6));
-				prof.v0 = prof.vS + prof.brT * (prof.brA + prof.brT * 0.0 / 2);
-			} else {
-				prof.brT = 0.0;
-			}
-			OtgBlock blk;
-			const bool ok1 = otg_step1(prof, mv, ma, blk);
-			// otg_calculate stops at the FIRST DoF whose step 1 fails; the result code is the same whichever it is
-			if (gany(!ok1)) res = OTG_ERR_STEP1;
-			int limiting = -1;
-			if (res == OTG_WORKING && n == 1) {  // :340-345
-				dur = blk.tmin;
-				otg_apply(prof, blk.pmin);
-			} else if (res == OTG_WORKING) {
-				// synchronize, :121-205: candidates t_min[j] (index j) and a.right[j] (index n + j), ascending (value, index); the first one
-				// from position n - 1 on that no DoF blocks.  Position of a candidate = how many candidates precede it.
-				const bool any = gany(blk.hasA);
-				const int cnt = any ? 2 * n : n;
-				const double c0 = blk.tmin, c1 = blk.hasA ? blk.aR : CUDART_INF;
-				int rank0 = 0, rank1 = 0;
-				unsigned blockedbits = 0u;
-				for (int i = 0; i < cnt; ++i) {
-					const double vi = gshfl(i < n ? c0 : c1, i % n);
-					rank0 += ((vi < c0) || (vi == c0 && i < d)) ? 1 : 0;
-					rank1 += ((vi < c1) || (vi == c1 && i < n + d)) ? 1 : 0;
-					if (gany(blk.blocked(vi))) blockedbits |= 1u << i;
-				}
-				auto key = [&](double v, int idx, int rank) {
-					const bool el = idx < cnt && rank >= n - 1 && !((blockedbits >> idx) & 1u) && (v == v) && !(v < 0.0) && !isinf(v);
-					return el ? rank : (1 << 20);
-				};
-				const int k0 = key(c0, d, rank0), k1 = key(c1, n + d, rank1);
-				const int mykey = k0 <= k1 ? k0 : k1, myidx = k0 <= k1 ? d : n + d;
-				int bestkey = 1 << 20, bi = -1;
-				for (int j = 0; j < n; ++j) {
-					const int kj = gshfli(mykey, j), ij = gshfli(myidx, j);
-					if (kj < bestkey) { bestkey = kj; bi = ij; }
-				}
-				if (bestkey >= (1 << 20)) res = OTG_ERR_SYNC;
-				else {
-					dur = gshfl(bi < n ? c0 : c1, bi % n);
-					limiting = bi % n;
-					if (d == limiting) otg_apply(prof, bi < n ? blk.pmin : blk.pa);
-				}
-				if (res == OTG_WORKING && dur > 7.6e3) res = OTG_ERR_DURATION;  // :388-392
-				bool finished = false;
-				if (res == OTG_WORKING && dur == 0.0) {                          // :394-400
-					otg_apply(prof, blk.pmin);
-					finished = true;
-				}
-				if (res == OTG_WORKING && !finished) {  // phase synchronisation, :46-119 and :406-473
-					const double pdd = tpd - cpd;
-					const int mywhich = fabs(pdd) > eps ? 0 : (fabs(cvd) > eps ? 1 : (fabs(cad) > eps ? 2 : (fabs(tvd) > eps ? 3 : -1)));
-					const unsigned has = (__ballot_sync(gmask, mywhich >= 0) & gmask) >> (grp * 8);
-					if (has) {
-						const int sd = __ffs(has) - 1;
-						const int which = gshfli(mywhich, sd);
-						const double svd = which == 0 ? pdd : (which == 1 ? cvd : (which == 2 ? cad : tvd));
-						const double scale = gshfl(svd, sd);
-						const double pd_s = gshfl(pdd, sd) / scale, v0_s = gshfl(cvd, sd) / scale, vf_s = gshfl(tvd, sd) / scale, a0_s = gshfl(cad, sd) / scale;
-						const double scale_lim = gshfl(svd, limiting);
-						const int up_l = gshfli(prof.up, limiting);
-						const double ma_l = gshfl(ma, limiting);
-						const double ctrl_lim = up_l ? ma_l : -ma_l;
-						const double t0l = gshfl(prof.t0, limiting), t1l = gshfl(prof.t1, limiting), t2l = gshfl(prof.t2, limiting), t6l = gshfl(prof.t6, limiting);
-						const bool col = !(fabs(pdd - pd_s * svd) > eps || fabs(cvd - v0_s * svd) > eps || fabs(cad - a0_s * svd) > eps || fabs(tvd - vf_s * svd) > eps);
-						if (gall(col)) {
-							OtgProf trial = prof;
-							bool okl = true;
-							if (d != limiting) {
-								const double c = ctrl_lim * svd / scale_lim;  // new_phase_control
-								trial.t0 = t0l; trial.t1 = t1l; trial.t2 = t2l; trial.t6 = t6l;
-								const bool lim_ok = (-ma - 1e-12 < c) && (c < ma + 1e-12) && (-ma - 1e-12 < -c) && (-c < ma + 1e-12);
-								okl = otg_check(trial, c, -c, mv, -mv) && lim_ok;
-							}
-							if (gall(okl)) { prof = trial; finished = true; }
-						}
-					}
-				}
-				if (res == OTG_WORKING && !finished) {  // time synchronisation, :476-520
-					bool fail = false;
-					if (d != limiting) {
-						const double tprof = dur - prof.brT;
-						if (fabs(tprof - blk.tmin) < 2 * eps) otg_apply(prof, blk.pmin);
-						else if (blk.hasA && fabs(tprof - blk.aR) < 2 * eps) otg_apply(prof, blk.pa);
-						else fail = !otg_step2(prof, tprof, mv, ma);
-					}
-					if (gany(fail)) res = OTG_ERR_SYNC;
-				}
-			}
-			if (res == OTG_WORKING) {
-				const int64_t rr = rix[rl];
-				double* Orow = job.O + rr;
-				const int o = L::TRAJ + 11 * d;
-				Orow[(int64_t)(o) * stride] = prof.brT; Orow[(int64_t)(o + 1) * stride] = prof.brA; Orow[(int64_t)(o + 2) * stride] = prof.pS;
-				Orow[(int64_t)(o + 3) * stride] = prof.vS; Orow[(int64_t)(o + 4) * stride] = prof.t0; Orow[(int64_t)(o + 5) * stride] = prof.t1;
-				Orow[(int64_t)(o + 6) * stride] = prof.t2; Orow[(int64_t)(o + 7) * stride] = prof.t6; Orow[(int64_t)(o + 8) * stride] = prof.a0;
-				Orow[(int64_t)(o + 9) * stride] = prof.a2; Orow[(int64_t)(o + 10) * stride] = prof.a6;
-				Orow[(int64_t)(L::SEG + 2 * D + d) * stride] = -1.0;  // cached segment stale
-			}
-			if (d == 0) { out[rl * 2] = dur; out[rl * 2 + 1] = (double)res; }
-		}
-	}
-	__syncwarp();
-	if (need) { duration = out[lane * 2]; result = (int)out[lane * 2 + 1]; }
-	__syncwarp();
-}
-
-// COOP: the Ruckig calculation in the middle of this routine is carried out by the whole warp, one lane per degree of freedom
-// (otg_calculate_coop), so every thread of the warp -- also one without a robot (active == false: r is then any valid robot, read
-// but never written) or with nothing to calculate -- must reach that call: no early return before it.
-template <class T, int D, bool CART, bool COOP = false>
-__device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool active = true, double* coop = nullptr) {
+template <class T, int D, bool CART>
+__device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r) {
 	using L = OtgL<D>;
 	const Row<double> O{job.O, stride, r};
 	const Row<int32_t> OI{job.OI, stride, r};
 	const Row<T> G{(T*)job.G, stride, r}, P{(T*)job.P, stride, r};
 	const int k = CART ? 6 : job.k;
-	const bool live = active && !(!CART && job.rank && job.rank[r] == 0);
-	if constexpr (!COOP) {
-		if (!live) return;
-	}
+	if (!CART && job.rank && job.rank[r] == 0) return;
 	int flags = OI(L::FLAGS);
 	const int flags_in = flags;
 	double tgt_p[D], tgt_v[D];
@@ -707,7 +538,6 @@ __device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool a
 	bool ref_dirty = false;
 
 	// ---- goal filter --------------------------------------------------------------------------------------------
-	if (live) {
 	if constexpr (!CART) {  // OTG_joints::setGoalPositionAndVelocity, OTG_joints.cpp:96-113
 		double gp[D], gv[D];
 		OSC_UNROLL for (int i = 0; i < D; ++i) { gp[i] = i < k ? (double)G.ro(i) : 0.0; gv[i] = i < k ? (double)G.ro(D + i) : 0.0; }
@@ -751,7 +581,6 @@ __device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool a
 			ref_dirty = true; out_dirty = true;
 		}
 	}
-	}  // if (live)
 
 	auto store_cart_frames = [&]() {
 		if constexpr (CART) {
@@ -782,20 +611,15 @@ __device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool a
 	};
 
 	// ---- update(), OTG_joints.cpp:115-150 / OTG_6dof_cartesian.cpp:201-236 ----------------------------------------
-	bool idle = !live;
-	if (live && (flags & OTG_REACHED)) {
+	if (flags & OTG_REACHED) {
 		if (flags != flags_in) OI(L::FLAGS) = flags;
-		idle = true;
-	}
-	if constexpr (!COOP) {
-		if (idle) return;
+		return;
 	}
 	OtgProf prof[D];
-	double duration = 0.0, time;
+	double duration, time;
 	int result = OTG_WORKING;
-	double cp[D], cv[D], ca[D];
-	const bool calc = !idle && ((flags & OTG_DIRTY) || !(flags & OTG_INIT));  // ruckig.hpp:193
-	if (calc) {
+	if ((flags & OTG_DIRTY) || !(flags & OTG_INIT)) {  // ruckig.hpp:193
+		double cp[D], cv[D], ca[D];
 		if (flags & OTG_IN_SYNCED) {
 			load_out();
 			OSC_UNROLL for (int i = 0; i < D; ++i) { cp[i] = out_p[i]; cv[i] = out_v[i]; ca[i] = out_a[i]; }
@@ -812,14 +636,7 @@ __device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool a
 #ifdef OSC_OTG_DEBUG
 		if (r == 0) printf("otg dbg CART=%d flags=%d cp=%g %g %g %g %g %g out_p=%g %g %g have_out=%d\n", (int)CART, flags, cp[0], cp[1], cp[2], cp[3], cp[4], cp[5], out_p[0], out_p[1], out_p[2], (int)have_out);
 #endif
-	}
-	if constexpr (COOP) {
-		otg_calculate_coop<D>(calc && result == OTG_WORKING, k, cp, cv, ca, tgt_p, tgt_v, job, stride, r, coop, result, duration);
-		if (idle) return;
-	} else {
-		if (calc && result == OTG_WORKING) result = otg_calculate<D>(k, cp, cv, ca, tgt_p, tgt_v, job.max_v, job.max_a, prof, duration);
-	}
-	if (calc) {
+		if (result == OTG_WORKING) result = otg_calculate<D>(k, cp, cv, ca, tgt_p, tgt_v, job.max_v, job.max_a, prof, duration);
 #ifdef OSC_OTG_DEBUG
 		if (r == 0) printf("otg dbg after calc res=%d dur=%g pS=%g %g %g\n", result, duration, prof[0].pS, prof[1].pS, prof[2].pS);
 #endif
@@ -839,18 +656,14 @@ __device__ void otg_general(const OtgJob& job, int64_t stride, int64_t r, bool a
 			if (out_dirty) { store_out(); store_cart_frames(); }
 			return;
 		}
-		if constexpr (COOP) {  // the lanes of the cooperative calculation stored the profiles (and marked the cached segments stale)
-			for (int d = 0; d < k; ++d) otg_load_prof<D>(O, d, prof[d]);
-		} else {
-			OSC_UNROLL for (int d = 0; d < D; ++d)
-				if (d < k) {
-					const OtgProf& p = prof[d];
-					const int o = L::TRAJ + 11 * d;
-					O(o) = p.brT; O(o + 1) = p.brA; O(o + 2) = p.pS; O(o + 3) = p.vS; O(o + 4) = p.t0; O(o + 5) = p.t1; O(o + 6) = p.t2;
-					O(o + 7) = p.t6; O(o + 8) = p.a0; O(o + 9) = p.a2; O(o + 10) = p.a6;
-					O(L::SEG + 2 * D + d) = -1.0;  // cached segment stale
-				}
-		}
+		OSC_UNROLL for (int d = 0; d < D; ++d)
+			if (d < k) {
+				const OtgProf& p = prof[d];
+				const int o = L::TRAJ + 11 * d;
+				O(o) = p.brT; O(o + 1) = p.brA; O(o + 2) = p.pS; O(o + 3) = p.vS; O(o + 4) = p.t0; O(o + 5) = p.t1; O(o + 6) = p.t2;
+				O(o + 7) = p.t6; O(o + 8) = p.a0; O(o + 9) = p.a2; O(o + 10) = p.a6;
+				O(L::SEG + 2 * D + d) = -1.0;  // cached segment stale
+			}
 		O(L::DUR) = duration;
 		time = 0.0;
 		flags = (flags | OTG_INIT) & ~OTG_DIRTY;
@@ -953,26 +766,6 @@ __global__ void __launch_bounds__(128, OSC_OTG_SLOW_BLOCKS) k_otg_slow(const __g
 		for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) otg_general<T, N, false>(job, stride, job.slow_list[i]);
 	}
 }
-
-#ifdef OSC_EXPERIMENT
-// k_otg_slow with the cooperative calculation: whole warps walk the list (a thread past its end stays in for the collectives).
-// Correct and tested, but slower than k_otg_slow (see otg_tick in osc_ops_inst.cu): experiment builds only.
-template <class T, int N>
-__global__ void __launch_bounds__(128, 4) k_otg_slow_coop(const __grid_constant__ OtgJobs js, int64_t stride) {
-	extern __shared__ __align__(16) double otg_coop_smem[];
-	asm volatile("griddepcontrol.wait;" ::: "memory");
-	const OtgJob& job = js.j[blockIdx.y];
-	const int n = *job.slow_count;
-	if (blockIdx.x == 0 && threadIdx.x == 0) *job.slow_next = 0;
-	for (int base = blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < n; base += gridDim.x * blockDim.x) {
-		const int i = base + (threadIdx.x & 31);
-		const bool active = i < n;
-		const int64_t r = job.slow_list[active ? i : base];
-		if (js.cart[blockIdx.y]) otg_general<T, 6, true, true>(job, stride, r, active, otg_coop_smem);
-		else otg_general<T, N, false, true>(job, stride, r, active, otg_coop_smem);
-	}
-}
-#endif  // OSC_EXPERIMENT
 
 template <class T, int D, bool CART>
 __device__ __forceinline__ void otg_advance_robot(const OtgJob& job, int64_t B, int64_t stride) {
