@@ -386,6 +386,23 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
  *     threads -- RACE on it.  Serialise them (same stream, or events).  osc_tick is unaffected and may overlap freely;
  *   - osc_tick_fallback_count() keeps reporting the last osc_tick, not this call. */
 int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_device, int layout);
+/* One control cycle with HOST buffers in one call (no counterpart in the reference, whose state lives in host memory): writes the
+ * n_inputs fields (each as osc_set_field would: q, dq, goals, ...), runs osc_tick and returns when the torques are in tau_out
+ * (host memory, AOS [B][n] or SOA [n][B]; NULL: read OSC_F_TAU later).  On a batch created over several shards
+ * (osc_batch_create_multi -- also several shards on ONE device, e.g. device_ids = {0, 0, 0, 0}) the shards are issued one after
+ * the other WITHOUT waiting in between: the host-to-device copies of shard k + 1 overlap the tick and the device-to-host copy of
+ * shard k (PCIe is full duplex), and the call waits for all of them at the end.  Pinned host buffers are required for the overlap
+ * (pageable memory makes every copy synchronous); AOS buffers give each shard one contiguous block (linear copies).
+ * Measured (profiles/README.md r2m, 65,536 robots, 27 MB per step): on ONE device the overlap does not pay -- the step is bound by
+ * the host-to-device copies, and cutting them into 2-8 x more, smaller (or pitched) copies costs more than hiding the 3.7 MB
+ * read-back saves; use several shards for several devices, where every device has its own link. */
+typedef struct osc_field_in {
+	int32_t task;      /* -1: robot field (OSC_F_Q, OSC_F_DQ) */
+	int32_t field;     /* OSC_F_* */
+	const void* data;  /* host memory, whole batch */
+	int32_t layout;    /* OSC_LAYOUT_AOS / _SOA / _UNIFORM */
+} osc_field_in;
+int osc_step_host(osc_batch_t* batch, const osc_field_in* inputs, int32_t n_inputs, int32_t stacked, void* tau_out, int32_t tau_layout);
 /* 1 if osc_tick runs the fused kernel for the current hierarchy / parameters */
 int osc_tick_is_fused(const osc_batch_t* batch);
 /* What osc_tick leaves behind besides tau and the persistent controller state (integrators, observers, history):

@@ -125,6 +125,46 @@ int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem
 	if (int rc = osc_update_task_models(batch)) return rc;
 	return osc_compute_torques(batch, stacked, tau_out, layout, mem);
 }
+int osc_step_host(osc_batch_t* batch, const osc_field_in* inputs, int32_t n_inputs, int32_t stacked, void* tau_out, int32_t tau_layout) {
+	OSC_RANGE("osc_step_host");
+	Batch* p = (Batch*)batch;
+	if (!p) return invalid("null batch");
+	if (n_inputs < 0 || (n_inputs > 0 && !inputs)) return invalid("null argument in osc_step_host");
+	for (int i = 0; i < n_inputs; ++i)
+		if (!inputs[i].data) return invalid("null input buffer in osc_step_host");
+	if (!is_multi(p)) {
+		for (int i = 0; i < n_inputs; ++i)
+			if (int rc = osc_set_field(batch, inputs[i].task, inputs[i].field, inputs[i].data, inputs[i].layout, OSC_MEM_HOST)) return rc;
+		return osc_tick(batch, stacked, tau_out, tau_layout, OSC_MEM_HOST);
+	}
+	// shard-major issue from this thread, nothing waits until every shard is queued: copy engine order = shard 0's inputs, shard 1's
+	// inputs, ...; shard k's kernels start when ITS inputs have landed, its torques travel back while shard k + 1 is still uploading
+	int rc = OSC_OK;
+	const int ns = (int)p->shards.size();
+	for (int k = 0; k < ns && rc == OSC_OK; ++k) {
+		Batch* s = p->shards[k];
+		s->defer_host_sync = true;
+		for (int i = 0; i < n_inputs && rc == OSC_OK; ++i) {
+			Loc l;
+			if (!s->ops->locate(*s, inputs[i].task, inputs[i].field, l)) { rc = invalid("unknown field for this task"); break; }
+			const size_t esz = l.is_int ? 4 : p->esz;
+			rc = osc_set_field((osc_batch_t*)s, inputs[i].task, inputs[i].field, multi_slice(p, k, inputs[i].data, l.width, inputs[i].layout, esz), inputs[i].layout, OSC_MEM_HOST);
+			s->io_pitch = 0;
+		}
+		if (rc == OSC_OK) {
+			rc = osc_tick((osc_batch_t*)s, stacked, multi_slice(p, k, tau_out, p->n, tau_layout, p->esz), tau_layout, OSC_MEM_HOST);
+			s->io_pitch = 0;
+		}
+		s->defer_host_sync = false;
+	}
+	const std::string err = rc == OSC_OK ? std::string() : last_error();
+	for (int k = 0; k < ns; ++k) {
+		const int r2 = osc_synchronize((osc_batch_t*)p->shards[k]);
+		if (rc == OSC_OK && r2 != OSC_OK) rc = r2;
+	}
+	if (!err.empty()) set_error(err);
+	return rc;
+}
 int osc_rollout_step(osc_batch_t* batch, double dt, int substeps, double joint_damping) {
 	OSC_RANGE("osc_rollout_step");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_rollout_step(s, dt, substeps, joint_damping); });

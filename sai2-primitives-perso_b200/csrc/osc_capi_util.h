@@ -235,7 +235,7 @@ template <class E> int export_rows_t(Batch& b, const E* rows, int w, void* out, 
 	} else {
 		return invalid("layout must be AOS or SOA for output buffers");
 	}
-	if (mem == OSC_MEM_HOST) OSC_CUDA(cudaStreamSynchronize(b.stream));
+	if (mem == OSC_MEM_HOST && !b.defer_host_sync) OSC_CUDA(cudaStreamSynchronize(b.stream));
 	return OSC_OK;
 }
 inline int export_rows(Batch& b, const void* rows, int w, bool is_int, void* out, int layout, int mem) {

@@ -118,6 +118,7 @@ struct Batch {
 	struct MultiPool* pool = nullptr;
 	// SOA user buffers of a shard call made by its parent: rows are `io_pitch` elements apart (0 = this batch's own size)
 	int64_t io_pitch = 0;
+	bool defer_host_sync = false;  // osc_step_host: a device-to-host export does not wait for the stream (the caller synchronises all shards at the end)
 	cudaStream_t owned_stream = nullptr;  // created for a shard by osc_batch_create_multi, destroyed with it
 };
 

@@ -84,6 +84,7 @@ def lib():
         "osc_compute_torques": (i, [vp, i, vp, i, i]),
         "osc_tick": (i, [vp, i, vp, i, i]),
         "osc_tick_noalloc": (i, [vp, i, vp, i]),
+        "osc_step_host": (i, [vp, vp, i, i, vp, i]),
         "osc_tick_is_fused": (i, [vp]),
         "osc_batch_set_tick_outputs": (i, [vp, i]),
         "osc_tick_fallback_count": (i64, [vp]),
@@ -117,7 +118,7 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_urdf_load"
             "osc_enable_gravity_compensation", "osc_joint_task_set_gains_unsafe", "osc_mft_selection_projectors", "osc_task_goal_reached", "osc_field_size", "osc_set_field", "osc_get_field",
             "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
-            "osc_tick", "osc_tick_noalloc", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
+            "osc_tick", "osc_tick_noalloc", "osc_step_host", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",
             "osc_task_enable_internal_otg_jerk_limited", "osc_task_disable_internal_otg", "osc_task_internal_otg_enabled",
             "osc_rollout_step", "osc_rollout"]
@@ -159,6 +160,10 @@ def measure_fp64_peak(device=0):
     if rc < 0:
         raise OscError(rc, lib().osc_last_error().decode())
     return t.value
+
+
+class FieldIn(C.Structure):  # osc_field_in
+    _fields_ = [("task", C.c_int32), ("field", C.c_int32), ("data", C.c_void_p), ("layout", C.c_int32)]
 
 
 class Batch:
@@ -318,6 +323,14 @@ class Batch:
         out = np.empty((self.B, self.n), dtype=self.dtype)
         self._chk(self.L.osc_tick(self.h, int(stacked), out.ctypes.data, abi.LAYOUT_AOS, abi.MEM_HOST))
         return out
+
+    def step_host(self, inputs, tau_ptr, stacked=True, tau_layout=abi.LAYOUT_AOS):
+        """osc_step_host: inputs = [(task, field, host pointer, layout), ...]; tau_ptr = host pointer or 0.  One call per control
+        cycle; on a batch sharded with devices=[...] (also the same device several times) the shards' copies and ticks overlap."""
+        arr = (FieldIn * len(inputs))()
+        for k, (task, field, ptr, layout) in enumerate(inputs):
+            arr[k].task, arr[k].field, arr[k].data, arr[k].layout = int(task), int(field), C.c_void_p(ptr), int(layout)
+        self._chk(self.L.osc_step_host(self.h, arr, len(inputs), int(stacked), C.c_void_p(tau_ptr) if tau_ptr else None, tau_layout))
 
     def tick_noalloc(self, tau_device_ptr, stacked=True, layout=abi.LAYOUT_AOS):
         """osc_tick_noalloc: fused tick with the library's static device scratch; tau lands in DEVICE memory (or nowhere)"""

@@ -97,3 +97,38 @@ def test_multi_batch_against_oracle(oracle_built):
     for f, t in ((abi.F_GOAL_POSITION, t0), (abi.F_GOAL_LINEAR_VELOCITY, t0), (abi.F_JT_GOAL_POSITION, t1)):
         ref.set(f, many.get(f, t), t)
     assert rel_err(many.tick(True), ref.tick(True))[0] <= FP64_TOL
+
+
+@pytest.mark.parametrize("layout", ["aos", "soa"])
+def test_step_host_one_call_cycle_single_and_sharded(layout):
+    """osc_step_host: the input fields, the tick and the torques back in one call.  On a single batch it must equal the
+    osc_set_field / osc_tick sequence; on a sharded batch (the shards are issued back to back without waiting, their copies
+    overlapping the other shards' kernels) it must give the same bits, also for a batch size that does not divide evenly."""
+    import osc_b200
+    chain = load_chain("panda")
+    B, n = 4099, chain["n"]
+    rng = np.random.default_rng(21)
+    q = random_q(chain, B, rng, 0.3); dq = rng.uniform(-0.5, 0.5, (B, n))
+    lay = abi.LAYOUT_AOS if layout == "aos" else abi.LAYOUT_SOA
+    q2 = q + rng.normal(0, 0.01, q.shape); dq2 = dq * 0.5; gq = q + rng.normal(0, 0.1, q.shape)
+
+    def arr(a):
+        return np.ascontiguousarray(a if lay == abi.LAYOUT_AOS else a.T)
+
+    taus = []
+    for devices, one_call in ((None, False), (None, True), (_devices(3), True)):
+        b, t0, t1 = _build(chain, B, q, dq, devices)
+        bufs = [arr(q2), arr(dq2), arr(gq)]
+        ins = [(-1, abi.F_Q, bufs[0].ctypes.data, lay), (-1, abi.F_DQ, bufs[1].ctypes.data, lay), (t1, abi.F_JT_GOAL_POSITION, bufs[2].ctypes.data, lay)]
+        out = np.zeros((B, n) if lay == abi.LAYOUT_AOS else (n, B))
+        for _ in range(2):
+            if one_call:
+                b.step_host(ins, out.ctypes.data, True, lay)
+            else:
+                for task, f, ptr, l_ in ins:
+                    b.set_raw(f, ptr, l_, abi.MEM_HOST, task)
+                b._chk(b.L.osc_tick(b.h, 1, out.ctypes.data, lay, abi.MEM_HOST))
+        taus.append(np.array(out if lay == abi.LAYOUT_AOS else out.T))
+    assert np.array_equal(taus[0], taus[1]), "osc_step_host on one batch differs from set_field + tick"
+    assert np.array_equal(taus[0], taus[2]), "osc_step_host on a sharded batch differs from the single batch"
+    assert np.isfinite(taus[0]).all() and np.abs(taus[0]).max() > 0
