@@ -18,6 +18,10 @@
  *     SOA [k][B] (the device-resident layout, zero-copy friendly) and UNIFORM [k] (one value broadcast to all robots).
  *   - buffers may live in host or device memory (OSC_MEM_*); device buffers must be on the batch's device.
  *   - calls are asynchronous on the batch's stream; a call that writes a HOST buffer returns after the data landed.
+ *     A call that READS a host buffer (osc_set_field, osc_mft_update_sensed_force_and_moment, osc_step_host inputs) has consumed
+ *     a PAGEABLE buffer when it returns (cudaMemcpyAsync stages pageable memory), but reads a PINNED (page-locked) buffer
+ *     asynchronously: leave a pinned input buffer unchanged until the next call that returns data to the host, or
+ *     osc_synchronize(), has returned.
  *   - one host thread drives one batch; a batch lives on one GPU; shard robots over GPUs with one batch per GPU
  *     (independent robots, no inter-GPU traffic, no collective: SURVEY.md 8e).
  */
