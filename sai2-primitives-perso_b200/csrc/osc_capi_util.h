@@ -128,12 +128,43 @@ inline void canonicalise_chain(Batch& b) {
 }
 
 // ---- layout moves between user buffers and SoA rows ----
-template <class E> __global__ void k_aos_to_soa(const E* __restrict__ aos, E* __restrict__ soa, int w, int64_t B, int64_t stride) {
+// AOS [B][w] <-> SoA rows, through a shared-memory tile of 32 robots x w per warp (two warps per block, <= 33 KB): the AOS side is read / written as ONE
+// contiguous, fully coalesced range (32 w elements), the SoA side row by row (32 consecutive robots each).  The direct form
+// (aos[r * w + e] per thread) is a stride-w gather: w x the sectors.  Row pitch w | 1 keeps the tile conflict free.
+constexpr int OSC_TILE_MAX_W = 64;
+template <class E> __global__ void __launch_bounds__(64) k_aos_to_soa(const E* __restrict__ aos, E* __restrict__ soa, int w, int64_t B, int64_t stride) {
+	extern __shared__ __align__(16) unsigned char osc_tile_raw[];
+	const int wp = w | 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	E* tile = reinterpret_cast<E*>(osc_tile_raw) + (size_t)warp * 32 * wp;
+	const int64_t r0 = ((int64_t)blockIdx.x * 2 + warp) * 32;
+	if (r0 >= B) return;
+	const int64_t base = r0 * w, end = B * (int64_t)w;
+	for (int i = lane; i < 32 * w; i += 32)
+		if (base + i < end) tile[(i / w) * wp + (i % w)] = aos[base + i];
+	__syncwarp();
+	if (r0 + lane < B)
+		for (int e = 0; e < w; ++e) soa[(int64_t)e * stride + r0 + lane] = tile[lane * wp + e];
+}
+template <class E> __global__ void __launch_bounds__(64) k_soa_to_aos(const E* __restrict__ soa, E* __restrict__ aos, int w, int64_t B, int64_t stride) {
+	extern __shared__ __align__(16) unsigned char osc_tile_raw[];
+	const int wp = w | 1, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	E* tile = reinterpret_cast<E*>(osc_tile_raw) + (size_t)warp * 32 * wp;
+	const int64_t r0 = ((int64_t)blockIdx.x * 2 + warp) * 32;
+	if (r0 >= B) return;
+	if (r0 + lane < B)
+		for (int e = 0; e < w; ++e) tile[lane * wp + e] = soa[(int64_t)e * stride + r0 + lane];
+	__syncwarp();
+	const int64_t base = r0 * w, end = B * (int64_t)w;
+	for (int i = lane; i < 32 * w; i += 32)
+		if (base + i < end) aos[base + i] = tile[(i / w) * wp + (i % w)];
+}
+// widths beyond the tile (none of the reference's fields: the widest getter is 7 x 7): one thread per robot
+template <class E> __global__ void k_aos_to_soa_wide(const E* __restrict__ aos, E* __restrict__ soa, int w, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	for (int e = 0; e < w; ++e) soa[(int64_t)e * stride + r] = aos[r * w + e];
 }
-template <class E> __global__ void k_soa_to_aos(const E* __restrict__ soa, E* __restrict__ aos, int w, int64_t B, int64_t stride) {
+template <class E> __global__ void k_soa_to_aos_wide(const E* __restrict__ soa, E* __restrict__ aos, int w, int64_t B, int64_t stride) {
 	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (r >= B) return;
 	for (int e = 0; e < w; ++e) aos[r * w + e] = soa[(int64_t)e * stride + r];
@@ -202,7 +233,8 @@ template <class E> int import_rows_t(Batch& b, E* rows, int w, const void* data,
 		OSC_CUDA(cudaMemcpyAsync(st, data, (size_t)b.B * w * sizeof(E), cudaMemcpyHostToDevice, b.stream));
 		src = (const E*)st;
 	}
-	k_aos_to_soa<E><<<g, 256, 0, b.stream>>>(src, rows, w, b.B, b.stride);
+	if (w <= OSC_TILE_MAX_W) k_aos_to_soa<E><<<dim3((unsigned)((b.B + 63) / 64)), 64, (size_t)2 * 32 * (w | 1) * sizeof(E), b.stream>>>(src, rows, w, b.B, b.stride);
+	else k_aos_to_soa_wide<E><<<g, 256, 0, b.stream>>>(src, rows, w, b.B, b.stride);
 	++b.launches;
 	OSC_CUDA(cudaGetLastError());
 	return OSC_OK;
@@ -228,7 +260,8 @@ template <class E> int export_rows_t(Batch& b, const E* rows, int w, void* out, 
 			dst = (E*)b.ensure_stage((size_t)b.B * w * sizeof(E));
 			if (!dst) return invalid("out of device memory (staging)");
 		}
-		k_soa_to_aos<E><<<g, 256, 0, b.stream>>>(rows, dst, w, b.B, b.stride);
+		if (w <= OSC_TILE_MAX_W) k_soa_to_aos<E><<<dim3((unsigned)((b.B + 63) / 64)), 64, (size_t)2 * 32 * (w | 1) * sizeof(E), b.stream>>>(rows, dst, w, b.B, b.stride);
+		else k_soa_to_aos_wide<E><<<g, 256, 0, b.stream>>>(rows, dst, w, b.B, b.stride);
 		++b.launches;
 		OSC_CUDA(cudaGetLastError());
 		if (mem == OSC_MEM_HOST) OSC_CUDA(cudaMemcpyAsync(out, dst, (size_t)b.B * w * sizeof(E), cudaMemcpyDeviceToHost, b.stream));
