@@ -139,7 +139,7 @@ public:
 	// Sai2Model::updateModel / updateKinematics (examples/05-using_robot_controller/05-using_robot_controller.cpp:143-145)
 	void updateModel() {
 		flushControlCycle();
-		if (_fuse) _pending = 1;
+		if (_fuse) { _pending = 1; check(osc_defer_model_update(_h)); }  // rows stale: getters / the sensed wrench follow the current q
 		else check(osc_update_model(_h));
 	}
 	void updateKinematics() { flushControlCycle(); check(osc_update_kinematics(_h)); }

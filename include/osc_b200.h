@@ -407,6 +407,11 @@ typedef struct osc_field_in {
 	int32_t layout;    /* OSC_LAYOUT_AOS / _SOA / _UNIFORM */
 } osc_field_in;
 int osc_step_host(osc_batch_t* batch, const osc_field_in* inputs, int32_t n_inputs, int32_t stacked, void* tau_out, int32_t tau_layout);
+/* Tells the batch that q / dq changed and that the caller DEFERS robot->updateModel() to the next osc_tick (control-cycle fusion of
+ * the C++ facade): the kinematic and dynamic rows are treated as stale exactly as after a fused osc_tick -- a getter
+ * evaluates them on demand at the current q, osc_mft_update_sensed_force_and_moment rotates through the compliant frame at the
+ * current q, and an explicit osc_update_model still does the full update.  No kernel is launched.  No counterpart in the reference. */
+int osc_defer_model_update(osc_batch_t* batch);
 /* 1 if osc_tick runs the fused kernel for the current hierarchy / parameters */
 int osc_tick_is_fused(const osc_batch_t* batch);
 /* What osc_tick leaves behind besides tau and the persistent controller state (integrators, observers, history):

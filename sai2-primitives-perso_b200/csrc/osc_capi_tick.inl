@@ -25,6 +25,16 @@ int osc_update_model(osc_batch_t* batch) {
 	if (b->stale) return b->ops->materialise(*b);  // model + task models at the current q (see osc_batch_set_tick_outputs)
 	return b->ops->model(*b, 1);
 }
+int osc_defer_model_update(osc_batch_t* batch) {
+	if (is_multi(batch)) {  // host-side flag only: no need for the shard threads
+		for (Batch* s : ((Batch*)batch)->shards) s->stale = true;
+		return OSC_OK;
+	}
+	Batch* b = (Batch*)batch;
+	if (!b) return invalid("null batch");
+	b->stale = true;
+	return OSC_OK;
+}
 int osc_update_kinematics(osc_batch_t* batch) {
 	OSC_RANGE("osc_update_kinematics");
 	if (is_multi(batch)) return multi_fan((Batch*)batch, [=](osc_batch_t* s, int) { return osc_update_kinematics(s); });

@@ -78,6 +78,7 @@ def lib():
         "osc_mft_update_sensed_force_and_moment": (i, [vp, i, vp, vp, i, i]),
         "osc_update_model": (i, [vp]),
         "osc_update_kinematics": (i, [vp]),
+        "osc_defer_model_update": (i, [vp]),
         "osc_task_update_model": (i, [vp, i, i]),
         "osc_update_task_models": (i, [vp]),
         "osc_task_compute_torques": (i, [vp, i, i]),
@@ -116,7 +117,7 @@ EXPORTED = ["osc_last_error", "osc_version", "osc_device_count", "osc_urdf_load"
             "osc_batch_task_dof", "osc_mft_default_params", "osc_joint_task_default_params", "osc_mft_get_params",
             "osc_mft_set_params", "osc_joint_task_get_params", "osc_joint_task_set_params",
             "osc_enable_gravity_compensation", "osc_joint_task_set_gains_unsafe", "osc_mft_selection_projectors", "osc_task_goal_reached", "osc_field_size", "osc_set_field", "osc_get_field",
-            "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics",
+            "osc_mft_update_sensed_force_and_moment", "osc_update_model", "osc_update_kinematics", "osc_defer_model_update",
             "osc_task_update_model", "osc_update_task_models", "osc_task_compute_torques", "osc_compute_torques",
             "osc_tick", "osc_tick_noalloc", "osc_step_host", "osc_tick_is_fused", "osc_batch_set_tick_outputs", "osc_tick_fallback_count", "osc_launch_count", "osc_reinitialize_tasks", "osc_snapshot_bytes",
             "osc_snapshot", "osc_restore", "osc_measure_fp64_peak", "osc_task_enable_internal_otg_acceleration_limited",

@@ -7,7 +7,9 @@
 // by default) they become one fused launch, which the demo checks;  1: RobotController::tick (fused);  2: manual chaining of
 // examples/04-task_and_redundancy/04-task_and_redundancy.cpp:137-206 (stack C, plain sum of the task torques);  3: mode 1 with the
 // reference's default internal OTGs;  4: mode 0 with fusion off (API-faithful kernels);  5: mode 0 with a getter and a setQ between
-// the calls of a cycle (the deferred updates are applied where the reference runs them).
+// the calls of a cycle (the deferred updates are applied where the reference runs them);  6 (7: with fusion off): mode 0 with closed-loop force control
+// along z and updateSensedForceAndMoment() inside every cycle (examples/09:176-182): the sensed wrench keeps the deferral and is
+// rotated with the kinematics of the q that was just set.
 #include <cstdio>
 #include <cstdlib>
 #include <memory>
@@ -71,13 +73,23 @@ int main(int argc, char** argv) {
 		motion_force_task->setGoalOrientation(hostAOS(go.data()));
 		motion_force_task->setGoalLinearVelocity({0.01, -0.02, 0.03});  // uniform over the batch
 		joint_task->setGoalPosition(hostAOS(gq.data()));
+		if (mode == 6 || mode == 7) {
+			motion_force_task->parametrizeForceMotionSpaces(1, {0.0, 0.0, 1.0});
+			motion_force_task->setClosedLoopForceControl(true);
+			motion_force_task->setGoalForce({0.0, 0.0, 5.0});
+		}
 		std::vector<double> tau(B * n), x(B * 3);
 		for (int t = 0; t < ticks; ++t) {
 			if (mode == 1 || mode == 3) {
 				robot_controller->tick(Out(tau.data()));
-			} else if (mode == 0 || mode == 4 || mode == 5) {
-				if (mode == 4) robot->setControlCycleFusion(false);
+			} else if (mode == 0 || mode == 4 || mode == 5 || mode == 6 || mode == 7) {
+				if (mode == 4 || mode == 7) robot->setControlCycleFusion(false);
+				if (mode == 6 || mode == 7) {  // the robot moved: new q every cycle, then the force sensor reading of this cycle
+					for (size_t i = 0; i < q.size(); ++i) q[i] += 1e-3 * ((i % 7) - 3.0);
+					robot->setQ(hostAOS(q.data()));
+				}
 				robot->updateModel();
+				if (mode == 6 || mode == 7) motion_force_task->updateSensedForceAndMoment({0.3, -0.2, 4.0 + 0.1 * t}, {0.01, 0.02, -0.03});
 				if (mode == 5 && t == 1) motion_force_task->getCurrentPosition(Out(x.data()));  // a getter inside the cycle
 				robot_controller->updateControllerTaskModels();
 				if (mode == 5 && t == 2) robot->setQ(hostAOS(q.data()));  // same values: only the ordering is exercised
@@ -93,7 +105,7 @@ int main(int argc, char** argv) {
 				for (size_t i = 0; i < tau.size(); ++i) tau[i] = t0[i] + t1[i];
 			}
 		}
-		if (mode == 0 && robot->fusedControlCycles() != ticks) return 12;
+		if ((mode == 0 || mode == 6) && robot->fusedControlCycles() != ticks) return 12;
 		if (mode == 4 && robot->fusedControlCycles() != 0) return 13;
 		if (mode == 5 && robot->fusedControlCycles() != ticks - 2) return 14;
 		motion_force_task->getCurrentPosition(Out(x.data()));

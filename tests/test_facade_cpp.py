@@ -51,11 +51,12 @@ def test_facade_compiles_and_refuses_cpu(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3, 4, 5, 6, 7])
 def test_facade_matches_oracle(tmp_path, oracle_built, mode):
     """Modes of tests/cpp/facade_demo.cpp.  0: the reference's three calls per cycle, which the facade's control-cycle fusion turns
     into one fused launch (the demo checks the count); 4: the same with fusion off; 5: the same with a getter / a setQ between the
-    calls of two of the cycles (those cycles run per call).  All must give the oracle's torques."""
+    calls of two of the cycles (those cycles run per call); 6: closed-loop force control with updateSensedForceAndMoment() inside every
+    (fused) cycle and a new q per cycle.  All must give the oracle's torques."""
     orc = oracle_built
     exe = _build()
     chain = load_chain("panda")
@@ -83,7 +84,22 @@ def test_facade_matches_oracle(tmp_path, oracle_built, mode):
         o.enable_internal_otg(t1, np.pi / 3, 2 * np.pi)
     o.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); o.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
     o.set(abi.F_GOAL_LINEAR_VELOCITY, np.array([0.01, -0.02, 0.03]), t0); o.set(abi.F_JT_GOAL_POSITION, w["jt_goal"], t1)
-    for _ in range(ticks):
+    if mode in (6, 7):
+        p = o.mft_params(t0)
+        p.force_space_dimension = 1
+        p.force_or_motion_axis[0], p.force_or_motion_axis[1], p.force_or_motion_axis[2] = 0.0, 0.0, 1.0
+        p.closed_loop_force_control = 1
+        o.set_mft_params(t0, p)
+        o.set(abi.F_GOAL_FORCE, np.array([0.0, 0.0, 5.0]), t0)
+    q = np.array(w["q"], float)
+    for t in range(ticks):
+        if mode in (6, 7):
+            q = q + 1e-3 * (np.arange(7) - 3.0)
+            o.set(abi.F_Q, q); o.update_model()
+            o.update_sensed_force_and_moment(t0, np.array([0.3, -0.2, 4.0 + 0.1 * t]), np.array([0.01, 0.02, -0.03]))
+            # parametrizeForceMotionSpaces re-initialised the linear goal to the current position (MotionForceTask.cpp:830-858); the
+            # demo writes its position goal again every cycle
+            o.set(abi.F_GOAL_POSITION, w["goal_pos"], t0)
         ref = o.tick(mode != 2)
     assert rel_err(tau, ref)[0] <= FP64_TOL
     assert rel_err(x, o.get(abi.F_CURRENT_POSITION, t0))[0] <= FP64_TOL
