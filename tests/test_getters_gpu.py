@@ -114,3 +114,53 @@ def test_set_gains_unsafe(oracle_built):
     jp.kp[0] = -5.0
     with pytest.raises(osc_b200.OscInvalidArgument, match="gains must be positive"):
         g.set_joint_task_params(t0, jp)
+
+
+def test_defer_model_update_makes_the_sensed_wrench_follow_q(oracle_built):
+    """osc_defer_model_update (what the facade's deferred updateModel() tells the batch): after a write of q the kinematic rows are
+    stale, and a sensed wrench handed over before the tick must be rotated with the compliant frame at the NEW q -- exactly what
+    robot->updateModel(); task->updateSensedForceAndMoment() does in the reference (MotionForceTask.cpp:805-828).  Closed-loop force
+    control along z, four cycles with a new posture each; with an explicit osc_update_model, with the deferral, and -- to show the
+    call is needed -- with neither, where the first cycle still uses the posture of the last model update."""
+    import orc
+    import osc_b200
+    import workloads
+    from common import load_chain, q0_of
+    chain = load_chain("panda")
+    B = 128
+    w = workloads.config2(chain, B, 46)
+
+    def setup(b):
+        b.set(abi.F_Q, w["q"]); b.set(abi.F_DQ, w["dq"]); b.update_model()
+        t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+        b.add_joint_task(abi.joint_task_desc(7))
+        p = b.mft_params(t0)
+        p.force_space_dimension = 1
+        p.force_or_motion_axis[0], p.force_or_motion_axis[1], p.force_or_motion_axis[2] = 0.0, 0.0, 1.0
+        p.closed_loop_force_control = 1
+        b.set_mft_params(t0, p)
+        b.set(abi.F_GOAL_FORCE, np.array([0.0, 0.0, 5.0]), t0)
+        return t0
+
+    errs = {}
+    for variant in ("update_model", "defer", "neither"):
+        g = osc_b200.Batch(chain, B, q0=q0_of(chain)); o = orc.OracleBatch(chain, B, q0=q0_of(chain))
+        t0 = setup(g); setup(o)
+        q = np.array(w["q"], float)
+        errs[variant] = []
+        for t in range(4):
+            q = q + 1e-3 * (np.arange(7) - 3.0)
+            f, m = np.array([0.3, -0.2, 4.0 + 0.1 * t]), np.array([0.01, 0.02, -0.03])
+            o.set(abi.F_Q, q); o.update_model(); o.update_sensed_force_and_moment(t0, f, m)
+            ref = o.tick(True)
+            g.set(abi.F_Q, q)
+            if variant == "update_model":
+                g.update_model()
+            elif variant == "defer":
+                g._chk(g.L.osc_defer_model_update(g.h))
+            g.update_sensed_force_and_moment(t0, f, m)
+            errs[variant].append(rel_err(g.tick(True), ref)[0])
+            assert g.tick_is_fused()
+    assert max(errs["update_model"]) <= FP64_TOL, errs
+    assert max(errs["defer"]) <= FP64_TOL, errs
+    assert errs["neither"][0] > 1e-6, "without the call the first cycle must show the stale compliant frame: %s" % errs["neither"]
