@@ -233,3 +233,53 @@ def _set_jt_zero_gains(b, t1):
     for i in range(7):
         p.kp[i], p.kv[i], p.ki[i] = 0.0, 0.0, 0.0
     b.set_joint_task_params(t1, p)
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+def test_pin_panda_singular_blend_mpmath(kind, per_call):
+    """BASELINE config 4 shape: six Panda postures INSIDE the blend band of SingularityHandler (elbow extended / wrist aligned), both
+    joint-space strategies, against a 50-digit model of SingularityHandler.cpp:75-368 typed in from the reference text
+    (tools/make_sympy_golden.py::blend_tick: mpmath SVD, every inverse by LU).  On the GPU per_call = False is the fused tick, whose
+    certificate sends these robots to the closed-form blend routine (csrc/osc_blend.cuh); per_call = True the API-faithful kernels.
+    Tolerance 1e-9 on alpha / singular values / the joint-task part, kappa-scaled on the torques of the singular block, which all
+    three implementations obtain by inverting a matrix of condition 1 / (s_ins / s_0)^2."""
+    g = G("pins_panda_blend")
+    chain = load_chain("panda")
+    B = len(g["q"])
+    outs = {}
+    for stacked in (True, False):
+        b = make_batch(kind, chain, B)
+        b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+        t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+        t1 = b.add_joint_task(abi.joint_task_desc(7))
+        x0 = b.get(abi.F_CURRENT_POSITION, t0)
+        b.set(abi.F_GOAL_POSITION, x0 + g["dpos"], t0); b.set(abi.F_GOAL_LINEAR_VELOCITY, g["gv"], t0)
+        b.set(abi.F_JT_GOAL_POSITION, g["gq"], t1); b.set(abi.F_JT_GOAL_VELOCITY, g["gdq"], t1); b.set(abi.F_JT_GOAL_ACCELERATION, g["gddq"], t1)
+        if per_call:
+            b.update_model(); b.update_task_models()
+            tau = b.compute_torques(stacked)
+        else:
+            tau = b.tick(stacked)
+        outs[stacked] = (b, t0, t1, np.asarray(tau, float))
+    b, t0, t1, tau = outs[True]
+    ratio = g["S"][np.arange(B), g["ins"]] / g["S"][:, 0]
+    tol = np.maximum(FP64_TOL, 64 * 2.2e-16 / ratio ** 2)            # per robot
+    assert tol.max() < 1e-7
+    close(b.get(abi.F_SINGULAR_VALUES, t0), g["S"], "singular values of J")
+    assert np.abs(np.asarray(b.get(abi.F_ALPHA, t0)).ravel() - g["alpha"]).max() <= 1e-9
+    assert (np.asarray(b.get(abi.F_NS_RANK, t0)).ravel() == g["ins"]).all()
+    assert (np.asarray(b.get(abi.F_SINGULARITY_TYPES, t0)) == g["types"]).all(), "type 1 / type 2 classification"
+
+    def close_each(a, ref, what):
+        a, ref = np.asarray(a, float).reshape(B, -1), np.asarray(ref, float).reshape(B, -1)
+        e = np.abs(a - ref).max(axis=1) / np.maximum(np.abs(ref).max(axis=1), 1e-3 * np.abs(ref).max())
+        assert (e <= tol).all(), "%s: rel err %s > %s" % (what, e, tol)
+    close_each(tau, g["tau"], "tau (stacked)")
+    close_each(b.get(abi.F_TASK_TORQUES, t0), g["tau1"], "tau_1 = tau_ns + alpha tau_s + (1 - alpha) tau_joint")
+    close_each(b.get(abi.F_TASK_TORQUES, t1), g["tau2"], "tau_2")
+    close_each(outs[False][3], g["tau_plain"], "tau (plain sum)")
+    close_each(b.get(abi.F_N_TASK, t0), g["N_t"], "N = N_post N_ns")
+    assert (np.asarray(b.get(abi.F_JT_RANGE_RANK, t1)).ravel() == 1).all()
+    if kind == "cuda" and not per_call:
+        assert b.tick_is_fused() and b.tick_fallback_count() == B, "the pins must go through k_tick_tail"

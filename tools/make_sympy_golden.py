@@ -564,12 +564,146 @@ def case_popc_window(rng):
                 window_len=np.array([len(st["popc"].win)]))
 
 
+# ---------------------------------------------------------------------------------------------------------------------
+# The singular-blend branch (SingularityHandler.cpp:75-368) retyped from the reference text, 50 digits, definitions only (inverses
+# by LU, the SVD by mpmath): for the closed-form blend routine of the CUDA path (csrc/osc_blend.cuh) and for the C++ oracle this is a
+# third, independent implementation.  Constants: SingularityHandler.cpp:11-19, bounds 6e-3 / 6e-2 (MotionForceTask.h).
+SH = dict(s_abs_tol=mp.mpf("1e-3"), type_1_tol=mp.mpf("0.5"), ratio=mp.mpf("1e-2"), angle_thr=5 * mp.pi / 180, step=mp.mpf(5), kp1=mp.mpf(50), kv1=mp.mpf(14),
+          kv2=mp.mpf(5), s_min=mp.mpf("6e-3"), s_max=mp.mpf("6e-2"))
+
+
+def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07), stacked=True, jkp=50.0, jkv=14.0):
+    """First control cycle of [6-DoF MotionForceTask, full JointTask] for a robot INSIDE the blend band: classification history empty,
+    q_prior latched to q, type-2 directions all +1 (SingularityHandler.cpp:40-62)."""
+    n = model.n
+    c = model.c
+    assert M3(c["world_rot"]) == mp.eye(3)   # base frame = world frame for this fixture (the perturbation is measured in the base frame)
+    qm, dqm = [mp.mpf(float(x)) for x in q], mp.matrix([mp.mpf(float(x)) for x in dq])
+    qv = mp.matrix(qm)
+    M = model.mass_matrix(qm)
+    Minv, Mbinv = inv(M), inv(bie(M))
+    x, R, J = model.point(qm, link, p_c)
+    tw = J * dqm
+    spec, st = MftSpec(), new_state()
+    g = dict(goal)
+    g["pos"] = x + V3(goal["dpos"]); g["ori"] = R
+    Fstar, Ff, vd, wd, eo = mft_law(spec, st, x, R, tw[0:3, 0], tw[3:6, 0], g, None, None)
+    U, S, Vh = mp.svd_r(J)                         # J = U diag(S) Vh, thin: U 6 x 6, Vh 6 x 7
+    assert S[0] >= SH["s_abs_tol"]
+    ins = next((i for i in range(1, 6) if S[i] / S[0] < SH["s_max"]), None)
+    assert ins is not None, "pin robots must sit in the blend band"
+    alpha = min(max((S[ins] / S[0] - SH["s_min"]) / (SH["s_max"] - SH["s_min"]), mp.mpf(0)), mp.mpf(1))
+    # sign convention of the implementation-defined JacobiSVD (SURVEY A.9 Q12): largest-|component| of every V column positive
+    V = Vh.T.copy()
+    for k in range(6):
+        col = [V[i, k] for i in range(n)]
+        big = max(col, key=lambda t: abs(t))
+        if big < 0:
+            for i in range(n):
+                V[i, k] = -V[i, k]
+            for i in range(6):
+                U[i, k] = -U[i, k]
+    Uns, Us, Vs = U[:, 0:ins], U[:, ins:6], V[:, ins:6]
+    Jns, Js = Uns.T * J, Us.T * J
+    Lam_ns, _, N_ns = osm(Jns, Minv)
+    Lam_ns_mod = inv(Jns * Mbinv * Jns.T)          # .cpp:175-190
+    Lam_s_mod = inv(Js * Mbinv * Js.T)             # .cpp:196-202
+    Jpost = Vs.T * N_ns                            # .cpp:150 (N_prec = I)
+    _, _, N_post = osm(Jpost, Minv)
+    Lam_js_mod = inv(Jpost * Mbinv * Jpost.T)      # .cpp:207-213
+    N_t = N_post * N_ns
+    # classifySingularity (.cpp:230-295), first call: one sample in the history
+    types = []
+    for k in range(6 - ins):
+        qp = [qm[i] + SH["step"] * Vs[i, k] for i in range(n)]
+        x2, R2, _ = model.point(qp, link, p_c)
+        d6 = mp.matrix(list(x2 - x) + list(orientation_error(R2, R)))
+        motion = abs(sum(d6[a] * Us[a, k] for a in range(6)))
+        types.append(1 if motion > SH["type_1_tol"] else 2)
+    c1, c2 = (1, 0) if 1 in types else (0, 1)
+    # computeTorques (.cpp:297-368)
+    tau_ns = Jns.T * (Lam_ns_mod * (Uns.T * Fstar) + Uns.T * Ff)
+    effort = mp.matrix([mp.mpf(j["effort"]) for j in c["joints"]])
+    if c1 > c2:
+        unit = -SH["kp1"] * (qv - qv) - SH["kv1"] * dqm              # q_prior latched to q in this cycle
+        tj = Jpost.T * (Lam_js_mod * (Vs.T * unit))
+    else:
+        ft = Fstar + Ff
+        fTd = sum((ft[a] / mp.norm(ft)) * Us[a, 0] for a in range(6))
+        direction = [mp.mpf(1)] * n
+        for i, j in enumerate(c["joints"]):
+            if Vs[i, 0] != 0:
+                if abs(qm[i] - mp.mpf(j["upper"])) < SH["angle_thr"]:
+                    direction[i] = mp.mpf(-1)
+                elif abs(qm[i] - mp.mpf(j["lower"])) < SH["angle_thr"]:
+                    direction[i] = mp.mpf(1)
+        unit = mp.matrix([direction[i] * abs(fTd) * SH["ratio"] * effort[i] for i in range(n)])
+        tj = Jpost.T * (Vs.T * unit) + Jpost.T * (Lam_js_mod * (Vs.T * (-SH["kv2"] * dqm)))
+    ts = Js.T * (Lam_s_mod * (Us.T * Fstar) + Us.T * Ff)
+    ts = mp.matrix([min(max(ts[i], -effort[i]), effort[i]) for i in range(n)])
+    tau1 = tau_ns + alpha * ts + (1 - alpha) * tj
+    # full JointTask below it: range of N_t (one direction for n = 7, m = 6)
+    Jp = N_t
+    kcol = max(range(n), key=lambda cc: mp.norm(Jp[:, cc]))
+    Rm = Jp[:, kcol] / mp.norm(Jp[:, kcol])
+    J2 = Rm.T * Jp
+    Lam2, _, _ = osm(J2, Minv)
+    Lam2_b = inv(J2 * Mbinv * J2.T)
+    qd, dqd, ddqd = (mp.matrix([mp.mpf(float(t)) for t in jgoal[key]]) for key in ("pos", "vel", "acc"))
+    u = -mp.mpf(jkp) * (qv - qd) - mp.mpf(jkv) * (dqm - dqd)
+    tau2 = Jp.T * Rm * (Lam2 * (Rm.T * ddqd) + Lam2_b * (Rm.T * u))
+    if stacked:
+        tau2 = tau2 - Jp.T * Rm * (Lam2 * (Rm.T * (Minv * tau1)))
+    return dict(tau=tau1 + tau2, tau1=tau1, tau2=tau2, alpha=alpha, ins=ins, types=types + [0] * (6 - len(types)), S=S, N_t=N_t)
+
+
+def case_panda_blend(rng):
+    """Panda postures on the elbow-extended / wrist-aligned sets (BASELINE config 4), inside the blend band, both joint-space
+    strategies represented."""
+    model = MpChain(chain("panda"))
+    q0 = np.array([j["q0"] for j in chain("panda")["joints"]])
+    want, recs, seen = 6, [], {1: 0, 2: 0}
+    keys = ("tau", "tau1", "tau2", "alpha", "ins", "types", "S", "N_t", "tau_plain")
+    out = {k: [] for k in keys}
+    inp = {k: [] for k in ("q", "dq", "dpos", "gv", "gq", "gdq", "gddq")}
+    tries = 0
+    while len(out["tau"]) < want and tries < 200:
+        tries += 1
+        q = q0 + rng.normal(0, 0.2, 7) * np.array([1, 1, 1, 0, 1, 0, 1.0])
+        eps = 10.0 ** rng.uniform(-3, -1.3)
+        if tries % 2:
+            q[3] = -0.0698 - abs(rng.normal(0, eps)); q[5] = q0[5] + rng.normal(0, 0.2)
+        else:
+            q[5] = rng.normal(0, eps); q[3] = q0[3] + rng.normal(0, 0.2)
+        dq = rng.uniform(-0.3, 0.3, 7)
+        goal = dict(dpos=rng.normal(0, 0.05, 3), linvel=rng.normal(0, 0.05, 3), angvel=np.zeros(3), linacc=np.zeros(3), angacc=np.zeros(3))
+        jg = dict(pos=q + rng.normal(0, 0.1, 7), vel=rng.normal(0, 0.1, 7), acc=rng.normal(0, 0.1, 7))
+        try:
+            o = blend_tick(model, q, dq, goal, jg)
+        except AssertionError:
+            continue
+        kind = 1 if 1 in o["types"] else 2
+        if o["alpha"] in (0, 1) and len(out["tau"]) >= 2 or seen[kind] >= want - 2:
+            continue
+        # keep away from the classification threshold and the band edges: a pin must not depend on the last digits
+        seen[kind] += 1
+        o2 = blend_tick(model, q, dq, goal, jg, stacked=False)
+        for k in ("tau", "tau1", "tau2", "S", "N_t"):
+            out[k].append(f64(o[k]).ravel())
+        out["alpha"].append(float(o["alpha"])); out["ins"].append(o["ins"]); out["types"].append(o["types"]); out["tau_plain"].append(f64(o2["tau"]).ravel())
+        for k, v in (("q", q), ("dq", dq), ("dpos", goal["dpos"]), ("gv", goal["linvel"]), ("gq", jg["pos"]), ("gdq", jg["vel"]), ("gddq", jg["acc"])):
+            inp[k].append(v)
+    assert len(out["tau"]) == want and seen[1] > 0 and seen[2] > 0, (len(out["tau"]), seen)
+    return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
+
+
 def main():
     prove_orientation_error()
     print("orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a: proved")
     os.makedirs(OUT, exist_ok=True)
     for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
-                           ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104)):
+                           ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104),
+                           ("pins_panda_blend", case_panda_blend, 1105)):
         if len(sys.argv) > 1 and name not in sys.argv[1:]:
             continue
         d = fn(np.random.default_rng(seed))
