@@ -283,3 +283,35 @@ def test_pin_panda_singular_blend_mpmath(kind, per_call):
     assert (np.asarray(b.get(abi.F_JT_RANGE_RANK, t1)).ravel() == 1).all()
     if kind == "cuda" and not per_call:
         assert b.tick_is_fused() and b.tick_fallback_count() == B, "the pins must go through k_tick_tail"
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+def test_pin_puma_single_task_blend_mpmath(kind, per_call):
+    """examples/19 / BASELINE config 4 (PUMA): a 6R arm at its wrist-lock posture under ONE 6-DoF MotionForceTask, bounded inertia
+    estimates clamping several joints, against the same 50-digit model of SingularityHandler (no joint task below).  On the GPU
+    per_call = False is the single-task fused tick (k_tick_fused2<6> with L_BIE for any clamp pattern + the n = 6 blend routine)."""
+    g = G("pins_puma_blend")
+    chain = load_chain("puma560_synthetic")
+    B = len(g["q"])
+    b = make_batch(kind, chain, B)
+    b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+    t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0)))
+    x0 = b.get(abi.F_CURRENT_POSITION, t0)
+    b.set(abi.F_GOAL_POSITION, x0 + g["dpos"], t0); b.set(abi.F_GOAL_LINEAR_VELOCITY, g["gv"], t0)
+    if per_call:
+        b.update_model(); b.update_task_models()
+        tau = b.compute_torques(True)
+    else:
+        tau = b.tick(True)
+    ratio = np.maximum(g["S"][np.arange(B), g["ins"]] / g["S"][:, 0], 1e-4)
+    tol = np.maximum(FP64_TOL, 64 * 2.2e-16 / ratio ** 2)
+    close(b.get(abi.F_SINGULAR_VALUES, t0), g["S"], "singular values of J", floor=1e-3)
+    assert np.abs(np.asarray(b.get(abi.F_ALPHA, t0)).ravel() - g["alpha"]).max() <= 1e-9
+    assert (np.asarray(b.get(abi.F_NS_RANK, t0)).ravel() == g["ins"]).all()
+    assert (np.asarray(b.get(abi.F_SINGULARITY_TYPES, t0)) == g["types"]).all()
+    a, ref = np.asarray(tau, float), g["tau"]
+    e = np.abs(a - ref).max(axis=1) / np.maximum(np.abs(ref).max(axis=1), 1e-3 * np.abs(ref).max())
+    assert (e <= tol).all(), "tau: rel err %s > %s" % (e, tol)
+    if kind == "cuda" and not per_call:
+        assert b.tick_is_fused() and b.tick_fallback_count() == B

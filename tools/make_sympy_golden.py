@@ -572,7 +572,7 @@ SH = dict(s_abs_tol=mp.mpf("1e-3"), type_1_tol=mp.mpf("0.5"), ratio=mp.mpf("1e-2
           kv2=mp.mpf(5), s_min=mp.mpf("6e-3"), s_max=mp.mpf("6e-2"))
 
 
-def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07), stacked=True, jkp=50.0, jkv=14.0):
+def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07), stacked=True, jkp=50.0, jkv=14.0, jt=True):
     """First control cycle of [6-DoF MotionForceTask, full JointTask] for a robot INSIDE the blend band: classification history empty,
     q_prior latched to q, type-2 directions all +1 (SingularityHandler.cpp:40-62)."""
     n = model.n
@@ -642,6 +642,8 @@ def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07),
     ts = Js.T * (Lam_s_mod * (Us.T * Fstar) + Us.T * Ff)
     ts = mp.matrix([min(max(ts[i], -effort[i]), effort[i]) for i in range(n)])
     tau1 = tau_ns + alpha * ts + (1 - alpha) * tj
+    if not jt:  # a 6-DoF arm under the one task (examples/19): nothing below it
+        return dict(tau=tau1, tau1=tau1, alpha=alpha, ins=ins, types=types + [0] * (6 - len(types)), S=S)
     # full JointTask below it: range of N_t (one direction for n = 7, m = 6)
     Jp = N_t
     kcol = max(range(n), key=lambda cc: mp.norm(Jp[:, cc]))
@@ -697,13 +699,44 @@ def case_panda_blend(rng):
     return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
 
 
+def case_puma_blend(rng):
+    """examples/19-puma_singularity: the 6R arm at its wrist-lock posture +- eps under ONE 6-DoF task (no joint task), bounded inertia
+    estimates clamping the three wrist joints (the general clamp pattern)."""
+    model = MpChain(chain("puma560_synthetic"))
+    base = np.array([0.0, -np.pi / 4, 3 * np.pi / 4, np.pi / 2, 0.0, np.pi])
+    want = 5
+    out = {k: [] for k in ("tau", "alpha", "ins", "types", "S")}
+    inp = {k: [] for k in ("q", "dq", "dpos", "gv")}
+    tries = 0
+    while len(out["tau"]) < want and tries < 400:
+        tries += 1
+        q = base + rng.normal(0, 0.05, 6)
+        q[4] = rng.choice([-1.0, 1.0]) * 10.0 ** rng.uniform(-2.5, 0.0)
+        dq = rng.uniform(-0.3, 0.3, 6)
+        goal = dict(dpos=rng.normal(0, 0.05, 3), linvel=rng.normal(0, 0.05, 3), angvel=np.zeros(3), linacc=np.zeros(3), angacc=np.zeros(3))
+        try:
+            o = blend_tick(model, q, dq, goal, None, p_c=(0, 0, 0), jt=False)
+        except AssertionError:
+            continue
+        inside = 0 < o["alpha"] < 1
+        if (inside and sum(1 for a in out["alpha"] if 0 < a < 1) >= 3) or (not inside and sum(1 for a in out["alpha"] if not 0 < a < 1) >= 2):
+            continue
+        assert sum(1 for i in range(6) if model.mass_matrix([mp.mpf(float(t)) for t in q])[i, i] < mp.mpf("0.1")) >= 2   # a general clamp pattern
+        out["tau"].append(f64(o["tau"]).ravel()); out["S"].append(f64(o["S"]).ravel())
+        out["alpha"].append(float(o["alpha"])); out["ins"].append(o["ins"]); out["types"].append(o["types"])
+        for k, v in (("q", q), ("dq", dq), ("dpos", goal["dpos"]), ("gv", goal["linvel"])):
+            inp[k].append(v)
+    assert len(out["tau"]) == want, len(out["tau"])
+    return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
+
+
 def main():
     prove_orientation_error()
     print("orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a: proved")
     os.makedirs(OUT, exist_ok=True)
     for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
                            ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104),
-                           ("pins_panda_blend", case_panda_blend, 1105)):
+                           ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106)):
         if len(sys.argv) > 1 and name not in sys.argv[1:]:
             continue
         d = fn(np.random.default_rng(seed))
