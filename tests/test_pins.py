@@ -315,3 +315,48 @@ def test_pin_puma_single_task_blend_mpmath(kind, per_call):
     assert (e <= tol).all(), "tau: rel err %s > %s" % (e, tol)
     if kind == "cuda" and not per_call:
         assert b.tick_is_fused() and b.tick_fallback_count() == B
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+def test_pin_panda_partial_task_blend_mpmath(kind, per_call):
+    """BASELINE config 3 shape inside ITS OWN singular band: translation-only MotionForceTask (rank 3, nullspace of dimension 4) + full
+    JointTask on Panda postures near full extension, against the 50-digit model of SingularityHandler for a partial task (the SVD of
+    the task in its range, U = B6 U_r).  GPU, per_call = False: k_tick_fused3's certificate -> closed-form blend routine, M = 3."""
+    g = G("pins_panda_blend_partial")
+    chain = load_chain("panda")
+    B = len(g["q"])
+    outs = {}
+    for stacked in (True, False):
+        b = make_batch(kind, chain, B)
+        b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+        t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07), dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[]))
+        t1 = b.add_joint_task(abi.joint_task_desc(7))
+        x0 = b.get(abi.F_CURRENT_POSITION, t0)
+        b.set(abi.F_GOAL_POSITION, x0 + g["dpos"], t0); b.set(abi.F_GOAL_LINEAR_VELOCITY, g["gv"], t0)
+        b.set(abi.F_JT_GOAL_POSITION, g["gq"], t1); b.set(abi.F_JT_GOAL_VELOCITY, g["gdq"], t1); b.set(abi.F_JT_GOAL_ACCELERATION, g["gddq"], t1)
+        if per_call:
+            b.update_model(); b.update_task_models()
+            tau = b.compute_torques(stacked)
+        else:
+            tau = b.tick(stacked)
+        outs[stacked] = (b, t0, t1, np.asarray(tau, float))
+    b, t0, t1, tau = outs[True]
+    ratio = g["S"][np.arange(B), g["ins"]] / g["S"][:, 0]
+    tol = np.maximum(FP64_TOL, 64 * 2.2e-16 / ratio ** 2)
+    assert np.abs(np.asarray(b.get(abi.F_SINGULAR_VALUES, t0))[:, :3] - g["S"]).max() <= 1e-9
+    assert np.abs(np.asarray(b.get(abi.F_ALPHA, t0)).ravel() - g["alpha"]).max() <= 1e-9
+    assert (np.asarray(b.get(abi.F_NS_RANK, t0)).ravel() == g["ins"]).all()
+    assert (np.asarray(b.get(abi.F_SINGULARITY_TYPES, t0)) == g["types"]).all()
+
+    def close_each(a, ref, what):
+        a, ref = np.asarray(a, float).reshape(B, -1), np.asarray(ref, float).reshape(B, -1)
+        e = np.abs(a - ref).max(axis=1) / np.maximum(np.abs(ref).max(axis=1), 1e-3 * np.abs(ref).max())
+        assert (e <= tol).all(), "%s: rel err %s > %s" % (what, e, tol)
+    close_each(tau, g["tau"], "tau (stacked)")
+    close_each(b.get(abi.F_TASK_TORQUES, t0), g["tau1"], "tau_1")
+    close_each(b.get(abi.F_TASK_TORQUES, t1), g["tau2"], "tau_2 (4-dimensional nullspace)")
+    close_each(outs[False][3], g["tau_plain"], "tau (plain sum)")
+    assert (np.asarray(b.get(abi.F_JT_RANGE_RANK, t1)).ravel() == 4).all()
+    if kind == "cuda" and not per_call:
+        assert b.tick_is_fused() and b.tick_fallback_count() == B

@@ -572,7 +572,7 @@ SH = dict(s_abs_tol=mp.mpf("1e-3"), type_1_tol=mp.mpf("0.5"), ratio=mp.mpf("1e-2
           kv2=mp.mpf(5), s_min=mp.mpf("6e-3"), s_max=mp.mpf("6e-2"))
 
 
-def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07), stacked=True, jkp=50.0, jkv=14.0, jt=True):
+def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07), stacked=True, jkp=50.0, jkv=14.0, jt=True, B6=None):
     """First control cycle of [6-DoF MotionForceTask, full JointTask] for a robot INSIDE the blend band: classification history empty,
     q_prior latched to q, type-2 directions all +1 (SingularityHandler.cpp:40-62)."""
     n = model.n
@@ -582,20 +582,25 @@ def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07),
     qv = mp.matrix(qm)
     M = model.mass_matrix(qm)
     Minv, Mbinv = inv(M), inv(bie(M))
-    x, R, J = model.point(qm, link, p_c)
+    x, R, J6 = model.point(qm, link, p_c)
+    B6 = mp.eye(6) if B6 is None else B6           # 6 x m orthonormal basis of the controlled directions (partial task)
+    m = B6.cols
+    P = B6 * B6.T
+    J = P * J6                                     # MotionForceTask.cpp:262
     tw = J * dqm
-    spec, st = MftSpec(), new_state()
+    spec, st = MftSpec(Pt=P[0:3, 0:3], Pr=P[3:6, 3:6]), new_state()
     g = dict(goal)
     g["pos"] = x + V3(goal["dpos"]); g["ori"] = R
     Fstar, Ff, vd, wd, eo = mft_law(spec, st, x, R, tw[0:3, 0], tw[3:6, 0], g, None, None)
-    U, S, Vh = mp.svd_r(J)                         # J = U diag(S) Vh, thin: U 6 x 6, Vh 6 x 7
+    Ur, S, Vh = mp.svd_r(B6.T * J)                 # the task in its own range: J_r = U_r diag(S) Vh (m x m, m, m x n); U = B6 U_r
+    U = B6 * Ur
     assert S[0] >= SH["s_abs_tol"]
-    ins = next((i for i in range(1, 6) if S[i] / S[0] < SH["s_max"]), None)
+    ins = next((i for i in range(1, m) if S[i] / S[0] < SH["s_max"]), None)
     assert ins is not None, "pin robots must sit in the blend band"
     alpha = min(max((S[ins] / S[0] - SH["s_min"]) / (SH["s_max"] - SH["s_min"]), mp.mpf(0)), mp.mpf(1))
     # sign convention of the implementation-defined JacobiSVD: largest-|component| of every V column positive
     V = Vh.T.copy()
-    for k in range(6):
+    for k in range(m):
         col = [V[i, k] for i in range(n)]
         big = max(col, key=lambda t: abs(t))
         if big < 0:
@@ -603,7 +608,7 @@ def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07),
                 V[i, k] = -V[i, k]
             for i in range(6):
                 U[i, k] = -U[i, k]
-    Uns, Us, Vs = U[:, 0:ins], U[:, ins:6], V[:, ins:6]
+    Uns, Us, Vs = U[:, 0:ins], U[:, ins:m], V[:, ins:m]
     Jns, Js = Uns.T * J, Us.T * J
     Lam_ns, _, N_ns = osm(Jns, Minv)
     Lam_ns_mod = inv(Jns * Mbinv * Jns.T)          # .cpp:175-190
@@ -614,7 +619,7 @@ def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07),
     N_t = N_post * N_ns
     # classifySingularity (.cpp:230-295), first call: one sample in the history
     types = []
-    for k in range(6 - ins):
+    for k in range(m - ins):
         qp = [qm[i] + SH["step"] * Vs[i, k] for i in range(n)]
         x2, R2, _ = model.point(qp, link, p_c)
         d6 = mp.matrix(list(x2 - x) + list(orientation_error(R2, R)))
@@ -646,8 +651,17 @@ def blend_tick(model, q, dq, goal, jgoal, link="end-effector", p_c=(0, 0, 0.07),
         return dict(tau=tau1, tau1=tau1, alpha=alpha, ins=ins, types=types + [0] * (6 - len(types)), S=S)
     # full JointTask below it: range of N_t (one direction for n = 7, m = 6)
     Jp = N_t
-    kcol = max(range(n), key=lambda cc: mp.norm(Jp[:, cc]))
-    Rm = Jp[:, kcol] / mp.norm(Jp[:, kcol])
+    cols = sorted(range(n), key=lambda cc: -mp.norm(Jp[:, cc]))   # orthonormal basis of range(N_t), dimension n - m (matrixRangeBasis)
+    Rb = []
+    for cc in cols:
+        vcol = Jp[:, cc]
+        for bb in Rb:
+            vcol = vcol - bb * (bb.T * vcol)[0]
+        if len(Rb) < n - m and mp.norm(vcol) > mp.mpf("1e-6"):
+            Rb.append(vcol / mp.norm(vcol))
+    Rm = mp.matrix(n, n - m)
+    for cc, bb in enumerate(Rb):
+        Rm[:, cc] = bb
     J2 = Rm.T * Jp
     Lam2, _, _ = osm(J2, Minv)
     Lam2_b = inv(J2 * Mbinv * J2.T)
@@ -699,6 +713,57 @@ def case_panda_blend(rng):
     return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
 
 
+def case_panda_blend_partial(rng):
+    """BASELINE config 3 shape inside ITS singular band: translation-only MotionForceTask (rank 3) + full JointTask (nullspace of
+    dimension 4), arm towards full extension."""
+    model = MpChain(chain("panda"))
+    q0 = np.array([j["q0"] for j in chain("panda")["joints"]])
+    B6 = mp.zeros(6, 3)
+    for a in range(3):
+        B6[a, a] = 1
+    want = 4
+    keys = ("tau", "tau1", "tau2", "alpha", "ins", "types", "S", "tau_plain")
+    out = {k: [] for k in keys}
+    inp = {k: [] for k in ("q", "dq", "dpos", "gv", "gq", "gdq", "gddq")}
+    # candidate postures: the position Jacobian is rank deficient only near full extension (about 5 % of the joint range); the C++ oracle
+    # is used to FIND such postures among random ones -- the pinned outputs below come from the mpmath model alone
+    sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "oracle")); sys.path.insert(0, os.path.join(ROOT, "sai2-primitives-perso_b200"))
+    import orc
+    import osc_abi as abi
+    from common import random_q
+    orc.build()
+    cj = chain("panda")
+    N = 4096
+    cand = random_q(cj, N, rng, 0.3)
+    ob = orc.OracleBatch(cj, N, q0=[j["q0"] for j in cj["joints"]])
+    ob.set(abi.F_Q, cand); ob.set(abi.F_DQ, np.zeros_like(cand)); ob.update_model()
+    t0 = ob.add_motion_force_task(abi.mft_desc(cj, "end-effector", (0, 0, 0.07), dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[]))
+    ob.add_joint_task(abi.joint_task_desc(7))
+    ob.tick(True)
+    al = ob.get(abi.F_ALPHA, t0)[:, 0]
+    pool = list(cand[(al > 0.05) & (al < 0.95)][:4]) + list(cand[al == 0][:1])
+    want = len(pool)
+    assert want >= 3
+    tries = 0
+    for q in pool:
+        tries += 1
+        dq = rng.uniform(-0.3, 0.3, 7)
+        goal = dict(dpos=rng.normal(0, 0.05, 3), linvel=rng.normal(0, 0.05, 3), angvel=np.zeros(3), linacc=np.zeros(3), angacc=np.zeros(3))
+        jg = dict(pos=q + rng.normal(0, 0.1, 7), vel=rng.normal(0, 0.1, 7), acc=rng.normal(0, 0.1, 7))
+        try:
+            o = blend_tick(model, q, dq, goal, jg, B6=B6)
+        except AssertionError:
+            continue
+        o2 = blend_tick(model, q, dq, goal, jg, B6=B6, stacked=False)
+        for k in ("tau", "tau1", "tau2", "S"):
+            out[k].append(f64(o[k]).ravel())
+        out["alpha"].append(float(o["alpha"])); out["ins"].append(o["ins"]); out["types"].append(o["types"]); out["tau_plain"].append(f64(o2["tau"]).ravel())
+        for k, v in (("q", q), ("dq", dq), ("dpos", goal["dpos"]), ("gv", goal["linvel"]), ("gq", jg["pos"]), ("gdq", jg["vel"]), ("gddq", jg["acc"])):
+            inp[k].append(v)
+    assert len(out["tau"]) == want, (len(out["tau"]), tries)
+    return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
+
+
 def case_puma_blend(rng):
     """examples/19-puma_singularity: the 6R arm at its wrist-lock posture +- eps under ONE 6-DoF task (no joint task), bounded inertia
     estimates clamping the three wrist joints (the general clamp pattern)."""
@@ -736,7 +801,7 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
                            ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104),
-                           ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106)):
+                           ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106), ("pins_panda_blend_partial", case_panda_blend_partial, 1107)):
         if len(sys.argv) > 1 and name not in sys.argv[1:]:
             continue
         d = fn(np.random.default_rng(seed))
