@@ -360,3 +360,30 @@ def test_pin_panda_partial_task_blend_mpmath(kind, per_call):
     assert (np.asarray(b.get(abi.F_JT_RANGE_RANK, t1)).ravel() == 4).all()
     if kind == "cuda" and not per_call:
         assert b.tick_is_fused() and b.tick_fallback_count() == B
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_pin_rollout_lagrange_mpmath(kind):
+    """Row f-2 (forward dynamics + symplectic Euler, examples/05...cpp:219-233 without contact) against Lagrange's equations at 50
+    digits: b + g = Mdot dq - 1/2 grad_q(dq' M dq) + grad_q V, with M the kinetic-energy Hessian -- no Newton-Euler recursion in the
+    model.  (A) one step under the torque of a two-task tick: h, and q / dq advanced with the model's M^-1 and h under the torque the
+    implementation itself reports; (B) three damped substeps of the unactuated arm, every number from the model."""
+    g = G("pins_panda_rollout")
+    chain = load_chain("panda")
+    b = make_batch(kind, chain, len(g["q"]))
+    b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+    b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07))); b.add_joint_task(abi.joint_task_desc(7))
+    tau = np.asarray(b.tick(True), float)
+    dt, damping = 1e-3, 0.3
+    b.rollout_step(dt, 1, damping)
+    close(b.get(abi.F_NONLINEAR_EFFECTS), g["h"], "b + g")
+    dq1 = g["dq"] + dt * np.einsum("rij,rj->ri", g["Minv"], tau - g["h"] - damping * g["dq"])
+    close(b.get(abi.F_DQ), dq1, "dq after one step")
+    close(b.get(abi.F_Q), g["q"] + dt * dq1, "q after one step")
+
+    f = make_batch(kind, chain, len(g["fall_q0"]))
+    f.set(abi.F_Q, g["fall_q0"]); f.set(abi.F_DQ, g["fall_dq0"]); f.update_model()
+    f.rollout_step(float(g["fall_dt"]), int(g["fall_substeps"]), float(g["fall_damping"]))   # no tick yet: OSC_F_TAU is zero
+    close(f.get(abi.F_NONLINEAR_EFFECTS), g["fall_h0"], "b + g of the falling arm")
+    close(f.get(abi.F_DQ), g["fall_dq"], "dq after three substeps")
+    close(f.get(abi.F_Q), g["fall_q"], "q after three substeps")

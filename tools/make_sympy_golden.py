@@ -795,13 +795,75 @@ def case_puma_blend(rng):
     return dict(**{k: np.array(v) for k, v in inp.items()}, **{k: np.array(v) for k, v in out.items()})
 
 
+def lagrange_nonlinear(model, q, dq):
+    """b(q, dq) + g(q) from Lagrange's equations: Mdot dq - 1/2 grad_q(dq' M dq) + grad_q V, V = -sum_b m_b g . c_b(q); M(q) is the
+    kinetic-energy Hessian above, its q-derivative a second central difference (step 1e-12 over an M that is good to 1e-30)."""
+    n = model.n
+    H2 = mp.mpf(10) ** -12
+    g = V3(model.c["gravity"])
+
+    def V(qq):
+        f = model.fk(qq)
+        return -sum(mp.mpf(body["mass"]) * (g.T * (f[b][1] + f[b][0] * V3(body["com"])))[0] for b, body in enumerate(model.c["bodies"]))
+
+    dM, dV = [], []
+    for k in range(n):
+        qp, qm = list(q), list(q)
+        qp[k] = q[k] + H2; qm[k] = q[k] - H2
+        dM.append((model.mass_matrix(qp) - model.mass_matrix(qm)) / (2 * H2))
+        qp[k] = q[k] + H; qm[k] = q[k] - H
+        dV.append((V(qp) - V(qm)) / (2 * H))
+    v = mp.matrix(dq)
+    Mdot = mp.zeros(n, n)
+    for k in range(n):
+        Mdot += dM[k] * dq[k]
+    c = Mdot * v
+    for k in range(n):
+        c[k] -= (v.T * dM[k] * v)[0] / 2
+    return c + mp.matrix(dV)
+
+
+def case_panda_rollout(rng):
+    """Row f-2: (A) b + g and M^-1 at six states for one step under the caller's own torque; (B) three symplectic-Euler substeps of the
+    unactuated arm with joint damping, entirely in the model (examples/05...cpp:219-233 without contact)."""
+    model = MpChain(chain("panda"))
+    c = chain("panda")
+    lo, hi = np.array([j["lower"] for j in c["joints"]]), np.array([j["upper"] for j in c["joints"]])
+    A = 6
+    q = lo + (0.15 + 0.7 * rng.random((A, 7))) * (hi - lo)
+    dq = rng.uniform(-1.0, 1.0, (A, 7))
+    h, Minv = [], []
+    for r in range(A):
+        qq, dd = [mp.mpf(float(t)) for t in q[r]], [mp.mpf(float(t)) for t in dq[r]]
+        h.append(f64(lagrange_nonlinear(model, qq, dd)).ravel())
+        Minv.append(f64(inv(model.mass_matrix(qq))))
+    # (B) passive fall: tau = 0
+    Bn, dt, damping, sub = 3, mp.mpf("0.001"), mp.mpf("0.2"), 3
+    q0 = lo + (0.2 + 0.6 * rng.random((Bn, 7))) * (hi - lo)
+    dq0 = rng.uniform(-0.5, 0.5, (Bn, 7))
+    q3, dq3, h0 = [], [], []
+    for r in range(Bn):
+        qq, dd = [mp.mpf(float(t)) for t in q0[r]], [mp.mpf(float(t)) for t in dq0[r]]
+        for s in range(sub):
+            hh = lagrange_nonlinear(model, qq, dd)
+            if s == 0:
+                h0.append(f64(hh).ravel())
+            qdd = inv(model.mass_matrix(qq)) * (-hh - damping * mp.matrix(dd))
+            dd = [dd[i] + qdd[i] * dt for i in range(7)]
+            qq = [qq[i] + dd[i] * dt for i in range(7)]
+        q3.append([float(t) for t in qq]); dq3.append([float(t) for t in dd])
+    return dict(q=q, dq=dq, h=np.array(h), Minv=np.array(Minv), fall_q0=q0, fall_dq0=dq0, fall_h0=np.array(h0), fall_q=np.array(q3), fall_dq=np.array(dq3),
+                fall_dt=float(dt), fall_damping=float(damping), fall_substeps=sub)
+
+
 def main():
     prove_orientation_error()
     print("orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a: proved")
     os.makedirs(OUT, exist_ok=True)
     for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
                            ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104),
-                           ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106), ("pins_panda_blend_partial", case_panda_blend_partial, 1107)):
+                           ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106), ("pins_panda_blend_partial", case_panda_blend_partial, 1107),
+                           ("pins_panda_rollout", case_panda_rollout, 1108)):
         if len(sys.argv) > 1 and name not in sys.argv[1:]:
             continue
         d = fn(np.random.default_rng(seed))
