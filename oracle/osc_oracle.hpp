@@ -3,7 +3,9 @@
 // PARITY UNPINNED: the reference has no tests / golden vectors for this path and cannot be compiled here (it needs
 // Eigen3 and the un-vendored sai2-model -> RBDL), so this oracle is a restatement pinned only by
 // (a) physics identities, (b) the independent numpy/LAPACK oracle oracle/np_oracle.py, (c) the golden vectors under
-// tests/golden/ that those two agree on.  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// tests/golden/ that those two agree on, and (d) the code-independent pins tests/golden/pins_*.npz (sympy closed forms, 50-digit
+// mpmath models of M, J, Lambda, N, the control law, POPC, the SingularityHandler blend and the rollout step typed in from the
+// reference text: tools/make_sympy_golden.py, replayed by tests/test_pins.py at 1e-9).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 // --impl reference legs may build, load or call anything in this directory.  The product (libosc_b200.so) never does.
 //
 // Every function cites the reference file:line it follows (paths relative to /root/reference/src unless noted).
@@ -573,7 +575,8 @@ struct Model {
 	}
 	// Sai2Model::coriolisPlusGravity: h = b(q, dq) + g(q) by the recursive Newton-Euler algorithm in LINK coordinates (the
 	// structure of RBDL's InverseDynamics with qdd = 0: velocities / accelerations base -> tip in each body's own frame,
-	// forces tip -> base).  Row f-2 of SURVEY.md 8(f); restatement only (sai2-model / RBDL are un-vendored).
+	// forces tip -> base).  Row f-2 of SURVEY.md 8(f); restatement (sai2-model / RBDL are un-vendored), pinned by Lagrange's
+	// equations at 50 digits (tests/test_pins.py::test_pin_rollout_lagrange_mpmath).
 	void nonlinearEffects(double* h) const {
 		M3 E[8]; V3 r[8];
 		V3 w[8], wd[8], a[8], F[8], Nn[8];
