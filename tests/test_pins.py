@@ -387,3 +387,48 @@ def test_pin_rollout_lagrange_mpmath(kind):
     close(f.get(abi.F_NONLINEAR_EFFECTS), g["fall_h0"], "b + g of the falling arm")
     close(f.get(abi.F_DQ), g["fall_dq"], "dq after three substeps")
     close(f.get(abi.F_Q), g["fall_q"], "q after three substeps")
+
+
+_HIER = {  # name -> (chain, task list): what RobotController accepts beyond [MotionForceTask, JointTask]
+    "h1": ("panda_sliding_base", lambda n: [("jt", np.eye(n)[[0, n - 1]]), ("mft", {})]),                      # examples/06
+    "h2": ("panda_sliding_base", lambda n: [("jt", np.eye(n)[:1]), ("mft", dict(dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[])), ("jt", None)]),
+    "h3": ("panda", lambda n: [("mft", dict(dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[])), ("jt", np.eye(n)[:3]), ("jt", None)]),
+}
+
+
+@pytest.mark.parametrize("kind", KINDS)
+@pytest.mark.parametrize("per_call", [False, True])
+@pytest.mark.parametrize("name", sorted(_HIER))
+def test_pin_hierarchies_mpmath(kind, per_call, name):
+    """Partial JointTask first (examples/06, n = 8 with a prismatic base), three-task hierarchies with a partial MotionForceTask in
+    the middle or in front: the N_prec chain, JointTask.cpp:218-356 with a selection matrix, the running-sum disturbance
+    compensation of the joint tasks and the (identically zero, quirk Q1) one of the motion task, from the 50-digit model."""
+    G_ = G("pins_hierarchies")
+    g = {k[len(name) + 1:]: v for k, v in G_.items() if k.startswith(name + "_")}
+    cname, build = _HIER[name]
+    chain = load_chain(cname)
+    n = chain["n"]
+    b = make_batch(kind, chain, len(g["q"]))
+    b.set(abi.F_Q, g["q"]); b.set(abi.F_DQ, g["dq"]); b.update_model()
+    ids, j = [], 0
+    for what, arg in build(n):
+        if what == "jt":
+            t = b.add_joint_task(abi.joint_task_desc(n, arg))
+            b.set(abi.F_JT_GOAL_POSITION, g["jg%d" % j], t); b.set(abi.F_JT_GOAL_VELOCITY, g["jgv%d" % j], t); b.set(abi.F_JT_GOAL_ACCELERATION, g["jga%d" % j], t)
+            j += 1
+        else:
+            t = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07), **arg))
+            b.set(abi.F_GOAL_POSITION, b.get(abi.F_CURRENT_POSITION, t) + g["dpos"], t); b.set(abi.F_GOAL_LINEAR_VELOCITY, g["gv"], t)
+        ids.append(t)
+    for stacked, key in ((True, "tau"), (False, "tau_plain")):
+        if per_call:
+            b.update_model(); b.update_task_models()
+            tau = b.compute_torques(stacked)
+        else:
+            tau = b.tick(stacked)
+        close(tau, g[key], key)
+        if stacked:
+            for i, t in enumerate(ids):
+                close(b.get(abi.F_TASK_TORQUES, t), g["t%d" % i], "torques of task %d" % i, floor=float(np.abs(g["tau"]).max()))
+            close(b.get(abi.F_N_TOTAL), g["N_total"], "N_total", floor=1.0)
+    assert [int(r) for r in g["ranks"][0][:len(ids)]] == {"h1": [2, 6], "h2": [1, 3, 4], "h3": [3, 3, 1]}[name]

@@ -856,6 +856,133 @@ def case_panda_rollout(rng):
                 fall_dt=float(dt), fall_damping=float(damping), fall_substeps=sub)
 
 
+def range_basis(A, tol=mp.mpf("1e-3")):
+    """orthonormal basis of the column space of A (definition of matrixRangeBasis, App. B: relative tolerance 1e-3 on the singular
+    values) by Gram-Schmidt on its largest columns; any basis of that space gives the same torques"""
+    sv = mp.svd_r(A, compute_uv=False)
+    if sv[0] < mp.mpf("1e-12"):
+        return None
+    r_dim = sum(1 for x in sv if x / sv[0] > tol)
+    gap = [sv[i] / sv[0] for i in range(len(sv))]
+    assert all(g > 10 * tol or g < tol / 10 for g in gap), "pin robots must have a clear rank gap"
+    Rb = []
+    for c in sorted(range(A.cols), key=lambda c: -mp.norm(A[:, c])):
+        v = A[:, c]
+        for b in Rb:
+            v = v - b * (b.T * v)[0]
+        if len(Rb) < r_dim and mp.norm(v) > mp.mpf("1e-6"):
+            Rb.append(v / mp.norm(v))
+    Rm = mp.matrix(A.rows, r_dim)
+    for c, b in enumerate(Rb):
+        Rm[:, c] = b
+    return Rm
+
+
+def hierarchy_tick(model, q, dq, tasks, stacked=True, link="end-effector", p_c=(0, 0, 0.07)):
+    """RobotController.cpp:53-74 over any list of tasks, every MotionForceTask in its non-singular branch (asserted), bounded inertia
+    estimates, no OTG.  tasks: ("jt", S k x n, goal dict pos/vel/acc of size k) | ("mft", B6 6 x m or None, goal dict).
+    JointTask.cpp:218-356 with _joint_selection = S and N_prec != I; MotionForceTask.cpp:247-276 (disturbance compensation == 0: the
+    _Lambda it multiplies by is only ever setZero, quirk Q1); SingularityHandler.cpp:75-160,300-309."""
+    n = model.n
+    qm, dqm = [mp.mpf(float(x)) for x in q], mp.matrix([mp.mpf(float(x)) for x in dq])
+    qv = mp.matrix(qm)
+    M = model.mass_matrix(qm)
+    Minv, Mbinv = inv(M), inv(bie(M))
+    Np = mp.eye(n)
+    tau = mp.zeros(n, 1)
+    per_task, ranks = [], []
+    for t in tasks:
+        if t[0] == "jt":
+            S = mp.matrix([[mp.mpf(float(x)) for x in row] for row in t[1]])
+            g = t[2]
+            Jp = S * Np
+            Rm = range_basis(Jp)
+            if Rm is None:
+                per_task.append(mp.zeros(n, 1)); ranks.append(0)
+                continue
+            J = Rm.T * Jp
+            Lam, Jbar, N = osm(J, Minv)
+            Lam_b = inv(J * Mbinv * J.T)
+            qd, dqd, ddqd = (mp.matrix([mp.mpf(float(x)) for x in g[key]]) for key in ("pos", "vel", "acc"))
+            u = -mp.mpf(50) * (S * qv - qd) - mp.mpf(14) * (S * dqm - dqd)
+            tt = Jp.T * Rm * (Lam * (Rm.T * ddqd) + Lam_b * (Rm.T * u))
+            if stacked:
+                tt = tt - Jp.T * Rm * (Lam * (Rm.T * (S * (Minv * tau))))
+            ranks.append(Rm.cols)
+        else:
+            B6 = mp.eye(6) if t[1] is None else t[1]
+            goal = t[2]
+            x, R, J6 = model.point(qm, link, p_c)
+            P = B6 * B6.T
+            J = P * J6
+            tw = J * dqm
+            g = dict(goal)
+            g["pos"], g["ori"] = x + V3(goal["dpos"]), R
+            Fstar, Ff, _, _, _ = mft_law(MftSpec(), new_state(), x, R, tw[0:3, 0], tw[3:6, 0], g)
+            Jr = B6.T * (J * Np)
+            sv = mp.svd_r(Jr, compute_uv=False)
+            assert sv[len(sv) - 1] / sv[0] > mp.mpf("0.07"), "pin robots must sit in the non-singular branch"
+            Lam, Jbar, N = osm(Jr, Minv)
+            Lam_b = inv(Jr * Mbinv * Jr.T)
+            tt = Jr.T * (Lam_b * (B6.T * Fstar) + B6.T * Ff)
+            ranks.append(B6.cols)
+        Np = N * Np
+        tau = tau + tt
+        per_task.append(tt)
+    return dict(tau=tau, per_task=per_task, N_total=Np, ranks=ranks)
+
+
+def case_hierarchies(rng):
+    """Row f-4: three hierarchies RobotController accepts beyond [MotionForceTask, JointTask]:
+    h1 examples/06: sliding-base Panda (n = 8), partial JointTask (slider + last joint) > 6-DoF MotionForceTask;
+    h2 sliding base: partial JointTask (slider) > translation-only MotionForceTask > full JointTask;
+    h3 Panda: translation-only MotionForceTask (examples/09) > partial JointTask (joints 1-3) > full JointTask."""
+    out = {}
+    e3 = mp.matrix(6, 3)
+    for i in range(3):
+        e3[i, i] = 1
+    for name, cname, build in (("h1", "panda_sliding_base", lambda n: [("jt", np.eye(n)[[0, n - 1]]), ("mft", None)]),
+                               ("h2", "panda_sliding_base", lambda n: [("jt", np.eye(n)[:1]), ("mft", e3), ("jt", np.eye(n))]),
+                               ("h3", "panda", lambda n: [("mft", e3), ("jt", np.eye(n)[:3]), ("jt", np.eye(n))])):
+        c = chain(cname)
+        model = MpChain(c)
+        n = c["n"]
+        q0 = np.array([j["q0"] for j in c["joints"]], float)
+        want, rec = 3, {k: [] for k in ("q", "dq", "dpos", "gv", "tau", "tau_plain", "N_total", "t0", "t1", "t2", "jg0", "jg1", "jgv0", "jgv1", "jga0", "jga1")}
+        tries = 0
+        while len(rec["q"]) < want and tries < 60:
+            tries += 1
+            q = q0 + rng.normal(0, 0.25, n)
+            dq = rng.uniform(-0.4, 0.4, n)
+            dpos, gv = rng.normal(0, 0.05, 3), rng.normal(0, 0.05, 3)
+            tasks, jgs = [], []
+            for kind, arg in build(n):
+                if kind == "jt":
+                    k = len(arg)
+                    g = dict(pos=arg @ q + rng.normal(0, 0.1, k), vel=rng.normal(0, 0.1, k), acc=rng.normal(0, 0.1, k))
+                    jgs.append(g)
+                    tasks.append(("jt", arg, g))
+                else:
+                    tasks.append(("mft", arg, dict(dpos=dpos, linvel=gv)))
+            try:
+                o = hierarchy_tick(model, q, dq, tasks, True)
+                o2 = hierarchy_tick(model, q, dq, tasks, False)
+            except AssertionError:
+                continue
+            for k, v in (("q", q), ("dq", dq), ("dpos", dpos), ("gv", gv), ("tau", f64(o["tau"]).ravel()), ("tau_plain", f64(o2["tau"]).ravel()), ("N_total", f64(o["N_total"]))):
+                rec[k].append(v)
+            for i in range(3):
+                rec["t%d" % i].append(f64(o["per_task"][i]).ravel() if i < len(tasks) else np.zeros(n))
+            for i, g in enumerate(jgs):
+                rec["jg%d" % i].append(g["pos"]); rec["jgv%d" % i].append(g["vel"]); rec["jga%d" % i].append(g["acc"])
+            rec.setdefault("ranks", []).append(o["ranks"] + [0] * (3 - len(o["ranks"])))
+        assert len(rec["q"]) == want, (name, len(rec["q"]))
+        for k, v in rec.items():
+            if len(v):
+                out[name + "_" + k] = np.array(v)
+    return out
+
+
 def main():
     prove_orientation_error()
     print("orientationError(R_d, Rot(a, theta) R_d) = sin(theta) a: proved")
@@ -863,7 +990,7 @@ def main():
     for name, fn, seed in (("pins_rrrr_two_task", case_rrrr, 1101), ("pins_panda_two_task", case_panda_two_task, 1102),
                            ("pins_panda_law", case_panda_law, 1103), ("pins_popc_window", case_popc_window, 1104),
                            ("pins_panda_blend", case_panda_blend, 1105), ("pins_puma_blend", case_puma_blend, 1106), ("pins_panda_blend_partial", case_panda_blend_partial, 1107),
-                           ("pins_panda_rollout", case_panda_rollout, 1108)):
+                           ("pins_panda_rollout", case_panda_rollout, 1108), ("pins_hierarchies", case_hierarchies, 1109)):
         if len(sys.argv) > 1 and name not in sys.argv[1:]:
             continue
         d = fn(np.random.default_rng(seed))
