@@ -177,7 +177,7 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 				}
 			}
 		} else
-		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || (has_jt && jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES)) {
 			const T thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
 			OSC_UNROLL for (int i = 0; i < N - 1; ++i) other = other || (Mx[i][i] < thr);
@@ -576,8 +576,9 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 		}
 	}
 
-	if constexpr (R == 0) {
-		// n = 6 under a full task: no nullspace left -- a joint task below it has range rank 0 and contributes nothing (JointTask.cpp:234-239)
+	// n = 6 under a full task: no nullspace left -- a joint task below it has range rank 0 and contributes nothing (JointTask.cpp:234-239);
+	// n = 7 with the motion task as the whole hierarchy (examples/07): there is no joint task
+	auto motion_task_only = [&]() {
 		OSC_UNROLL for (int i = 0; i < N; ++i) {
 			T t = tau1[i];
 			if (gravity) t += (T)rS(RobotL<N>::GRAV + i);
@@ -587,7 +588,12 @@ __device__ __forceinline__ bool blend_robot(const ChainC<T, N>& ch, const MftC<T
 				if (has_jt) { jS(JL::TASK_TAU + i) = T(0); jS(JL::CUR_POS + i) = q[i]; jS(JL::CUR_VEL + i) = dq[i]; }
 			}
 		}
+	};
+	if constexpr (R == 0) {
+		motion_task_only();
 		(void)jP; (void)stacked;
+	} else if (!has_jt) {
+		motion_task_only();
 	} else {
 	// ---- Q = orthonormal basis of the complement of range(W) (n x R): pivoted Gram-Schmidt on the unit vectors (k_tick_fused3 P9);
 	// sin/cos are dead, Q takes their slots ----

@@ -341,8 +341,9 @@ template <class T, int N> bool fused_tick_supported(Batch& b) {
 	if (b.tasks.empty() || b.tasks[0].type != OSC_TASK_MOTION_FORCE) return false;
 	const TaskH& m = b.tasks[0];
 	if (b.tasks.size() == 1) {
-		// single-task hierarchy: a 6-DoF arm under one full MotionForceTask (examples/19 on the PUMA; BASELINE config 4), second-generation kernel only
-		if (!(N == 6 && !m.md.partial && m.dof == 6)) return false;
+		// single-task hierarchy, second-generation kernel only: a 6-DoF arm under one full MotionForceTask (examples/19 on the PUMA; BASELINE
+		// config 4), or a 7-DoF arm whose RobotController holds that one task (examples/07-surface_surface_contact on the Panda)
+		if (!((N == 6 || N == 7) && !m.md.partial && m.dof == 6)) return false;
 		if (m.md.body != b.n - 1) return false;
 		for (int i = 0; i < b.n; ++i)
 			if (b.chain.joint_type[i] != OSC_JOINT_REVOLUTE) return false;

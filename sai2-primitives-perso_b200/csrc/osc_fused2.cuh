@@ -39,12 +39,16 @@ template <class T> __device__ __noinline__ void sincos_outlined(T x, T* s, T* c)
 // host selects this instantiation from the uniform task parameters; F_f is identically zero there.
 // BT threads per block; SYNC: block-wide barriers at the phase boundaries keep the warps of a block inside the same stretch of
 // this 100 KB straight-line kernel, so that they share instruction-cache lines (r1k: instruction fetch was the top stall).
-template <class T, int N, int MAXREG, bool SIMPLE, int BT = OSC_FUSED_THREADS, bool SYNC = false>
+// SINGLE (n = 7): the MotionForceTask is the whole hierarchy (examples/07-surface_surface_contact: RobotController over one task):
+// no joint task below it -- every joint-task argument aliases the motion task and is never touched, tau = tau_1.
+template <class T, int N, int MAXREG, bool SIMPLE, int BT = OSC_FUSED_THREADS, bool SYNC = false, bool SINGLE = false>
 __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ MftC<T> tc,
 																		 const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk0, Arena<T> tk1,
 																		 int64_t B, int64_t stride, int stacked, int gravity, int exports,
 																		 int* __restrict__ fb_count, int* __restrict__ fb_list) {
 	static_assert(N == 6 || N == 7, "the fused tick covers n - 6 <= 1");
+	static_assert(!SINGLE || N == 7, "n = 6 under one task needs no instantiation of its own: it has no nullspace");
+	constexpr bool JT7 = N == 7 && !SINGLE;  // a full JointTask in the one-dimensional nullspace of the motion task
 	using ML = MftL<N>;
 	using JL = JtL<N>;
 	using F = F2<N>;
@@ -81,7 +85,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 
 	// ---- P1: sin/cos of every joint.  q and dq are fetched as ONE batch of independent loads into the stash (a load per
 	// rolled iteration would pay a DRAM round trip each: profiles/README.md r1f) ----
-	if constexpr (SIMPLE && N == 7) {
+	if constexpr (SIMPLE && JT7) {
 		// ... together with every input of the joint task: its PID command u_pd and the goal acceleration wait in the stash for
 		// the range basis (P11), so that the kernel ends without a load phase.  The integrated error is stored here; a robot
 		// that falls back tells k_tick_tail not to integrate again (reuse_law bit 1).
@@ -103,7 +107,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 			auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); };
 			_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
 			_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
-			if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+			if (!(SIMPLE && N == 7) && !SINGLE) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
 		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) SM(F::SC + 2 * i) = q[i];
 		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
@@ -135,7 +139,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 			auto pf = [](const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p) : "memory"); };
 			_Pragma("unroll 1") for (int e = ML::GOAL_POS; e < (SIMPLE ? ML::GOAL_FORCE : ML::CUR_POS); ++e) pf(&mP(e));
 			_Pragma("unroll 1") for (int e = ML::INT_POS; e < (SIMPLE ? ML::INT_F : ML::POPC_VSQ + 1); ++e) pf(&mP(e));
-			if (!(SIMPLE && N == 7)) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
+			if (!(SIMPLE && N == 7) && !SINGLE) _Pragma("unroll 1") for (int e = 0; e < JL::P_SIZE; ++e) pf(&jP(e));
 		}
 		OSC_UNROLL for (int i = 0; i < N; ++i) { SM(F::SC + 2 * i) = q[i]; SM(F::MM + i) = dq[i]; }
 		_Pragma("unroll 1") for (int i = 0; i < N; ++i) {
@@ -272,7 +276,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 					if (Mx[i][i] < (A)tc.bie_threshold) Mx[i][i] = (A)tc.bie_threshold;
 			}
 		} else
-		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES) {
+		if (tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES || (!SINGLE && jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES)) {
 			const A thr = tc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES ? tc.bie_threshold : jc.bie_threshold;
 			bool other = false;
 			OSC_UNROLL for (int i = 0; i < N - 1; ++i) other = other || (Mx[i][i] < thr);
@@ -399,7 +403,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 	// ---- P9: u = unit vector orthogonal to the rows of W (n = 7): P = I - W^T W = u u^T, N_1 = (L^-T u)(L u)^T ----
 	A u[N];
 	OSC_UNROLL for (int i = 0; i < N; ++i) u[i] = A(0);
-	if constexpr (N == 7) {
+	if constexpr (JT7) {
 		A best = A(-1);
 		int kb = 0;
 		OSC_UNROLL for (int k = 0; k < N; ++k) {  // residual of e_k: P_kk = 1 - |W[:,k]|^2
@@ -499,10 +503,10 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 			sw = Num<A>::fma_(l, u[m], sw);
 		}
 		if (ex) mS(ML::TASK_TAU + i) = s1;
-		if constexpr (N == 7) { SM(TAU1 + i) = s1; SM(WW + i) = sw; }
+		if constexpr (JT7) { SM(TAU1 + i) = s1; SM(WW + i) = sw; }
 		else rS(RobotL<N>::TAU + i) = gravity ? s1 + rS(RobotL<N>::GRAV + i) : s1;
 	}
-	if constexpr (N == 7) {
+	if constexpr (JT7) {
 		OSC_FENCE();
 		// v = L^-T u, M^-1 tau_1 = L^-T h: in place (u -> v, h -> mt), one backward sweep over L
 		const A u_last = u[N - 1];
@@ -554,7 +558,7 @@ __global__ void __launch_bounds__(BT) __maxnreg__(MAXREG) k_tick_fused2(const __
 		OSC_UNROLL for (int i = 0; i < N; ++i) { jS(JL::CUR_POS + i) = rP(RobotL<N>::Q + i); jS(JL::CUR_VEL + i) = rP(RobotL<N>::DQ + i); jS(JL::TASK_TAU + i) = A(0); }
 	}
 	if (ex) {
-		if (!(exports & OSC_EXPORT_NO_JT)) tk1.I[(int64_t)JL::RANK * stride + r] = N == 7 ? 1 : 0;
+		if (!(exports & OSC_EXPORT_NO_JT)) tk1.I[(int64_t)JL::RANK * stride + r] = JT7 ? 1 : 0;
 		mS(ML::ALPHA) = T(1);
 		mI(ML::INS) = 6;
 	}

@@ -165,7 +165,7 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 			if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync(fallback counters)");
 			b.fb_parity = 0;
 		}
-		const bool single = b.tasks.size() == 1;  // 6-DoF arm under one MotionForceTask: every joint-task argument below aliases the motion task and is never used
+		const bool single = b.tasks.size() == 1;  // one MotionForceTask is the whole hierarchy: every joint-task argument below aliases the motion task and is never used
 		TaskH &m = b.tasks[0], &j = single ? b.tasks[0] : b.tasks[1];
 		int* cnt = b.fb + b.fb_parity;
 		int* nxt = b.fb + (b.fb_parity ^ 1);
@@ -223,7 +223,7 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				if (int rc = done(b, "k_gravity")) return rc;
 			}
 			const bool simple = fused2_simple(b) && !nosimple;
-			if (simple && N == 7) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
+			if (simple && N == 7 && !single) reuse_law |= 2;  // the joint PID error is integrated at the top of the SIMPLE kernel
 			// block shape: 224 threads with phase barriers once the batch fills two such blocks per SM (r1l: 44.7 us against
 			// 45.7 us for 64-thread blocks at 65,536 robots), 64-thread blocks below that so that small batches still spread
 			// over the SMs
@@ -244,7 +244,17 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 				return OSC_OK;
 			};
 			int rc = OSC_OK;
-			if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true>, 224);
+			bool launched = false;
+			if constexpr (N == 7) {
+				if (single) {  // the motion task is the whole hierarchy (examples/07): SINGLE instantiations, same block shapes
+					launched = true;
+					if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true, true>, 224);
+					else rc = simple ? go(k_tick_fused2<T, N, 128, true, OSC_FUSED_THREADS, false, true>, OSC_FUSED_THREADS)
+									 : go(k_tick_fused2<T, N, 128, false, OSC_FUSED_THREADS, false, true>, OSC_FUSED_THREADS);
+				}
+			}
+			if (launched) {}
+			else if (bt == 224) rc = simple ? go(k_tick_fused2<T, N, 128, true, 224, true>, 224) : go(k_tick_fused2<T, N, 128, false, 224, true>, 224);
 #ifdef OSC_EXPERIMENT
 			else if (bt == 65) rc = simple ? go(k_tick_fused2<T, N, 128, true, 64, true>, 64) : go(k_tick_fused2<T, N, 128, false, 64, true>, 64);
 			else if (bt == 448) rc = simple ? go(k_tick_fused2<T, N, 128, true, 448, true>, 448) : go(k_tick_fused2<T, N, 128, false, 448, true>, 448);

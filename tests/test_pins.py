@@ -165,9 +165,11 @@ def _set_params(b, t0, kw):
 
 
 @pytest.mark.parametrize("kind", KINDS)
-def test_pin_control_law_known_answers(kind):
+@pytest.mark.parametrize("route", ["per_call", "tick"])
+def test_pin_control_law_known_answers(kind, route):
     """one Panda per case, a single MotionForceTask, two ticks (integrators): Sigma projectors, velocity saturation, gains,
-    closed-loop force / moment feedback and its saturation, feed-forward scaling"""
+    closed-loop force / moment feedback and its saturation, feed-forward scaling.  Route "tick" on the GPU: the fused tick of a 7-DoF
+    arm under one task (k_tick_fused2<.., SINGLE>, general and SIMPLE instantiations)"""
     g = G("pins_panda_law")
     chain = load_chain("panda")
     for r, name in enumerate(g["names"]):
@@ -180,9 +182,14 @@ def test_pin_control_law_known_answers(kind):
         b.set(abi.F_GOAL_FORCE, g["goal_force"][r][None], t0); b.set(abi.F_GOAL_MOMENT, g["goal_moment"][r][None], t0)
         for tick in range(2):
             b.set(abi.F_Q, (g["q"][r] + g["dq"][r] * 0.001 * tick)[None])
-            b.update_model(); b.update_task_models()
-            b.update_sensed_force_and_moment(t0, g["sensed_f"][r, tick][None], g["sensed_m"][r, tick][None])
-            tau = b.compute_torques(True)
+            if route == "per_call":
+                b.update_model(); b.update_task_models()
+                b.update_sensed_force_and_moment(t0, g["sensed_f"][r, tick][None], g["sensed_m"][r, tick][None])
+                tau = b.compute_torques(True)
+            else:
+                b.update_model()
+                b.update_sensed_force_and_moment(t0, g["sensed_f"][r, tick][None], g["sensed_m"][r, tick][None])
+                tau = b.tick(True)
             close(tau, g["tau_t%d" % tick][r][None], "%s tick %d tau" % (name, tick))
         close(b.get(abi.F_UNIT_MASS_FORCE, t0), g["Fstar_t1"][r][None], name + " F*")
         close(b.get(abi.F_INTEGRATED_FORCE_ERROR, t0), g["int_f"][r][None], name + " integrated force error", floor=1e-6)
@@ -195,7 +202,7 @@ def test_pin_control_law_known_answers(kind):
 
 
 @pytest.mark.parametrize("kind", KINDS)
-@pytest.mark.parametrize("route", ["per_call", "tick"])
+@pytest.mark.parametrize("route", ["per_call", "tick", "tick_single"])
 def test_pin_popc_window(kind, route):
     """520 ticks of closed-loop force control with the passivity observer / controller at a fixed posture: the 250-sample window
     slides, the 50-tick controller period fires 10 times, R_c leaves 1 and recovers (POPCExplicitForceControl.cpp:30-96)"""
@@ -204,7 +211,7 @@ def test_pin_popc_window(kind, route):
     b = make_batch(kind, chain, 1)
     b.set(abi.F_Q, g["q"][None]); b.set(abi.F_DQ, g["dq"][None]); b.update_model()
     t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
-    t1 = b.add_joint_task(abi.joint_task_desc(7)) if route == "tick" else None   # the fused tick needs the two-task hierarchy
+    t1 = b.add_joint_task(abi.joint_task_desc(7)) if route == "tick" else None   # "tick": two-task fused tick; "tick_single": the task alone
     _set_params(b, t0, dict(force_space_dimension=1, force_or_motion_axis=(0, 0, 1), closed_loop_force_control=1, passivity_enabled=1))
     b.set(abi.F_GOAL_FORCE, np.array([[0, 0, -5.0]]), t0)
     if t1 is not None:

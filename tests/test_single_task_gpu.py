@@ -94,3 +94,111 @@ def test_single_task_fp32(oracle_built):
     tg, tr = p.both("tick", True)
     alpha = p.ref.get(abi.F_ALPHA, t0)[:, 0]
     assert _tau_err(tg, tr)[alpha == 1].max() <= FP32_TOL
+
+
+# ---- n = 7 with the motion task as the whole hierarchy (examples/07-surface_surface_contact: RobotController over one task) ----
+def _panda_single(q, rng, precision=abi.PRECISION_F64, **params):
+    chain = load_chain("panda")
+    B = len(q)
+    p = Pair(chain, B, precision, q0=q0_of(chain))
+    p.set(abi.F_Q, q); p.set(abi.F_DQ, rng.uniform(-0.3, 0.3, q.shape)); p.both("update_model")
+    t0 = p.add_mft("end-effector", (0, 0, 0.07))
+    if params:
+        p.set_mft_params(t0, **params)   # parametrize* re-initialises the goal pose: goals are set afterwards
+    x = p.ref.get(abi.F_CURRENT_POSITION, t0)
+    p.set(abi.F_GOAL_POSITION, x + rng.normal(0, 0.05, (B, 3)), t0)
+    p.set(abi.F_GOAL_LINEAR_VELOCITY, rng.normal(0, 0.05, (B, 3)), t0)
+    p.set(abi.F_GOAL_ANGULAR_VELOCITY, rng.normal(0, 0.05, (B, 3)), t0)
+    return p, t0
+
+
+@pytest.mark.parametrize("decoupling", [abi.BOUNDED_INERTIA_ESTIMATES, abi.FULL_DYNAMIC_DECOUPLING, abi.IMPEDANCE])
+@pytest.mark.parametrize("B", [1024, 224 * 148 + 5])
+def test_single_task_seven_dof_arm_is_fused(oracle_built, decoupling, B):
+    """Both block shapes of k_tick_fused2<.., SINGLE> (64 threads; 224 with phase barriers from 33,152 robots on), plain motion task
+    (the SIMPLE instantiation), stacked and plain sums, gravity compensation on the larger batch."""
+    chain = load_chain("panda")
+    rng = np.random.default_rng(81 + decoupling)
+    q = random_q(chain, B, rng, 0.3)
+    p, t0 = _panda_single(q, rng, dynamic_decoupling_type=decoupling)
+    assert p.gpu.tick_is_fused(), "one full MotionForceTask on a 7-DoF revolute arm must take the fused tick"
+    if B > 2000:
+        p.both("enable_gravity_compensation", True)
+    for tick in range(2):
+        p.set(abi.F_Q, q + 0.01 * tick * rng.normal(0, 1, q.shape))
+        for stacked in (True, False):
+            tg, tr = p.both("tick", stacked)
+            alpha = p.ref.get(abi.F_ALPHA, t0)[:, 0]
+            e = _tau_err(tg, tr)
+            assert e[alpha == 1].max() <= FP64_TOL, "non-singular robots: %.3e" % e[alpha == 1].max()
+            assert e.max() <= 1e-7, "blend robots: %.3e" % e.max()
+    alpha = p.ref.get(abi.F_ALPHA, t0)[:, 0]
+    fb = p.gpu.tick_fallback_count()
+    print("decoupling %d: %d of %d robots through k_tick_tail, %d of them in the blend band" % (decoupling, fb, B, int((alpha < 1).sum())))
+    # over 40 % of the joint range more than half of the postures sit in the reference's blend band (a 6 x 7 Jacobian in mixed units); the
+    # certificate of the fused kernel adds its margin (a few per cent of the batch)
+    assert int((alpha < 1).sum()) <= fb <= int((alpha < 1).sum()) + B // 8
+    if B < 2000:
+        p.compare(1e-6)   # every getter afterwards (lazy materialisation)
+
+
+def test_single_task_seven_dof_in_the_singular_set(oracle_built):
+    """examples/18's postures (elbow extended, wrist aligned) under the single task: the closed-form blend routine without a joint
+    task below it, flat 1e-9, discrete classification state equal to the oracle's."""
+    from test_singular_gpu import _panda_q
+    rng = np.random.default_rng(83)
+    q = _panda_q(rng)
+    p, t0 = _panda_single(q, rng)
+    assert p.gpu.tick_is_fused()
+    for tick in range(5):
+        p.set(abi.F_Q, q + 2e-4 * tick * rng.normal(0, 1, q.shape))
+        tg, tr = p.both("tick", True)
+        e = _tau_err(tg, tr)
+        assert e.max() <= FP64_TOL, "%.3e at robot %d" % (e.max(), int(e.argmax()))
+        for f in (abi.F_SINGULARITY_TYPES, abi.F_SINGULARITY_COUNTERS, abi.F_NS_RANK):
+            assert (np.asarray(p.gpu.get(f, t0)) == p.ref.get(f, t0)).all()
+    alpha = p.ref.get(abi.F_ALPHA, t0)[:, 0]
+    assert (alpha < 1).sum() >= len(q) // 2 and p.gpu.tick_fallback_count() >= int((alpha < 1).sum())
+
+
+def test_single_task_seven_dof_surface_contact_control(oracle_built):
+    """examples/07: force control along the tool axis and moment control about the two others, closed loop with the passivity
+    observer, sensed wrench refreshed every tick -- the general (non-SIMPLE) SINGLE instantiation, 300 ticks so that the POPC
+    controller period fires and the integrators matter."""
+    chain = load_chain("panda")
+    rng = np.random.default_rng(87)
+    B = 192
+    q = random_q(chain, B, rng, 0.25)
+    p, t0 = _panda_single(q, rng, force_space_dimension=1, force_or_motion_axis=(0, 0, 1), moment_space_dimension=2, moment_or_rotmotion_axis=(0, 0, 1),
+                          closed_loop_force_control=1, closed_loop_moment_control=1, passivity_enabled=1)
+    assert p.gpu.tick_is_fused()
+    p.set(abi.F_GOAL_FORCE, np.tile([0, 0, -5.0], (B, 1)), t0)
+    amp = rng.normal(0, 0.02, q.shape)
+    worst = 0.0
+    for tick in range(300):
+        t = tick * 1e-3
+        p.set(abi.F_Q, q + amp * np.sin(2 * np.pi * 2.0 * t)); p.set(abi.F_DQ, amp * 2 * np.pi * 2.0 * np.cos(2 * np.pi * 2.0 * t))
+        f = np.tile([0, 0, 5.0], (B, 1)) + rng.normal(0, 1.0, (B, 3)); m = rng.normal(0, 0.1, (B, 3))
+        # the reference's order robot->updateModel(); task->updateSensedForceAndMoment() (examples/07...cpp:150-175): the product evaluates
+        # the compliant frame at the batch's current q once a fused tick has run (stale rows), see tests/test_fused3_gpu.py
+        p.ref.update_model()
+        if tick == 0:
+            p.gpu.update_model()
+        p.both("update_sensed_force_and_moment", t0, f, m)
+        tg, tr = p.both("tick", True)
+        worst = max(worst, _tau_err(tg, tr).max())
+    assert worst <= FP64_TOL, worst
+    rc = p.ref.get(abi.F_POPC_RC, t0)[:, 0]
+    assert np.abs(np.asarray(p.gpu.get(abi.F_POPC_RC, t0))[:, 0] - rc).max() <= 1e-9
+    p.compare(1e-6)
+
+
+def test_single_task_seven_dof_fp32(oracle_built):
+    chain = load_chain("panda")
+    rng = np.random.default_rng(89)
+    q = random_q(chain, 512, rng, 0.3)
+    p, t0 = _panda_single(q, rng, precision=abi.PRECISION_F32)
+    assert p.gpu.tick_is_fused()
+    tg, tr = p.both("tick", True)
+    alpha = p.ref.get(abi.F_ALPHA, t0)[:, 0]
+    assert _tau_err(tg, tr)[alpha == 1].max() <= FP32_TOL

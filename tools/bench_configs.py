@@ -157,6 +157,38 @@ def single_task(torch, name="puma560_synthetic", B=65536, ticks=50):
     return out
 
 
+def single_task7(torch, chain, B=65536, ticks=50):
+    """examples/07's hierarchy: a Panda whose RobotController holds ONE MotionForceTask, config 2's postures.  Plain motion task (the SIMPLE
+    SINGLE instantiation) and force along z + two moment axes in closed loop with the passivity observer (the general one), each through the
+    fused tick and through the per-call kernels."""
+    w = workloads.config2(chain, B, seed=5)
+    f = np.tile([0.0, 0.0, 5.0], (B, 1)); m = np.zeros((B, 3))
+    out = []
+    for law in ("motion", "surface contact (force 1 + moment 2, closed loop, POPC)"):
+        for outputs, tag in ((None, "fused tick (k_tick_fused2<7, SINGLE> + k_tick_tail)"), (abi.TICK_OUTPUTS_ALL, "per-call kernels (API-faithful route)")):
+            b = osc_b200.Batch(chain, B, q0=[j["q0"] for j in chain["joints"]])
+            b.set_stream(torch.cuda.current_stream().cuda_stream)
+            t0 = b.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+            if outputs is not None:
+                b.set_tick_outputs(outputs)
+            b.set(abi.F_Q, w["q"]); b.set(abi.F_DQ, w["dq"]); b.update_model()
+            if law != "motion":
+                p = b.mft_params(t0)
+                p.force_space_dimension, p.moment_space_dimension, p.closed_loop_force_control, p.closed_loop_moment_control, p.passivity_enabled = 1, 2, 1, 1, 1
+                for i, x in enumerate((0.0, 0.0, 1.0)):
+                    p.force_or_motion_axis[i] = x; p.moment_or_rotmotion_axis[i] = x
+                b.set_mft_params(t0, p)
+                b.set(abi.F_GOAL_FORCE, np.tile([0.0, 0.0, -5.0], (B, 1)), t0)
+                b.update_sensed_force_and_moment(t0, f, m)
+            b.set(abi.F_GOAL_POSITION, w["goal_pos"], t0); b.set(abi.F_GOAL_ORIENTATION, w["goal_ori"], t0)
+            ms = timed(torch, lambda: b.tick(True, fetch=False), ticks)
+            out.append({"config": "single 6-DoF task on the 7-DoF Panda", "law": law, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+                        "robot_ticks_per_s": B / (ms.mean() * 1e-3), "fallback_robots": int(b.tick_fallback_count()) if outputs is None else 0, "route": tag,
+                        "fused": bool(b.tick_is_fused())})
+            del b
+    return out
+
+
 def config4_stages(torch, name="panda", B=65536, ticks=10):
     """Where the per-call route spends its time when EVERY robot is in the singular blend branch (what k_tick_tail runs per robot)."""
     import test_singular_gpu as S
@@ -184,7 +216,7 @@ def config4_stages(torch, name="panda", B=65536, ticks=10):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-batch", type=int, default=3000000)
-    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5, st")
+    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5, st, st7")
     args = ap.parse_args()
     import torch
     panda = chain_of("panda")
@@ -204,6 +236,9 @@ def main():
             print(json.dumps(config4(torch, "puma560_synthetic")), flush=True)
         if "st" in only:
             for rec in single_task(torch):
+                print(json.dumps(rec), flush=True)
+        if "st7" in only:
+            for rec in single_task7(torch, panda):
                 print(json.dumps(rec), flush=True)
         if "4s" in only:
             print(json.dumps(config4_stages(torch, "panda")), flush=True)
