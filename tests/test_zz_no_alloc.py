@@ -84,9 +84,13 @@ def test_noalloc_rejects_what_it_cannot_serve():
     assert L.osc_tick_noalloc(big.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_INVALID_ARGUMENT
     assert b"OSC_NOALLOC_MAX_ROBOTS" in L.osc_last_error()
     big.close()
-    one = osc_b200.Batch(chain, 64, q0=q0_of(chain))      # a single-task hierarchy runs the per-call route: not served
+    jt_only = osc_b200.Batch(chain, 64, q0=q0_of(chain))  # a hierarchy without a MotionForceTask in front runs the per-call route: not served
+    jt_only.add_joint_task(abi.joint_task_desc(chain["n"]))
+    assert L.osc_tick_noalloc(jt_only.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_UNSUPPORTED
+    jt_only.close()
+    one = osc_b200.Batch(chain, 64, q0=q0_of(chain))
     one.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
-    assert L.osc_tick_noalloc(one.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_UNSUPPORTED
+    assert L.osc_tick_noalloc(one.h, 1, None, abi.LAYOUT_AOS) == abi.OK   # the task alone (examples/07): fused since round 2
     one.add_joint_task(abi.joint_task_desc(chain["n"]))
     assert L.osc_tick_noalloc(one.h, 1, C.c_void_p(8), abi.LAYOUT_UNIFORM) == abi.ERR_INVALID_ARGUMENT
     assert L.osc_tick_noalloc(one.h, 1, None, abi.LAYOUT_AOS) == abi.OK
