@@ -373,7 +373,8 @@ int osc_task_compute_torques(osc_batch_t* batch, int task, int with_tau_prec);
 int osc_compute_torques(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
 /* updateModel + updateControllerTaskModels + computeControlTorques in one call; uses the fused single-launch kernel
  * when the hierarchy is [MotionForceTask, full JointTask] (n = 6 or 7; the motion task full, or partial of rank 2-5 on n = 7) or
- * one full MotionForceTask alone (n = 6 or 7) on an all-revolute chain, otherwise the sequence above (osc_tick_is_fused tells). */
+ * one full MotionForceTask alone (n = 6 or 7) on an all-revolute chain, or one full JointTask alone (any chain); otherwise the
+ * sequence above (osc_tick_is_fused tells). */
 int osc_tick(osc_batch_t* batch, int stacked, void* tau_out, int layout, int mem);
 /* osc_tick for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
  * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.

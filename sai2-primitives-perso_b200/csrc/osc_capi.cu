@@ -227,7 +227,7 @@ extern "C" int osc_tick_noalloc(osc_batch_t* batch, int stacked, void* tau_out_d
 	if (b->stride > OSC_NOALLOC_MAX_ROBOTS) return invalid("osc_tick_noalloc: the batch has more than OSC_NOALLOC_MAX_ROBOTS (262144) robots; use osc_tick");
 	if (tau_out_device && layout != OSC_LAYOUT_AOS && layout != OSC_LAYOUT_SOA) return invalid("osc_tick_noalloc: tau_out layout must be AOS or SOA");
 	if (!b->ops->fused_supported(*b)) {
-		set_error("osc_tick_noalloc: only the fused tick ([6-DoF MotionForceTask, full JointTask], outputs LAZY or TAU) runs without allocating; use osc_tick");
+		set_error("osc_tick_noalloc: only the hierarchies of the fused tick (osc_tick_is_fused() == 1, outputs LAZY or TAU) run without allocating; use osc_tick");
 		return OSC_ERR_UNSUPPORTED;
 	}
 	for (const TaskH& t : b->tasks)

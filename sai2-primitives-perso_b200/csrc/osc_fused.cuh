@@ -334,8 +334,55 @@ __global__ void __launch_bounds__(OSC_THREADS) k_tick_tail(const __grid_constant
 	}
 }
 
+// ---- [full JointTask] alone (examples/01-joint_control, 02-joint_control_internal_otg) -------------------------------------------
+// N_prec = I, so the projected Jacobian and its range basis are the identity, Lambda = (M^-1)^-1 = M and Lambda_mod = M_BIE, M or I
+// (JointTask.cpp:218-283); tau = M a_des + Lambda_mod u (:342-355): the mass matrix and two products, no factorisation at all.
+// Any serial chain (prismatic joints included), one robot per thread.
+template <class T, int N>
+__global__ void __launch_bounds__(OSC_THREADS) k_tick_joint(const __grid_constant__ ChainC<T, N> ch, const __grid_constant__ JtC<T, N> jc, Arena<T> rob, Arena<T> tk,
+															 int64_t B, int64_t stride, int gravity, int exports) {
+	using JL = JtL<N>;
+	const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (r >= B) return;
+	const Row<T> rP{rob.P, stride, r}, rS{rob.S, stride, r}, jP{tk.P, stride, r}, jS{tk.S, stride, r};
+	const bool ex = (exports & OSC_EXPORT_VECTORS) != 0;
+	T q[N], dq[N], u[N], acc[N];
+	ld_vec<T, N>(rP, RobotL<N>::Q, q);
+	ld_vec<T, N>(rP, RobotL<N>::DQ, dq);
+	jt_pd_law<T, N>(jc, jP, jS, q, dq, u, acc, ex);
+	Kin<T, N> kin;
+	forward_kinematics<T, N>(ch, q, kin);
+	T M[N][N], tau[N];
+	mass_matrix<T, N>(ch, kin, M);
+	OSC_UNROLL for (int i = 0; i < N; ++i) {
+		T s = T(0);
+		if (jc.decoupling == OSC_IMPEDANCE) {
+			OSC_UNROLL for (int j = 0; j < N; ++j) s = Num<T>::fma_(M[i][j], acc[j], s);
+			s += u[i];
+		} else {
+			OSC_UNROLL for (int j = 0; j < N; ++j) s = Num<T>::fma_(M[i][j], acc[j] + u[j], s);
+			if (jc.decoupling == OSC_BOUNDED_INERTIA_ESTIMATES && M[i][i] < jc.bie_threshold) s = Num<T>::fma_(jc.bie_threshold - M[i][i], u[i], s);  // :253-267
+		}
+		tau[i] = s;
+	}
+	if (ex) {
+		st_vec<T, N>(jS, JL::TASK_TAU, tau);
+		st_vec<T, N>(jS, JL::CUR_POS, q);
+		st_vec<T, N>(jS, JL::CUR_VEL, dq);
+		tk.I[(int64_t)JL::RANK * stride + r] = N;
+	}
+	if (gravity) {  // RobotController.cpp:70-72
+		T g[N];
+		gravity_vector<T, N>(ch, kin, g);
+		OSC_UNROLL for (int i = 0; i < N; ++i) tau[i] += g[i];
+	}
+	st_vec<T, N>(rS, RobotL<N>::TAU, tau);
+}
+inline bool joint_only_hierarchy(const Batch& b) { return b.tasks.size() == 1 && b.tasks[0].type == OSC_TASK_JOINT && b.tasks[0].jd.full; }
+
 // hierarchy / parameter combinations the fused tick serves (everything else: the kernel sequence of osc_capi_tick.inl)
 template <class T, int N> bool fused_tick_supported(Batch& b) {
+	if (b.tick_outputs != OSC_TICK_OUTPUTS_ALL && joint_only_hierarchy(b)) return true;
 	if constexpr (N != 6 && N != 7) return false;
 	if (b.tick_outputs == OSC_TICK_OUTPUTS_ALL) return false;
 	if (b.tasks.empty() || b.tasks[0].type != OSC_TASK_MOTION_FORCE) return false;

@@ -157,6 +157,14 @@ template <class T, int N> int OpsImpl<T, N>::pack_special(Batch& b, const Loc& l
 
 template <class T, int N> bool OpsImpl<T, N>::fused_supported(Batch& b) { return fused_tick_supported<T, N>(b); }
 template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
+	if (joint_only_hierarchy(b)) {  // examples/01, 02: no motion task, no nullspace, no fallback list
+		TaskH& j = b.tasks[0];
+		const int exports = b.tick_outputs == OSC_TICK_OUTPUTS_TAU ? 0 : OSC_EXPORT_VECTORS;
+		k_tick_joint<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, jtc(b, j), rob(b), tk(j), b.B, b.stride, b.gravity ? 1 : 0, exports);
+		if (int rc = done(b, "k_tick_joint")) return rc;
+		b.stale = true;
+		return OSC_OK;
+	}
 	if constexpr (N == 6 || N == 7) {
 		if (!b.fb) {
 			cudaError_t e = cudaMalloc((void**)&b.fb, (size_t)(b.stride + 2) * sizeof(int));

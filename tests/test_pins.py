@@ -397,6 +397,7 @@ def test_pin_rollout_lagrange_mpmath(kind):
 
 
 _HIER = {  # name -> (chain, task list): what RobotController accepts beyond [MotionForceTask, JointTask]
+    "h0": ("puma560_synthetic", lambda n: [("jt", None)]),                                                        # examples/01
     "h1": ("panda_sliding_base", lambda n: [("jt", np.eye(n)[[0, n - 1]]), ("mft", {})]),                      # examples/06
     "h2": ("panda_sliding_base", lambda n: [("jt", np.eye(n)[:1]), ("mft", dict(dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[])), ("jt", None)]),
     "h3": ("panda", lambda n: [("mft", dict(dirs_translation=[(1, 0, 0), (0, 1, 0), (0, 0, 1)], dirs_rotation=[])), ("jt", np.eye(n)[:3]), ("jt", None)]),
@@ -438,4 +439,4 @@ def test_pin_hierarchies_mpmath(kind, per_call, name):
             for i, t in enumerate(ids):
                 close(b.get(abi.F_TASK_TORQUES, t), g["t%d" % i], "torques of task %d" % i, floor=float(np.abs(g["tau"]).max()))
             close(b.get(abi.F_N_TOTAL), g["N_total"], "N_total", floor=1.0)
-    assert [int(r) for r in g["ranks"][0][:len(ids)]] == {"h1": [2, 6], "h2": [1, 3, 4], "h3": [3, 3, 1]}[name]
+    assert [int(r) for r in g["ranks"][0][:len(ids)]] == {"h0": [6], "h1": [2, 6], "h2": [1, 3, 4], "h3": [3, 3, 1]}[name]

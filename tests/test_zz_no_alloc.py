@@ -84,9 +84,14 @@ def test_noalloc_rejects_what_it_cannot_serve():
     assert L.osc_tick_noalloc(big.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_INVALID_ARGUMENT
     assert b"OSC_NOALLOC_MAX_ROBOTS" in L.osc_last_error()
     big.close()
-    jt_only = osc_b200.Batch(chain, 64, q0=q0_of(chain))  # a hierarchy without a MotionForceTask in front runs the per-call route: not served
+    part = osc_b200.Batch(chain, 64, q0=q0_of(chain))  # a partial JointTask in front (examples/06) runs the per-call route: not served
+    part.add_joint_task(abi.joint_task_desc(chain["n"], np.eye(chain["n"])[:2]))
+    part.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))
+    assert L.osc_tick_noalloc(part.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_UNSUPPORTED
+    part.close()
+    jt_only = osc_b200.Batch(chain, 64, q0=q0_of(chain))
     jt_only.add_joint_task(abi.joint_task_desc(chain["n"]))
-    assert L.osc_tick_noalloc(jt_only.h, 1, None, abi.LAYOUT_AOS) == abi.ERR_UNSUPPORTED
+    assert L.osc_tick_noalloc(jt_only.h, 1, None, abi.LAYOUT_AOS) == abi.OK   # the full JointTask alone (examples/01): k_tick_joint, no scratch at all
     jt_only.close()
     one = osc_b200.Batch(chain, 64, q0=q0_of(chain))
     one.add_motion_force_task(abi.mft_desc(chain, "end-effector", (0, 0, 0.07)))

@@ -189,6 +189,29 @@ def single_task7(torch, chain, B=65536, ticks=50):
     return out
 
 
+def joint_only(torch, name="puma560_synthetic", B=65536, ticks=50):
+    """examples/01: a full JointTask alone (k_tick_joint) against the per-call kernels"""
+    from common import q0_of, random_q
+    chain = chain_of(name)
+    rng = np.random.default_rng(8)
+    n = chain["n"]
+    q = random_q(chain, B, rng, 0.3)
+    out = []
+    for outputs, tag in ((None, "fused tick (k_tick_joint)"), (abi.TICK_OUTPUTS_ALL, "per-call kernels (API-faithful route)")):
+        b = osc_b200.Batch(chain, B, q0=q0_of(chain))
+        b.set_stream(torch.cuda.current_stream().cuda_stream)
+        t0 = b.add_joint_task(abi.joint_task_desc(n))
+        if outputs is not None:
+            b.set_tick_outputs(outputs)
+        b.set(abi.F_Q, q); b.set(abi.F_DQ, rng.uniform(-0.3, 0.3, (B, n))); b.update_model()
+        b.set(abi.F_JT_GOAL_POSITION, q + 0.1, t0)
+        ms = timed(torch, lambda: b.tick(True, fetch=False), ticks)
+        out.append({"config": "full JointTask alone", "chain": name, "robots": B, "ms_per_tick": float(ms.mean()), "p50_us": float(np.median(ms) * 1e3),
+                    "robot_ticks_per_s": B / (ms.mean() * 1e-3), "route": tag, "fused": bool(b.tick_is_fused())})
+        del b
+    return out
+
+
 def config4_stages(torch, name="panda", B=65536, ticks=10):
     """Where the per-call route spends its time when EVERY robot is in the singular blend branch (what k_tick_tail runs per robot)."""
     import test_singular_gpu as S
@@ -216,7 +239,7 @@ def config4_stages(torch, name="panda", B=65536, ticks=10):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-batch", type=int, default=3000000)
-    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5, st, st7")
+    ap.add_argument("--only", default="", help="comma list of: 1, 3, 4, 4s, 5, st, st7, jt")
     args = ap.parse_args()
     import torch
     panda = chain_of("panda")
@@ -240,6 +263,10 @@ def main():
         if "st7" in only:
             for rec in single_task7(torch, panda):
                 print(json.dumps(rec), flush=True)
+        if "jt" in only:
+            for nm in ("puma560_synthetic", "panda"):
+                for rec in joint_only(torch, nm):
+                    print(json.dumps(rec), flush=True)
         if "4s" in only:
             print(json.dumps(config4_stages(torch, "panda")), flush=True)
             print(json.dumps(config4_stages(torch, "puma560_synthetic")), flush=True)

@@ -936,14 +936,16 @@ def case_hierarchies(rng):
     """Row f-4: three hierarchies RobotController accepts beyond [MotionForceTask, JointTask]:
     h1 examples/06: sliding-base Panda (n = 8), partial JointTask (slider + last joint) > 6-DoF MotionForceTask;
     h2 sliding base: partial JointTask (slider) > translation-only MotionForceTask > full JointTask;
-    h3 Panda: translation-only MotionForceTask (examples/09) > partial JointTask (joints 1-3) > full JointTask."""
+    h3 Panda: translation-only MotionForceTask (examples/09) > partial JointTask (joints 1-3) > full JointTask;
+    h0 PUMA: the full JointTask alone (examples/01-joint_control)."""
     out = {}
     e3 = mp.matrix(6, 3)
     for i in range(3):
         e3[i, i] = 1
     for name, cname, build in (("h1", "panda_sliding_base", lambda n: [("jt", np.eye(n)[[0, n - 1]]), ("mft", None)]),
                                ("h2", "panda_sliding_base", lambda n: [("jt", np.eye(n)[:1]), ("mft", e3), ("jt", np.eye(n))]),
-                               ("h3", "panda", lambda n: [("mft", e3), ("jt", np.eye(n)[:3]), ("jt", np.eye(n))])):
+                               ("h3", "panda", lambda n: [("mft", e3), ("jt", np.eye(n)[:3]), ("jt", np.eye(n))]),
+                               ("h0", "puma560_synthetic", lambda n: [("jt", np.eye(n))])):   # examples/01: the joint task alone
         c = chain(cname)
         model = MpChain(c)
         n = c["n"]
