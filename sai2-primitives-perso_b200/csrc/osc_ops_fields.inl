@@ -160,8 +160,28 @@ template <class T, int N> int OpsImpl<T, N>::tick_fused(Batch& b, int stacked) {
 	if (joint_only_hierarchy(b)) {  // examples/01, 02: no motion task, no nullspace, no fallback list
 		TaskH& j = b.tasks[0];
 		const int exports = b.tick_outputs == OSC_TICK_OUTPUTS_TAU ? 0 : OSC_EXPORT_VECTORS;
-		k_tick_joint<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, jtc(b, j), rob(b), tk(j), b.B, b.stride, b.gravity ? 1 : 0, exports);
-		if (int rc = done(b, "k_tick_joint")) return rc;
+		bool revolute = true;
+		for (int i = 0; i < N; ++i) revolute = revolute && !ch.prismatic[i];
+		if (revolute) {  // body-frame kernel with a shared-memory stash (osc_fused_jt.cuh); block shape as the fused tick
+			if (b.gravity) {
+				k_gravity<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, rob(b), b.B, b.stride);
+				if (int rc = done(b, "k_gravity")) return rc;
+			}
+			auto go = [&](auto kern, int threads) -> int {
+				const size_t smem = (size_t)FJ<N>::SLOTS * threads * sizeof(T);
+				if (smem > 48 * 1024 && first_launch_on_device((const void*)kern, b.device)) {
+					cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+					if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(k_tick_joint2)");
+				}
+				kern<<<dim3((unsigned)((b.B + threads - 1) / threads)), threads, smem, b.stream>>>(ch, jtc(b, j), rob(b), tk(j), b.B, b.stride, b.gravity ? 1 : 0, exports);
+				return OSC_OK;
+			};
+			if (int rc = b.B >= 224 * 148 ? go(k_tick_joint2<T, N, 224>, 224) : go(k_tick_joint2<T, N, 64>, 64)) return rc;
+			if (int rc = done(b, "k_tick_joint2")) return rc;
+		} else {
+			k_tick_joint<T, N><<<grid(b), OSC_THREADS, 0, b.stream>>>(ch, jtc(b, j), rob(b), tk(j), b.B, b.stride, b.gravity ? 1 : 0, exports);
+			if (int rc = done(b, "k_tick_joint")) return rc;
+		}
 		b.stale = true;
 		return OSC_OK;
 	}

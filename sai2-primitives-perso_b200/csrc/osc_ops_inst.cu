@@ -6,6 +6,7 @@
 
 #include "osc_aux_kernels.cuh"
 #include "osc_fused3.cuh"
+#include "osc_fused_jt.cuh"
 #include "osc_blend.cuh"
 #include "osc_otg.cuh"
 #include "osc_rollout.cuh"

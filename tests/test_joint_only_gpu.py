@@ -1,6 +1,7 @@
 """[full JointTask] alone on the fused tick (examples/01-joint_control on the PUMA, 02-joint_control_internal_otg): with N_prec = I the
 task's range is the whole joint space, Lambda = M and Lambda_mod = M_BIE | M | I (JointTask.cpp:218-283), tau = M a_des + Lambda_mod u
-(:342-355) -- k_tick_joint forms the mass matrix and two products, no factorisation.  Against the C++ oracle (which, like the reference,
+(:342-355) -- k_tick_joint2 (all-revolute chains: body-frame composite-rigid-body recursion, shared-memory stash) and k_tick_joint
+(any chain) form the mass matrix and two products, no factorisation.  Against the C++ oracle (which, like the reference,
 goes through M^-1, the SVD range basis and the projected inertias), FP64 1e-9 / FP32 1e-4."""
 import numpy as np
 import pytest
@@ -69,3 +70,15 @@ def test_joint_task_alone_fp32_and_large_batch(oracle_built):
     assert p.gpu.tick_is_fused()
     tg, tr = p.both("tick", True)
     assert rel_err(np.asarray(tg, float), tr)[0] <= FP32_TOL
+
+
+@pytest.mark.parametrize("name", ["puma560_synthetic", "panda"])
+def test_joint_task_alone_large_batch_block_shape(oracle_built, name):
+    """224-thread blocks of k_tick_joint2 (from 33,152 robots on), ragged last block, gravity compensation through k_gravity"""
+    p, t0, q, rng = _pair(name, 224 * 148 + 5, 101)
+    p.both("enable_gravity_compensation", True)
+    assert p.gpu.tick_is_fused()
+    tg, tr = p.both("tick", True)
+    e, where = rel_err(tg, tr)
+    assert e <= FP64_TOL, "%.3e at robot %d" % (e, where)
+    assert rel_err(p.gpu.get(abi.F_TASK_TORQUES, t0), p.ref.get(abi.F_TASK_TORQUES, t0))[0] <= FP64_TOL
